@@ -1,0 +1,138 @@
+/* nerf_b200.h -- C ABI of libnerf_b200.so: the render_rays hot path on B200 (sm_100a).
+ *
+ * Boundary contract:
+ *   - every entry point is `extern "C"`, takes raw DEVICE pointers + sizes + a cudaStream_t (passed
+ *     as void*), returns int: 0 = ok, > 0 = a cudaError_t from the launch, < 0 = NERFB_E_* below;
+ *   - never throws, never allocates, never synchronises, never touches the legacy default stream
+ *     unless the caller passes it; tensors are dense row-major fp32 unless stated otherwise;
+ *   - inputs are never written (the reference never mutates its inputs, models/rendering.py:37).
+ * The reference has no FFI for this path -- it is a Python call API over torch ops; each function
+ * names the reference code (file:line under /root/reference) it replaces.  The native precedent for
+ * the checks-then-launch shape is torchsearchsorted/src/cuda/searchsorted_cuda_wrapper.cpp:5-20.
+ */
+#ifndef NERF_B200_H
+#define NERF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NERFB_OK            0
+#define NERFB_E_BADARG     (-1)   /* null pointer / negative size / unsupported shape */
+#define NERFB_E_UNSUPPORTED (-2)  /* configuration outside what the kernels implement */
+#define NERFB_E_WORKSPACE  (-3)   /* workspace too small */
+#define NERFB_E_ARCH       (-4)   /* device is not sm_100 */
+
+/* Model family.  Parameter blobs are flat fp32 in the reference's state_dict order. */
+#define NERFB_KIND_NERF   0       /* models/nerf.py:41-124 NeRF; with n_cls>0: models/nerf_cls.py:12-112 NeRF_3D */
+#define NERFB_KIND_SIREN  1       /* models/nerf.py:159-216 SemanticNeRF (FiLM sine layers) */
+
+/* Arithmetic of the MLP contraction. */
+#define NERFB_PREC_FP32   0       /* fp32 operands, fp32 accumulate, CUDA cores (tight-parity path) */
+#define NERFB_PREC_BF16   1       /* bf16 operands on tcgen05 tensor cores, fp32 accumulate in TMEM */
+
+/* Where the MLP input comes from. */
+#define NERFB_IN_RAYS     0       /* rays (N,8) + z (N,S): x = o + d*z, encodings computed in-kernel
+                                     (replaces models/rendering.py:224,131-150 + models/nerf.py:33-38) */
+#define NERFB_IN_EMBEDDED 1       /* x (P, in_xyz [+ in_dir]) already embedded -- NeRF.forward(x) called
+                                     directly, e.g. extract_color_mesh.py:136-139 */
+
+typedef struct nerfb_mlp_desc {
+  int32_t kind;        /* NERFB_KIND_* */
+  int32_t D;           /* trunk depth (8) */
+  int32_t W;           /* width (256) */
+  int32_t n_freq_xyz;  /* 10 -> in_xyz = 3*(1+2*10) = 63; 0 = identity (SIREN) */
+  int32_t n_freq_dir;  /* 4  -> in_dir = 27 */
+  int32_t skip_mask;   /* bit i: trunk layer i (0-based) consumes cat([xyz_enc, h]) (models/nerf.py:108-109) */
+  int32_t n_cls;       /* NeRF_3D class channels (0 = plain NeRF) */
+  int32_t logscale;    /* Embedding(logscale=...) models/nerf.py:16-19 */
+  float   box;         /* SIREN UniformBoxWarp side length (models/nerf.py:193: 51) */
+  int32_t in_xyz;      /* NERFB_IN_EMBEDDED only: columns of x that are the xyz encoding */
+  int32_t in_dir;      /* NERFB_IN_EMBEDDED only: columns of x that are the dir encoding */
+} nerfb_mlp_desc;
+
+int         nerfb_version(void);                 /* 100*major + minor */
+int         nerfb_arch(void);                    /* 100: built for sm_100a only */
+const char* nerfb_error_string(int status);
+int64_t     nerfb_param_count(const nerfb_mlp_desc* d);   /* floats in the flat parameter blob */
+int         nerfb_out_channels(const nerfb_mlp_desc* d);  /* 4 (+ n_cls) */
+
+/* ---- (2) stratified ray sampling: models/rendering.py:206-222 -------------------------------
+ * rays (N,8) [o d near far]; perturb_rand (N,S) U[0,1) or NULL when perturb == 0; z_out (N,S). */
+int nerfb_sample_coarse(const float* rays, const float* perturb_rand, float perturb, int use_disp,
+                        int64_t n_rays, int n_samples, float* z_out, void* stream);
+
+/* ---- (1a) positional encoding alone: models/nerf.py:21-38 Embedding.forward -----------------
+ * x (B,C) -> out (B, C*(1+2*n_freqs)), channel order [x, sin f0 x, cos f0 x, sin f1 x, ...]. */
+int nerfb_embed(const float* x, int64_t rows, int channels, int n_freqs, int logscale, float* out,
+                void* stream);
+
+/* ---- (1b) embedding + MLP, forward: models/rendering.py:129-159 + models/nerf.py:83-124 ------
+ * in_mode RAYS: in0 = rays (N,8), in1 = z (N,S), n_rows = N, n_samples = S, P = N*S.
+ * in_mode EMBEDDED: in0 = x (P, in_xyz(+in_dir)), in1 = NULL, n_rows = P, n_samples = 1.
+ * SIREN: film = [15*frequencies+30 ((D+1)*W) | phase_shifts ((D+1)*W)]: the two FiLM vectors of
+ *        forward_with_frequencies_phase_shifts (models/nerf.py:201) AFTER its 15*f+30 map (:202), which
+ *        the host applies; slice l*W..(l+1)*W drives trunk layer l, the last slice the colour layer.
+ *        NULL for NeRF.
+ * out (P, sigma_only ? 1 : 4+n_cls): [r g b sigma cls...], sigma raw (models/nerf.py:112,122).
+ * workspace: >= nerfb_mlp_workspace_bytes(..) bytes, 1024-aligned; with save_for_backward != 0 it
+ * holds the activations nerfb_mlp_bwd needs and must be kept alive unchanged until then. */
+int64_t nerfb_mlp_workspace_bytes(const nerfb_mlp_desc* d, int precision, int64_t n_points,
+                                  int sigma_only, int save_for_backward);
+int nerfb_mlp_fwd(const nerfb_mlp_desc* d, int precision, int in_mode, const float* params,
+                  const float* film, const float* in0, const float* in1, int64_t n_rows,
+                  int n_samples, int sigma_only, int save_for_backward, float* out,
+                  void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- (1c) embedding + MLP, backward (autograd of the above) -----------------------------------
+ * d_out (P, 4+n_cls) upstream gradient; grad_params (param_count) is ACCUMULATED into (+=), the
+ * caller zeroes it; d_in (P, in_xyz+in_dir) or NULL (only NERFB_IN_EMBEDDED may ask for it). */
+int nerfb_mlp_bwd(const nerfb_mlp_desc* d, int precision, int in_mode, const float* params,
+                  const float* film, const float* in0, const float* in1, int64_t n_rows,
+                  int n_samples, const float* out, const float* d_out, float* grad_params,
+                  float* d_in, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- (4) alpha compositing: models/rendering.py:161-190 (+ :379 class channels) --------------
+ * raw (N,S,C) with C = 1 (sigma only -> weights only) or >= 4 ([rgb sigma extra...]); z (N,S);
+ * rays (N,8) (direction norm, :168); noise (N,S) N(0,1) or NULL (:170).
+ * Outputs (any may be NULL except weights): weights (N,S); rgb (N,3); depth (N); opacity (N);
+ * extra (N,C-4). */
+int nerfb_composite_fwd(const float* raw, int channels, const float* z, const float* rays,
+                        const float* noise, float noise_std, int white_back, int64_t n_rays,
+                        int n_samples, float* weights, float* rgb, float* depth, float* opacity,
+                        float* extra, void* stream);
+/* Backward: upstream d_rgb (N,3), d_depth (N), d_opacity (N), d_weights (N,S), d_extra (N,C-4), any
+ * NULL = zero; writes d_raw (N,S,C) in full (no gradient reaches z: models/rendering.py:244). */
+int nerfb_composite_bwd(const float* raw, int channels, const float* z, const float* rays,
+                        const float* noise, float noise_std, int white_back, int64_t n_rays,
+                        int n_samples, const float* d_rgb, const float* d_depth,
+                        const float* d_opacity, const float* d_weights, const float* d_extra,
+                        float* d_raw, void* stream);
+
+/* ---- (3) importance resampling ------------------------------------------------------------------
+ * nerfb_searchsorted: the torchsearchsorted contract (src/torchsearchsorted/searchsorted.py:20-53,
+ *   src/cuda/searchsorted_cuda_kernel.cu:83-107): a (rows_a,A) sorted rows, v (rows_v,V), rows_a ==
+ *   rows_v or either == 1; out int64 (max(rows),V) = numpy.searchsorted(a[r], v[r], side).
+ *   With side_left = 0 and a = cdf, v = u this is the index step of sample_pdf
+ *   (models/rendering.py:54), bit-exact for identical (cdf,u).
+ * nerfb_sample_pdf: models/rendering.py:22-67 on explicit bins (N,nb), weights (N,nb-1); u (N,n_imp)
+ *   or NULL when det (u = linspace(0,1,n_imp), :44); optional cdf_out (N,nb), inds_out (N,n_imp).
+ * nerfb_resample: the render_rays call site :241-247 fused: z_mid, weights[:,1:-1], sample_pdf,
+ *   cat, sort -> z_fine (N, S_c+S_i) ascending. */
+int nerfb_searchsorted(const float* a, int64_t rows_a, int64_t len_a, const float* v, int64_t rows_v,
+                       int64_t len_v, int side_left, int64_t* out, void* stream);
+int nerfb_sample_pdf(const float* bins, const float* weights, const float* u, int det, float eps,
+                     int64_t n_rays, int n_bins, int n_importance, float* samples, float* cdf_out,
+                     int64_t* inds_out, void* stream);
+int nerfb_resample(const float* z_coarse, const float* weights_coarse, const float* u, int det,
+                   int64_t n_rays, int n_coarse, int n_importance, float* z_fine, void* stream);
+
+/* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
+int64_t nerfb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H */

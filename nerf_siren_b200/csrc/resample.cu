@@ -1,0 +1,180 @@
+// Kernel (3): importance resampling -- replaces models/rendering.py:22-67 (sample_pdf), its call site
+// :241-247 (mid-points, weights[:,1:-1], cat, sort) and the legacy torchsearchsorted extension
+// (torchsearchsorted/src/cuda/searchsorted_cuda_kernel.cu:3-142).
+// One warp per ray; the row's bins / cdf live in shared memory, the searches are warp-parallel over the
+// queries, and the final sort is a rank-by-counting merge in shared memory (exact multiset of
+// torch.sort's values, no assumption that the inverse-CDF output is monotone to the ulp).
+#include "common.cuh"
+
+#define RS_WARPS 4
+
+// ---- searchsorted: out = #(a[row] <  v) (left)  or  #(a[row] <= v) (right) ---------------------------
+__global__ void __launch_bounds__(256)
+searchsorted_kernel(const float* __restrict__ a, int64_t rows_a, int64_t A, const float* __restrict__ v, int64_t rows_v,
+                    int64_t V, int side_left, int64_t rows, int64_t* __restrict__ out) {
+  const int64_t total = rows * V;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / V, c = idx - r * V;
+    const float* ar = a + (rows_a == 1 ? 0 : r) * A;
+    const float val = __ldg(v + (rows_v == 1 ? 0 : r) * V + c);
+    int64_t lo = 0, hi = A;                                  // first position whose element fails the test
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      const float x = __ldg(ar + mid);
+      const bool go_right = side_left ? (x < val) : (x <= val);
+      if (go_right) lo = mid + 1; else hi = mid;
+    }
+    out[idx] = lo;
+  }
+}
+
+extern "C" int nerfb_searchsorted(const float* a, int64_t rows_a, int64_t len_a, const float* v, int64_t rows_v,
+                                  int64_t len_v, int side_left, int64_t* out, void* stream) {
+  NERFB_CHECK_ARG(a && v && out && rows_a >= 1 && rows_v >= 1 && len_a >= 0 && len_v >= 0);
+  NERFB_CHECK_ARG(rows_a == rows_v || rows_a == 1 || rows_v == 1);
+  const int64_t rows = rows_a > rows_v ? rows_a : rows_v;
+  if (rows * len_v == 0) return NERFB_OK;
+  const int64_t want = ceil_div64(rows * len_v, 256);
+  const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
+  NERFB_LAUNCH(searchsorted_kernel, grid, 256, 0, stream, a, rows_a, len_a, v, rows_v, len_v, side_left, rows, out);
+  return NERFB_OK;
+}
+
+// ---- inverse-CDF sampling for one ray, executed by one warp -------------------------------------------
+// s_bins[nb], s_w[nb-1] filled by the caller; s_cdf[nb] produced here.  Returns samples through `emit`.
+__device__ __forceinline__ void warp_build_cdf(const float* s_w, float* s_cdf, int nb, float eps, int lane) {
+  const int nw = nb - 1;
+  float part = 0.f;
+  for (int i = lane; i < nw; i += 32) part += s_w[i] + eps;                      // rendering.py:37
+  const float total = warp_sum(part);
+  // inclusive scan of pdf in blocks of 32 with a running carry (rendering.py:38-41)
+  float carry = 0.f;
+  if (lane == 0) s_cdf[0] = 0.f;
+  for (int base = 0; base < nw; base += 32) {
+    const int i = base + lane;
+    float p = (i < nw) ? (s_w[i] + eps) / total : 0.f;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float q = __shfl_up_sync(0xffffffffu, p, o);
+      if (lane >= o) p += q;
+    }
+    if (i < nw) s_cdf[i + 1] = carry + p;
+    carry += __shfl_sync(0xffffffffu, p, 31);
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ float invert_cdf(const float* s_bins, const float* s_cdf, int nb, float u, float eps,
+                                            int* ind_out) {
+  int lo = 0, hi = nb;                                   // searchsorted(cdf, u, right=True): #(cdf <= u)
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (s_cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  }
+  if (ind_out) *ind_out = lo;
+  const int below = max(lo - 1, 0);                      // rendering.py:55-56
+  const int above = min(lo, nb - 1);
+  const float c0 = s_cdf[below], c1 = s_cdf[above];
+  const float b0 = s_bins[below], b1 = s_bins[above];
+  float denom = __fsub_rn(c1, c0);
+  if (denom < eps) denom = 1.0f;                         // rendering.py:63
+  // bins_g0 + (u - cdf_g0) / denom * (bins_g1 - bins_g0), left to right (rendering.py:66)
+  return __fadd_rn(b0, __fmul_rn(__fdiv_rn(__fsub_rn(u, c0), denom), __fsub_rn(b1, b0)));
+}
+
+__global__ void __launch_bounds__(RS_WARPS * 32)
+sample_pdf_kernel(const float* __restrict__ bins, const float* __restrict__ weights, const float* __restrict__ u, int det,
+                  float eps, int64_t N, int nb, int n_imp, float* __restrict__ samples, float* __restrict__ cdf_out,
+                  int64_t* __restrict__ inds_out) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* s_bins = smem + (size_t)wib * 3 * nb;
+  float* s_w = s_bins + nb;
+  float* s_cdf = s_w + nb;
+  for (int64_t r = (int64_t)blockIdx.x * RS_WARPS + wib; r < N; r += (int64_t)gridDim.x * RS_WARPS) {
+    for (int i = lane; i < nb; i += 32) s_bins[i] = __ldg(bins + r * nb + i);
+    for (int i = lane; i < nb - 1; i += 32) s_w[i] = __ldg(weights + r * (nb - 1) + i);
+    __syncwarp();
+    warp_build_cdf(s_w, s_cdf, nb, eps, lane);
+    if (cdf_out) for (int i = lane; i < nb; i += 32) cdf_out[r * nb + i] = s_cdf[i];
+    for (int j = lane; j < n_imp; j += 32) {
+      const float uj = det ? linspace01(j, n_imp) : __ldg(u + r * n_imp + j);
+      int ind;
+      samples[r * n_imp + j] = invert_cdf(s_bins, s_cdf, nb, uj, eps, &ind);
+      if (inds_out) inds_out[r * n_imp + j] = ind;
+    }
+    __syncwarp();
+  }
+}
+
+extern "C" int nerfb_sample_pdf(const float* bins, const float* weights, const float* u, int det, float eps,
+                                int64_t n_rays, int n_bins, int n_importance, float* samples, float* cdf_out,
+                                int64_t* inds_out, void* stream) {
+  NERFB_CHECK_ARG(bins && weights && samples && n_rays >= 0 && n_bins >= 2 && n_importance >= 1);
+  NERFB_CHECK_ARG(det || u);
+  if (n_rays == 0) return NERFB_OK;
+  const size_t smem = (size_t)RS_WARPS * 3 * n_bins * sizeof(float);
+  if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
+  if (smem > 48 * 1024)
+    NERFB_CUDA(cudaFuncSetAttribute(sample_pdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = ceil_div64(n_rays, RS_WARPS);
+  const int grid = (int)(want < NERFB_SM_COUNT * 16 ? want : NERFB_SM_COUNT * 16);
+  NERFB_LAUNCH(sample_pdf_kernel, grid, RS_WARPS * 32, smem, stream, bins, weights, u, det, eps, n_rays, n_bins,
+               n_importance, samples, cdf_out, inds_out);
+  return NERFB_OK;
+}
+
+// ---- the fused call site: z_mid -> sample_pdf(weights[1:-1]) -> cat -> sort ---------------------------
+__global__ void __launch_bounds__(RS_WARPS * 32)
+resample_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse, const float* __restrict__ u, int det,
+                int64_t N, int Sc, int Si, float* __restrict__ z_fine) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int nb = Sc - 1, St = Sc + Si;
+  float* s_bins = smem + (size_t)wib * (3 * Sc + St);
+  float* s_w = s_bins + Sc;
+  float* s_cdf = s_w + Sc;
+  float* s_all = s_cdf + Sc;                               // [0,Sc) coarse z, [Sc,St) new samples
+  const float eps = 1e-5f;
+  for (int64_t r = (int64_t)blockIdx.x * RS_WARPS + wib; r < N; r += (int64_t)gridDim.x * RS_WARPS) {
+    for (int i = lane; i < Sc; i += 32) s_all[i] = __ldg(z_coarse + r * Sc + i);
+    for (int i = lane; i < Sc - 2; i += 32) s_w[i] = __ldg(w_coarse + r * Sc + i + 1);      // weights[:, 1:-1]
+    __syncwarp();
+    for (int i = lane; i < nb; i += 32) s_bins[i] = __fmul_rn(0.5f, __fadd_rn(s_all[i], s_all[i + 1]));  // :242
+    __syncwarp();
+    warp_build_cdf(s_w, s_cdf, nb, eps, lane);
+    for (int j = lane; j < Si; j += 32) {
+      const float uj = det ? linspace01(j, Si) : __ldg(u + r * Si + j);
+      s_all[Sc + j] = invert_cdf(s_bins, s_cdf, nb, uj, eps, nullptr);
+    }
+    __syncwarp();
+    // rank-by-counting: position of element k = #(x < x_k) + #(x == x_k with index < k)
+    for (int k = lane; k < St; k += 32) {
+      const float xk = s_all[k];
+      int rank = 0;
+      for (int m = 0; m < St; ++m) {
+        const float xm = s_all[m];
+        rank += (xm < xk) || (xm == xk && m < k);
+      }
+      z_fine[r * St + rank] = xk;
+    }
+    __syncwarp();
+  }
+}
+
+extern "C" int nerfb_resample(const float* z_coarse, const float* weights_coarse, const float* u, int det,
+                              int64_t n_rays, int n_coarse, int n_importance, float* z_fine, void* stream) {
+  NERFB_CHECK_ARG(z_coarse && weights_coarse && z_fine && n_rays >= 0 && n_coarse >= 3 && n_importance >= 1);
+  NERFB_CHECK_ARG(det || u);
+  if (n_rays == 0) return NERFB_OK;
+  const size_t smem = (size_t)RS_WARPS * (4 * n_coarse + n_importance) * sizeof(float);
+  if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
+  if (smem > 48 * 1024)
+    NERFB_CUDA(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = ceil_div64(n_rays, RS_WARPS);
+  const int grid = (int)(want < NERFB_SM_COUNT * 16 ? want : NERFB_SM_COUNT * 16);
+  NERFB_LAUNCH(resample_kernel, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
+               n_importance, z_fine);
+  return NERFB_OK;
+}

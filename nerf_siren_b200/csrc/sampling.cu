@@ -1,0 +1,88 @@
+// Kernel (2): stratified ray sampling, and the stand-alone positional encoding.
+//   replaces models/rendering.py:206-222 (z_steps, depth/disparity lerp, mid-point perturbation)
+//   and models/nerf.py:21-38 (Embedding.forward) when a caller embeds outside the fused MLP.
+// Both are pure streaming kernels (HBM-bound): one element per thread, coalesced, grid-stride with the
+// grid sized as a multiple of the SM count.  Arithmetic uses explicit round-to-nearest intrinsics in the
+// reference's operation order so fp32 results are bit-identical to the torch-CPU oracle.
+#include "common.cuh"
+
+__device__ __forceinline__ float z_at(float near, float far, int i, int n, int use_disp) {
+  const float t = linspace01(i, n);
+  const float omt = __fsub_rn(1.0f, t);
+  if (!use_disp) return __fadd_rn(__fmul_rn(near, omt), __fmul_rn(far, t));            // rendering.py:209
+  const float a = __fmul_rn(__fdiv_rn(1.0f, near), omt);
+  const float b = __fmul_rn(__fdiv_rn(1.0f, far), t);
+  return __fdiv_rn(1.0f, __fadd_rn(a, b));                                              // rendering.py:211
+}
+
+__global__ void __launch_bounds__(256)
+sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ perturb_rand, float perturb,
+                     int use_disp, int64_t total, int S, float* __restrict__ z_out) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / S;
+    const int i = (int)(idx - r * S);
+    const float near = __ldg(rays + r * 8 + 6), far = __ldg(rays + r * 8 + 7);
+    float z = z_at(near, far, i, S, use_disp);
+    if (perturb > 0.f) {                                                                 // rendering.py:215-222
+      const float lower = (i > 0) ? __fmul_rn(0.5f, __fadd_rn(z_at(near, far, i - 1, S, use_disp), z)) : z;
+      const float upper = (i < S - 1) ? __fmul_rn(0.5f, __fadd_rn(z, z_at(near, far, i + 1, S, use_disp))) : z;
+      const float pr = __fmul_rn(perturb, __ldg(perturb_rand + idx));
+      z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), pr));
+    }
+    z_out[idx] = z;
+  }
+}
+
+extern "C" int nerfb_sample_coarse(const float* rays, const float* perturb_rand, float perturb, int use_disp,
+                                   int64_t n_rays, int n_samples, float* z_out, void* stream) {
+  NERFB_CHECK_ARG(rays && z_out && n_rays >= 0 && n_samples >= 1);
+  NERFB_CHECK_ARG(perturb <= 0.f || perturb_rand);
+  if (n_rays == 0) return NERFB_OK;
+  const int64_t total = n_rays * n_samples;
+  const int64_t want = ceil_div64(total, 256);
+  const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
+  NERFB_LAUNCH(sample_coarse_kernel, grid, 256, 0, stream, rays, perturb_rand, perturb, use_disp, total,
+               n_samples, z_out);
+  return NERFB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float band(int k, int n_freqs, int logscale) {
+  if (logscale) return (float)(1u << k);                       // 2**linspace(0,N-1,N): exact powers of two
+  if (n_freqs <= 1) return 1.0f;
+  const float end = (float)(1u << (n_freqs - 1));
+  const float step = __fdiv_rn(end - 1.0f, (float)(n_freqs - 1));
+  return (k < n_freqs / 2) ? __fmaf_rn((float)k, step, 1.0f) : __fmaf_rn(-(float)(n_freqs - 1 - k), step, end);
+}
+
+__global__ void __launch_bounds__(256)
+embed_kernel(const float* __restrict__ x, int64_t total, int C, int F, int logscale, float* __restrict__ out) {
+  const int width = C * (1 + 2 * F);
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = idx / C;
+    const int c = (int)(idx - row * C);
+    const float v = __ldg(x + idx);
+    float* o = out + row * width;
+    o[c] = v;
+    for (int k = 0; k < F; ++k) {
+      const float a = __fmul_rn(band(k, F, logscale), v);      // models/nerf.py:36 func(freq*x)
+      float s, co;
+      sincosf(a, &s, &co);
+      o[C + (2 * k) * C + c] = s;
+      o[C + (2 * k + 1) * C + c] = co;
+    }
+  }
+}
+
+extern "C" int nerfb_embed(const float* x, int64_t rows, int channels, int n_freqs, int logscale, float* out,
+                           void* stream) {
+  NERFB_CHECK_ARG(x && out && rows >= 0 && channels >= 1 && n_freqs >= 0 && n_freqs <= 24);
+  if (rows == 0) return NERFB_OK;
+  const int64_t total = rows * channels;
+  const int64_t want = ceil_div64(total, 256);
+  const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
+  NERFB_LAUNCH(embed_kernel, grid, 256, 0, stream, x, total, channels, n_freqs, logscale, out);
+  return NERFB_OK;
+}

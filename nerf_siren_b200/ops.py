@@ -1,0 +1,186 @@
+"""Thin tensor-level wrappers over the C ABI: argument validation, output allocation, current stream.
+
+Every function here launches hand-written sm_100a kernels from libnerf_b200.so on
+``torch.cuda.current_stream()``; nothing falls back to torch ops or to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import lib, check, MlpDesc
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _req(t: Optional[torch.Tensor], name: str, dtype=torch.float32, allow_none=False) -> int:
+    if t is None:
+        if allow_none:
+            return 0
+        raise ValueError(f"{name} is required")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (nerf_siren_b200 has no CPU path); got {t.device}")
+    if t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t.data_ptr()
+
+
+def launch_count() -> int:
+    return int(lib.nerfb_launch_count())
+
+
+def sample_coarse(rays, n_samples, use_disp=False, perturb=0.0, perturb_rand=None):
+    n = rays.shape[0]
+    if rays.dim() != 2 or rays.shape[1] != 8:
+        raise ValueError(f"rays must be (N,8), got {tuple(rays.shape)}")
+    z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
+    pr = _req(perturb_rand, "perturb_rand", allow_none=not perturb > 0)
+    if perturb > 0 and tuple(perturb_rand.shape) != (n, n_samples):
+        raise ValueError("perturb_rand must be (N, n_samples)")
+    check(lib.nerfb_sample_coarse(_req(rays, "rays"), pr, float(perturb), int(bool(use_disp)), n, n_samples,
+                                  z.data_ptr(), _stream()), "nerfb_sample_coarse")
+    return z
+
+
+def embed(x, n_freqs, logscale=True):
+    if x.dim() != 2:
+        raise ValueError("embed expects (B, C)")
+    b, c = x.shape
+    out = torch.empty(b, c * (1 + 2 * n_freqs), device=x.device, dtype=torch.float32)
+    check(lib.nerfb_embed(_req(x, "x"), b, c, n_freqs, int(bool(logscale)), out.data_ptr(), _stream()), "nerfb_embed")
+    return out
+
+
+def composite_fwd(raw, z, rays, noise, noise_std, white_back):
+    """raw (N,S,C) C in {1} u [4,32]; returns (weights, rgb, depth, opacity, extra) -- rgb.. None for C == 1."""
+    n, s, c = raw.shape
+    dev = raw.device
+    weights = torch.empty(n, s, device=dev, dtype=torch.float32)
+    opacity = torch.empty(n, device=dev, dtype=torch.float32)
+    rgb = depth = extra = None
+    if c != 1:
+        rgb = torch.empty(n, 3, device=dev, dtype=torch.float32)
+        depth = torch.empty(n, device=dev, dtype=torch.float32)
+        if c > 4:
+            extra = torch.empty(n, c - 4, device=dev, dtype=torch.float32)
+    check(lib.nerfb_composite_fwd(_req(raw, "raw"), c, _req(z, "z"), _req(rays, "rays"),
+                                  _req(noise, "noise", allow_none=True), float(noise_std), int(bool(white_back)), n, s,
+                                  weights.data_ptr(), rgb.data_ptr() if rgb is not None else 0,
+                                  depth.data_ptr() if depth is not None else 0, opacity.data_ptr(),
+                                  extra.data_ptr() if extra is not None else 0, _stream()), "nerfb_composite_fwd")
+    return weights, rgb, depth, opacity, extra
+
+
+def composite_bwd(raw, z, rays, noise, noise_std, white_back, d_rgb=None, d_depth=None, d_opacity=None,
+                  d_weights=None, d_extra=None):
+    n, s, c = raw.shape
+    d_raw = torch.empty_like(raw)
+    check(lib.nerfb_composite_bwd(_req(raw, "raw"), c, _req(z, "z"), _req(rays, "rays"),
+                                  _req(noise, "noise", allow_none=True), float(noise_std), int(bool(white_back)), n, s,
+                                  _req(d_rgb, "d_rgb", allow_none=True), _req(d_depth, "d_depth", allow_none=True),
+                                  _req(d_opacity, "d_opacity", allow_none=True),
+                                  _req(d_weights, "d_weights", allow_none=True),
+                                  _req(d_extra, "d_extra", allow_none=True), d_raw.data_ptr(), _stream()),
+          "nerfb_composite_bwd")
+    return d_raw
+
+
+def searchsorted(a, v, side="left", out=None):
+    """torchsearchsorted.searchsorted(a, v, out, side) (src/torchsearchsorted/searchsorted.py:20-53)."""
+    if a.dim() != 2 or v.dim() != 2:
+        raise ValueError("input `a` and `v` must be 2-D")
+    if not (a.shape[0] == v.shape[0] or a.shape[0] == 1 or v.shape[0] == 1):
+        raise ValueError("`a` and `v` must have the same number of rows or one of them must have only one")
+    if a.device != v.device:
+        raise ValueError("`a` and `v` must be on the same device")
+    shape = (max(a.shape[0], v.shape[0]), v.shape[1])
+    if out is None:
+        out = torch.empty(shape, device=v.device, dtype=torch.long)
+    elif out.dtype != torch.long or tuple(out.shape) != shape or out.device != a.device:
+        raise ValueError("out must be a torch.long tensor of the result shape on the same device")
+    check(lib.nerfb_searchsorted(_req(a, "a"), a.shape[0], a.shape[1], _req(v, "v"), v.shape[0], v.shape[1],
+                                 1 if side == "left" else 0, _req(out, "out", dtype=torch.long), _stream()),
+          "nerfb_searchsorted")
+    return out
+
+
+def sample_pdf(bins, weights, n_importance, det=False, eps=1e-5, u=None, return_aux=False):
+    n, nb = bins.shape
+    if tuple(weights.shape) != (n, nb - 1):
+        raise ValueError("weights must be (N, bins-1)")
+    if not det and u is None:
+        u = torch.rand(n, n_importance, device=bins.device)          # models/rendering.py:47
+    samples = torch.empty(n, n_importance, device=bins.device, dtype=torch.float32)
+    cdf = inds = None
+    if return_aux:
+        cdf = torch.empty(n, nb, device=bins.device, dtype=torch.float32)
+        inds = torch.empty(n, n_importance, device=bins.device, dtype=torch.long)
+    check(lib.nerfb_sample_pdf(_req(bins, "bins"), _req(weights, "weights"), _req(u, "u", allow_none=det),
+                               int(bool(det)), float(eps), n, nb, n_importance, samples.data_ptr(),
+                               cdf.data_ptr() if cdf is not None else 0, inds.data_ptr() if inds is not None else 0,
+                               _stream()), "nerfb_sample_pdf")
+    if return_aux:
+        return samples, cdf, inds
+    return samples
+
+
+def resample(z_coarse, weights_coarse, n_importance, det, u=None):
+    n, sc = z_coarse.shape
+    z_fine = torch.empty(n, sc + n_importance, device=z_coarse.device, dtype=torch.float32)
+    check(lib.nerfb_resample(_req(z_coarse, "z_coarse"), _req(weights_coarse, "weights_coarse"),
+                             _req(u, "u", allow_none=det), int(bool(det)), n, sc, n_importance, z_fine.data_ptr(),
+                             _stream()), "nerfb_resample")
+    return z_fine
+
+
+# ---------------------------------------------------------------------------------------------------------
+# MLP
+# ---------------------------------------------------------------------------------------------------------
+def mlp_supported(desc: MlpDesc, precision: int, in_mode: int) -> bool:
+    return int(lib.nerfb_mlp_workspace_bytes(C.byref(desc), precision, 128, 0, 0)) >= 0
+
+
+def mlp_workspace(desc: MlpDesc, precision: int, n_points: int, sigma_only: bool, save: bool, device) -> torch.Tensor:
+    nbytes = int(lib.nerfb_mlp_workspace_bytes(C.byref(desc), precision, n_points, int(sigma_only), int(save)))
+    if nbytes < 0:
+        check(nbytes, "nerfb_mlp_workspace_bytes")
+    # uint8 storage from the caching allocator is >= 512-byte aligned; round the base up to 1024 ourselves
+    buf = torch.empty(nbytes + 1024, device=device, dtype=torch.uint8)
+    return buf
+
+
+def _aligned(buf: torch.Tensor):
+    base = buf.data_ptr()
+    off = (-base) % 1024
+    return base + off, buf.numel() - off
+
+
+def mlp_fwd(desc, precision, in_mode, params, film, in0, in1, n_rows, n_samples, sigma_only, save, workspace):
+    p = n_rows * n_samples if in_mode == _lib.IN_RAYS else n_rows
+    c = 1 if sigma_only else int(lib.nerfb_out_channels(C.byref(desc)))
+    out = torch.empty(p, c, device=params.device, dtype=torch.float32)
+    ws_ptr, ws_bytes = _aligned(workspace)
+    check(lib.nerfb_mlp_fwd(C.byref(desc), precision, in_mode, _req(params, "params"), _req(film, "film", allow_none=True),
+                            _req(in0, "in0"), _req(in1, "in1", allow_none=in_mode == _lib.IN_EMBEDDED), n_rows, n_samples,
+                            int(sigma_only), int(save), out.data_ptr(), ws_ptr, ws_bytes, _stream()), "nerfb_mlp_fwd")
+    return out
+
+
+def mlp_bwd(desc, precision, in_mode, params, film, in0, in1, n_rows, n_samples, out, d_out, workspace, want_d_in=False):
+    grad = torch.zeros_like(params)
+    d_in = None
+    if want_d_in:
+        d_in = torch.zeros_like(in0)
+    ws_ptr, ws_bytes = _aligned(workspace)
+    check(lib.nerfb_mlp_bwd(C.byref(desc), precision, in_mode, _req(params, "params"), _req(film, "film", allow_none=True),
+                            _req(in0, "in0"), _req(in1, "in1", allow_none=in_mode == _lib.IN_EMBEDDED), n_rows, n_samples,
+                            _req(out, "out"), _req(d_out, "d_out"), grad.data_ptr(),
+                            d_in.data_ptr() if d_in is not None else 0, ws_ptr, ws_bytes, _stream()), "nerfb_mlp_bwd")
+    return grad, d_in

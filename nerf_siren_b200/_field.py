@@ -40,8 +40,8 @@ class MLPFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, flat, x, film, desc, precision, sigma_only):
-        need = torch.is_grad_enabled() and (flat.requires_grad or x.requires_grad) and not sigma_only
-        if x.requires_grad and precision != _lib.PREC_FP32:
+        need = bool(ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) and not sigma_only
+        if ctx.needs_input_grad[1] and precision != _lib.PREC_FP32:
             raise RuntimeError("gradients w.r.t. the embedded input are only implemented by the fp32 arm")
         ws = ops.mlp_workspace(desc, precision, x.shape[0], sigma_only, need, x.device)
         out = ops.mlp_fwd(desc, precision, _lib.IN_EMBEDDED, flat, film, x, None, x.shape[0], 1, sigma_only, need, ws)

@@ -73,9 +73,9 @@ class _RenderFn(torch.autograd.Function):
     def forward(ctx, flat_c, flat_f, rays, cfg, perturb_rand, noise_c, u, noise_f):
         ctx.set_materialize_grads(False)
         n, S, Si = rays.shape[0], cfg.S, cfg.Si
-        grad_on = torch.is_grad_enabled() and not cfg.test_time
-        need_c = grad_on and flat_c.requires_grad
-        need_f = grad_on and flat_f is not None and flat_f.requires_grad and Si > 0
+        # (torch.is_grad_enabled() is always False inside Function.forward: ask the node instead)
+        need_c = bool(ctx.needs_input_grad[0]) and not cfg.test_time
+        need_f = bool(ctx.needs_input_grad[1]) and flat_f is not None and Si > 0
         nz_c = noise_c if cfg.noise_std != 0 else None
         nz_f = noise_f if cfg.noise_std != 0 else None
 
@@ -255,6 +255,12 @@ def _render(models, embeddings, rays, N_samples, use_disp, perturb, noise_std, N
         raise ValueError("N_importance > 0 needs a fine model: models = [coarse, fine]")
     if N_importance > 0 and N_samples < 3:
         raise ValueError("hierarchical sampling needs at least 3 coarse samples")
+    if rays.shape[0] == 0:                       # empty batch: same keys, empty tensors, no launch
+        e1, e3 = rays.new_zeros(0), rays.new_zeros(0, 3)
+        out = {"opacity_coarse": e1} if test_time else {"rgb_coarse": e3, "depth_coarse": e1, "opacity_coarse": e1}
+        if N_importance > 0:
+            out.update({"rgb_fine": e3, "depth_fine": e1, "opacity_fine": e1})
+        return out
     fused = _fusable(models[0], embeddings[0], embeddings[1]) and (
         N_importance == 0 or (_fusable(models[1], embeddings[0], embeddings[1]) and type(models[1]) is type(models[0])))
     if fused:

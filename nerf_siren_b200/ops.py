@@ -41,6 +41,8 @@ def sample_coarse(rays, n_samples, use_disp=False, perturb=0.0, perturb_rand=Non
     if rays.dim() != 2 or rays.shape[1] != 8:
         raise ValueError(f"rays must be (N,8), got {tuple(rays.shape)}")
     z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
+    if n == 0:
+        return z
     pr = _req(perturb_rand, "perturb_rand", allow_none=not perturb > 0)
     if perturb > 0 and tuple(perturb_rand.shape) != (n, n_samples):
         raise ValueError("perturb_rand must be (N, n_samples)")
@@ -54,6 +56,8 @@ def embed(x, n_freqs, logscale=True):
         raise ValueError("embed expects (B, C)")
     b, c = x.shape
     out = torch.empty(b, c * (1 + 2 * n_freqs), device=x.device, dtype=torch.float32)
+    if b == 0:
+        return out
     check(lib.nerfb_embed(_req(x, "x"), b, c, n_freqs, int(bool(logscale)), out.data_ptr(), _stream()), "nerfb_embed")
     return out
 

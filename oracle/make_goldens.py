@@ -282,7 +282,7 @@ def main():
 
     base = dict(N_samples=64, use_disp=False, perturb=0.0, noise_std=0.0, N_importance=64, chunk=32768,
                 white_back=True, test_time=False)
-    pc, pf = O.nerf_init(seed=21, gain=3.0), O.nerf_init(seed=22, gain=3.0)
+    pc, pf = O.nerf_field(seed=21), O.nerf_field(seed=22)
     rb, rl = O.blender_rays(48, seed=1), O.llff_rays(48, seed=2)
     run_case("blender_det", rb, pc, pf, False, **base)
     run_case("blender_train", rb, pc, pf, False, **{**base, "perturb": 1.0, "noise_std": 1.0})
@@ -292,7 +292,7 @@ def main():
     run_case("blender_disp", rb, pc, pf, False, **{**base, "use_disp": True, "perturb": 1.0})
     run_case("llff_train", rl, pc, pf, False, **{**base, "perturb": 1.0, "noise_std": 1.0, "white_back": False})
     if ref_cls is not None:
-        pc3, pf3 = O.nerf_init(seed=31, gain=3.0, n_cls=6), O.nerf_init(seed=32, gain=3.0, n_cls=6)
+        pc3, pf3 = O.nerf_field(seed=31, n_cls=6), O.nerf_field(seed=32, n_cls=6)
         run_case("llff_cls", rl, pc3, pf3, True, **{**base, "perturb": 1.0, "noise_std": 1.0, "white_back": False})
 
     # ---------------- G6 compositing alone, with grads -----------------------------------------

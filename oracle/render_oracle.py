@@ -343,6 +343,22 @@ def nerf_init(seed: int = 0, gain: float = 1.0, **kw) -> Params:
     return p
 
 
+def nerf_field(seed: int = 0, gain: float = 3.0, sigma_mean: float = 0.5, sigma_std: float = 3.0, **kw) -> Params:
+    """A non-degenerate synthetic field for parity tests: ``nerf_init`` weights whose sigma head is affinely
+    re-calibrated so that raw sigma has the given mean / std over a probe set of Blender-shaped samples (a plain
+    random init yields sigma < 0 almost everywhere, i.e. an empty scene that would hide errors)."""
+    p = nerf_init(seed=seed, gain=gain, **kw)
+    rays = blender_rays(32, seed=99)
+    z = stratified_z(rays, 16)
+    xyz = (rays[:, None, :3] + rays[:, None, 3:6] * z[..., None]).reshape(-1, 3)
+    with torch.no_grad():
+        s = nerf_mlp({k: v for k, v in p.items() if not k.startswith("parse")}, embed(xyz, 10), sigma_only=True)
+        k = sigma_std / float(s.std())
+        p["sigma.weight"] = p["sigma.weight"] * k
+        p["sigma.bias"] = (p["sigma.bias"] - float(s.mean())) * k + sigma_mean
+    return p
+
+
 def blender_rays(n: int, seed: int = 0, hw: int = 800, radius: float = 4.0311, near: float = 2.0,
                  far: float = 6.0) -> torch.Tensor:
     """Synthetic Blender-shaped rays (datasets/blender.py:30-42,64-69; datasets/ray_utils.py:17-50):

@@ -43,5 +43,5 @@ CASES = {
 
 def case_params(name):
     if name == "llff_cls":
-        return O.nerf_init(seed=31, gain=3.0, n_cls=6), O.nerf_init(seed=32, gain=3.0, n_cls=6)
-    return O.nerf_init(seed=21, gain=3.0), O.nerf_init(seed=22, gain=3.0)
+        return O.nerf_field(seed=31, n_cls=6), O.nerf_field(seed=32, n_cls=6)
+    return O.nerf_field(seed=21), O.nerf_field(seed=22)

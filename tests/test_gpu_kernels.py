@@ -131,23 +131,57 @@ def test_resampling_indices_bit_exact_on_identical_cdf(name, ni):
         assert torch.equal(got, want)
 
 
+def _pdf_tolerance(bins, weights, u, eps=1e-5):
+    """Per-sample tolerance for comparing two fp32 evaluations of models/rendering.py:36-66 whose cdf differ by
+    summation order (<= 2e-6).  The formula b0 + (u-c0)/denom*(b1-b0) amplifies a cdf perturbation dc by
+    (b1-b0)/denom, and the reference's `denom < eps -> 1` switch (:63) is discontinuous: samples whose denom is
+    within 3e-6 of eps may legitimately land anywhere in their bin (`stable` False)."""
+    _, cdf, uu, inds = O.sample_pdf(bins, weights, u.shape[1], det=False, u=u, return_aux=True)
+    below, above = (inds - 1).clamp_min(0), inds.clamp_max(weights.shape[1])
+    c0, c1 = cdf.gather(1, below), cdf.gather(1, above)
+    b0, b1 = bins.gather(1, below), bins.gather(1, above)
+    denom = c1 - c0
+    stable = (denom - eps).abs() > 3e-6
+    # an index flip (u within the cdf noise of a knot) is harmless unless a bin touching that knot is "tiny"
+    # (denom < eps -> 1 collapses the whole bin onto its lower edge, so the two sides of the knot disagree)
+    dn = cdf[:, 1:] - cdf[:, :-1]
+    tiny = torch.nn.functional.pad((dn < eps + 3e-6), (1, 1), value=False)     # tiny[:, j+1] <-> bin j
+    for knot, ck in ((below, c0), (above, c1)):
+        near = (uu - ck).abs() < 4e-6
+        exact0 = (knot == 0) & (ck == 0)                                        # cdf[0] = 0 in both: cannot flip
+        touch = tiny.gather(1, knot) | tiny.gather(1, knot + 1)                 # bins knot-1 and knot
+        stable &= ~(near & touch & ~exact0)
+    amp = torch.where(denom < eps, torch.ones_like(denom), denom)
+    tol = 4e-6 + (b1 - b0).abs() * (4e-6 / amp).clamp_max(1.0)
+    # u >= cdf[-1] (the det endpoint u = 1): the reference returns the last edge exactly; an implementation whose
+    # cdf[-1] rounds above 1 interpolates inside the last bin instead -- same point up to cdf noise / last denom
+    top = inds == cdf.shape[1]
+    last_dn = torch.where(dn[:, -1:] < eps, torch.ones_like(dn[:, -1:]), dn[:, -1:])
+    tol_top = 4e-6 + (bins[:, -1:] - bins[:, -2:-1]).abs() * (4e-6 / last_dn).clamp_max(1.0)
+    tol = torch.where(top, tol_top.expand_as(tol), tol)
+    stable &= ~(top & tiny[:, -2:-1].expand_as(top))
+    return tol, stable, b0, b1
+
+
 @pytest.mark.parametrize("name", ["peaky", "flat", "zero", "rand"])
 @pytest.mark.parametrize("ni", [64, 128])
 def test_sample_pdf_values_and_self_consistent_indices(name, ni):
     g = gold("g7_sample_pdf")
-    bins, w = g["bins"].to(DEV), g[f"{name}_w"].to(DEV)
+    bins, w = g["bins"], g[f"{name}_w"]
     ops = nb().ops
-    s_det, cdf, inds = ops.sample_pdf(bins, w, ni, det=True, return_aux=True)
-    s_rnd = ops.sample_pdf(bins, w, ni, det=False, u=g[f"{name}_{ni}_u"].to(DEV))
-    # the in-kernel cdf is a warp scan (the reference: sequential cumsum): 1e-6 on the cdf, and the inverse CDF is
-    # continuous in (cdf,u), so samples agree to 1e-5 of the [2,6] range even where an index flips
+    u_det = O.linspace01(ni).expand(bins.shape[0], ni).contiguous()
+    s_det, cdf, inds = ops.sample_pdf(bins.to(DEV), w.to(DEV), ni, det=True, return_aux=True)
+    s_rnd = ops.sample_pdf(bins.to(DEV), w.to(DEV), ni, det=False, u=g[f"{name}_{ni}_u"].to(DEV))
+    # the in-kernel cdf is a warp scan (the reference: sequential cumsum): <= 2e-6 apart
     assert (cdf.cpu() - g[f"{name}_{ni}_cdf"]).abs().max().item() <= 2e-6
-    assert (s_det.cpu() - g[f"{name}_{ni}_det"]).abs().max().item() <= 4e-5
-    assert (s_rnd.cpu() - g[f"{name}_{ni}_rnd"]).abs().max().item() <= 4e-5
+    for got, ref, u in ((s_det.cpu(), g[f"{name}_{ni}_det"], u_det), (s_rnd.cpu(), g[f"{name}_{ni}_rnd"], g[f"{name}_{ni}_u"])):
+        tol, stable, b0, b1 = _pdf_tolerance(bins, w, u)
+        assert bool(((got - ref).abs() <= tol)[stable].all())
+        assert stable.float().mean().item() > 0.9
+        assert bool((got >= bins[:, :1] - 1e-6).all()) and bool((got <= bins[:, -1:] + 1e-6).all())
     # indices are exact with respect to the kernel's own cdf
-    u = O.linspace01(ni).expand(bins.shape[0], ni).contiguous()
-    assert torch.equal(inds.cpu(), torch.searchsorted(cdf.cpu(), u, right=True))
-    assert nb().sample_pdf(bins, w, ni, det=True).shape == (bins.shape[0], ni)
+    assert torch.equal(inds.cpu(), torch.searchsorted(cdf.cpu(), u_det, right=True))
+    assert nb().sample_pdf(bins.to(DEV), w.to(DEV), ni, det=True).shape == (bins.shape[0], ni)
 
 
 @pytest.mark.parametrize("det", [True, False])
@@ -159,11 +193,21 @@ def test_resample_fused_call_site(det, si):
     z = O.stratified_z(rays, sc, False, 0.0 if det else 1.0, torch.rand(n, sc))
     w = torch.rand(n, sc) ** 6
     w[:7] = 0                                                     # zero-weight rows
-    u = torch.rand(n, si)
+    u = O.linspace01(si).expand(n, si).contiguous() if det else torch.rand(n, si)
     mid = 0.5 * (z[:, :-1] + z[:, 1:])
     z_new = O.sample_pdf(mid, w[:, 1:-1], si, det=det, u=u)
     ref = torch.sort(torch.cat([z, z_new], -1), -1)[0]
     got = nb().ops.resample(z.to(DEV), w.to(DEV), si, det, None if det else u.to(DEV)).cpu()
     assert got.shape == (n, sc + si)
     assert bool((got[:, 1:] >= got[:, :-1]).all())                # sortedness, exact
-    assert (got - ref).abs().max().item() <= 4e-5
+    assert bool((got >= z[:, :1]).all()) and bool((got <= z[:, -1:]).all())
+    # sorting is 1-Lipschitz in the sup norm: per ray, |sorted got - sorted ref| <= the largest per-sample tolerance;
+    # rays holding a sample on the reference's discontinuous `denom < eps` switch are only checked as above
+    tol, stable, _, _ = _pdf_tolerance(mid, w[:, 1:-1], u)
+    ok_rays = stable.all(1)
+    assert ok_rays.float().mean().item() > 0.5
+    err = (got - ref).abs().max(1)[0]
+    assert bool((err <= tol.max(1)[0])[ok_rays].all())
+    # every coarse depth survives the merge exactly (values-only sort of the concatenation)
+    for r in (0, 7, n - 1):
+        assert set(z[r].tolist()) <= set(got[r].tolist())

@@ -161,13 +161,18 @@ def test_render_rays_matches_reference(prec, name):
                  cfg["n_importance"], cfg["chunk"], cfg["white_back"], test_time=cfg["test_time"])
     want = {k[4:] for k in g if k.startswith("out:")}
     assert set(out) == want
-    # rgb/opacity in [0,1], depth in [near,far]: max-abs tolerances.  fp32 arm: 2e-4 (resampled z moves by 1e-6
-    # relative); bf16 arm: 2.5e-2 on rgb/opacity, 6e-2 on depth (of range ~4..6), and PSNR(rgb, ref) >= 35 dB.
+    # rgb/opacity in [0,1], depth in [near,far]: max-abs tolerances.  End to end the fine pass is evaluated at
+    # RESAMPLED depths, which are an ill-conditioned function of the coarse weights (rendering.py:63's
+    # `denom < eps -> 1` switch moves a sample by up to a bin; the test field has spatial frequencies up to 2^9), so
+    # fp32 summation-order noise in the coarse pass shows up at the 1e-3 level in fine outputs.  fp32 arm: coarse
+    # outputs 5e-5, fine outputs 5e-3; the same-depths test below pins the fine pass itself to 5e-5.
+    # bf16 arm: 2.5e-2 on rgb/opacity, 6e-2 on depth, and PSNR(rgb, ref) >= 35 dB.
     for k in want:
         ref = g["out:" + k]
         err = (out[k].cpu() - ref).abs().max().item()
         if prec == "fp32":
-            assert err <= 2e-4 * max(1.0, ref.abs().max().item()), (k, err)
+            lim = 5e-5 if k.endswith("coarse") else 5e-3
+            assert err <= lim * max(1.0, ref.abs().max().item()), (k, err)
         else:
             lim = 6e-2 * max(1.0, ref.abs().max().item()) if k.startswith("depth") else 2.5e-2
             assert err <= lim, (k, err)
@@ -191,7 +196,8 @@ def test_training_step_gradients(prec, name):
     t = g["target"].to(DEV)
     loss = ((out["rgb_coarse"] - t) ** 2).mean() + ((out["rgb_fine"] - t) ** 2).mean()
     loss.backward()
-    ltol, gtol = (1e-5, 2e-3) if prec == "fp32" else (2e-2, 1.5e-1)
+    # end to end (resampled depths move, see above): loss 2e-4, gradients 3e-2 of their norm on the fp32 arm
+    ltol, gtol = (2e-4, 3e-2) if prec == "fp32" else (2e-2, 1.5e-1)
     assert abs(loss.item() - float(g["loss"])) <= ltol * float(g["loss"]) + 1e-7
     for tag, m in (("gradc:", mc), ("gradf:", mf)):
         for k, p in m.named_parameters():
@@ -201,6 +207,48 @@ def test_training_step_gradients(prec, name):
             if f"{tag}{k}" in g:
                 err = (p.grad.cpu() - g[f"{tag}{k}"]).double().norm().item()
                 assert err <= gtol * ref_norm + 1e-9, (tag, k, err, ref_norm)
+
+
+@pytest.mark.parametrize("prec", PRECS)
+@pytest.mark.parametrize("name", ["blender_train", "llff_train", "blender_det"])
+def test_fine_pass_on_reference_depths(prec, name):
+    """Stage-wise parity with the ill-conditioned resampling step factored out: kernels (1)+(4) forward and
+    backward on the REFERENCE's own z_fine (fixture aux:z_fine), against the reference's rgb/depth/opacity and
+    its fine-model gradients."""
+    _set(prec)
+    n = nb()
+    g = gold("g9_" + name)
+    cfg = CASES[name]
+    _, mf = _models_for(name)
+    rays, z = g["rays"].to(DEV), g["aux:z_fine"].to(DEV).contiguous()
+    noise = g["rng:noise_fine"].to(DEV) if cfg["noise_std"] != 0 else None
+    desc = mf._desc(False)
+    precision = n._lib.PREC_FP32 if prec == "fp32" else n._lib.PREC_BF16
+    flat = n._field.flat_params(mf).detach()
+    N, S = z.shape
+    ws = n.ops.mlp_workspace(desc, precision, N * S, False, True, rays.device)
+    raw = n.ops.mlp_fwd(desc, precision, n._lib.IN_RAYS, flat, None, rays, z, N, S, False, True, ws).view(N, S, 4)
+    w, rgb, depth, op, _ = n.ops.composite_fwd(raw, z, rays, noise, cfg["noise_std"], cfg["white_back"])
+    tol = 5e-5 if prec == "fp32" else 2.5e-2
+    assert (rgb.cpu() - g["out:rgb_fine"]).abs().max().item() <= tol
+    assert (op.cpu() - g["out:opacity_fine"]).abs().max().item() <= tol
+    assert (depth.cpu() - g["out:depth_fine"]).abs().max().item() <= tol * 6
+    assert (w.cpu() - g["aux:weights_fine"]).abs().max().item() <= tol
+    d_rgb = (2.0 / (N * 3)) * (rgb - g["target"].to(DEV))                     # d/d rgb of mean((rgb - t)^2)
+    d_raw = n.ops.composite_bwd(raw, z, rays, noise, cfg["noise_std"], cfg["white_back"], d_rgb=d_rgb.contiguous())
+    grad, _ = n.ops.mlp_bwd(desc, precision, n._lib.IN_RAYS, flat, None, rays, z, N, S, raw.view(N * S, 4),
+                            d_raw.view(N * S, 4), ws)
+    gtol = 5e-4 if prec == "fp32" else 8e-2
+    off = 0
+    for k, p in mf.named_parameters():
+        gk = grad[off:off + p.numel()].view_as(p).cpu(); off += p.numel()
+        ref_norm = float(g[f"gradf:{k}@norm"])
+        assert abs(float(gk.double().norm()) - ref_norm) <= gtol * ref_norm + 1e-9, (k, float(gk.double().norm()), ref_norm)
+        if f"gradf:{k}" in g:
+            assert (gk - g[f"gradf:{k}"]).double().norm().item() <= gtol * ref_norm + 1e-9, k
+        if f"gradf:{k}@rows" in g:
+            rows = torch.linspace(0, p.shape[0] - 1, 4).long()
+            assert (gk[rows] - g[f"gradf:{k}@rows"]).double().norm().item() <= gtol * ref_norm + 1e-9, k
 
 
 @pytest.mark.parametrize("prec", PRECS)

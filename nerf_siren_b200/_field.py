@@ -21,13 +21,14 @@ def flat_params(module: torch.nn.Module) -> torch.Tensor:
     return torch.cat([p.reshape(-1) for p in ps])
 
 
-def pick_precision(desc: MlpDesc, in_mode: int) -> int:
+def pick_precision(desc: MlpDesc, need_grad: bool) -> int:
     want = config.get_precision()
     if want == "fp32":
         return _lib.PREC_FP32
-    ok = ops.mlp_supported(desc, _lib.PREC_BF16, in_mode)
+    ok = ops.mlp_supported(desc, _lib.PREC_BF16, need_grad)
     if want == "bf16" and not ok:
-        raise RuntimeError("precision 'bf16' requested but this model shape is outside the tcgen05 kernels")
+        raise RuntimeError("precision 'bf16' requested but this model shape (or its backward) is outside the "
+                           "tcgen05 kernels")
     return _lib.PREC_BF16 if ok else _lib.PREC_FP32
 
 
@@ -67,7 +68,9 @@ def run_embedded(module, desc: MlpDesc, x: torch.Tensor, sigma_only: bool, film:
     if not x.is_cuda:
         raise RuntimeError("input must be a CUDA tensor (nerf_siren_b200 has no CPU path)")
     x = x.contiguous().float()
-    precision = pick_precision(desc, _lib.IN_EMBEDDED)
+    need_grad = torch.is_grad_enabled() and not sigma_only and (
+        x.requires_grad or any(p.requires_grad for p in module.parameters()))
+    precision = pick_precision(desc, need_grad)
     flat = flat_params(module)
     cap = max_points(precision)
     if x.shape[0] <= cap:

@@ -165,8 +165,10 @@ def _render_fused(models, embeddings, rays, S, use_disp, perturb, noise_std, Si,
     cfg.desc_f = mf._desc(False, emb_xyz.N_freqs, emb_dir.N_freqs, emb_xyz.logscale) if mf is not None else None
     cfg.film_c = mc._film()
     cfg.film_f = mf._film() if mf is not None else None
-    pc = _field.pick_precision(cfg.desc_c, _lib.IN_RAYS)
-    pf = _field.pick_precision(cfg.desc_f, _lib.IN_RAYS) if mf is not None else pc
+    need_grad = torch.is_grad_enabled() and not test_time and any(
+        p.requires_grad for m in (mc, mf) if m is not None for p in m.parameters())
+    pc = _field.pick_precision(cfg.desc_c, need_grad)
+    pf = _field.pick_precision(cfg.desc_f, need_grad) if mf is not None else pc
     cfg.precision = pc if pc == pf else _lib.PREC_FP32
     flat_c = _field.flat_params(mc)
     flat_f = _field.flat_params(mf) if mf is not None else None

@@ -147,8 +147,9 @@ def resample(z_coarse, weights_coarse, n_importance, det, u=None):
 # ---------------------------------------------------------------------------------------------------------
 # MLP
 # ---------------------------------------------------------------------------------------------------------
-def mlp_supported(desc: MlpDesc, precision: int, in_mode: int) -> bool:
-    return int(lib.nerfb_mlp_workspace_bytes(C.byref(desc), precision, 128, 0, 0)) >= 0
+def mlp_supported(desc: MlpDesc, precision: int, need_grad: bool = False) -> bool:
+    """Does this arm implement the model (forward, and backward when need_grad)?"""
+    return int(lib.nerfb_mlp_workspace_bytes(C.byref(desc), precision, 128, 0, int(bool(need_grad)))) >= 0
 
 
 def mlp_workspace(desc: MlpDesc, precision: int, n_points: int, sigma_only: bool, save: bool, device) -> torch.Tensor:

@@ -16,17 +16,17 @@ def nb():
     return nerf_siren_b200
 
 
-def bf16_available():
+def bf16_available(need_grad=False):
     m = nb().NeRF()
-    return nb().ops.mlp_supported(m._desc(False), nb()._lib.PREC_BF16, 0)
+    return nb().ops.mlp_supported(m._desc(False), nb()._lib.PREC_BF16, need_grad)
 
 
 PRECS = ["fp32", "bf16"]
 
 
-def _set(prec):
-    if prec == "bf16" and not bf16_available():
-        pytest.skip("tcgen05 arm not built")
+def _set(prec, need_grad=False):
+    if prec == "bf16" and not bf16_available(need_grad):
+        pytest.skip("tcgen05 arm does not cover this yet")
     nb().set_precision(prec)
 
 
@@ -50,6 +50,8 @@ def test_nerf_module_forward_backward(prec, tag, gain):
     assert y.shape == (96, 4) and s.shape == (96, 1)
     assert (y.cpu() - g["y"]).abs().max().item() <= tol * ys
     assert (s.cpu() - g["sigma"]).abs().max().item() <= tol * ys
+    if prec == "bf16" and not bf16_available(True):
+        return
     (y * g["up"].to(DEV)).sum().backward()
     gtol = 1e-4 if prec == "fp32" else 6e-2
     for k, p in m.named_parameters():
@@ -62,6 +64,29 @@ def test_nerf_module_forward_backward(prec, tag, gain):
             rows = torch.linspace(0, p.shape[0] - 1, 4).long()
             err = (p.grad.cpu()[rows] - g[f"grad:{k}@rows"]).double().norm().item()
             assert err <= gtol * float(g[f"grad:{k}@rows"].double().norm()) + 1e-7, k
+
+
+@pytest.mark.parametrize("D,skips,sigma_only", [(1, [], True), (1, [], False), (2, [], False), (3, [1], False),
+                                                (8, [4], True), (8, [4], False), (9, [2, 5], False)])
+def test_tensor_core_forward_depth_ladder(D, skips, sigma_only):
+    """bf16 tcgen05 arm on networks of growing depth (each rung adds one piece of the fused kernel: X tile + one
+    UMMA K-block + sigma head, activation hand-off between layers, skip K-block, final / direction / rgb head), on
+    130 + 257 rows (ragged last tile, multi-tile).  Tolerance: bf16 operands (2^-9 relative per rounding) through
+    D+2 layers, against the fp32 oracle: 3e-2 of the output scale."""
+    _set("bf16")
+    p = O.nerf_init(seed=40 + D, gain=2.0, D=D, skips=tuple(skips))
+    m = nb().NeRF(D=D, skips=skips).to(DEV)
+    m.load_state_dict(p)
+    for rows in (130, 257):
+        x = torch.randn(rows, 90, generator=torch.Generator().manual_seed(rows))
+        x[:, :3] *= 2
+        xin = x[:, :63].contiguous() if sigma_only else x
+        ref = O.nerf_mlp(p, xin, sigma_only, D=D, skips=tuple(skips))
+        with torch.no_grad():
+            got = m(xin.to(DEV), sigma_only=sigma_only).cpu()
+        assert got.shape == ref.shape
+        scale = ref.abs().max().item()
+        assert (got - ref).abs().max().item() <= 3e-2 * scale, (rows, (got - ref).abs().max().item(), scale)
 
 
 @pytest.mark.parametrize("prec", ["fp32"])
@@ -80,7 +105,7 @@ def test_nerf_input_gradient_fp32(prec):
 
 @pytest.mark.parametrize("prec", PRECS)
 def test_nerf3d_module(prec):
-    _set(prec)
+    _set(prec, True)
     g = gold("g2_nerf3d")
     m = _load(nb().NeRF_3D, O.nerf_init(seed=5, gain=2.0, n_cls=6), CLS=6)
     y = m(g["x"].to(DEV))
@@ -100,7 +125,7 @@ def test_siren_module(prec, tag):
     _set(prec)
     g = gold("g4_siren_" + tag)
     m = _load(nb().SemanticNeRF, O.siren_init(seed=7))
-    if prec == "bf16" and not nb().ops.mlp_supported(m._desc(), nb()._lib.PREC_BF16, 1):
+    if prec == "bf16" and not nb().ops.mlp_supported(m._desc(), nb()._lib.PREC_BF16, True):
         pytest.skip("SIREN not on the tensor-core arm yet")
     y = m.forward_with_frequencies_phase_shifts(g["pts"].to(DEV), g["freq"].to(DEV), g["phase"].to(DEV), g["dirs"].to(DEV))
     assert y.shape == (1, 96, 4)
@@ -154,6 +179,8 @@ def test_render_rays_matches_reference(prec, name):
     g = gold("g9_" + name)
     cfg = CASES[name]
     mc, mf = _models_for(name)
+    if prec == "bf16" and not nb().ops.mlp_supported(mc._desc(False), nb()._lib.PREC_BF16, False):
+        pytest.skip("model family not on the tensor-core arm yet")
     emb = [nb().Embedding(3, 10), nb().Embedding(3, 4)]
     fn = nb().render_rays_3d if name == "llff_cls" else nb().render_rays
     with _ReplayRNG(rng_of(g), cfg), torch.no_grad():
@@ -185,7 +212,7 @@ def test_render_rays_matches_reference(prec, name):
 @pytest.mark.parametrize("name", ["blender_train", "llff_train", "blender_det"])
 def test_training_step_gradients(prec, name):
     """G10: render + MSELoss (losses.py:15-20) + backward; every parameter gradient against the reference's."""
-    _set(prec)
+    _set(prec, True)
     g = gold("g9_" + name)
     cfg = CASES[name]
     mc, mf = _models_for(name)
@@ -215,7 +242,7 @@ def test_fine_pass_on_reference_depths(prec, name):
     """Stage-wise parity with the ill-conditioned resampling step factored out: kernels (1)+(4) forward and
     backward on the REFERENCE's own z_fine (fixture aux:z_fine), against the reference's rgb/depth/opacity and
     its fine-model gradients."""
-    _set(prec)
+    _set(prec, True)
     n = nb()
     g = gold("g9_" + name)
     cfg = CASES[name]
@@ -256,7 +283,7 @@ def test_render_siren_field_against_oracle(prec):
     _set(prec)
     ps = O.siren_init(seed=9)
     m = nb().SirenField().to(DEV)
-    if prec == "bf16" and not nb().ops.mlp_supported(m._desc(), nb()._lib.PREC_BF16, 0):
+    if prec == "bf16" and not nb().ops.mlp_supported(m._desc(), nb()._lib.PREC_BF16, False):
         pytest.skip("SIREN not on the tensor-core arm yet")
     m.load_state_dict({**ps, "frequencies": torch.zeros(9 * 256), "phase_shifts": torch.zeros(9 * 256)})
     rays = O.blender_rays(64, seed=8)

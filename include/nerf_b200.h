@@ -129,6 +129,16 @@ int nerfb_sample_pdf(const float* bins, const float* weights, const float* u, in
 int nerfb_resample(const float* z_coarse, const float* weights_coarse, const float* u, int det,
                    int64_t n_rays, int n_coarse, int n_importance, float* z_fine, void* stream);
 
+/* ---- (5) ray-sharded data-parallel step, device side ---------------------------------------------
+ * The reference's step boundary is Lightning DDP + torch.optim.Adam (train.py:41-66, utils/__init__.py:11-31,
+ * system.py:257-275).  Here the host all-reduces ONE flat gradient buffer over NCCL (SUM) and this entry applies
+ * the Adam update (torch.optim.Adam semantics: lr, betas, eps, no weight decay, no amsgrad) to the flat
+ * parameter buffer in one launch; grad_scale (= 1/world_size) turns the SUM into the DDP mean.  step >= 1 is
+ * the 1-based update count (bias correction).  All four buffers hold n floats, 16-byte aligned. */
+int nerfb_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                    float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
+                    void* stream);
+
 /* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
 int64_t nerfb_launch_count(void);
 

@@ -12,6 +12,11 @@ from ._lib import MlpDesc
 
 def flat_params(module: torch.nn.Module) -> torch.Tensor:
     """One contiguous fp32 blob in state_dict order; torch.cat keeps autograd routing grads to the params."""
+    sl = getattr(module, "_nerfb_flat_slice", None)
+    if sl is not None:                       # parameters already live in one flat buffer (dp.FlatParameters)
+        flat = sl.get(module)
+        if flat is not None:
+            return flat
     ps = list(module.parameters())
     for p in ps:
         if not p.is_cuda:

@@ -46,6 +46,7 @@ SIGNATURES = {
     "nerfb_searchsorted": (_I, [_P, _L, _L, _P, _L, _L, _I, _P, _P]),
     "nerfb_sample_pdf": (_I, [_P, _P, _P, _I, _F, _L, _I, _I, _P, _P, _P, _P]),
     "nerfb_resample": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P]),
+    "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P]),
 }
 
 if not os.path.exists(LIB_PATH):

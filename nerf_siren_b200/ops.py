@@ -144,6 +144,17 @@ def resample(z_coarse, weights_coarse, n_importance, det, u=None):
     return z_fine
 
 
+def adam_step(params, grads, exp_avg, exp_avg_sq, step, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+    """In-place Adam update of a flat fp32 parameter buffer (one launch); see nerfb_adam_step."""
+    n = params.numel()
+    for t, name in ((params, "params"), (grads, "grads"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        if t.numel() != n:
+            raise ValueError(f"{name} must have {n} elements")
+    check(lib.nerfb_adam_step(_req(params, "params"), _req(grads, "grads"), _req(exp_avg, "exp_avg"),
+                              _req(exp_avg_sq, "exp_avg_sq"), n, float(lr), float(betas[0]), float(betas[1]),
+                              float(eps), int(step), float(grad_scale), _stream()), "nerfb_adam_step")
+
+
 # ---------------------------------------------------------------------------------------------------------
 # MLP
 # ---------------------------------------------------------------------------------------------------------

@@ -406,6 +406,7 @@ bool tc_supported(const nerfb_mlp_desc& d, int in_mode) {
   return true;
 }
 
+TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P);
 static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool save) {
   TcPlan pl{};
   const NerfOffsets o = nerf_offsets(d);
@@ -475,7 +476,7 @@ int64_t tc_workspace_bytes(const nerfb_mlp_desc& d, int64_t P, int sigma_only, i
   if (!tc_supported(d, 0)) return NERFB_E_UNSUPPORTED;
   if (save && !tc_bwd_supported(d)) return NERFB_E_UNSUPPORTED;
   int64_t total = tc_plan(d, P, sigma_only != 0, save != 0).total;
-  if (save) total += tc_bwd_workspace_bytes(d, P);
+  if (save) total = round_up64(total, 1024) + tc_bwd_workspace_bytes(d, P);
   return total;
 }
 
@@ -508,4 +509,16 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
   NERFB_LAUNCH(mlp_tc_fwd_kernel, grid, NUM_THREADS, smem, stream, a);
   return NERFB_OK;
+}
+
+// Layout of the saved-activation records, for the backward kernels (mlp_tc_bwd.cu).
+TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P) {
+  const TcPlan pl = tc_plan(d, P, false, true);
+  TcFwdLayout L{};
+  L.n_steps = pl.prog.n_steps;
+  for (int s = 0; s < pl.prog.n_steps; ++s) L.step_save_off[s] = pl.prog.s[s].save_off;
+  L.save_x_off = pl.prog.save_x_off; L.save_dir_off = pl.prog.save_dir_off;
+  L.tile_save_bytes = pl.prog.tile_save_bytes;
+  L.off_save = pl.off_save; L.total = round_up64(pl.total, 1024);
+  return L;
 }

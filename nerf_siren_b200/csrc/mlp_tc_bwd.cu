@@ -1,7 +1,600 @@
-// Kernel (1), tensor-core arm, backward -- under construction: reports "unsupported" so that callers needing
-// gradients stay on the fp32 arm (there is no CPU fallback either way).
+// Kernel (1), tensor-core arm, backward: autograd of the fused encoding + NeRF MLP (models/nerf.py:100-124) on
+// tcgen05 / TMEM, from the bf16 activations the forward kernel parked per 128-sample tile.
+//
+// Three launches per call:
+//   A. mlp_tc_dgrad_kernel   -- persistent, one CTA per SM, same warp roles / K-block pipelined layer chain as the
+//      forward but walking the network backwards: per tile, dZ_dir (rgb head folded in on the CUDA cores) ->
+//      x W_dir^T -> dZ_final -> x W_final^T (+ d_sigma (x) w_sigma) (.) [h8 > 0] -> dZ_8 -> ... -> dZ_1.  Every dZ block
+//      is a [128 x 64] bf16 swizzled image that is (a) the next UMMA's K-major A operand and (b) bulk-stored to HBM.
+//   B. mlp_tc_wgrad_kernel   -- dW_l = dZ_l^T A_{l-1}: M = out features, N = in features, K = SAMPLES.  The very same
+//      [samples x 64] block images are read back as MN-major UMMA operands (no transpose anywhere); each CTA owns a
+//      contiguous range of tiles, accumulates one weight matrix at a time in TMEM (2 x 128 lanes x N columns) over
+//      its whole range, flushes it once to a per-CTA partial, and spare warps column-sum dZ from shared memory for
+//      the bias gradients.  head_wgrad_kernel does the 1- and 3-row heads on the CUDA cores.
+//   C. reduce_partials_kernel -- grad += sum over CTAs of the partials (the gradient buffer is accumulated into).
 #include "common.cuh"
-bool tc_bwd_supported(const nerfb_mlp_desc&) { return false; }
-int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc&, int64_t) { return 0; }
-int tc_mlp_bwd(const nerfb_mlp_desc&, int, const float*, const float*, const float*, const float*, int64_t, int,
-               const float*, const float*, float*, float*, void*, int64_t, void*) { return NERFB_E_UNSUPPORTED; }
+#include "tc_common.cuh"
+
+using namespace tc;
+
+TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P);     // mlp_tc.cu
+bool tc_supported(const nerfb_mlp_desc& d, int in_mode);
+
+namespace {
+
+constexpr int N_STAGES = 4;
+constexpr int STAGE_BYTES = 256 * 128;
+constexpr int NUM_THREADS = 320;
+constexpr int EPI_THREADS = 256;
+constexpr int MAX_BSTEPS = 12;
+
+// ---- weight packing for the dgrad chain: slab (n, kk) = W[(row0 + kk) * ld + col0 + n]  (W^T, K-major) -----------
+struct PackTSlab { int64_t w_off; int ld; int row0; int nrows; int col0; int64_t dst_off; };
+struct PackTArgs { int n_slabs; PackTSlab slab[40]; };
+
+__global__ void __launch_bounds__(256) pack_weights_t_kernel(const float* __restrict__ params, PackTArgs pa,
+                                                             uint8_t* __restrict__ blob) {
+  const PackTSlab sl = pa.slab[blockIdx.x];
+  for (int idx = threadIdx.x; idx < 256 * 8; idx += blockDim.x) {        // n fastest across threads: coalesced reads
+    const int n = idx & 255, ch = idx >> 8;
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int kk = ch * 8 + e;
+      f[e] = (kk < sl.nrows) ? __ldg(params + sl.w_off + (int64_t)(sl.row0 + kk) * sl.ld + sl.col0 + n) : 0.f;
+    }
+    uint4 o;
+    o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+    *reinterpret_cast<uint4*>(blob + sl.dst_off + (int64_t)n * 128 + ((ch ^ (n & 7)) << 4)) = o;
+  }
+}
+
+// ---- dgrad chain program -------------------------------------------------------------------------------------------
+struct BStep {
+  int n_kb;          // K-blocks (64 upstream features each) of this step's A operand = blocks 0..n_kb-1
+  int mask_off;      // forward-record offset of the activation whose sign gates this step's output (-1: no gate)
+  int add_sigma;     // output += d_sigma (x) w_sigma before gating (the sigma head reads the same activation)
+  int save_off;      // backward-record offset of this step's output dZ (4 blocks)
+};
+struct BProgram {
+  int n_steps;
+  BStep s[MAX_BSTEPS];
+  int hd_off;        // forward-record offset of the direction layer's activations (2 blocks), gate of dZ_dir
+  int dzdir_off;     // backward-record offset of dZ_dir (2 blocks)
+  int fwd_tile_bytes, bwd_tile_bytes;
+};
+
+struct DgradArgs {
+  BProgram prog;
+  const uint8_t* wblob;            // transposed bf16 slabs in schedule order
+  const float* heads;              // w_sigma[256] | w_rgb[3*128]
+  const float* out; const float* d_out;
+  const uint8_t* fwd_rec; uint8_t* bwd_rec;
+  int64_t P; int64_t n_tiles;
+};
+
+struct __align__(1024) SmemD {
+  uint8_t g[4][BLK_BYTES];               // current dZ tile: 4 K-blocks
+  uint8_t ring[N_STAGES][STAGE_BYTES];
+  float w_sigma[256];
+  float w_rgb[3 * 128];
+  uint64_t w_full[N_STAGES], w_empty[N_STAGES];
+  uint64_t a_ready[4];
+  uint64_t acc_full[2];
+  uint32_t tmem_base;
+};
+
+}  // namespace
+
+namespace {
+
+// 32 bf16 gate values (this thread's row, 32 consecutive columns) of a saved [128 x 64] block: 4 x 16 B
+__device__ __forceinline__ void load_gate(const uint8_t* blk, int row, int h, uint4 (&m)[4]) {
+#pragma unroll
+  for (int ch = 0; ch < 4; ++ch)
+    m[ch] = __ldg(reinterpret_cast<const uint4*>(blk + (uint32_t)row * 128u + ((((uint32_t)(4 * h + ch)) ^ ((uint32_t)row & 7u)) << 4)));
+}
+__device__ __forceinline__ void apply_gate(float (&f)[32], const uint4 (&m)[4]) {
+#pragma unroll
+  for (int ch = 0; ch < 4; ++ch) {
+    const uint32_t w[4] = {m[ch].x, m[ch].y, m[ch].z, m[ch].w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {              // post-ReLU activations are >= +0: "h > 0" == "bits != 0"
+      if ((w[e] & 0xFFFFu) == 0u) f[8 * ch + 2 * e] = 0.f;
+      if ((w[e] >> 16) == 0u) f[8 * ch + 2 * e + 1] = 0.f;
+    }
+  }
+}
+__device__ __forceinline__ void store_block_row(uint32_t blk, int row, int h, const float (&f)[32]) {
+#pragma unroll
+  for (int ch = 0; ch < 4; ++ch) {
+    const uint32_t addr = blk + (uint32_t)row * 128u + ((((uint32_t)(4 * h + ch)) ^ ((uint32_t)row & 7u)) << 4);
+    sts128(addr, pack_bf16(f[8 * ch + 0], f[8 * ch + 1]), pack_bf16(f[8 * ch + 2], f[8 * ch + 3]),
+           pack_bf16(f[8 * ch + 4], f[8 * ch + 5]), pack_bf16(f[8 * ch + 6], f[8 * ch + 7]));
+  }
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __grid_constant__ DgradArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemD& sm = *reinterpret_cast<SmemD*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const BProgram& pg = args.prog;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __shared__ uint64_t g_free;
+
+  for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.heads + i);
+  for (int i = threadIdx.x; i < 384; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.heads + 256 + i);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.a_ready[i], 8);
+    mbar_init(&sm.acc_full[0], 1); mbar_init(&sm.acc_full[1], 1);
+    mbar_init(&g_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {                       // ===== weight producer: W^T slabs, 32 KB each =====
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+        const uint8_t* src = args.wblob;
+        for (int s = 0; s < pg.n_steps; ++s)
+          for (int kb = 0; kb < pg.s[s].n_kb; ++kb) {
+            mbar_wait(&sm.w_empty[stage], phase ^ 1);
+            mbar_expect_tx(&sm.w_full[stage], STAGE_BYTES);
+            bulk_g2s(sm.ring[stage], src, STAGE_BYTES, &sm.w_full[stage]);
+            src += STAGE_BYTES;
+            if (++stage == N_STAGES) { stage = 0; phase ^= 1; }
+          }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {                       // ===== MMA issuer =====
+      int stage = 0; uint32_t phase = 0;
+      uint32_t a_phase[4] = {0, 0, 0, 0};
+      uint32_t gs = 0;
+      const uint32_t idesc = umma_idesc_bf16(TILE_M, 256);
+      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+        uint8_t* rec = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes;
+        for (int s = 0; s < pg.n_steps; ++s, ++gs) {
+          const BStep& st = pg.s[s];
+          const uint32_t d_tmem = tmem + (gs & 1) * 256;
+          const int in_off = (s == 0) ? pg.dzdir_off : pg.s[s - 1].save_off;
+          for (int kb = 0; kb < st.n_kb; ++kb) {
+            mbar_wait(&sm.a_ready[kb], a_phase[kb]); a_phase[kb] ^= 1;
+            bulk_s2g(rec + in_off + kb * BLK_BYTES, sm.g[kb], BLK_BYTES);        // dZ block -> HBM for the wgrad
+            mbar_wait(&sm.w_full[stage], phase);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(sm.g[kb]), b_addr = smem_u32(sm.ring[stage]);
+#pragma unroll
+            for (int k = 0; k < KBLK / 16; ++k)
+              umma_bf16(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
+                        (kb > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&sm.w_empty[stage]);
+            if (++stage == N_STAGES) { stage = 0; phase ^= 1; }
+          }
+          bulk_commit(); bulk_wait_read0();
+          umma_commit(&sm.acc_full[gs & 1]);
+        }
+        const int last_off = pg.s[pg.n_steps - 1].save_off;
+        for (int j = 0; j < 4; ++j) {
+          mbar_wait(&sm.a_ready[j], a_phase[j]); a_phase[j] ^= 1;
+          bulk_s2g(rec + last_off + j * BLK_BYTES, sm.g[j], BLK_BYTES);
+        }
+        bulk_commit(); bulk_wait_read0();
+        mbar_arrive(&g_free);                 // the next tile's prologue may overwrite the dZ blocks
+      }
+      bulk_wait_all0();
+    }
+  } else {
+    // ===== prologue (rgb head + direction-layer gate) and per-step epilogues =====
+    const int ew = warp - 2, q = warp & 3, h = ew >> 2;
+    const int row = q * 32 + lane;
+    uint32_t acc_phase[2] = {0, 0}, free_phase = 0;
+    uint32_t gs = 0;
+    bool first = true;
+    for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+      const int64_t p = tile * TILE_M + row;
+      const bool live = p < args.P;
+      const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes;
+      float g0 = 0.f, g1 = 0.f, g2 = 0.f, dsig = 0.f;
+      if (live) {
+        const float4 y = __ldg(reinterpret_cast<const float4*>(args.out + p * 4));
+        const float4 dy = __ldg(reinterpret_cast<const float4*>(args.d_out + p * 4));
+        g0 = dy.x * y.x * (1.f - y.x); g1 = dy.y * y.y * (1.f - y.y); g2 = dy.z * y.z * (1.f - y.z);   // sigmoid'
+        dsig = dy.w;
+      }
+      uint4 gate[4];
+      load_gate(frec + pg.hd_off, row, h, gate);
+      if (!first) { mbar_wait(&g_free, free_phase); free_phase ^= 1; }
+      first = false;
+#pragma unroll 1
+      for (int j = 0; j < 2; ++j) {           // dZ_dir = (g . W_rgb) (.) [hd > 0]     (models/nerf.py:119-120)
+        float f[32];
+        const int col0 = 64 * j + 32 * h;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[128 + col0 + i] + g2 * sm.w_rgb[256 + col0 + i];
+        apply_gate(f, gate);
+        if (j == 0) load_gate(frec + pg.hd_off + BLK_BYTES, row, h, gate);
+        store_block_row(smem_u32(sm.g[j]), row, h, f);
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.a_ready[j]);
+      }
+      for (int s = 0; s < pg.n_steps; ++s, ++gs) {
+        const BStep& st = pg.s[s];
+        const int a = gs & 1;
+        const bool gated = st.mask_off >= 0;
+        if (gated) load_gate(frec + st.mask_off, row, h, gate);
+        mbar_wait(&sm.acc_full[a], acc_phase[a]); acc_phase[a] ^= 1;
+        tc_fence_after();
+#pragma unroll 1
+        for (int j = 0; j < 4; ++j) {
+          uint32_t v[32];
+          const int col0 = 64 * j + 32 * h;
+          tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * 256 + col0), v);
+          tmem_ld_wait();
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+          if (st.add_sigma) {                 // sigma = <h8, w_sigma> + b reads the same activation (models/nerf.py:112)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaf(dsig, sm.w_sigma[col0 + i], f[i]);
+          }
+          if (gated) {
+            apply_gate(f, gate);
+            if (j < 3) load_gate(frec + st.mask_off + (j + 1) * BLK_BYTES, row, h, gate);
+          }
+          store_block_row(smem_u32(sm.g[j]), row, h, f);
+          fence_proxy_async();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.a_ready[j]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+}  // namespace
+
+// =====================================================================================================================
+// B. wgrad: dW = dZ^T A over samples, MN-major operands straight from the saved tile images
+// =====================================================================================================================
+namespace {
+
+constexpr int W_STAGES = 3;
+constexpr int W_HALF = 8192;                 // 64 sample rows of one [128 x 64] block
+constexpr int W_STAGE_BYTES = 8 * W_HALF;    // dZ blocks [0,4) | input blocks [4,8)
+constexpr int W_THREADS = 192;               // warp 0 producer, warp 1 MMA, warps 2..5 bias sums + accumulator flush
+constexpr int MAX_ITEMS = 16;
+
+struct WItem {
+  int dz_off, nM;            // backward-record offset of dZ, number of 64-column blocks (4: M = 256, 2: M = 128)
+  int a_fwd, a_off, nN;      // input activation: record (1 = forward record, 0 = backward record), offset, blocks
+  int N;                     // UMMA N = 64 * nN
+  int64_t w_off; int ld, col0, nvalid;   // destination: grad[w_off + out * ld + col0 + n], n < nvalid
+  int64_t bias_off;          // destination of colsum(dZ), or -1
+};
+struct WgradArgs {
+  int n_items; WItem item[MAX_ITEMS];
+  const uint8_t* fwd_rec; const uint8_t* bwd_rec; int fwd_tile_bytes, bwd_tile_bytes;
+  int64_t n_tiles; int n_active;
+  float* partial; int64_t partial_stride;
+  float* grad;
+};
+
+struct __align__(1024) SmemW {
+  uint8_t stage[W_STAGES][W_STAGE_BYTES];
+  uint64_t full[W_STAGES], empty[W_STAGES];
+  uint64_t acc_done, acc_free;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid_constant__ WgradArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemW& sm = *reinterpret_cast<SmemW*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t t0 = args.n_tiles * blockIdx.x / args.n_active, t1 = args.n_tiles * (blockIdx.x + 1) / args.n_active;
+  const int n_chunks = (int)(t1 - t0) * 2;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < W_STAGES; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 5); }
+    mbar_init(&sm.acc_done, 1); mbar_init(&sm.acc_free, 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {                         // ===== producer: 64-sample halves of the dZ and input blocks =====
+      int st = 0; uint32_t ph = 0;
+      for (int it = 0; it < args.n_items; ++it) {
+        const WItem& im = args.item[it];
+        const uint8_t* abase = im.a_fwd ? args.fwd_rec : args.bwd_rec;
+        const int64_t astride = im.a_fwd ? args.fwd_tile_bytes : args.bwd_tile_bytes;
+        for (int c = 0; c < n_chunks; ++c) {
+          const int64_t tile = t0 + (c >> 1); const int half = c & 1;
+          mbar_wait(&sm.empty[st], ph ^ 1);
+          mbar_expect_tx(&sm.full[st], (uint32_t)(im.nM + im.nN) * W_HALF);
+          const uint8_t* dz = args.bwd_rec + tile * (int64_t)args.bwd_tile_bytes + im.dz_off + half * W_HALF;
+          for (int j = 0; j < im.nM; ++j) bulk_g2s(sm.stage[st] + j * W_HALF, dz + j * BLK_BYTES, W_HALF, &sm.full[st]);
+          const uint8_t* a = abase + tile * astride + im.a_off + half * W_HALF;
+          for (int j = 0; j < im.nN; ++j) bulk_g2s(sm.stage[st] + (4 + j) * W_HALF, a + j * BLK_BYTES, W_HALF, &sm.full[st]);
+          if (++st == W_STAGES) { st = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {                         // ===== MMA issuer =====
+      int st = 0; uint32_t ph = 0, free_ph = 0;
+      for (int it = 0; it < args.n_items; ++it) {
+        const WItem& im = args.item[it];
+        const uint32_t idesc = umma_idesc_bf16(128, im.N, 1, 1);
+        if (it > 0) { mbar_wait(&sm.acc_free, free_ph); free_ph ^= 1; tc_fence_after(); }
+        for (int c = 0; c < n_chunks; ++c) {
+          mbar_wait(&sm.full[st], ph);
+          tc_fence_after();
+          const uint32_t base = smem_u32(sm.stage[st]);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)       // 16 samples per UMMA
+            for (int mh = 0; mh < (im.nM >> 1); ++mh)
+              umma_bf16(tmem + mh * 256, umma_desc_mn128(base + mh * 2 * W_HALF + ks * 2048, W_HALF),
+                        umma_desc_mn128(base + 4 * W_HALF + ks * 2048, W_HALF), idesc, (c > 0 || ks > 0) ? 1u : 0u);
+          umma_commit(&sm.empty[st]);
+          if (++st == W_STAGES) { st = 0; ph ^= 1; }
+        }
+        umma_commit(&sm.acc_done);
+      }
+    }
+  } else {
+    // ===== bias column sums (from shared memory) + accumulator flush =====
+    const int q = warp & 3, bt = (warp - 2) * 32 + lane;
+    const int blk = bt >> 5, c2 = bt & 31;
+    int st = 0; uint32_t ph = 0, done_ph = 0;
+    float* part = args.partial + (int64_t)blockIdx.x * args.partial_stride;
+    for (int it = 0; it < args.n_items; ++it) {
+      const WItem& im = args.item[it];
+      float b0 = 0.f, b1 = 0.f;
+      const bool sum_here = im.bias_off >= 0 && blk < im.nM;
+      for (int c = 0; c < n_chunks; ++c) {
+        mbar_wait(&sm.full[st], ph);
+        if (sum_here) {
+          const uint8_t* src = sm.stage[st] + blk * W_HALF + ((c2 & 3) << 2);
+#pragma unroll 8
+          for (int r = 0; r < 64; ++r) {
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(src + r * 128 + ((((uint32_t)c2 >> 2) ^ ((uint32_t)r & 7u)) << 4));
+            b0 += __uint_as_float(w << 16); b1 += __uint_as_float(w & 0xFFFF0000u);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[st]);
+        if (++st == W_STAGES) { st = 0; ph ^= 1; }
+      }
+      if (sum_here && n_chunks > 0) {
+        atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
+        atomicAdd(args.grad + im.bias_off + 2 * bt + 1, b1);
+      }
+      mbar_wait(&sm.acc_done, done_ph); done_ph ^= 1;
+      tc_fence_after();
+      for (int mh = 0; mh < (im.nM >> 1); ++mh) {
+        float* dst = part + im.w_off + (int64_t)(mh * 128 + q * 32 + lane) * im.ld + im.col0;
+        for (int c0 = 0; c0 < im.N; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(mh * 256 + c0), v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c0 + i < im.nvalid) dst[c0 + i] = __uint_as_float(v[i]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.acc_free);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// grad[w_off + r * ld + col0 + n] += sum over the active CTAs' partials
+struct ReduceArgs { int n_items; WItem item[MAX_ITEMS]; int n_active; const float* partial; int64_t partial_stride; float* grad; };
+__global__ void __launch_bounds__(256) reduce_partials_kernel(ReduceArgs ra) {
+  const WItem im = ra.item[blockIdx.x];
+  const int M = im.nM * 32 * 2;
+  const int total = M * im.nvalid;
+  for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < total; e += gridDim.y * blockDim.x) {
+    const int r = e / im.nvalid, n = e - r * im.nvalid;
+    const int64_t idx = im.w_off + (int64_t)r * im.ld + im.col0 + n;
+    float s = 0.f;
+    for (int c = 0; c < ra.n_active; ++c) s += ra.partial[(int64_t)c * ra.partial_stride + idx];
+    ra.grad[idx] += s;
+  }
+}
+
+}  // namespace
+
+// =====================================================================================================================
+// heads: dW_sigma = d_sigma^T h_D, dW_rgb = g^T hd (g = d_rgb * y (1 - y)), and their biases -- CUDA cores
+// =====================================================================================================================
+namespace {
+
+struct HeadArgs {
+  const float* out; const float* d_out; const uint8_t* fwd_rec; int fwd_tile_bytes; int hD_off, hd_off;
+  int64_t P, n_tiles; int n_active;
+  float* grad; int64_t w_sigma, b_sigma, w_rgb, b_rgb;
+};
+
+__device__ __forceinline__ float bf16_at(const uint8_t* blocks, int row, int col) {     // blocks: consecutive [128 x 64] images
+  const uint8_t* p = blocks + (col >> 6) * BLK_BYTES + swz_off(row, col & 63);
+  return __uint_as_float(((uint32_t)*reinterpret_cast<const uint16_t*>(p)) << 16);
+}
+
+__global__ void __launch_bounds__(256) head_wgrad_kernel(HeadArgs a) {
+  __shared__ float4 gs[TILE_M];
+  const int t = threadIdx.x;
+  const int64_t t0 = a.n_tiles * blockIdx.x / a.n_active, t1 = a.n_tiles * (blockIdx.x + 1) / a.n_active;
+  float acc_s = 0.f, acc_r[3] = {0.f, 0.f, 0.f}, acc_b[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int64_t tile = t0; tile < t1; ++tile) {
+    if (t < TILE_M) {
+      const int64_t p = tile * TILE_M + t;
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p < a.P) {
+        const float4 y = __ldg(reinterpret_cast<const float4*>(a.out + p * 4));
+        const float4 dy = __ldg(reinterpret_cast<const float4*>(a.d_out + p * 4));
+        g = make_float4(dy.x * y.x * (1.f - y.x), dy.y * y.y * (1.f - y.y), dy.z * y.z * (1.f - y.z), dy.w);
+      }
+      gs[t] = g;
+    }
+    __syncthreads();
+    const uint8_t* rec = a.fwd_rec + tile * (int64_t)a.fwd_tile_bytes;
+    for (int r = 0; r < TILE_M; ++r) {
+      const float4 g = gs[r];
+      acc_s = fmaf(g.w, bf16_at(rec + a.hD_off, r, t), acc_s);
+      if (t < 128) {
+        const float hv = bf16_at(rec + a.hd_off, r, t);
+        acc_r[0] = fmaf(g.x, hv, acc_r[0]); acc_r[1] = fmaf(g.y, hv, acc_r[1]); acc_r[2] = fmaf(g.z, hv, acc_r[2]);
+      }
+    }
+    if (t < 4) {
+      for (int r = 0; r < TILE_M; ++r) { const float4 g = gs[r]; acc_b[t] += (t == 0) ? g.x : (t == 1) ? g.y : (t == 2) ? g.z : g.w; }
+    }
+    __syncthreads();
+  }
+  if (t1 > t0) {
+    atomicAdd(a.grad + a.w_sigma + t, acc_s);
+    if (t < 128) for (int c = 0; c < 3; ++c) atomicAdd(a.grad + a.w_rgb + c * 128 + t, acc_r[c]);
+    if (t < 3) atomicAdd(a.grad + a.b_rgb + t, acc_b[t]);
+    if (t == 3) atomicAdd(a.grad + a.b_sigma, acc_b[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) gather_heads_kernel(const float* __restrict__ params, int64_t w_sigma, int64_t w_rgb,
+                                                           float* __restrict__ heads) {
+  for (int i = threadIdx.x; i < 640; i += blockDim.x) heads[i] = __ldg(params + (i < 256 ? w_sigma + i : w_rgb + (i - 256)));
+}
+
+struct BwdPlan {
+  BProgram prog; PackTArgs pack; WgradArgs wg; HeadArgs head;
+  int64_t off_wblob, off_heads, off_rec, off_partial, total;
+  int n_active; int64_t n_tiles; int64_t param_count;
+};
+
+BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
+  BwdPlan pl{};
+  const NerfOffsets o = nerf_offsets(d);
+  const TcFwdLayout L = tc_fwd_layout(d, P);
+  const int D = d.D;
+  const int dzdir = 0, dzfin = 2 * BLK_BYTES;
+  auto dz_off = [&](int i) { return (6 + 4 * (D - i)) * BLK_BYTES; };          // dZ_i, i = D..1 (grad of trunk step i-1's pre-activation)
+  BProgram& pg = pl.prog;
+  pg.hd_off = L.step_save_off[D + 1]; pg.dzdir_off = dzdir;
+  pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (6 + 4 * D) * BLK_BYTES;
+  int ns = 0, nslab = 0; int64_t wb = 0;
+  auto slabs = [&](int64_t w_off, int ld, int col0, int n_kb) {
+    for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
+  };
+  pg.s[ns++] = BStep{2, -1, 0, dzfin};                       slabs(o.w_dir, 256 + o.in_dir, 0, 2);
+  pg.s[ns++] = BStep{4, L.step_save_off[D - 1], 1, dz_off(D)}; slabs(o.w_final, 256, 0, 4);
+  for (int i = D - 1; i >= 1; --i) {
+    const bool skip = (d.skip_mask >> i) & 1;
+    pg.s[ns++] = BStep{4, L.step_save_off[i - 1], 0, dz_off(i)};
+    slabs(o.w[i], o.in[i], skip ? o.in_xyz : 0, 4);
+  }
+  pg.n_steps = ns; pl.pack.n_slabs = nslab;
+  // wgrad work list
+  WgradArgs& wg = pl.wg; int ni = 0;
+  for (int i = 0; i < D; ++i) {
+    const bool skip = i > 0 && ((d.skip_mask >> i) & 1);
+    if (i == 0) wg.item[ni++] = WItem{dz_off(1), 4, 1, L.save_x_off, 1, 64, o.w[0], o.in[0], 0, o.in_xyz, o.b[0]};
+    else {
+      wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.step_save_off[i - 1], 4, 256, o.w[i], o.in[i], skip ? o.in_xyz : 0, 256, o.b[i]};
+      if (skip) wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.save_x_off, 1, 64, o.w[i], o.in[i], 0, o.in_xyz, -1};
+    }
+  }
+  wg.item[ni++] = WItem{dzfin, 4, 1, L.step_save_off[D - 1], 4, 256, o.w_final, 256, 0, 256, o.b_final};
+  wg.item[ni++] = WItem{dzdir, 2, 1, L.step_save_off[D], 4, 256, o.w_dir, 256 + o.in_dir, 0, 256, o.b_dir};
+  wg.item[ni++] = WItem{dzdir, 2, 1, L.save_dir_off, 1, 64, o.w_dir, 256 + o.in_dir, 256, o.in_dir, -1};
+  wg.n_items = ni;
+  pl.n_tiles = ceil_div64(P, TILE_M);
+  pl.n_active = (int)(pl.n_tiles < NERFB_SM_COUNT ? pl.n_tiles : NERFB_SM_COUNT);
+  pl.param_count = o.total;
+  wg.fwd_tile_bytes = pg.fwd_tile_bytes; wg.bwd_tile_bytes = pg.bwd_tile_bytes; wg.n_tiles = pl.n_tiles; wg.n_active = pl.n_active;
+  wg.partial_stride = round_up64(o.total, 32);
+  HeadArgs& h = pl.head;
+  h.fwd_tile_bytes = pg.fwd_tile_bytes; h.hD_off = L.step_save_off[D - 1]; h.hd_off = L.step_save_off[D + 1];
+  h.P = P; h.n_tiles = pl.n_tiles; h.n_active = pl.n_active;
+  h.w_sigma = o.w_sigma; h.b_sigma = o.b_sigma; h.w_rgb = o.w_rgb; h.b_rgb = o.b_rgb;
+  int64_t off = 0;
+  pl.off_wblob = off;   off += round_up64(wb, 1024);
+  pl.off_heads = off;   off += 4096;
+  pl.off_rec = off;     off += pl.n_tiles * (int64_t)pg.bwd_tile_bytes;
+  pl.off_partial = off; off += (int64_t)pl.n_active * wg.partial_stride * 4;
+  pl.total = round_up64(off, 1024);
+  return pl;
+}
+
+}  // namespace
+
+bool tc_bwd_supported(const nerfb_mlp_desc& d) {
+  if (!tc_supported(d, 0)) return false;
+  int skips = 0;
+  for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
+  return d.D + skips + 3 <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
+}
+int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) { return bwd_plan(d, P).total; }
+
+int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
+               const float* in1, int64_t n_rows, int n_samples, const float* out, const float* d_out, float* grad,
+               float* d_in, void* ws, int64_t ws_bytes, void* stream) {
+  (void)film; (void)in0; (void)in1;
+  if (d_in || !tc_bwd_supported(d)) return NERFB_E_UNSUPPORTED;
+  const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
+  const TcFwdLayout L = tc_fwd_layout(d, P);
+  BwdPlan pl = bwd_plan(d, P);
+  if (ws_bytes < L.total + pl.total) return NERFB_E_WORKSPACE;
+  if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return NERFB_E_BADARG;
+  uint8_t* base = static_cast<uint8_t*>(ws);
+  uint8_t* bb = base + L.total;
+  const uint8_t* fwd_rec = base + L.off_save;
+  float* heads = reinterpret_cast<float*>(bb + pl.off_heads);
+  NERFB_LAUNCH(pack_weights_t_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, bb + pl.off_wblob);
+  NERFB_LAUNCH(gather_heads_kernel, 1, 256, 0, stream, params, pl.head.w_sigma, pl.head.w_rgb, heads);
+
+  static bool attr_set = false;
+  const size_t smem_d = sizeof(SmemD) + 1024, smem_w = sizeof(SmemW) + 1024;
+  if (!attr_set) {
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w));
+    attr_set = true;
+  }
+  DgradArgs da{};
+  da.prog = pl.prog; da.wblob = bb + pl.off_wblob; da.heads = heads; da.out = out; da.d_out = d_out;
+  da.fwd_rec = fwd_rec; da.bwd_rec = bb + pl.off_rec; da.P = P; da.n_tiles = pl.n_tiles;
+  NERFB_LAUNCH(mlp_tc_dgrad_kernel, pl.n_active, NUM_THREADS, smem_d, stream, da);
+
+  pl.wg.fwd_rec = fwd_rec; pl.wg.bwd_rec = bb + pl.off_rec;
+  pl.wg.partial = reinterpret_cast<float*>(bb + pl.off_partial); pl.wg.grad = grad;
+  NERFB_LAUNCH(mlp_tc_wgrad_kernel, pl.n_active, W_THREADS, smem_w, stream, pl.wg);
+
+  pl.head.out = out; pl.head.d_out = d_out; pl.head.fwd_rec = fwd_rec; pl.head.grad = grad;
+  NERFB_LAUNCH(head_wgrad_kernel, pl.n_active, 256, 0, stream, pl.head);
+
+  ReduceArgs ra{};
+  ra.n_items = pl.wg.n_items;
+  for (int i = 0; i < ra.n_items; ++i) ra.item[i] = pl.wg.item[i];
+  ra.n_active = pl.n_active; ra.partial = pl.wg.partial; ra.partial_stride = pl.wg.partial_stride; ra.grad = grad;
+  NERFB_LAUNCH(reduce_partials_kernel, dim3(ra.n_items, 32), 256, 0, stream, ra);
+  return NERFB_OK;
+}

@@ -7,6 +7,12 @@
 #include <stdint.h>
 #include <cstdio>
 
+// where the forward kernel parked each tile's activations (byte offsets inside one tile record)
+struct TcFwdLayout {
+  int n_steps; int step_save_off[12]; int save_x_off, save_dir_off; int tile_save_bytes;
+  int64_t off_save, total;     // record array offset inside the workspace; end of the forward's workspace part
+};
+
 namespace tc {
 
 constexpr int TILE_M = 128;                 // samples per tile = TMEM lanes

@@ -398,3 +398,60 @@ def llff_rays(n: int, seed: int = 0, w: int = 504, h: int = 378, focal: float = 
     d_ndc = torch.stack([-focal / (w / 2) * (d[:, 0] / d[:, 2] - ox), -focal / (h / 2) * (d[:, 1] / d[:, 2] - oy),
                          1 - o_ndc[:, 2]], dim=-1)
     return torch.cat([o_ndc, d_ndc, torch.zeros(n, 1), torch.ones(n, 1)], dim=1).contiguous()
+
+
+# ----------------------------------------------------------------------------------------------
+# bf16 tensor-core arithmetic, emulated  (checker for the tcgen05 arm's OWN arithmetic)
+# ----------------------------------------------------------------------------------------------
+def _r16(t: torch.Tensor) -> torch.Tensor:
+    """Round to bf16 (nearest even) and back: the value a bf16 UMMA operand carries."""
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def nerf_mlp_bf16(p: Params, x: torch.Tensor, d_out: Optional[torch.Tensor] = None, D: int = 8, in_xyz: int = 63,
+                  in_dir: int = 27, skips: Sequence[int] = (4,)):
+    """models/nerf.py:100-124 evaluated the way the tensor-core kernels evaluate it: bf16 weights and bf16
+    layer inputs, fp32 accumulation, fp32 bias / ReLU / heads on the un-rounded accumulators; and, when
+    ``d_out`` (B,4) is given, the manual backward with bf16 dZ and gates taken from the bf16 activations.
+    Returns ``out`` or ``(out, {param name: grad})``.  The fp32 reference differs from this by bf16 rounding
+    (and, for gradients, by ReLU gates that flip under that rounding); the CUDA kernels must match THIS to
+    fp32-summation noise, which separates "bf16 is coarse" from "the kernel is wrong"."""
+    W = lambda n: _r16(p[n + ".weight"])
+    b = lambda n: p[n + ".bias"]
+    X = _r16(x[:, :in_xyz])
+    Xd = _r16(x[:, in_xyz:in_xyz + in_dir])
+    acts, h, h32 = [], X, None                       # acts[i] = bf16 input of trunk layer i
+    for i in range(D):
+        inp = torch.cat([X, h], -1) if i in skips else h
+        acts.append(inp)
+        h32 = torch.relu(inp @ W(f"xyz_encoding_{i + 1}.0").T + b(f"xyz_encoding_{i + 1}.0"))
+        h = _r16(h32)
+    hD = h
+    sigma = h32 @ p["sigma.weight"].T + p["sigma.bias"]
+    feat = _r16(hD @ W("xyz_encoding_final").T + b("xyz_encoding_final"))
+    din = torch.cat([feat, Xd], -1)
+    hd32 = torch.relu(din @ W("dir_encoding.0").T + b("dir_encoding.0"))
+    hd = _r16(hd32)
+    rgb = torch.sigmoid(hd32 @ p["rgb.0.weight"].T + p["rgb.0.bias"])
+    out = torch.cat([rgb, sigma], -1)
+    if d_out is None:
+        return out
+    g = {}
+    gr = d_out[:, :3] * rgb * (1 - rgb)
+    dsig = d_out[:, 3:4]
+    g["rgb.0.weight"], g["rgb.0.bias"] = gr.T @ hd, gr.sum(0)
+    g["sigma.weight"], g["sigma.bias"] = dsig.T @ hD, dsig.sum(0)
+    dz = _r16((gr @ p["rgb.0.weight"]) * (hd != 0))
+    g["dir_encoding.0.weight"], g["dir_encoding.0.bias"] = dz.T @ din, dz.sum(0)
+    dz = _r16(dz @ W("dir_encoding.0")[:, :feat.shape[1]])
+    g["xyz_encoding_final.weight"], g["xyz_encoding_final.bias"] = dz.T @ hD, dz.sum(0)
+    dh = dz @ W("xyz_encoding_final") + dsig @ p["sigma.weight"]
+    for i in range(D - 1, -1, -1):
+        name = f"xyz_encoding_{i + 1}.0"
+        out_act = hD if i == D - 1 else (acts[i + 1][:, in_xyz:] if (i + 1) in skips else acts[i + 1])
+        dz = _r16(dh * (out_act != 0))
+        g[name + ".weight"], g[name + ".bias"] = dz.T @ acts[i], dz.sum(0)
+        if i > 0:
+            Wi = W(name)
+            dh = dz @ (Wi[:, in_xyz:] if i in skips else Wi)
+    return out, g

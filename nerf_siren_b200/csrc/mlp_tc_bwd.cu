@@ -10,7 +10,7 @@
 //      [samples x 64] block images are read back as MN-major UMMA operands (no transpose anywhere); each CTA owns a
 //      contiguous range of tiles, accumulates one weight matrix at a time in TMEM (2 x 128 lanes x N columns) over
 //      its whole range, flushes it once to a per-CTA partial, and spare warps column-sum dZ from shared memory for
-//      the bias gradients.  head_wgrad_kernel does the 1- and 3-row heads on the CUDA cores.
+//      the bias gradients.  The sigma / rgb heads ride along as two more items on a 4-column "head block".
 //   C. reduce_partials_kernel -- grad += sum over CTAs of the partials (the gradient buffer is accumulated into).
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -61,6 +61,7 @@ struct BProgram {
   BStep s[MAX_BSTEPS];
   int hd_off;        // forward-record offset of the direction layer's activations (2 blocks), gate of dZ_dir
   int dzdir_off;     // backward-record offset of dZ_dir (2 blocks)
+  int h_off;         // backward-record offset of the head block: columns 0..3 = [g_r g_g g_b d_sigma] per sample
   int fwd_tile_bytes, bwd_tile_bytes;
 };
 
@@ -207,6 +208,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         g0 = dy.x * y.x * (1.f - y.x); g1 = dy.y * y.y * (1.f - y.y); g2 = dy.z * y.z * (1.f - y.z);   // sigmoid'
         dsig = dy.w;
       }
+      if (h == 0) {                           // head block for the wgrad kernel: 4 bf16 per sample, rest of the row unused
+        uint2 hw; hw.x = pack_bf16(g0, g1); hw.y = pack_bf16(g2, dsig);
+        *reinterpret_cast<uint2*>(args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off + swz_off(row, 0)) = hw;
+      }
       uint4 gate[4];
       load_gate(frec + pg.hd_off, row, h, gate);
       if (!first) { mbar_wait(&g_free, free_phase); free_phase ^= 1; }
@@ -282,6 +287,8 @@ struct WItem {
   int N;                     // UMMA N = 64 * nN
   int64_t w_off; int ld, col0, nvalid;   // destination: grad[w_off + out * ld + col0 + n], n < nvalid
   int64_t bias_off;          // destination of colsum(dZ), or -1
+  int m_lo, m_hi;            // rows (out features) of the accumulator that are real: [m_lo, m_hi)
+  int64_t bias_alt;          // head block only (>= 0): colsum of column 3 goes here (b_sigma), columns 0..2 to bias_off
 };
 struct WgradArgs {
   int n_items; WItem item[MAX_ITEMS];
@@ -382,20 +389,28 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
         if (++st == W_STAGES) { st = 0; ph ^= 1; }
       }
       if (sum_here && n_chunks > 0) {
-        atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
-        atomicAdd(args.grad + im.bias_off + 2 * bt + 1, b1);
+        if (im.bias_alt < 0) {
+          atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
+          atomicAdd(args.grad + im.bias_off + 2 * bt + 1, b1);
+        } else if (bt < 2) {               // head block: columns [g_r g_g g_b d_sigma]
+          atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
+          atomicAdd(bt == 0 ? args.grad + im.bias_off + 1 : args.grad + im.bias_alt, b1);
+        }
       }
       mbar_wait(&sm.acc_done, done_ph); done_ph ^= 1;
       tc_fence_after();
       for (int mh = 0; mh < (im.nM >> 1); ++mh) {
-        float* dst = part + im.w_off + (int64_t)(mh * 128 + q * 32 + lane) * im.ld + im.col0;
+        const int m = mh * 128 + q * 32 + lane;
+        if (mh * 128 + q * 32 >= im.m_hi || mh * 128 + q * 32 + 32 <= im.m_lo) continue;      // warp-uniform
+        float* dst = part + im.w_off + (int64_t)m * im.ld + im.col0;
+        const bool real = m >= im.m_lo && m < im.m_hi;
         for (int c0 = 0; c0 < im.N; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(mh * 256 + c0), v);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i)
-            if (c0 + i < im.nvalid) dst[c0 + i] = __uint_as_float(v[i]);
+            if (real && c0 + i < im.nvalid) dst[c0 + i] = __uint_as_float(v[i]);
         }
       }
       tc_fence_before();
@@ -412,10 +427,9 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
 struct ReduceArgs { int n_items; WItem item[MAX_ITEMS]; int n_active; const float* partial; int64_t partial_stride; float* grad; };
 __global__ void __launch_bounds__(256) reduce_partials_kernel(ReduceArgs ra) {
   const WItem im = ra.item[blockIdx.x];
-  const int M = im.nM * 32 * 2;
-  const int total = M * im.nvalid;
+  const int total = (im.m_hi - im.m_lo) * im.nvalid;
   for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < total; e += gridDim.y * blockDim.x) {
-    const int r = e / im.nvalid, n = e - r * im.nvalid;
+    const int r = im.m_lo + e / im.nvalid, n = e % im.nvalid;
     const int64_t idx = im.w_off + (int64_t)r * im.ld + im.col0 + n;
     float s = 0.f;
     for (int c = 0; c < ra.n_active; ++c) s += ra.partial[(int64_t)c * ra.partial_stride + idx];
@@ -426,7 +440,7 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(ReduceArgs ra) {
 }  // namespace
 
 // =====================================================================================================================
-// heads: dW_sigma = d_sigma^T h_D, dW_rgb = g^T hd (g = d_rgb * y (1 - y)), and their biases -- CUDA cores
+// head parameter gather + the launch plan
 // =====================================================================================================================
 namespace {
 
@@ -435,50 +449,6 @@ struct HeadArgs {
   int64_t P, n_tiles; int n_active;
   float* grad; int64_t w_sigma, b_sigma, w_rgb, b_rgb;
 };
-
-__device__ __forceinline__ float bf16_at(const uint8_t* blocks, int row, int col) {     // blocks: consecutive [128 x 64] images
-  const uint8_t* p = blocks + (col >> 6) * BLK_BYTES + swz_off(row, col & 63);
-  return __uint_as_float(((uint32_t)*reinterpret_cast<const uint16_t*>(p)) << 16);
-}
-
-__global__ void __launch_bounds__(256) head_wgrad_kernel(HeadArgs a) {
-  __shared__ float4 gs[TILE_M];
-  const int t = threadIdx.x;
-  const int64_t t0 = a.n_tiles * blockIdx.x / a.n_active, t1 = a.n_tiles * (blockIdx.x + 1) / a.n_active;
-  float acc_s = 0.f, acc_r[3] = {0.f, 0.f, 0.f}, acc_b[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int64_t tile = t0; tile < t1; ++tile) {
-    if (t < TILE_M) {
-      const int64_t p = tile * TILE_M + t;
-      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (p < a.P) {
-        const float4 y = __ldg(reinterpret_cast<const float4*>(a.out + p * 4));
-        const float4 dy = __ldg(reinterpret_cast<const float4*>(a.d_out + p * 4));
-        g = make_float4(dy.x * y.x * (1.f - y.x), dy.y * y.y * (1.f - y.y), dy.z * y.z * (1.f - y.z), dy.w);
-      }
-      gs[t] = g;
-    }
-    __syncthreads();
-    const uint8_t* rec = a.fwd_rec + tile * (int64_t)a.fwd_tile_bytes;
-    for (int r = 0; r < TILE_M; ++r) {
-      const float4 g = gs[r];
-      acc_s = fmaf(g.w, bf16_at(rec + a.hD_off, r, t), acc_s);
-      if (t < 128) {
-        const float hv = bf16_at(rec + a.hd_off, r, t);
-        acc_r[0] = fmaf(g.x, hv, acc_r[0]); acc_r[1] = fmaf(g.y, hv, acc_r[1]); acc_r[2] = fmaf(g.z, hv, acc_r[2]);
-      }
-    }
-    if (t < 4) {
-      for (int r = 0; r < TILE_M; ++r) { const float4 g = gs[r]; acc_b[t] += (t == 0) ? g.x : (t == 1) ? g.y : (t == 2) ? g.z : g.w; }
-    }
-    __syncthreads();
-  }
-  if (t1 > t0) {
-    atomicAdd(a.grad + a.w_sigma + t, acc_s);
-    if (t < 128) for (int c = 0; c < 3; ++c) atomicAdd(a.grad + a.w_rgb + c * 128 + t, acc_r[c]);
-    if (t < 3) atomicAdd(a.grad + a.b_rgb + t, acc_b[t]);
-    if (t == 3) atomicAdd(a.grad + a.b_sigma, acc_b[3]);
-  }
-}
 
 __global__ void __launch_bounds__(256) gather_heads_kernel(const float* __restrict__ params, int64_t w_sigma, int64_t w_rgb,
                                                            float* __restrict__ heads) {
@@ -500,7 +470,9 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   auto dz_off = [&](int i) { return (6 + 4 * (D - i)) * BLK_BYTES; };          // dZ_i, i = D..1 (grad of trunk step i-1's pre-activation)
   BProgram& pg = pl.prog;
   pg.hd_off = L.step_save_off[D + 1]; pg.dzdir_off = dzdir;
-  pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (6 + 4 * D) * BLK_BYTES;
+  const int hblk = (6 + 4 * D) * BLK_BYTES;                     // head block (+ one never-written block behind it)
+  pg.h_off = hblk;
+  pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (8 + 4 * D) * BLK_BYTES;
   int ns = 0, nslab = 0; int64_t wb = 0;
   auto slabs = [&](int64_t w_off, int ld, int col0, int n_kb) {
     for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
@@ -517,15 +489,19 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   WgradArgs& wg = pl.wg; int ni = 0;
   for (int i = 0; i < D; ++i) {
     const bool skip = i > 0 && ((d.skip_mask >> i) & 1);
-    if (i == 0) wg.item[ni++] = WItem{dz_off(1), 4, 1, L.save_x_off, 1, 64, o.w[0], o.in[0], 0, o.in_xyz, o.b[0]};
+    if (i == 0) wg.item[ni++] = WItem{dz_off(1), 4, 1, L.save_x_off, 1, 64, o.w[0], o.in[0], 0, o.in_xyz, o.b[0], 0, 256, -1};
     else {
-      wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.step_save_off[i - 1], 4, 256, o.w[i], o.in[i], skip ? o.in_xyz : 0, 256, o.b[i]};
-      if (skip) wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.save_x_off, 1, 64, o.w[i], o.in[i], 0, o.in_xyz, -1};
+      wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.step_save_off[i - 1], 4, 256, o.w[i], o.in[i], skip ? o.in_xyz : 0, 256, o.b[i], 0, 256, -1};
+      if (skip) wg.item[ni++] = WItem{dz_off(i + 1), 4, 1, L.save_x_off, 1, 64, o.w[i], o.in[i], 0, o.in_xyz, -1, 0, 256, -1};
     }
   }
-  wg.item[ni++] = WItem{dzfin, 4, 1, L.step_save_off[D - 1], 4, 256, o.w_final, 256, 0, 256, o.b_final};
-  wg.item[ni++] = WItem{dzdir, 2, 1, L.step_save_off[D], 4, 256, o.w_dir, 256 + o.in_dir, 0, 256, o.b_dir};
-  wg.item[ni++] = WItem{dzdir, 2, 1, L.save_dir_off, 1, 64, o.w_dir, 256 + o.in_dir, 256, o.in_dir, -1};
+  wg.item[ni++] = WItem{dzfin, 4, 1, L.step_save_off[D - 1], 4, 256, o.w_final, 256, 0, 256, o.b_final, 0, 256, -1};
+  wg.item[ni++] = WItem{dzdir, 2, 1, L.step_save_off[D], 4, 256, o.w_dir, 256 + o.in_dir, 0, 256, o.b_dir, 0, 128, -1};
+  wg.item[ni++] = WItem{dzdir, 2, 1, L.save_dir_off, 1, 64, o.w_dir, 256 + o.in_dir, 256, o.in_dir, -1, 0, 128, -1};
+  // heads (models/nerf.py:112,119-120): the head block H holds [g_r g_g g_b d_sigma] in columns 0..3, so rows 0..2 of
+  // H^T hd are dW_rgb and row 3 of H^T h_D is dW_sigma; its column sums are the two head biases
+  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D + 1], 2, 128, o.w_rgb, 128, 0, 128, o.b_rgb, 0, 3, o.b_sigma};
+  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D - 1], 4, 256, o.w_sigma - 3 * 256, 256, 0, 256, -1, 3, 4, -1};
   wg.n_items = ni;
   pl.n_tiles = ceil_div64(P, TILE_M);
   pl.n_active = (int)(pl.n_tiles < NERFB_SM_COUNT ? pl.n_tiles : NERFB_SM_COUNT);
@@ -551,7 +527,7 @@ bool tc_bwd_supported(const nerfb_mlp_desc& d) {
   if (!tc_supported(d, 0)) return false;
   int skips = 0;
   for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
-  return d.D + skips + 3 <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
+  return d.D + skips + 5 <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
 }
 int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) { return bwd_plan(d, P).total; }
 
@@ -587,9 +563,6 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   pl.wg.fwd_rec = fwd_rec; pl.wg.bwd_rec = bb + pl.off_rec;
   pl.wg.partial = reinterpret_cast<float*>(bb + pl.off_partial); pl.wg.grad = grad;
   NERFB_LAUNCH(mlp_tc_wgrad_kernel, pl.n_active, W_THREADS, smem_w, stream, pl.wg);
-
-  pl.head.out = out; pl.head.d_out = d_out; pl.head.fwd_rec = fwd_rec; pl.head.grad = grad;
-  NERFB_LAUNCH(head_wgrad_kernel, pl.n_active, 256, 0, stream, pl.head);
 
   ReduceArgs ra{};
   ra.n_items = pl.wg.n_items;

@@ -55,6 +55,84 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (clock64() - t0 > 4000000000LL) {   // ~2 s at 2 GHz
       printf("nerf_b200: mbarrier timeout (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x, (int)threadIdx.x,
              smem_u32(bar), parity);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }   // let the other stuck roles report before the grid is torn down
+      __trap();
+    }
+  }
+}
+
+// Same, for roles that are not on the critical path (producers, store / encoder lanes): back off between polls so the
+// spinning warp does not take issue slots from the epilogue warps of its SM sub-partition.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(100);
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: mbarrier timeout (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x, (int)threadIdx.x,
+             smem_u32(bar), parity);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
+      __trap();
+    }
+  }
+}
+
+// raw shared-address forms (no pointer arithmetic on the issuing thread's critical path)
+__device__ __forceinline__ bool mbar_try_wait_addr(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait_addr(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait_addr(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: mbarrier timeout (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, bar, parity);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
+      __trap();
+    }
+  }
+}
+
+// ---- shared-memory publish counters (cheaper to poll than an mbarrier) ----------------------------------------------
+// producer: st.shared data -> fence.proxy.async -> __syncwarp -> lane 0: cnt_publish (release, +1 per warp)
+// consumer: cnt_wait (acquire) until the monotonic counter reaches its target, then issues the async-proxy reads
+__device__ __forceinline__ void cnt_publish(uint32_t cnt_addr) {
+  asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(cnt_addr) : "memory");
+}
+__device__ __forceinline__ uint32_t cnt_load(uint32_t cnt_addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(cnt_addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cnt_wait(uint32_t cnt_addr, uint32_t target) {
+  if ((int32_t)(cnt_load(cnt_addr) - target) >= 0) return;
+  const long long t0 = clock64();
+  while ((int32_t)(cnt_load(cnt_addr) - target) < 0) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: counter timeout (block %d thread %d cnt %u target %u)\n", (int)blockIdx.x, (int)threadIdx.x, cnt_addr, target);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void cnt_wait_relaxed(uint32_t cnt_addr, uint32_t target) {
+  const long long t0 = clock64();
+  while ((int32_t)(cnt_load(cnt_addr) - target) < 0) {
+    __nanosleep(100);
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: counter timeout (block %d thread %d cnt %u target %u)\n", (int)blockIdx.x, (int)threadIdx.x, cnt_addr, target);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
       __trap();
     }
   }
@@ -114,6 +192,23 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// One 64-wide K-block = four K=16 UMMAs on consecutive 32-byte slices of the swizzled rows; descriptors are
+// {low word, 0x40004040}: SBO = 1024 B, version 1, SWIZZLE_128B (see umma_desc_k128); a 32-byte step is +2 in the low word.
+__device__ __forceinline__ void umma_bf16_k64(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 a0, b0, a1, b1, a2, b2, a3, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\tsetp.eq.b32 t, 0, 0;\n\t"
+      "mov.b64 a0, {%1, 0x40004040};\n\tmov.b64 b0, {%2, 0x40004040};\n\t"
+      "add.u64 a1, a0, 2;\n\tadd.u64 b1, b0, 2;\n\tadd.u64 a2, a0, 4;\n\tadd.u64 b2, b0, 4;\n\tadd.u64 a3, a0, 6;\n\tadd.u64 b3, b0, 6;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a0, b0, %3, p;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, t;\n\t}"
+      ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
 // mbarrier arrive once every previously issued UMMA of this thread has completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -128,6 +223,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
         "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr) : "memory");
+}
+// TMEM -> registers: this warp's 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
       : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -145,6 +249,24 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float a, float b) {
 }
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t r;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ float4 lds128f(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+  return r;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");

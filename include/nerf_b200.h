@@ -139,6 +139,38 @@ int nerfb_adam_step(float* params, const float* grads, float* exp_avg, float* ex
                     float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                     void* stream);
 
+/* ---- (6) EG3D tri-plane renderer --------------------------------------------
+ * nerfb_triplane_relayout: planes (3, 32, H, W) as the reference holds them (eg3d_training/triplane.py:65,
+ *   volumetric_rendering/renderer.py:57-61) -> channels-last (3, H, W, 32) so a texel is one 128-byte line.
+ * nerfb_triplane_field: ImportanceRenderer.run_model (renderer.py:144-151) = sample_from_planes (:57-68: projections
+ *   (x,y),(x,z),(z,x), bilinear, zeros padding, align_corners=False, coordinates * 2/box_warp) + OSGDecoder
+ *   (triplane.py:144-167).  decoder = W1 (64x32) | b1 (64) | W2 (4x64) | b2 (4), the raw parameters of the two
+ *   FullyConnectedLayers (networks_stylegan2.py:95-122; gains lr_mul/sqrt(fan_in) applied in-kernel).
+ *   coords (P,3) -> rgb (P,3), sigma (P).
+ * nerfb_mip_march: MipRayMarcher2.run_forward (ray_marcher.py:25-57) on colors (R,S,3), densities (R,S), depths
+ *   (R,S) -> rgb (R,3), depth (R) [clamped to the call-global depth range], weights (R,S-1) (may be null).
+ *   workspace: >= 16 bytes of device memory.
+ * nerfb_triplane_render: ImportanceRenderer.forward (renderer.py:94-142) fused, one warp per ray: stratified depths
+ *   (:172-195; numeric ray_start/ray_end, or per-ray arrays as produced by math_utils.get_ray_limits_box), coarse
+ *   field + march, smoothed-weight importance sampling (:197-256), fine field, sorted merge (:160-170), final march.
+ *   rand_coarse (R,S) / u (R,Si) are the reference's torch.rand_like / torch.rand draws; pass null to draw from the
+ *   in-kernel counter-based generator seeded by `seed`.  Outputs: rgb (R,3), depth (R), opacity = sum of weights (R),
+ *   coarse and final; depths_fine_out (R,Si) optional.  workspace: >= 16 bytes. */
+int nerfb_triplane_relayout(const float* planes, int channels, int H, int W, float* planes_cl, void* stream);
+int nerfb_triplane_field(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                         const float* coords, int64_t n_points, float box_warp, float* rgb, float* sigma,
+                         void* stream);
+int nerfb_mip_march(const float* colors, const float* densities, const float* depths, int64_t n_rays,
+                    int n_samples, int white_back, float* rgb, float* depth, float* weights, void* workspace,
+                    void* stream);
+int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                          const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                          int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                          const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                          const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                          float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                          float* opacity_final, float* depths_fine_out, void* workspace, void* stream);
+
 /* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
 int64_t nerfb_launch_count(void);
 

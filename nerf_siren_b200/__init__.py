@@ -9,7 +9,7 @@ package falls back to torch ops or to the CPU.
 import sys as _sys
 
 from . import _lib  # noqa: F401  (raises ImportError when libnerf_b200.so is missing)
-from . import config, dp, ops, synth  # noqa: F401
+from . import config, dp, eg3d, ops, synth  # noqa: F401
 from .config import get_precision, set_precision  # noqa: F401
 from .models import nerf, nerf_cls, rendering  # noqa: F401
 from .models.nerf import Embedding, NeRF, SemanticNeRF, SirenField  # noqa: F401
@@ -27,3 +27,15 @@ def install_as_models() -> None:
     _sys.modules["models.rendering"] = rendering
     _sys.modules["models.nerf"] = nerf
     _sys.modules["models.nerf_cls"] = nerf_cls
+
+
+def install_as_eg3d() -> None:
+    """Make ``from volumetric_rendering.renderer import ImportanceRenderer`` / ``...ray_marcher import MipRayMarcher2``
+    (eg3d_training/triplane.py:15-16 in the reference) resolve to this package's kernel-backed mirror."""
+    import types
+    pkg = types.ModuleType("volumetric_rendering")
+    pkg.renderer = eg3d
+    pkg.ray_marcher = eg3d
+    _sys.modules["volumetric_rendering"] = pkg
+    _sys.modules["volumetric_rendering.renderer"] = eg3d
+    _sys.modules["volumetric_rendering.ray_marcher"] = eg3d

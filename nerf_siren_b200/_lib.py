@@ -46,6 +46,11 @@ SIGNATURES = {
     "nerfb_searchsorted": (_I, [_P, _L, _L, _P, _L, _L, _I, _P, _P]),
     "nerfb_sample_pdf": (_I, [_P, _P, _P, _I, _F, _L, _I, _I, _P, _P, _P, _P]),
     "nerfb_resample": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P]),
+    "nerfb_triplane_relayout": (_I, [_P, _I, _I, _I, _P, _P]),
+    "nerfb_triplane_field": (_I, [_P, _I, _I, _P, _F, _P, _L, _F, _P, _P, _P]),
+    "nerfb_mip_march": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P]),
+    "nerfb_triplane_render": (_I, [_P, _I, _I, _P, _F, _P, _P, _L, _I, _I, C.c_double, C.c_double, _P, _P, _I, _F, _I,
+                                   _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P]),
 }
 

@@ -1,0 +1,430 @@
+// Kernel (6): the EG3D tri-plane renderer (BASELINE config 5).
+//   replaces volumetric_rendering/renderer.py:57-68 (sample_from_planes: 3 x grid_sample), eg3d_training/triplane.py:
+//   144-167 (OSGDecoder 32 -> 64 softplus -> 4), volumetric_rendering/ray_marcher.py:25-57 (MipRayMarcher2) and
+//   renderer.py:94-142,160-256 (ImportanceRenderer: stratified depths, smoothed-weight importance sampling, merge sort).
+//
+// One warp per ray does the WHOLE pipeline; nothing per-sample ever reaches HBM (the reference materialises
+// coordinates, (1,3,M*S,32) features, colours, densities, three marcher passes and a sort + 3 gathers).
+//   * planes are re-laid out once per call to channels-last (3, H, W, 32): a texel is ONE 128-byte line and lane = channel,
+//     so each of the 12 bilinear taps of a sample is a single coalesced request served by L2 (the 25 MB of planes stay
+//     resident in the 126 MB L2).  Bound: L2 gather bandwidth, 1,536 B per sample.
+//   * decoder on CUDA cores with its 2 x 64 x 32 first-layer weights in registers (lane j owns hidden units j, j + 32),
+//     features broadcast by shuffles; 2,304 MACs per sample is far below the gather cost.
+//   * marcher = warp product-scan over the S-1 intervals with a running carry (same scheme as composite.cu).
+//   * the chunk-global depth clamp (ray_marcher.py:49-50: torch.min / torch.max over ALL depths) is two ordered-int
+//     atomics per warp plus a tiny second kernel.
+#include "common.cuh"
+#include "resample_dev.cuh"
+
+namespace {
+
+constexpr int TP_WARPS = 8;
+constexpr int TP_C = 32;          // feature channels (lane = channel)
+constexpr int TP_HID = 64;
+constexpr int TP_MAX_S = 256;     // samples per ray after the merge
+
+// ---- channels-last re-layout: (3, C=32, H, W) -> (3, H, W, 32) ----------------------------------------------------
+__global__ void __launch_bounds__(256) triplane_relayout_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t HW) {
+  __shared__ float tile[32][33];
+  const int p = blockIdx.y;
+  const int64_t hw0 = (int64_t)blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
+  for (int c = ty; c < 32; c += 8) {
+    const int64_t hw = hw0 + tx;
+    tile[c][tx] = hw < HW ? __ldg(in + ((int64_t)p * 32 + c) * HW + hw) : 0.f;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t hw = hw0 + r;
+    if (hw < HW) out[((int64_t)p * HW + hw) * 32 + tx] = tile[tx][r];
+  }
+}
+
+// ---- decoder weights held per lane --------------------------------------------------------------------------------
+struct Dec {
+  float w1a[TP_C], w1b[TP_C];    // rows lane and lane + 32 of W1 (already times the FullyConnectedLayer gain)
+  float b1a, b1b;
+  float w2a[4], w2b[4];          // columns lane and lane + 32 of W2
+  float b2;                      // bias of the output this lane finalises (lanes 0 / 8 / 16 / 24)
+};
+
+// params: W1 (64 x 32) | b1 (64) | W2 (4 x 64) | b2 (4), raw nn.Parameters; gains as networks_stylegan2.py:109-110
+__device__ __forceinline__ void load_decoder(Dec& d, const float* __restrict__ p, float lr_mul, int lane) {
+  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
+#pragma unroll
+  for (int c = 0; c < TP_C; ++c) {
+    d.w1a[c] = __fmul_rn(__ldg(p + lane * TP_C + c), g1);
+    d.w1b[c] = __fmul_rn(__ldg(p + (lane + 32) * TP_C + c), g1);
+  }
+  const float* b1 = p + TP_HID * TP_C;
+  d.b1a = __ldg(b1 + lane) * lr_mul; d.b1b = __ldg(b1 + lane + 32) * lr_mul;
+  const float* w2 = b1 + TP_HID;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    d.w2a[k] = __fmul_rn(__ldg(w2 + k * TP_HID + lane), g2);
+    d.w2b[k] = __fmul_rn(__ldg(w2 + k * TP_HID + lane + 32), g2);
+  }
+  d.b2 = __ldg(w2 + 4 * TP_HID + (lane >> 3)) * lr_mul;
+}
+
+__device__ __forceinline__ float softplusf(float x) { return x > 20.f ? x : log1pf(expf(x)); }   // F.softplus, beta 1
+
+// bilinear tap of one plane at normalised (gx -> W, gy -> H), zeros padding, align_corners=False; lane = channel
+__device__ __forceinline__ float plane_tap(const float* __restrict__ pl, int H, int W, float gx, float gy, int lane) {
+  const float ix = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gx, 1.f), (float)W), 1.f), 0.5f);
+  const float iy = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gy, 1.f), (float)H), 1.f), 0.5f);
+  const float fx = floorf(ix), fy = floorf(iy);
+  const float w = ix - fx, e = 1.f - w, n = iy - fy, s = 1.f - n;
+  // NaN / huge coordinates compare false everywhere -> no tap, as in grid_sample's bounds checks
+  const bool x0 = fx >= 0.f && fx < (float)W, x1 = fx >= -1.f && fx < (float)(W - 1);
+  const bool y0 = fy >= 0.f && fy < (float)H, y1 = fy >= -1.f && fy < (float)(H - 1);
+  const int xi = (int)fmaxf(fminf(fx, (float)W), -2.f), yi = (int)fmaxf(fminf(fy, (float)H), -2.f);
+  const float* base = pl + ((int64_t)yi * W + xi) * TP_C + lane;
+  float acc = 0.f;
+  if (y0 && x0) acc = __ldg(base) * (s * e);
+  if (y0 && x1) acc = fmaf(__ldg(base + TP_C), s * w, acc);
+  if (y1 && x0) acc = fmaf(__ldg(base + (int64_t)W * TP_C), n * e, acc);
+  if (y1 && x1) acc = fmaf(__ldg(base + (int64_t)W * TP_C + TP_C), n * w, acc);
+  return acc;
+}
+
+// run_model for one point (renderer.py:144-151 + triplane.py:155-167).  Returns on lane 0: sigma, lane 8 / 16 / 24: r, g, b.
+__device__ __forceinline__ float field_eval(const float* __restrict__ planes, int H, int W, float x, float y, float z,
+                                            const Dec& d, int lane) {
+  const int64_t ps = (int64_t)H * W * TP_C;
+  // plane axes (renderer.py:29-39): projections (x, y), (x, z), (z, x)
+  const float f0 = plane_tap(planes, H, W, x, y, lane);
+  const float f1 = plane_tap(planes + ps, H, W, x, z, lane);
+  const float f2 = plane_tap(planes + 2 * ps, H, W, z, x, lane);
+  const float f = __fdiv_rn(__fadd_rn(__fadd_rn(f0, f1), f2), 3.f);      // sampled_features.mean(1)
+  float ha = d.b1a, hb = d.b1b;
+#pragma unroll
+  for (int c = 0; c < TP_C; ++c) {
+    const float fc = __shfl_sync(0xffffffffu, f, c);
+    ha = fmaf(d.w1a[c], fc, ha);
+    hb = fmaf(d.w1b[c], fc, hb);
+  }
+  ha = softplusf(ha); hb = softplusf(hb);
+  float p0 = fmaf(d.w2a[0], ha, d.w2b[0] * hb), p1 = fmaf(d.w2a[1], ha, d.w2b[1] * hb);
+  float p2 = fmaf(d.w2a[2], ha, d.w2b[2] * hb), p3 = fmaf(d.w2a[3], ha, d.w2b[3] * hb);
+  // transposing warp reduction of 4 values: lanes [0,8) end with output 0, [8,16) 1, [16,24) 2, [24,32) 3
+  const bool hi16 = lane & 16, hi8 = lane & 8;
+  float a = hi16 ? p2 : p0, sa = hi16 ? p0 : p2;
+  float b = hi16 ? p3 : p1, sb = hi16 ? p1 : p3;
+  a += __shfl_xor_sync(0xffffffffu, sa, 16);
+  b += __shfl_xor_sync(0xffffffffu, sb, 16);
+  float c = hi8 ? b : a, sc = hi8 ? a : b;
+  c += __shfl_xor_sync(0xffffffffu, sc, 8);
+  c += __shfl_xor_sync(0xffffffffu, c, 4);
+  c += __shfl_xor_sync(0xffffffffu, c, 2);
+  c += __shfl_xor_sync(0xffffffffu, c, 1);
+  c += d.b2;
+  if (lane >= 8) c = __fsub_rn(__fmul_rn(1.f / (1.f + expf(-c)), 1.002f), 0.001f);     // triplane.py:165
+  return c;
+}
+
+// ---- MipRayMarcher2.run_forward for one ray held in shared memory (ray_marcher.py:25-57) ---------------------------
+// s_d / s_sig / s_rgb[3] hold S sorted samples.  Writes the S-1 weights to s_w (if non-null) and returns, on every
+// lane, (rgb, sum w z_mid, sum w).  dmin / dmax receive the ray's depth range for the chunk-global clamp.
+struct March { float r, g, b, wz, wsum, dmin, dmax; };
+__device__ __forceinline__ March march_ray(const float* s_d, const float* s_sig, const float* s_r, const float* s_g,
+                                           const float* s_b, int S, float* s_w, int lane) {
+  March m{0.f, 0.f, 0.f, 0.f, 0.f, INFINITY, -INFINITY};
+  float carry = 1.f;                                       // prod_{j < base} (1 - alpha_j + 1e-10)
+  for (int base = 0; base < S - 1; base += 32) {
+    const int i = base + lane;
+    const bool on = i < S - 1;
+    float alpha = 0.f, zmid = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+    if (on) {
+      const float d0 = s_d[i], d1 = s_d[i + 1];
+      const float delta = __fsub_rn(d1, d0);
+      zmid = __fmul_rn(__fadd_rn(d0, d1), 0.5f);
+      const float dm = softplusf(__fsub_rn(__fmul_rn(__fadd_rn(s_sig[i], s_sig[i + 1]), 0.5f), 1.f));
+      alpha = __fsub_rn(1.f, expf(-__fmul_rn(dm, delta)));
+      cr = __fmul_rn(__fadd_rn(s_r[i], s_r[i + 1]), 0.5f);
+      cg = __fmul_rn(__fadd_rn(s_g[i], s_g[i + 1]), 0.5f);
+      cb = __fmul_rn(__fadd_rn(s_b[i], s_b[i + 1]), 0.5f);
+      m.dmin = fminf(m.dmin, fminf(d0, d1)); m.dmax = fmaxf(m.dmax, fmaxf(d0, d1));
+    }
+    float t = on ? __fadd_rn(__fsub_rn(1.f, alpha), 1e-10f) : 1.f;       // inclusive product scan
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float q = __shfl_up_sync(0xffffffffu, t, o);
+      if (lane >= o) t *= q;
+    }
+    float excl = __shfl_up_sync(0xffffffffu, t, 1);
+    if (lane == 0) excl = 1.f;
+    const float wgt = on ? __fmul_rn(alpha, carry * excl) : 0.f;
+    carry *= __shfl_sync(0xffffffffu, t, 31);
+    if (on && s_w) s_w[i] = wgt;
+    m.r = fmaf(wgt, cr, m.r); m.g = fmaf(wgt, cg, m.g); m.b = fmaf(wgt, cb, m.b);
+    m.wz = fmaf(wgt, zmid, m.wz); m.wsum += wgt;
+  }
+  m.r = warp_sum(m.r); m.g = warp_sum(m.g); m.b = warp_sum(m.b); m.wz = warp_sum(m.wz); m.wsum = warp_sum(m.wsum);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    m.dmin = fminf(m.dmin, __shfl_xor_sync(0xffffffffu, m.dmin, o));
+    m.dmax = fmaxf(m.dmax, __shfl_xor_sync(0xffffffffu, m.dmax, o));
+  }
+  return m;
+}
+
+// order-preserving float <-> uint map so that atomicMin / atomicMax on unsigned give the float min / max
+__device__ __forceinline__ uint32_t f2ord(float f) { const uint32_t b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+__device__ __forceinline__ float ord2f(uint32_t u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u); }
+
+__global__ void minmax_init_kernel(uint32_t* mm) { if (threadIdx.x < 4) mm[threadIdx.x] = (threadIdx.x & 1) ? 0u : 0xFFFFFFFFu; }
+
+// composite_depth = clamp(nan_to_num(sum w z / sum w, inf), min(depths), max(depths))   (ray_marcher.py:46-50)
+__global__ void __launch_bounds__(256) depth_clamp_kernel(float* __restrict__ d0, float* __restrict__ d1, int64_t R, const uint32_t* __restrict__ mm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R) return;
+  if (d0) { float v = d0[i]; if (v != v) v = INFINITY; d0[i] = fminf(fmaxf(v, ord2f(mm[0])), ord2f(mm[1])); }
+  if (d1) { float v = d1[i]; if (v != v) v = INFINITY; d1[i] = fminf(fmaxf(v, ord2f(mm[2])), ord2f(mm[3])); }
+}
+
+__device__ __forceinline__ void emit_march(const March& m, int white_back, int64_t r, float* rgb, float* depth, float* opac,
+                                           uint32_t* mm, int lane) {
+  if (lane == 0) {
+    // white_back: composite_rgb + 1 - weight_total, left to right
+    rgb[r * 3 + 0] = white_back ? __fadd_rn(__fadd_rn(m.r, 1.f), -m.wsum) : m.r;
+    rgb[r * 3 + 1] = white_back ? __fadd_rn(__fadd_rn(m.g, 1.f), -m.wsum) : m.g;
+    rgb[r * 3 + 2] = white_back ? __fadd_rn(__fadd_rn(m.b, 1.f), -m.wsum) : m.b;
+    depth[r] = __fdiv_rn(m.wz, m.wsum);
+    if (opac) opac[r] = m.wsum;
+    atomicMin(mm, f2ord(m.dmin)); atomicMax(mm + 1, f2ord(m.dmax));
+  }
+}
+
+// counter-based uniform in [0,1) for callers that pass no random tensors (not torch's Philox stream)
+__device__ __forceinline__ float hash_uniform(uint64_t seed, uint64_t idx) {
+  uint64_t x = seed * 0x9E3779B97F4A7C15ull + idx + 0x632BE59BD9B4E019ull;
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+  return (float)(x >> 40) * (1.0f / 16777216.0f);
+}
+
+struct RenderArgs {
+  const float* planes; int H, W;
+  const float* dec; float lr_mul;
+  const float* o; const float* d; int64_t R;
+  int S, Si;
+  float ray_start, ray_end, inv_start, inv_end, delta; const float* start_arr; const float* end_arr;
+  int disparity; float coord_scale; int white_back;
+  const float* rand_coarse; const float* u; uint64_t seed;
+  float *rgb_c, *depth_c, *opac_c, *rgb_f, *depth_f, *opac_f;
+  float* depths_fine_out;        // optional (R, Si): the importance samples, for stage parity tests
+  uint32_t* mm;
+};
+
+// torch.linspace(a, b, n)[i] in fp32: step = (b - a) / (n - 1); first half a + i*step, second half b - (n-1-i)*step
+__device__ __forceinline__ float linspace_ab(float a, float b, int i, int n) {
+  const float step = __fdiv_rn(__fsub_rn(b, a), (float)(n - 1));
+  return (i < n / 2) ? __fmaf_rn((float)i, step, a) : __fmaf_rn(-(float)(n - 1 - i), step, b);
+}
+
+__global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const RenderArgs a) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int S = a.S, Si = a.Si, St = S + Si;
+  // per warp: two sample sets of 5 arrays (depth, sigma, r, g, b) x St, weights St, bins / cdf 2 x S
+  float* base = smem + (size_t)wib * (11 * St + 2 * S);
+  float* A[5]; float* B[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) { A[k] = base + k * St; B[k] = base + (5 + k) * St; }
+  float* s_w = base + 10 * St;
+  float* s_bins = s_w + St;
+  float* s_cdf = s_bins + S;
+  Dec dec;
+  load_decoder(dec, a.dec, a.lr_mul, lane);
+  for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < a.R; r += (int64_t)gridDim.x * TP_WARPS) {
+    const float ox = __ldg(a.o + r * 3), oy = __ldg(a.o + r * 3 + 1), oz = __ldg(a.o + r * 3 + 2);
+    const float dx = __ldg(a.d + r * 3), dy = __ldg(a.d + r * 3 + 1), dz = __ldg(a.d + r * 3 + 2);
+    const float rs = a.start_arr ? __ldg(a.start_arr + r) : a.ray_start, re = a.end_arr ? __ldg(a.end_arr + r) : a.ray_end;
+    // ---- stratified depths (renderer.py:172-195) ----
+    for (int i = lane; i < S; i += 32) {
+      const float rnd = a.rand_coarse ? __ldg(a.rand_coarse + r * S + i) : hash_uniform(a.seed, (uint64_t)(r * S + i));
+      float dep;
+      if (a.disparity) {
+        const float t = __fadd_rn(linspace01(i, S), __fmul_rn(rnd, (float)(1.0 / (double)(S - 1))));
+        const float is = a.start_arr ? __fdiv_rn(1.f, rs) : a.inv_start, ie = a.end_arr ? __fdiv_rn(1.f, re) : a.inv_end;
+        dep = __fdiv_rn(1.f, __fadd_rn(__fmul_rn(is, __fsub_rn(1.f, t)), __fmul_rn(ie, t)));
+      } else if (a.start_arr) {       // math_utils.linspace: start + (i / (S-1)) * (stop - start), delta = (stop - start) / (S-1)
+        const float st = __fdiv_rn((float)i, (float)(S - 1));
+        dep = __fadd_rn(__fadd_rn(rs, __fmul_rn(st, __fsub_rn(re, rs))), __fmul_rn(rnd, __fdiv_rn(__fsub_rn(re, rs), (float)(S - 1))));
+      } else {
+        dep = __fadd_rn(linspace_ab(rs, re, i, S), __fmul_rn(rnd, a.delta));
+      }
+      A[0][i] = dep;
+    }
+    __syncwarp();
+    // ---- coarse field pass ----
+#pragma unroll 2
+    for (int s = 0; s < S; ++s) {
+      const float t = A[0][s];
+      const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
+                                 __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
+                                 __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
+      if ((lane & 7) == 0) A[1 + (lane >> 3)][s] = v;
+    }
+    __syncwarp();
+    const March mc = march_ray(A[0], A[1], A[2], A[3], A[4], S, s_w, lane);
+    emit_march(mc, a.white_back, r, a.rgb_c, a.depth_c, a.opac_c, a.mm, lane);
+    __syncwarp();
+    // ---- importance sampling (renderer.py:197-215): smooth, + 0.01, inverse CDF over the mid-points ----
+    const int nwt = S - 1;                                  // weights from the marcher
+    for (int i = lane; i < nwt; i += 32) {                  // max_pool1d(2,1,pad 1) then avg_pool1d(2,1): S-1 values
+      const float wm1 = i > 0 ? s_w[i - 1] : -INFINITY, w0 = s_w[i], wp1 = i + 1 < nwt ? s_w[i + 1] : -INFINITY;
+      const float m0 = fmaxf(wm1, w0), m1 = fmaxf(w0, wp1);
+      B[0][i] = __fadd_rn(__fmul_rn(__fadd_rn(m0, m1), 0.5f), 0.01f);
+    }
+    for (int i = lane; i < S - 1; i += 32) s_bins[i] = __fmul_rn(0.5f, __fadd_rn(A[0][i], A[0][i + 1]));
+    __syncwarp();
+    const int nb = S - 2;                                   // cdf length: weights[:, 1:-1] has S-3 entries
+    warp_build_cdf(B[0] + 1, s_cdf, nb, 1e-5f, lane);
+    for (int j = lane; j < Si; j += 32) {
+      const float uj = a.u ? __ldg(a.u + r * Si + j) : hash_uniform(a.seed ^ 0x5851F42D4C957F2Dull, (uint64_t)(r * Si + j));
+      const float zf = invert_cdf(s_bins, s_cdf, nb, uj, 1e-5f, nullptr);
+      A[0][S + j] = zf;
+      if (a.depths_fine_out) a.depths_fine_out[r * Si + j] = zf;
+    }
+    __syncwarp();
+    // ---- fine field pass ----
+#pragma unroll 2
+    for (int s = S; s < St; ++s) {
+      const float t = A[0][s];
+      const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
+                                 __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
+                                 __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
+      if ((lane & 7) == 0) A[1 + (lane >> 3)][s] = v;
+    }
+    __syncwarp();
+    // ---- unify_samples (renderer.py:160-170): rank-by-counting sort of the depths, payload moved along ----
+    for (int k = lane; k < St; k += 32) {
+      const float xk = A[0][k];
+      int rank = 0;
+      for (int m = 0; m < St; ++m) { const float xm = A[0][m]; rank += (xm < xk) || (xm == xk && m < k); }
+#pragma unroll
+      for (int q = 0; q < 5; ++q) B[q][rank] = A[q][k];
+    }
+    __syncwarp();
+    const March mf = march_ray(B[0], B[1], B[2], B[3], B[4], St, nullptr, lane);
+    emit_march(mf, a.white_back, r, a.rgb_f, a.depth_f, a.opac_f, a.mm + 2, lane);
+    __syncwarp();
+  }
+}
+
+// ---- stand-alone pieces (the reference's public sub-APIs) -----------------------------------------------------------
+// run_model on explicit coordinates: rgb (P,3), sigma (P)
+__global__ void __launch_bounds__(TP_WARPS * 32) triplane_field_kernel(const float* __restrict__ planes, int H, int W,
+    const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
+    float* __restrict__ rgb, float* __restrict__ sigma) {
+  const int lane = threadIdx.x & 31;
+  Dec dec;
+  load_decoder(dec, decp, lr_mul, lane);
+  for (int64_t p = (int64_t)blockIdx.x * TP_WARPS + (threadIdx.x >> 5); p < P; p += (int64_t)gridDim.x * TP_WARPS) {
+    const float x = __ldg(coords + p * 3), y = __ldg(coords + p * 3 + 1), z = __ldg(coords + p * 3 + 2);
+    const float v = field_eval(planes, H, W, __fmul_rn(coord_scale, x), __fmul_rn(coord_scale, y), __fmul_rn(coord_scale, z), dec, lane);
+    if (lane == 0) sigma[p] = v;
+    else if ((lane & 7) == 0) rgb[p * 3 + (lane >> 3) - 1] = v;
+  }
+}
+
+// MipRayMarcher2 on explicit (R,S,3) colours, (R,S) densities, (R,S) depths
+__global__ void __launch_bounds__(TP_WARPS * 32) mip_march_kernel(const float* __restrict__ colors, const float* __restrict__ dens,
+    const float* __restrict__ depths, int64_t R, int S, int white_back, float* __restrict__ rgb, float* __restrict__ depth,
+    float* __restrict__ weights, uint32_t* mm) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* s = smem + (size_t)wib * 6 * S;
+  for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < R; r += (int64_t)gridDim.x * TP_WARPS) {
+    for (int i = lane; i < S; i += 32) {
+      s[i] = __ldg(depths + r * S + i); s[S + i] = __ldg(dens + r * S + i);
+      s[2 * S + i] = __ldg(colors + (r * S + i) * 3); s[3 * S + i] = __ldg(colors + (r * S + i) * 3 + 1);
+      s[4 * S + i] = __ldg(colors + (r * S + i) * 3 + 2);
+    }
+    __syncwarp();
+    const March m = march_ray(s, s + S, s + 2 * S, s + 3 * S, s + 4 * S, S, s + 5 * S, lane);
+    emit_march(m, white_back, r, rgb, depth, nullptr, mm, lane);
+    __syncwarp();
+    if (weights) for (int i = lane; i < S - 1; i += 32) weights[r * (S - 1) + i] = s[5 * S + i];
+    __syncwarp();
+  }
+}
+
+inline int grid_for(int64_t units) {
+  const int64_t want = ceil_div64(units, TP_WARPS);
+  const int64_t cap = (int64_t)NERFB_SM_COUNT * 8;           // 8 resident 256-thread CTAs per SM
+  return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+
+}  // namespace
+
+extern "C" int nerfb_triplane_relayout(const float* planes, int channels, int H, int W, float* planes_cl, void* stream) {
+  NERFB_CHECK_ARG(planes && planes_cl && H >= 1 && W >= 1);
+  if (channels != TP_C) return NERFB_E_UNSUPPORTED;
+  const int64_t HW = (int64_t)H * W;
+  NERFB_LAUNCH(triplane_relayout_kernel, dim3((unsigned)ceil_div64(HW, 32), 3), 256, 0, stream, planes, planes_cl, HW);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_triplane_field(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                    const float* coords, int64_t n_points, float box_warp, float* rgb, float* sigma,
+                                    void* stream) {
+  NERFB_CHECK_ARG(planes_cl && decoder && rgb && sigma && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
+  if (n_points == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(coords);
+  NERFB_LAUNCH(triplane_field_kernel, grid_for(n_points), TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords,
+               n_points, (float)(2.0 / (double)box_warp), rgb, sigma);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_mip_march(const float* colors, const float* densities, const float* depths, int64_t n_rays,
+                               int n_samples, int white_back, float* rgb, float* depth, float* weights, void* workspace,
+                               void* stream) {
+  NERFB_CHECK_ARG(rgb && depth && workspace && n_rays >= 0 && n_samples >= 2);
+  if (n_samples > 2048) return NERFB_E_UNSUPPORTED;
+  if (n_rays == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(colors && densities && depths);
+  uint32_t* mm = static_cast<uint32_t*>(workspace);
+  const size_t smem = (size_t)TP_WARPS * 6 * n_samples * sizeof(float);
+  if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(mip_march_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NERFB_LAUNCH(minmax_init_kernel, 1, 32, 0, stream, mm);
+  NERFB_LAUNCH(mip_march_kernel, grid_for(n_rays), TP_WARPS * 32, smem, stream, colors, densities, depths, n_rays, n_samples,
+               white_back, rgb, depth, weights, mm);
+  NERFB_LAUNCH(depth_clamp_kernel, (unsigned)ceil_div64(n_rays, 256), 256, 0, stream, depth, (float*)nullptr, n_rays, mm);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                     const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                     int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                                     const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                                     const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                                     float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                                     float* opacity_final, float* depths_fine_out, void* workspace, void* stream) {
+  NERFB_CHECK_ARG(planes_cl && decoder && rgb_coarse && depth_coarse && opacity_coarse && rgb_final && depth_final &&
+                  opacity_final && workspace);
+  NERFB_CHECK_ARG(n_rays >= 0 && n_samples >= 4 && n_importance >= 1 && H >= 1 && W >= 1 && box_warp != 0.f);
+  NERFB_CHECK_ARG((ray_start_arr == nullptr) == (ray_end_arr == nullptr));
+  if (n_samples + n_importance > TP_MAX_S) return NERFB_E_UNSUPPORTED;
+  if (n_rays == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(rays_o && rays_d);
+  RenderArgs a{};
+  a.planes = planes_cl; a.H = H; a.W = W; a.dec = decoder; a.lr_mul = lr_mul; a.o = rays_o; a.d = rays_d; a.R = n_rays;
+  a.S = n_samples; a.Si = n_importance; a.ray_start = (float)ray_start; a.ray_end = (float)ray_end; a.start_arr = ray_start_arr;
+  a.inv_start = (float)(1.0 / ray_start); a.inv_end = (float)(1.0 / ray_end); a.delta = (float)((ray_end - ray_start) / (double)(n_samples - 1));
+  a.end_arr = ray_end_arr; a.disparity = disparity; a.coord_scale = (float)(2.0 / (double)box_warp); a.white_back = white_back;
+  a.rand_coarse = rand_coarse; a.u = u; a.seed = seed;
+  a.rgb_c = rgb_coarse; a.depth_c = depth_coarse; a.opac_c = opacity_coarse; a.rgb_f = rgb_final; a.depth_f = depth_final;
+  a.opac_f = opacity_final; a.depths_fine_out = depths_fine_out; a.mm = static_cast<uint32_t*>(workspace);
+  const size_t smem = (size_t)TP_WARPS * (11 * (n_samples + n_importance) + 2 * n_samples) * sizeof(float);
+  if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
+  if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(triplane_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NERFB_LAUNCH(minmax_init_kernel, 1, 32, 0, stream, a.mm);
+  // register-heavy kernel (64 decoder weights per lane): grid = resident CTAs only, rays strided
+  const int64_t want = ceil_div64(n_rays, TP_WARPS);
+  const int64_t cap = (int64_t)NERFB_SM_COUNT * 2;
+  NERFB_LAUNCH(triplane_render_kernel, (int)(want < cap ? want : cap), TP_WARPS * 32, smem, stream, a);
+  NERFB_LAUNCH(depth_clamp_kernel, (unsigned)ceil_div64(n_rays, 256), 256, 0, stream, depth_coarse, depth_final, n_rays, a.mm);
+  return NERFB_OK;
+}

@@ -1,0 +1,184 @@
+"""EG3D tri-plane renderer, host mirror of the reference's API:
+
+    volumetric_rendering/renderer.py    generate_planes, sample_from_planes, ImportanceRenderer
+    volumetric_rendering/ray_marcher.py MipRayMarcher2
+    eg3d_training/triplane.py:144-167   OSGDecoder        (over networks_stylegan2.py:95-122 FullyConnectedLayer)
+
+Same class / function names, argument meaning, state-dict keys (``net.0.weight`` ...) and output tuple as the
+reference; all arithmetic runs in the hand-written kernels of csrc/triplane.cu (kernel 6).  Inference only (the
+reference's EG3DSystem renders through this path under ``torch.no_grad`` in eval_eg3d.py:63-75); there is no CPU
+fallback and no torch-op fallback.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import ops
+
+
+def generate_planes() -> torch.Tensor:
+    """renderer.py:23-39 (kept for API parity; the kernel hard-codes these three projections, quirk included)."""
+    return torch.tensor([[[1, 0, 0], [0, 1, 0], [0, 0, 1]],
+                         [[1, 0, 0], [0, 0, 1], [0, 1, 0]],
+                         [[0, 0, 1], [1, 0, 0], [0, 1, 0]]], dtype=torch.float32)
+
+
+class FullyConnectedLayer(nn.Module):
+    """Parameter container with the reference's init and gains (networks_stylegan2.py:95-122).  Only used as a
+    sub-module of OSGDecoder here, so it has no forward of its own: the decoder runs fused inside kernel (6)."""
+
+    def __init__(self, in_features, out_features, bias=True, activation="linear", lr_multiplier=1, bias_init=0):
+        super().__init__()
+        if activation != "linear" or not bias:
+            raise NotImplementedError("only the linear+bias FullyConnectedLayer of OSGDecoder is on the hot path")
+        self.in_features, self.out_features, self.activation = in_features, out_features, activation
+        self.weight = nn.Parameter(torch.randn([out_features, in_features]) / lr_multiplier)
+        self.bias = nn.Parameter(torch.full([out_features], np.float32(bias_init)))
+        self.weight_gain = lr_multiplier / np.sqrt(in_features)
+        self.bias_gain = lr_multiplier
+
+    def extra_repr(self):
+        return f"in_features={self.in_features:d}, out_features={self.out_features:d}, activation={self.activation:s}"
+
+
+class OSGDecoder(nn.Module):
+    """triplane.py:144-167.  ``forward(sampled_features (N, 3, M, 32), ray_directions)`` is served by the same fused
+    decoder code as the renderer, on features that the caller has already gathered."""
+
+    def __init__(self, n_features, options):
+        super().__init__()
+        if n_features != 32 or options.get("decoder_output_dim", 3) != 3:
+            raise NotImplementedError("kernel (6) is built for 32 feature channels and 1 + 3 outputs")
+        self.hidden_dim = 64
+        self.lr_mul = float(options.get("decoder_lr_mul", 1))
+        self.net = nn.Sequential(
+            FullyConnectedLayer(n_features, self.hidden_dim, lr_multiplier=self.lr_mul),
+            nn.Softplus(),
+            FullyConnectedLayer(self.hidden_dim, 1 + options.get("decoder_output_dim", 3), lr_multiplier=self.lr_mul))
+
+    def flat(self) -> torch.Tensor:
+        return torch.cat([self.net[0].weight.reshape(-1), self.net[0].bias, self.net[2].weight.reshape(-1),
+                          self.net[2].bias]).detach().float().contiguous()
+
+    def forward(self, sampled_features, ray_directions=None):
+        raise NotImplementedError(
+            "OSGDecoder is fused into the tri-plane kernel: call ImportanceRenderer.run_model(planes, decoder, coords, ...) "
+            "(renderer.py:144-151) instead of gathering features first")
+
+
+class _Planes:
+    """Channels-last copy of one batch element's planes, cached on the source tensor's identity + version."""
+
+    def __init__(self):
+        self.key, self.cl = None, None
+
+    def get(self, planes: torch.Tensor) -> torch.Tensor:
+        key = (planes.data_ptr(), planes._version, tuple(planes.shape))
+        if key != self.key:
+            self.cl = ops.triplane_relayout(planes)
+            self.key = key
+        return self.cl
+
+
+class MipRayMarcher2(nn.Module):
+    """ray_marcher.py:20-63."""
+
+    def __init__(self):
+        super().__init__()
+
+    def run_forward(self, colors, densities, depths, rendering_options):
+        if rendering_options["clamp_mode"] != "softplus":
+            assert False, "MipRayMarcher only supports `clamp_mode`=`softplus`!"
+        B, R, S, _ = depths.shape
+        rgb, depth, w = ops.mip_march(colors.reshape(B * R, S, 3), densities.reshape(B * R, S), depths.reshape(B * R, S),
+                                      bool(rendering_options.get("white_back", False)))
+        return rgb.view(B, R, 3), depth.view(B, R, 1), w.view(B, R, S - 1, 1)
+
+    def forward(self, colors, densities, depths, rendering_options):
+        return self.run_forward(colors, densities, depths, rendering_options)
+
+
+def get_ray_limits_box(rays_o, rays_d, box_side_length):
+    """math_utils.py:48-99 restated with torch ops on the caller's device (host-side glue for ray_start == 'auto';
+    slab test against the axis-aligned box, -1 / -2 for misses)."""
+    o_shape = rays_o.shape
+    o, d = rays_o.detach().reshape(-1, 3), rays_d.detach().reshape(-1, 3)
+    half = box_side_length / 2
+    inv = 1 / d
+    lo = torch.where(inv < 0, torch.full_like(o, half), torch.full_like(o, -half))
+    hi = torch.where(inv < 0, torch.full_like(o, -half), torch.full_like(o, half))
+    t0, t1 = (lo - o) * inv, (hi - o) * inv
+    valid = ~((t0[:, 0] > t1[:, 1]) | (t0[:, 1] > t1[:, 0]))
+    tmin, tmax = torch.max(t0[:, 0], t0[:, 1]), torch.min(t1[:, 0], t1[:, 1])
+    valid &= ~((tmin > t1[:, 2]) | (t0[:, 2] > tmax))
+    tmin, tmax = torch.max(tmin, t0[:, 2]), torch.min(tmax, t1[:, 2])
+    tmin = torch.where(valid, tmin, torch.full_like(tmin, -1.0))
+    tmax = torch.where(valid, tmax, torch.full_like(tmax, -2.0))
+    return tmin.reshape(*o_shape[:-1], 1), tmax.reshape(*o_shape[:-1], 1)
+
+
+class ImportanceRenderer(nn.Module):
+    """renderer.py:88-142.  ``forward`` returns the reference's 6-tuple
+    (rgb_coarse, depth_coarse, weights_coarse.sum(2), rgb_final, depth_final, weights.sum(2))."""
+
+    def __init__(self):
+        super().__init__()
+        self.ray_marcher = MipRayMarcher2()
+        self.plane_axes = generate_planes()
+        self._cache = _Planes()
+        self.seed = 0
+
+    def forward(self, planes, decoder, ray_origins, ray_directions, rendering_options, rand_coarse=None, u=None):
+        opts = rendering_options
+        if opts.get("clamp_mode", "softplus") != "softplus":
+            assert False, "MipRayMarcher only supports `clamp_mode`=`softplus`!"
+        if opts.get("density_noise", 0) > 0:
+            raise NotImplementedError("density_noise > 0 is a training-time option; kernel (6) is the render path")
+        n_imp = opts["depth_resolution_importance"]
+        if n_imp <= 0:
+            raise SystemExit(0)                     # the reference calls exit() here (renderer.py:138)
+        B, R, _ = ray_origins.shape
+        start_arr = end_arr = None
+        rs, re = opts["ray_start"], opts["ray_end"]
+        if isinstance(rs, str) and rs == re == "auto":
+            start_arr, end_arr = get_ray_limits_box(ray_origins, ray_directions, box_side_length=opts["box_warp"])
+            ok = end_arr > start_arr
+            if torch.any(ok).item():                # renderer.py:101-103
+                start_arr, end_arr = start_arr.clone(), end_arr.clone()
+                start_arr[~ok] = start_arr[ok].min()
+                end_arr[~ok] = start_arr[ok].max()
+            rs = re = 0.0
+        elif isinstance(rs, torch.Tensor):
+            start_arr, end_arr, rs, re = rs, re, 0.0, 0.0
+        outs = [[] for _ in range(6)]
+        for b in range(B):                          # planes differ per batch element; rays of one element form one launch
+            self.seed += 1
+            res = ops.triplane_render(
+                self._cache.get(planes[b]) if B == 1 else ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
+                ray_origins[b].contiguous(), ray_directions[b].contiguous(), opts["depth_resolution"], n_imp, float(rs), float(re),
+                None if start_arr is None else start_arr[b].reshape(-1).contiguous(),
+                None if end_arr is None else end_arr[b].reshape(-1).contiguous(),
+                bool(opts.get("disparity_space_sampling", False)), float(opts["box_warp"]), bool(opts.get("white_back", False)),
+                None if rand_coarse is None else rand_coarse[b].reshape(R, -1).contiguous(),
+                None if u is None else u.reshape(B, R, -1)[b].contiguous(), self.seed)
+            for k in range(6):
+                outs[k].append(res[k])
+        rgb_c, depth_c, op_c, rgb_f, depth_f, op_f = [torch.stack(o, 0) for o in outs]
+        return rgb_c, depth_c.unsqueeze(-1), op_c.unsqueeze(-1), rgb_f, depth_f.unsqueeze(-1), op_f.unsqueeze(-1)
+
+    def run_model(self, planes, decoder, sample_coordinates, sample_directions, options):
+        """renderer.py:144-151 -> {'rgb': (N, M, 3), 'sigma': (N, M, 1)}."""
+        if options.get("density_noise", 0) > 0:
+            raise NotImplementedError("density_noise > 0 is not on the render path")
+        N, M, _ = sample_coordinates.shape
+        rgbs, sigmas = [], []
+        for b in range(N):
+            rgb, sigma = ops.triplane_field(ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
+                                            sample_coordinates[b].contiguous(), float(options["box_warp"]))
+            rgbs.append(rgb); sigmas.append(sigma)
+        return {"rgb": torch.stack(rgbs, 0), "sigma": torch.stack(sigmas, 0).unsqueeze(-1)}

@@ -200,3 +200,81 @@ def mlp_bwd(desc, precision, in_mode, params, film, in0, in1, n_rows, n_samples,
                             _req(out, "out"), _req(d_out, "d_out"), grad.data_ptr(),
                             d_in.data_ptr() if d_in is not None else 0, ws_ptr, ws_bytes, _stream()), "nerfb_mlp_bwd")
     return grad, d_in
+
+
+# ---- kernel (6): EG3D tri-plane renderer ------------------------------------------------------------------
+def triplane_relayout(planes):
+    """(3, 32, H, W) reference layout -> channels-last (3, H, W, 32)."""
+    if planes.dim() != 4 or planes.shape[0] != 3:
+        raise ValueError(f"planes must be (3, C, H, W), got {tuple(planes.shape)}")
+    _, c, h, w = planes.shape
+    out = torch.empty(3, h, w, c, device=planes.device, dtype=torch.float32)
+    check(lib.nerfb_triplane_relayout(_req(planes, "planes"), c, h, w, out.data_ptr(), _stream()), "nerfb_triplane_relayout")
+    return out
+
+
+def _check_planes_cl(planes_cl):
+    if planes_cl.dim() != 4 or planes_cl.shape[0] != 3 or planes_cl.shape[3] != 32:
+        raise ValueError(f"planes_cl must be (3, H, W, 32), got {tuple(planes_cl.shape)}")
+    return planes_cl.shape[1], planes_cl.shape[2]
+
+
+def triplane_field(planes_cl, decoder_flat, lr_mul, coords, box_warp):
+    h, w = _check_planes_cl(planes_cl)
+    if decoder_flat.numel() != 64 * 32 + 64 + 4 * 64 + 4:
+        raise ValueError("decoder_flat must hold W1(64x32) b1(64) W2(4x64) b2(4)")
+    if coords.dim() != 2 or coords.shape[1] != 3:
+        raise ValueError("coords must be (P, 3)")
+    p = coords.shape[0]
+    rgb = torch.empty(p, 3, device=coords.device, dtype=torch.float32)
+    sigma = torch.empty(p, device=coords.device, dtype=torch.float32)
+    if p == 0:
+        return rgb, sigma
+    check(lib.nerfb_triplane_field(_req(planes_cl, "planes_cl"), h, w, _req(decoder_flat, "decoder"), float(lr_mul),
+                                   _req(coords, "coords"), p, float(box_warp), rgb.data_ptr(), sigma.data_ptr(), _stream()),
+          "nerfb_triplane_field")
+    return rgb, sigma
+
+
+def mip_march(colors, densities, depths, white_back=False):
+    if depths.dim() != 2 or colors.shape != (*depths.shape, 3) or densities.shape != depths.shape:
+        raise ValueError("mip_march expects colors (R,S,3), densities (R,S), depths (R,S)")
+    r, s = depths.shape
+    rgb = torch.empty(r, 3, device=depths.device, dtype=torch.float32)
+    depth = torch.empty(r, device=depths.device, dtype=torch.float32)
+    weights = torch.empty(r, s - 1, device=depths.device, dtype=torch.float32)
+    ws = torch.empty(4, device=depths.device, dtype=torch.int32)
+    if r == 0:
+        return rgb, depth, weights
+    check(lib.nerfb_mip_march(_req(colors, "colors"), _req(densities, "densities"), _req(depths, "depths"), r, s,
+                              int(bool(white_back)), rgb.data_ptr(), depth.data_ptr(), weights.data_ptr(), ws.data_ptr(),
+                              _stream()), "nerfb_mip_march")
+    return rgb, depth, weights
+
+
+def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, n_importance, ray_start, ray_end,
+                    ray_start_arr=None, ray_end_arr=None, disparity=False, box_warp=1.0, white_back=False,
+                    rand_coarse=None, u=None, seed=0, return_depths_fine=False):
+    h, w = _check_planes_cl(planes_cl)
+    if rays_o.dim() != 2 or rays_o.shape[1] != 3 or rays_d.shape != rays_o.shape:
+        raise ValueError("rays_o / rays_d must be (R, 3)")
+    r = rays_o.shape[0]
+    if rand_coarse is not None and tuple(rand_coarse.shape) != (r, n_samples):
+        raise ValueError("rand_coarse must be (R, n_samples)")
+    if u is not None and tuple(u.shape) != (r, n_importance):
+        raise ValueError("u must be (R, n_importance)")
+    dev = rays_o.device
+    out = [torch.empty(r, 3, device=dev), torch.empty(r, device=dev), torch.empty(r, device=dev),
+           torch.empty(r, 3, device=dev), torch.empty(r, device=dev), torch.empty(r, device=dev)]
+    fine = torch.empty(r, n_importance, device=dev) if return_depths_fine else None
+    ws = torch.empty(4, device=dev, dtype=torch.int32)
+    if r == 0:
+        return (*out, fine) if return_depths_fine else tuple(out)
+    check(lib.nerfb_triplane_render(
+        _req(planes_cl, "planes_cl"), h, w, _req(decoder_flat, "decoder"), float(lr_mul), _req(rays_o, "rays_o"),
+        _req(rays_d, "rays_d"), r, int(n_samples), int(n_importance), float(ray_start), float(ray_end),
+        _req(ray_start_arr, "ray_start_arr", allow_none=True), _req(ray_end_arr, "ray_end_arr", allow_none=True),
+        int(bool(disparity)), float(box_warp), int(bool(white_back)), _req(rand_coarse, "rand_coarse", allow_none=True),
+        _req(u, "u", allow_none=True), int(seed) & 0xFFFFFFFFFFFFFFFF, *[o.data_ptr() for o in out],
+        0 if fine is None else fine.data_ptr(), ws.data_ptr(), _stream()), "nerfb_triplane_render")
+    return (*out, fine) if return_depths_fine else tuple(out)

@@ -67,36 +67,55 @@ __device__ __forceinline__ void load_decoder(Dec& d, const float* __restrict__ p
   d.b2 = __ldg(w2 + 4 * TP_HID + (lane >> 3)) * lr_mul;
 }
 
-__device__ __forceinline__ float softplusf(float x) { return x > 20.f ? x : log1pf(expf(x)); }   // F.softplus, beta 1
+// F.softplus (beta 1, threshold 20) in the overflow-safe form max(x,0) + log(1 + exp(-|x|)); the fast exp / log
+// intrinsics keep the ABSOLUTE error below 2e-7 (1 + t is formed exactly to fp32, t in (0,1]), far inside the stated
+// parity tolerance, at a quarter of the instructions of log1pf(expf(x)).
+__device__ __forceinline__ float softplusf(float x) {
+  return x > 20.f ? x : fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(x)));
+}
 
-// bilinear tap of one plane at normalised (gx -> W, gy -> H), zeros padding, align_corners=False; lane = channel
-__device__ __forceinline__ float plane_tap(const float* __restrict__ pl, int H, int W, float gx, float gy, int lane) {
+// the 4 bilinear taps of one plane at normalised (gx -> W, gy -> H), zeros padding, align_corners=False
+// (F.grid_sample semantics, renderer.py:64).  Offsets are clamped in-bounds and out-of-range taps get weight 0, so the
+// loads are unconditional and all 12 of a sample are in flight together.  NaN coordinates fail every test -> no tap.
+__device__ __forceinline__ void plane_taps(int H, int W, float gx, float gy, int (&off)[4], float (&wt)[4]) {
   const float ix = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gx, 1.f), (float)W), 1.f), 0.5f);
   const float iy = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gy, 1.f), (float)H), 1.f), 0.5f);
   const float fx = floorf(ix), fy = floorf(iy);
   const float w = ix - fx, e = 1.f - w, n = iy - fy, s = 1.f - n;
-  // NaN / huge coordinates compare false everywhere -> no tap, as in grid_sample's bounds checks
   const bool x0 = fx >= 0.f && fx < (float)W, x1 = fx >= -1.f && fx < (float)(W - 1);
   const bool y0 = fy >= 0.f && fy < (float)H, y1 = fy >= -1.f && fy < (float)(H - 1);
   const int xi = (int)fmaxf(fminf(fx, (float)W), -2.f), yi = (int)fmaxf(fminf(fy, (float)H), -2.f);
-  const float* base = pl + ((int64_t)yi * W + xi) * TP_C + lane;
-  float acc = 0.f;
-  if (y0 && x0) acc = __ldg(base) * (s * e);
-  if (y0 && x1) acc = fmaf(__ldg(base + TP_C), s * w, acc);
-  if (y1 && x0) acc = fmaf(__ldg(base + (int64_t)W * TP_C), n * e, acc);
-  if (y1 && x1) acc = fmaf(__ldg(base + (int64_t)W * TP_C + TP_C), n * w, acc);
-  return acc;
+  const int xa = min(max(xi, 0), W - 1), xb = min(max(xi + 1, 0), W - 1);
+  const int ya = min(max(yi, 0), H - 1) * W, yb = min(max(yi + 1, 0), H - 1) * W;
+  off[0] = (ya + xa) * TP_C; wt[0] = (y0 && x0) ? s * e : 0.f;
+  off[1] = (ya + xb) * TP_C; wt[1] = (y0 && x1) ? s * w : 0.f;
+  off[2] = (yb + xa) * TP_C; wt[2] = (y1 && x0) ? n * e : 0.f;
+  off[3] = (yb + xb) * TP_C; wt[3] = (y1 && x1) ? n * w : 0.f;
 }
 
 // run_model for one point (renderer.py:144-151 + triplane.py:155-167).  Returns on lane 0: sigma, lane 8 / 16 / 24: r, g, b.
 __device__ __forceinline__ float field_eval(const float* __restrict__ planes, int H, int W, float x, float y, float z,
                                             const Dec& d, int lane) {
-  const int64_t ps = (int64_t)H * W * TP_C;
+  const int ps = H * W * TP_C;
   // plane axes (renderer.py:29-39): projections (x, y), (x, z), (z, x)
-  const float f0 = plane_tap(planes, H, W, x, y, lane);
-  const float f1 = plane_tap(planes + ps, H, W, x, z, lane);
-  const float f2 = plane_tap(planes + 2 * ps, H, W, z, x, lane);
-  const float f = __fdiv_rn(__fadd_rn(__fadd_rn(f0, f1), f2), 3.f);      // sampled_features.mean(1)
+  int off[3][4]; float wt[3][4], v[3][4];
+  plane_taps(H, W, x, y, off[0], wt[0]);
+  plane_taps(H, W, x, z, off[1], wt[1]);
+  plane_taps(H, W, z, x, off[2], wt[2]);
+  const float* pl = planes + lane;
+#pragma unroll
+  for (int p = 0; p < 3; ++p)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) v[p][t] = __ldg(pl + p * ps + off[p][t]);
+  float fp[3];
+#pragma unroll
+  for (int p = 0; p < 3; ++p) {
+    float acc = v[p][0] * wt[p][0];
+    acc = fmaf(v[p][1], wt[p][1], acc);
+    acc = fmaf(v[p][2], wt[p][2], acc);
+    fp[p] = fmaf(v[p][3], wt[p][3], acc);
+  }
+  const float f = __fdiv_rn(__fadd_rn(__fadd_rn(fp[0], fp[1]), fp[2]), 3.f);      // sampled_features.mean(1)
   float ha = d.b1a, hb = d.b1b;
 #pragma unroll
   for (int c = 0; c < TP_C; ++c) {
@@ -119,7 +138,7 @@ __device__ __forceinline__ float field_eval(const float* __restrict__ planes, in
   c += __shfl_xor_sync(0xffffffffu, c, 2);
   c += __shfl_xor_sync(0xffffffffu, c, 1);
   c += d.b2;
-  if (lane >= 8) c = __fsub_rn(__fmul_rn(1.f / (1.f + expf(-c)), 1.002f), 0.001f);     // triplane.py:165
+  if (lane >= 8) c = __fsub_rn(__fmul_rn(__fdividef(1.f, 1.f + __expf(-c)), 1.002f), 0.001f);     // triplane.py:165
   return c;
 }
 
@@ -228,9 +247,8 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
   const int S = a.S, Si = a.Si, St = S + Si;
   // per warp: two sample sets of 5 arrays (depth, sigma, r, g, b) x St, weights St, bins / cdf 2 x S
   float* base = smem + (size_t)wib * (11 * St + 2 * S);
-  float* A[5]; float* B[5];
-#pragma unroll
-  for (int k = 0; k < 5; ++k) { A[k] = base + k * St; B[k] = base + (5 + k) * St; }
+  float* const A = base;               // sample set A: [depth | sigma | r | g | b] x St, coarse [0,S) then fine [S,St)
+  float* const B = base + 5 * St;      // sample set B: the merged, sorted samples
   float* s_w = base + 10 * St;
   float* s_bins = s_w + St;
   float* s_cdf = s_bins + S;
@@ -254,60 +272,55 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
       } else {
         dep = __fadd_rn(linspace_ab(rs, re, i, S), __fmul_rn(rnd, a.delta));
       }
-      A[0][i] = dep;
+      A[i] = dep;
     }
     __syncwarp();
-    // ---- coarse field pass ----
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      // ---- field pass over the coarse (pass 0) / importance (pass 1) samples: ONE copy of the decoder code ----
+      const int s0 = pass ? S : 0, s1 = pass ? St : S;
 #pragma unroll 2
-    for (int s = 0; s < S; ++s) {
-      const float t = A[0][s];
-      const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
-                                 __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
-                                 __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
-      if ((lane & 7) == 0) A[1 + (lane >> 3)][s] = v;
+      for (int s = s0; s < s1; ++s) {
+        const float t = A[s];
+        const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
+                                   __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
+                                   __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
+        if ((lane & 7) == 0) A[(1 + (lane >> 3)) * St + s] = v;
+      }
+      __syncwarp();
+      if (pass) break;
+      const March mc = march_ray(A, A + St, A + 2 * St, A + 3 * St, A + 4 * St, S, s_w, lane);
+      emit_march(mc, a.white_back, r, a.rgb_c, a.depth_c, a.opac_c, a.mm, lane);
+      __syncwarp();
+      // ---- importance sampling (renderer.py:197-215): smooth, + 0.01, inverse CDF over the mid-points ----
+      const int nwt = S - 1;                                  // weights from the marcher
+      for (int i = lane; i < nwt; i += 32) {                  // max_pool1d(2,1,pad 1) then avg_pool1d(2,1): S-1 values
+        const float wm1 = i > 0 ? s_w[i - 1] : -INFINITY, w0 = s_w[i], wp1 = i + 1 < nwt ? s_w[i + 1] : -INFINITY;
+        const float m0 = fmaxf(wm1, w0), m1 = fmaxf(w0, wp1);
+        B[i] = __fadd_rn(__fmul_rn(__fadd_rn(m0, m1), 0.5f), 0.01f);
+      }
+      for (int i = lane; i < S - 1; i += 32) s_bins[i] = __fmul_rn(0.5f, __fadd_rn(A[i], A[i + 1]));
+      __syncwarp();
+      const int nb = S - 2;                                   // cdf length: weights[:, 1:-1] has S-3 entries
+      warp_build_cdf(B + 1, s_cdf, nb, 1e-5f, lane);
+      for (int j = lane; j < Si; j += 32) {
+        const float uj = a.u ? __ldg(a.u + r * Si + j) : hash_uniform(a.seed ^ 0x5851F42D4C957F2Dull, (uint64_t)(r * Si + j));
+        const float zf = invert_cdf(s_bins, s_cdf, nb, uj, 1e-5f, nullptr);
+        A[S + j] = zf;
+        if (a.depths_fine_out) a.depths_fine_out[r * Si + j] = zf;
+      }
+      __syncwarp();
     }
-    __syncwarp();
-    const March mc = march_ray(A[0], A[1], A[2], A[3], A[4], S, s_w, lane);
-    emit_march(mc, a.white_back, r, a.rgb_c, a.depth_c, a.opac_c, a.mm, lane);
-    __syncwarp();
-    // ---- importance sampling (renderer.py:197-215): smooth, + 0.01, inverse CDF over the mid-points ----
-    const int nwt = S - 1;                                  // weights from the marcher
-    for (int i = lane; i < nwt; i += 32) {                  // max_pool1d(2,1,pad 1) then avg_pool1d(2,1): S-1 values
-      const float wm1 = i > 0 ? s_w[i - 1] : -INFINITY, w0 = s_w[i], wp1 = i + 1 < nwt ? s_w[i + 1] : -INFINITY;
-      const float m0 = fmaxf(wm1, w0), m1 = fmaxf(w0, wp1);
-      B[0][i] = __fadd_rn(__fmul_rn(__fadd_rn(m0, m1), 0.5f), 0.01f);
-    }
-    for (int i = lane; i < S - 1; i += 32) s_bins[i] = __fmul_rn(0.5f, __fadd_rn(A[0][i], A[0][i + 1]));
-    __syncwarp();
-    const int nb = S - 2;                                   // cdf length: weights[:, 1:-1] has S-3 entries
-    warp_build_cdf(B[0] + 1, s_cdf, nb, 1e-5f, lane);
-    for (int j = lane; j < Si; j += 32) {
-      const float uj = a.u ? __ldg(a.u + r * Si + j) : hash_uniform(a.seed ^ 0x5851F42D4C957F2Dull, (uint64_t)(r * Si + j));
-      const float zf = invert_cdf(s_bins, s_cdf, nb, uj, 1e-5f, nullptr);
-      A[0][S + j] = zf;
-      if (a.depths_fine_out) a.depths_fine_out[r * Si + j] = zf;
-    }
-    __syncwarp();
-    // ---- fine field pass ----
-#pragma unroll 2
-    for (int s = S; s < St; ++s) {
-      const float t = A[0][s];
-      const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
-                                 __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
-                                 __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
-      if ((lane & 7) == 0) A[1 + (lane >> 3)][s] = v;
-    }
-    __syncwarp();
     // ---- unify_samples (renderer.py:160-170): rank-by-counting sort of the depths, payload moved along ----
     for (int k = lane; k < St; k += 32) {
-      const float xk = A[0][k];
+      const float xk = A[k];
       int rank = 0;
-      for (int m = 0; m < St; ++m) { const float xm = A[0][m]; rank += (xm < xk) || (xm == xk && m < k); }
+      for (int m = 0; m < St; ++m) { const float xm = A[m]; rank += (xm < xk) || (xm == xk && m < k); }
 #pragma unroll
-      for (int q = 0; q < 5; ++q) B[q][rank] = A[q][k];
+      for (int q = 0; q < 5; ++q) B[q * St + rank] = A[q * St + k];
     }
     __syncwarp();
-    const March mf = march_ray(B[0], B[1], B[2], B[3], B[4], St, nullptr, lane);
+    const March mf = march_ray(B, B + St, B + 2 * St, B + 3 * St, B + 4 * St, St, nullptr, lane);
     emit_march(mf, a.white_back, r, a.rgb_f, a.depth_f, a.opac_f, a.mm + 2, lane);
     __syncwarp();
   }

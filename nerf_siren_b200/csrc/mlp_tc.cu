@@ -17,6 +17,12 @@
 // The layer chain is pipelined at K-block granularity: the MMA of layer l+1 starts on block 0 while blocks 1..3 of layer
 // l are still in the epilogue, into the other accumulator.  Skip / direction concatenations are extra K-blocks (the
 // resident X tile), never a cat.  sigma (256->1) and rgb (128->3, sigmoid) heads are fp32 dot products in the epilogue.
+//
+// SIREN / FiLM variant (models/nerf.py:142-216, forward only): same kernel, template parameter SIREN.  The epilogue is
+// sin(freq (.) acc + (freq (.) b + phase)) -- one packed FMA against two per-column tables, then MUFU.SIN; the 3-wide
+// first layer (and the 3 direction columns of the colour layer) are carried as 9 K-columns [x_hi x_lo x_hi] against
+// [W_hi W_hi W_lo], which restores ~16 mantissa bits where the first-layer frequency scale w0 = 30 amplifies input
+// rounding; the colour layer is N = 256 and its 256->3 sigmoid head rides in the epilogue like NeRF's.
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -51,6 +57,7 @@ struct TcStep {
   int x_done;          // this step is the last reader of the current X contents (xyz or direction encoding)
   int save_off;        // byte offset of this step's output blocks in the tile's saved record (-1 = not saved)
   int store_only;      // the output blocks feed no later MMA (saved for the backward only): published on s_ready
+  int film;            // SIREN: FiLM layer index of this step's frequency / phase vectors
 };
 
 constexpr int MAX_OPS = 64;
@@ -70,12 +77,15 @@ struct TcProgram {
   int tile_save_bytes;             // saved bytes per tile (0 = nothing saved)
   int n_freq_xyz, n_freq_dir, in_xyz, in_dir;
   int sigma_only, out_c;
+  int siren, rgb_in;               // rgb head fan-in: 128 (NeRF direction layer) or 256 (SIREN colour layer)
+  float xyz_scale;                 // SIREN: UniformBoxWarp 2 / sidelength (models/nerf.py:134-140)
 };
 
 struct TcFwdArgs {
   TcProgram prog;
   const uint8_t* wblob;            // packed bf16 weight slabs in schedule order
-  const float* bias;               // fp32 bias table [n_bias] | w_sigma[256] | b_sigma | w_rgb[3*128] | b_rgb[3]
+  const float* bias;               // fp32 bias table [n_bias] | w_sigma[256] | b_sigma | w_rgb[3*rgb_in] | b_rgb[3]
+  const float* scale;              // SIREN: per-column frequency table [n_bias] (bias table then holds freq*b + phase)
   const float* in0; const float* in1; int in_mode; int S;
   int64_t P; int64_t n_tiles;
   float* out;
@@ -89,8 +99,9 @@ struct __align__(1024) Smem {
   uint8_t x[2][BLK_BYTES];               // encoding tiles (double buffer: tile t uses x[t & 1])
   uint8_t ring[N_STAGES][STAGE_BYTES];   // weight slabs
   float bias[10 * 256 + 128];
+  float scale[9 * 256];                  // SIREN frequencies
   float w_sigma[256];
-  float w_rgb[3 * 128];
+  float w_rgb[3 * 256];
   float b_heads[4];                      // b_sigma, b_rgb[3]
   float part[4][3][TILE_M];              // head partial sums [column quarter][channel][row]
   float sigma[TILE_M];
@@ -144,6 +155,20 @@ __device__ __forceinline__ void encode_row(float vx, float vy, float vz, int n_f
   store_row64(base, row, buf);
 }
 
+// SIREN input row: v (3 values, fp32) as 9 bf16 columns [hi(3) lo(3) hi(3)], hi = bf16(v), lo = bf16(v - hi)
+__device__ __forceinline__ void hilo_row(float vx, float vy, float vz, uint32_t base, int row) {
+  float buf[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) buf[i] = 0.f;
+  const float v[3] = {vx, vy, vz};
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float hi = __bfloat162float(__float2bfloat16_rn(v[j]));
+    buf[j] = hi; buf[3 + j] = v[j] - hi; buf[6 + j] = hi;
+  }
+  store_row64(base, row, buf);
+}
+
 // already-embedded input: src[0..width) (zero padded to 64 columns) -> X tile row
 __device__ __forceinline__ void copy_row(const float* src, int width, uint32_t base, int row) {
   float buf[64];
@@ -152,6 +177,7 @@ __device__ __forceinline__ void copy_row(const float* src, int width, uint32_t b
   store_row64(base, row, buf);
 }
 
+template <bool SIREN>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid_constant__ TcFwdArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);            // keeps the shared address space: native LDS / STS
@@ -164,8 +190,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
   for (int i = threadIdx.x; i < pg.n_bias; i += NUM_THREADS) sm.bias[i] = __ldg(args.bias + i);
   for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.bias + pg.n_bias + i);
   if (threadIdx.x == 0) sm.b_heads[0] = __ldg(args.bias + pg.n_bias + 256);
-  for (int i = threadIdx.x; i < 3 * 128; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.bias + pg.n_bias + 257 + i);
-  if (threadIdx.x < 3) sm.b_heads[1 + threadIdx.x] = __ldg(args.bias + pg.n_bias + 257 + 384 + threadIdx.x);
+  constexpr int RGB_IN = SIREN ? 256 : 128;
+  for (int i = threadIdx.x; i < 3 * RGB_IN; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.bias + pg.n_bias + 257 + i);
+  if (threadIdx.x < 3) sm.b_heads[1 + threadIdx.x] = __ldg(args.bias + pg.n_bias + 257 + 3 * RGB_IN + threadIdx.x);
+  if (SIREN) for (int i = threadIdx.x; i < pg.n_bias; i += NUM_THREADS) sm.scale[i] = __ldg(args.scale + i);
   if (threadIdx.x < 2 * pg.n_ops) {       // decode the MMA op list once, for both X buffers
     const int b = threadIdx.x / pg.n_ops, i = threadIdx.x % pg.n_ops;
     const uint32_t w = pg.ops[i];
@@ -313,6 +341,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         px = __fadd_rn(__ldg(ray + 0), __fmul_rn(dirx, z));
         py = __fadd_rn(__ldg(ray + 1), __fmul_rn(diry, z));
         pz = __fadd_rn(__ldg(ray + 2), __fmul_rn(dirz, z));
+      } else if (SIREN) {                                  // x = [xyz(3) | dir(3)] rows (SirenField.forward)
+        const float* src = args.in0 + pc * (int64_t)(pg.sigma_only ? 3 : 6);
+        px = __ldg(src); py = __ldg(src + 1); pz = __ldg(src + 2);
+        if (!pg.sigma_only) { dirx = __ldg(src + 3); diry = __ldg(src + 4); dirz = __ldg(src + 5); }
       } else {
         emb_src = args.in0 + pc * (int64_t)(pg.in_xyz + (pg.sigma_only ? 0 : pg.in_dir));
       }
@@ -320,7 +352,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         mbar_wait_relaxed(&sm.x_consumed[b], xc_par[b]); xc_par[b] ^= 1;
         if (saving) { mbar_wait_relaxed(&sm.x_stored[b], xs_par[b]); xs_par[b] ^= 1; }
       }
-      if (args.in_mode == NERFB_IN_RAYS) encode_row(px, py, pz, pg.n_freq_xyz, x_base, row);
+      if (SIREN) hilo_row(__fmul_rn(px, pg.xyz_scale), __fmul_rn(py, pg.xyz_scale), __fmul_rn(pz, pg.xyz_scale), x_base, row);
+      else if (args.in_mode == NERFB_IN_RAYS) encode_row(px, py, pz, pg.n_freq_xyz, x_base, row);
       else copy_row(emb_src, pg.in_xyz, x_base, row);
       fence_proxy_async();
       __syncwarp();
@@ -328,7 +361,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
       if (!pg.sigma_only) {                                // direction encoding, once the last xyz reader is done
         mbar_wait_relaxed(&sm.x_consumed[b], xc_par[b]); xc_par[b] ^= 1;
         if (saving) { mbar_wait_relaxed(&sm.x_stored[b], xs_par[b]); xs_par[b] ^= 1; }
-        if (args.in_mode == NERFB_IN_RAYS) encode_row(dirx, diry, dirz, pg.n_freq_dir, x_base, row);
+        if (SIREN) hilo_row(dirx, diry, dirz, x_base, row);
+        else if (args.in_mode == NERFB_IN_RAYS) encode_row(dirx, diry, dirz, pg.n_freq_dir, x_base, row);
         else copy_row(emb_src + pg.in_xyz, pg.in_dir, x_base, row);
         fence_proxy_async();
         __syncwarp();
@@ -358,6 +392,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         const bool st_saved = saving && ((sw >> 16) & 1u);
         const uint32_t ready = ((sw >> 15) & 1u) ? smem_u32(sm.s_ready) : smem_u32(sm.a_ready);
         const uint32_t bias_base = smem_u32(sm.bias) + sb * 4u + 64u * (uint32_t)c4;
+        const uint32_t scale_base = smem_u32(sm.scale) + sb * 4u + 64u * (uint32_t)c4;
         const uint32_t a = gs & 1;
         mbar_wait(&sm.acc_full[a], (acc_par >> a) & 1u); acc_par ^= 1u << a;
         tc_fence_after();
@@ -372,6 +407,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             float4 bb[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) bb[i] = lds128f(bias_base + 256u * (uint32_t)j + 16u * i);
+            float4 sc[4];
+            if (SIREN) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) sc[i] = lds128f(scale_base + 256u * (uint32_t)j + 16u * i);
+            }
             tmem_ld_wait();
             NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 21] = clock64();)
             if (j + 1 < nb) tmem_ld16(t_lane + a * 256u + 64u * (uint32_t)(j + 1), v[(j + 1) & 1]);
@@ -380,8 +420,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             float f[16];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              const float2 r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
-              const float2 r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
+              float2 r0, r1;
+              if (SIREN) {      // sin(freq * (acc + b) + phase) = sin(freq * acc + (freq * b + phase))   (models/nerf.py:149-151)
+                r0 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(sc[i].x, sc[i].y), make_float2(bb[i].x, bb[i].y));
+                r1 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(sc[i].z, sc[i].w), make_float2(bb[i].z, bb[i].w));
+                r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y);
+              } else {
+                r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
+                r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
+              }
               f[4 * i] = r0.x; f[4 * i + 1] = r0.y; f[4 * i + 2] = r1.x; f[4 * i + 3] = r1.y;
             }
             if (st_head == 1) {               // sigma = <relu(h_D), w_sigma> + b on the un-rounded activations (nerf.py:112)
@@ -389,22 +436,22 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 const float4 w = lds128f(wb + 16u * i);
-                head_acc[0] = fmaf(fmaxf(f[4 * i], 0.f), w.x, head_acc[0]);
-                head_acc[0] = fmaf(fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[0]);
-                head_acc[0] = fmaf(fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[0]);
-                head_acc[0] = fmaf(fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[0]);
+                head_acc[0] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[0]);
+                head_acc[0] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[0]);
+                head_acc[0] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[0]);
+                head_acc[0] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[0]);
               }
             } else if (st_head == 2) {        // rgb pre-activations on the un-rounded direction-layer activations
 #pragma unroll
               for (int c = 0; c < 3; ++c) {
-                const uint32_t wb = smem_u32(sm.w_rgb) + (uint32_t)(c * 128) * 4u + col0 * 4u;
+                const uint32_t wb = smem_u32(sm.w_rgb) + (uint32_t)(c * RGB_IN) * 4u + col0 * 4u;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                   const float4 w = lds128f(wb + 16u * i);
-                  head_acc[c] = fmaf(fmaxf(f[4 * i], 0.f), w.x, head_acc[c]);
-                  head_acc[c] = fmaf(fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[c]);
-                  head_acc[c] = fmaf(fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[c]);
-                  head_acc[c] = fmaf(fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[c]);
+                  head_acc[c] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[c]);
+                  head_acc[c] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[c]);
+                  head_acc[c] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[c]);
+                  head_acc[c] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[c]);
                 }
               }
             }
@@ -470,7 +517,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
 }
 
 // ---- weight packing: fp32 nn.Linear weights -> bf16 slabs in the swizzled shared-memory image, schedule order ----
-struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; };   // W[n*ld + col0 + kk], kk < ncols
+struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; };   // W[n*ld + col0 + kk], kk < ncols
+// hilo: 3 source columns expanded to 9 K-columns [W_hi W_hi W_lo] (pairs with hilo_row's [x_hi x_lo x_hi])
 struct PackArgs { int n_slabs; PackSlab slab[48]; };
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params, PackArgs pa, uint8_t* __restrict__ blob) {
@@ -481,6 +529,14 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int kk = ch * 8 + e;
+      if (sl.hilo) {
+        f[e] = 0.f;
+        if (kk < 9) {
+          const float w = __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk % 3);
+          const float hi = __bfloat162float(__float2bfloat16_rn(w));
+          f[e] = kk < 6 ? hi : w - hi;
+        }
+      } else
       f[e] = (kk < sl.ncols) ? __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk) : 0.f;
     }
     uint4 o;
@@ -490,11 +546,22 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 }
 
 // bias table: [step biases ...] | w_sigma | b_sigma | w_rgb | b_rgb, gathered from the flat parameter blob
-struct BiasSeg { int64_t src; int n; int dst; };
-struct BiasArgs { int n_segs; BiasSeg seg[20]; };
-__global__ void __launch_bounds__(256) gather_bias_kernel(const float* __restrict__ params, BiasArgs ba, float* __restrict__ table) {
+struct BiasSeg { int64_t src; int n; int dst; int film; };     // film >= 0: FiLM layer whose freq / phase fold into this bias
+struct BiasArgs { int n_segs; BiasSeg seg[20]; int film_stride; };
+// film = [freq (L x W) | phase (L x W)]: table = freq * b + phase, scale = freq  (models/nerf.py:149-151)
+__global__ void __launch_bounds__(256) gather_bias_kernel(const float* __restrict__ params, BiasArgs ba, float* __restrict__ table,
+                                                          const float* __restrict__ film, float* __restrict__ scale) {
   const BiasSeg sg = ba.seg[blockIdx.x];
-  for (int i = threadIdx.x; i < sg.n; i += blockDim.x) table[sg.dst + i] = __ldg(params + sg.src + i);
+  for (int i = threadIdx.x; i < sg.n; i += blockDim.x) {
+    const float b = __ldg(params + sg.src + i);
+    if (sg.film >= 0 && film) {
+      const float fr = __ldg(film + sg.film * sg.n + i), ph = __ldg(film + ba.film_stride + sg.film * sg.n + i);
+      table[sg.dst + i] = fmaf(fr, b, ph);
+      scale[sg.dst + i] = fr;
+    } else {
+      table[sg.dst + i] = b;
+    }
+  }
 }
 
 // ---- host side: program construction, workspace plan, launch ---------------------------------------------------
@@ -503,11 +570,12 @@ struct TcPlan {
   PackArgs pack;
   BiasArgs bias;
   int64_t wblob_bytes, bias_floats;
-  int64_t off_wblob, off_bias, off_save, total;
+  int64_t off_wblob, off_bias, off_scale, off_save, total;
 };
 
 bool tc_supported(const nerfb_mlp_desc& d, int in_mode) {
   (void)in_mode;
+  if (d.kind == NERFB_KIND_SIREN) return d.W == 256 && d.D >= 1 && d.D <= 9 && d.box > 0.f;   // forward only, see tc_bwd_supported
   if (d.kind != NERFB_KIND_NERF || d.W != 256 || d.n_cls != 0) return false;
   if (d.D < 1 || d.D > 9) return false;
   if (!d.logscale && d.in_xyz <= 0) return false;                 // in-kernel encoding is the power-of-two ladder
@@ -524,14 +592,35 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   pg.n_freq_xyz = d.n_freq_xyz; pg.n_freq_dir = d.n_freq_dir; pg.in_xyz = o.in_xyz; pg.in_dir = o.in_dir;
   pg.sigma_only = sigma_only; pg.out_c = sigma_only ? 1 : 4;
   int64_t wb = 0; int nb = 0, ns = 0, nslab = 0, nseg = 0, sv = 0;
-  auto add_slab = [&](int64_t w_off, int ld, int col0, int ncols, int N) {
-    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb};
+  auto add_slab = [&](int64_t w_off, int ld, int col0, int ncols, int N, int hilo = 0) {
+    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb, hilo};
     wb += (int64_t)N * 128;
   };
-  auto add_bias = [&](int64_t src, int n) { pl.bias.seg[nseg++] = BiasSeg{src, n, nb}; nb += n; return nb - n; };
+  auto add_bias = [&](int64_t src, int n, int film = -1) { pl.bias.seg[nseg++] = BiasSeg{src, n, nb, film}; nb += n; return nb - n; };
+  const bool siren = d.kind == NERFB_KIND_SIREN;
+  pg.siren = siren; pg.rgb_in = siren ? 256 : 128; pg.xyz_scale = siren ? 2.0f / d.box : 1.0f;
+  pl.bias.film_stride = (d.D + 1) * d.W;
   pg.save_x_off = -1; pg.save_dir_off = -1;
   if (save) { pg.save_x_off = sv; sv += BLK_BYTES; }
   int last_x_reader = 0;
+  if (siren) {      // models/nerf.py:204-214: 8 FiLM layers, sigma head on the last, colour FiLM layer on [dir | h] + rgb head
+    for (int i = 0; i < d.D; ++i) {
+      TcStep& st = pg.s[ns++];
+      st = TcStep{};
+      st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1;
+      if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], 3, 0, 3, 256, 1); }
+      else for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], 256, 64 * j, 64, 256); }
+      st.bias_off = add_bias(o.b[i], 256, i);
+      if (sigma_only && i == d.D - 1) st.out_blocks = 0;
+    }
+    if (!sigma_only) {
+      TcStep& cl = pg.s[ns++]; cl = TcStep{};
+      cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = 0; cl.film = d.D; cl.save_off = -1;
+      for (int j = 0; j < 4; ++j) { cl.src[cl.n_kb++] = j; add_slab(o.w_dir, 259, 3 + 64 * j, 64, 256); }
+      cl.src[cl.n_kb++] = SRC_X; cl.wait_x = 1; cl.x_done = 1; add_slab(o.w_dir, 259, 0, 3, 256, 1);
+      cl.bias_off = add_bias(o.b_dir, 256, d.D);
+    }
+  } else
   for (int i = 0; i < d.D; ++i) {
     TcStep& st = pg.s[ns++];
     st = TcStep{};
@@ -549,7 +638,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     if (sigma_only && i == d.D - 1) { st.out_blocks = 0; st.save_off = -1; }
   }
   pg.s[last_x_reader].x_done = 1;
-  if (!sigma_only) {
+  if (!sigma_only && !siren) {
     TcStep& fin = pg.s[ns++]; fin = TcStep{};
     fin.N = 256; fin.relu = 0; fin.out_blocks = 4;
     for (int j = 0; j < 4; ++j) { fin.src[fin.n_kb++] = j; add_slab(o.w_final, 256, 64 * j, 64, 256); }
@@ -581,14 +670,15 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
                       ((uint32_t)st.store_only << 15) | ((st.save_off >= 0 ? 1u : 0u) << 16);
   }
   add_bias(o.w_sigma, 256); add_bias(o.b_sigma, 1);
-  if (!sigma_only) { add_bias(o.w_rgb, 384); add_bias(o.b_rgb, 3); }
+  if (!sigma_only) { add_bias(o.w_rgb, 3 * pg.rgb_in); add_bias(o.b_rgb, 3); }
   pl.pack.n_slabs = nslab; pl.bias.n_segs = nseg;
   pg.tile_save_bytes = save ? sv : 0;
-  pl.wblob_bytes = wb; pl.bias_floats = pg.n_bias + 256 + 1 + 384 + 3;
+  pl.wblob_bytes = wb; pl.bias_floats = pg.n_bias + 256 + 1 + 768 + 3;
   const int64_t n_tiles = ceil_div64(P, TILE_M);
   int64_t off = 0;
   pl.off_wblob = off; off += round_up64(wb, 1024);
   pl.off_bias = off;  off += round_up64(pl.bias_floats * 4, 1024);
+  pl.off_scale = off; off += siren ? round_up64((int64_t)pg.n_bias * 4, 1024) : 0;
   pl.off_save = off;  off += save ? n_tiles * (int64_t)sv : 0;
   pl.total = off;
   return pl;
@@ -611,7 +701,8 @@ int64_t tc_workspace_bytes(const nerfb_mlp_desc& d, int64_t P, int sigma_only, i
 int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, int sigma_only, int save, float* out, void* ws,
                int64_t ws_bytes, void* stream) {
-  (void)film;
+  const bool siren = d.kind == NERFB_KIND_SIREN;
+  if (siren && (!film || save)) return siren && save ? NERFB_E_UNSUPPORTED : NERFB_E_BADARG;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0);
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;
@@ -619,11 +710,13 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   uint8_t* base = static_cast<uint8_t*>(ws);
   NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob);
   NERFB_LAUNCH(gather_bias_kernel, pl.bias.n_segs, 256, 0, stream, params, pl.bias,
-               reinterpret_cast<float*>(base + pl.off_bias));
+               reinterpret_cast<float*>(base + pl.off_bias), siren ? film : (const float*)nullptr,
+               reinterpret_cast<float*>(base + pl.off_scale));
   TcFwdArgs a{};
   a.prog = pl.prog;
   a.wblob = base + pl.off_wblob;
   a.bias = reinterpret_cast<const float*>(base + pl.off_bias);
+  a.scale = reinterpret_cast<const float*>(base + pl.off_scale);
   a.in0 = in0; a.in1 = in1; a.in_mode = in_mode; a.S = n_samples;
   a.P = P; a.n_tiles = ceil_div64(P, TILE_M);
   a.out = out;
@@ -632,11 +725,13 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   const size_t smem = sizeof(Smem) + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
-  NERFB_LAUNCH(mlp_tc_fwd_kernel, grid, NUM_THREADS, smem, stream, a);
+  if (siren) NERFB_LAUNCH(mlp_tc_fwd_kernel<true>, grid, NUM_THREADS, smem, stream, a);
+  else NERFB_LAUNCH(mlp_tc_fwd_kernel<false>, grid, NUM_THREADS, smem, stream, a);
   return NERFB_OK;
 }
 

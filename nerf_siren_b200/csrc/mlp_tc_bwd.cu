@@ -524,7 +524,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
 }  // namespace
 
 bool tc_bwd_supported(const nerfb_mlp_desc& d) {
-  if (!tc_supported(d, 0)) return false;
+  if (!tc_supported(d, 0) || d.kind != NERFB_KIND_NERF) return false;      // SIREN: tcgen05 arm is forward-only
   int skips = 0;
   for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
   return d.D + skips + 5 <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;

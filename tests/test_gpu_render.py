@@ -161,6 +161,31 @@ def test_siren_module(prec, tag):
         assert abs(float(p.grad.double().norm()) - ref_norm) <= gtol * ref_norm + 1e-7, k
 
 
+@pytest.mark.parametrize("tag", ["zero", "rand"])
+def test_siren_module_tensor_core_forward(tag):
+    """SIREN on the tcgen05 arm (forward only): bf16 operands, fp32 accumulate, sin epilogue, hi/lo-split first layer.
+    Tolerance 3e-2 absolute on O(1) outputs (sigmoid rgb, sigma ~ +-0.1) against the fp32 reference fixture."""
+    _set("bf16")
+    g = gold("g4_siren_" + tag)
+    m = _load(nb().SemanticNeRF, O.siren_init(seed=7))
+    assert nb().ops.mlp_supported(m._desc(), nb()._lib.PREC_BF16, False)
+    with torch.no_grad():
+        y = m.forward_with_frequencies_phase_shifts(g["pts"].to(DEV), g["freq"].to(DEV), g["phase"].to(DEV), g["dirs"].to(DEV))
+    assert y.shape == (1, 96, 4)
+    err = (y.cpu() - g["y"]).abs()
+    assert err.max().item() <= 3e-2, err.max().item()
+    # many tiles, ragged tail, against the oracle: mean error far below the max bound
+    ps = O.siren_init(seed=7)
+    gen = torch.Generator().manual_seed(4)
+    pts = (torch.rand(1, 3000, 3, generator=gen) * 2 - 1) * 6
+    dirs = torch.nn.functional.normalize(torch.randn(1, 3000, 3, generator=gen), dim=-1)
+    ref = O.siren_mlp(ps, pts, g["freq"], g["phase"], dirs)
+    with torch.no_grad():
+        y = m.forward_with_frequencies_phase_shifts(pts.to(DEV), g["freq"].to(DEV), g["phase"].to(DEV), dirs.to(DEV))
+    err = (y.cpu() - ref).abs()
+    assert err.max().item() <= 3e-2 and err.mean().item() <= 3e-3, (err.max().item(), err.mean().item())
+
+
 def _models_for(name):
     pc, pf = case_params(name)
     if name == "llff_cls":

@@ -292,11 +292,31 @@ struct WItem {
 };
 struct WgradArgs {
   int n_items; WItem item[MAX_ITEMS];
+  int64_t item_off[MAX_ITEMS + 1];     // prefix sums of cost_i * n_tiles: the linearised (item, tile) work space
   const uint8_t* fwd_rec; const uint8_t* bwd_rec; int fwd_tile_bytes, bwd_tile_bytes;
   int64_t n_tiles; int n_active;
-  float* partial; int64_t partial_stride;
+  float* partial;                      // [n_active + n_items slots][256 x 256] dense per-item partials
   float* grad;
 };
+constexpr int64_t W_SLOT = 256 * 256;  // floats per partial slot
+
+// Work split: the (item, tile) space is linearised with each item weighted by the bytes it streams per tile
+// (cost = nM + nN blocks) and cut into n_active equal pieces, so a CTA owns ONE long K-range of one weight matrix
+// (sometimes the tail of one and the head of the next) instead of a short range of all 16: 148 x 16 accumulator
+// flushes and 352 MB of partials become ~160 flushes and 40 MB.  Tiles [t0, t1) of item i that CTA c owns:
+__host__ __device__ inline int item_cost(const WItem& im) { return im.nM + im.nN; }
+__host__ __device__ inline int64_t seg_tile(int64_t x, int64_t off, int cost, int64_t n_tiles) {
+  if (x <= off) return 0;
+  const int64_t t = (x - off + cost - 1) / cost;
+  return t < n_tiles ? t : n_tiles;
+}
+__host__ __device__ inline void seg_range(const WgradArgs& a, int c, int i, int64_t& t0, int64_t& t1) {
+  const int64_t total = a.item_off[a.n_items];
+  const int64_t lo = total * c / a.n_active, hi = total * (c + 1) / a.n_active;
+  const int cost = item_cost(a.item[i]);
+  t0 = seg_tile(lo, a.item_off[i], cost, a.n_tiles);
+  t1 = seg_tile(hi, a.item_off[i], cost, a.n_tiles);
+}
 
 struct __align__(1024) SmemW {
   uint8_t stage[W_STAGES][W_STAGE_BYTES];
@@ -309,8 +329,15 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
   extern __shared__ uint8_t smem_raw[];
   SmemW& sm = *reinterpret_cast<SmemW*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t t0 = args.n_tiles * blockIdx.x / args.n_active, t1 = args.n_tiles * (blockIdx.x + 1) / args.n_active;
-  const int n_chunks = (int)(t1 - t0) * 2;
+  // the items this CTA touches: [it_lo, it_hi]
+  int it_lo = 0, it_hi = -1;
+  {
+    const int64_t total = args.item_off[args.n_items];
+    const int64_t lo = total * blockIdx.x / args.n_active, hi = total * (blockIdx.x + 1) / args.n_active;
+    while (it_lo + 1 < args.n_items && args.item_off[it_lo + 1] <= lo) ++it_lo;
+    it_hi = it_lo;
+    while (it_hi + 1 < args.n_items && args.item_off[it_hi + 1] < hi) ++it_hi;
+  }
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < W_STAGES; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 5); }
@@ -326,8 +353,10 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
   if (warp == 0) {
     if (lane == 0) {                         // ===== producer: 64-sample halves of the dZ and input blocks =====
       int st = 0; uint32_t ph = 0;
-      for (int it = 0; it < args.n_items; ++it) {
+      for (int it = it_lo; it <= it_hi; ++it) {
         const WItem& im = args.item[it];
+        int64_t t0, t1; seg_range(args, blockIdx.x, it, t0, t1);
+        const int n_chunks = (int)(t1 - t0) * 2;
         const uint8_t* abase = im.a_fwd ? args.fwd_rec : args.bwd_rec;
         const int64_t astride = im.a_fwd ? args.fwd_tile_bytes : args.bwd_tile_bytes;
         for (int c = 0; c < n_chunks; ++c) {
@@ -345,10 +374,12 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
   } else if (warp == 1) {
     if (lane == 0) {                         // ===== MMA issuer =====
       int st = 0; uint32_t ph = 0, free_ph = 0;
-      for (int it = 0; it < args.n_items; ++it) {
+      for (int it = it_lo; it <= it_hi; ++it) {
         const WItem& im = args.item[it];
+        int64_t t0, t1; seg_range(args, blockIdx.x, it, t0, t1);
+        const int n_chunks = (int)(t1 - t0) * 2;
         const uint32_t idesc = umma_idesc_bf16(128, im.N, 1, 1);
-        if (it > 0) { mbar_wait(&sm.acc_free, free_ph); free_ph ^= 1; tc_fence_after(); }
+        if (it > it_lo) { mbar_wait(&sm.acc_free, free_ph); free_ph ^= 1; tc_fence_after(); }
         for (int c = 0; c < n_chunks; ++c) {
           mbar_wait(&sm.full[st], ph);
           tc_fence_after();
@@ -369,9 +400,11 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
     const int q = warp & 3, bt = (warp - 2) * 32 + lane;
     const int blk = bt >> 5, c2 = bt & 31;
     int st = 0; uint32_t ph = 0, done_ph = 0;
-    float* part = args.partial + (int64_t)blockIdx.x * args.partial_stride;
-    for (int it = 0; it < args.n_items; ++it) {
+    for (int it = it_lo; it <= it_hi; ++it) {
       const WItem& im = args.item[it];
+      int64_t t0, t1; seg_range(args, blockIdx.x, it, t0, t1);
+      const int n_chunks = (int)(t1 - t0) * 2;
+      float* part = args.partial + (int64_t)(blockIdx.x + it) * W_SLOT;      // slot (c, i) -> c + i is unique
       float b0 = 0.f, b1 = 0.f;
       const bool sum_here = im.bias_off >= 0 && blk < im.nM;
       for (int c = 0; c < n_chunks; ++c) {
@@ -402,15 +435,18 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
       for (int mh = 0; mh < (im.nM >> 1); ++mh) {
         const int m = mh * 128 + q * 32 + lane;
         if (mh * 128 + q * 32 >= im.m_hi || mh * 128 + q * 32 + 32 <= im.m_lo) continue;      // warp-uniform
-        float* dst = part + im.w_off + (int64_t)m * im.ld + im.col0;
-        const bool real = m >= im.m_lo && m < im.m_hi;
+        float* dst = part + (int64_t)m * 256;
+        const bool real = m >= im.m_lo && m < im.m_hi && n_chunks > 0;
         for (int c0 = 0; c0 < im.N; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(mh * 256 + c0), v);
           tmem_ld_wait();
+          if (real && c0 < im.nvalid) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (real && c0 + i < im.nvalid) dst[c0 + i] = __uint_as_float(v[i]);
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                                                                    __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+          }
         }
       }
       tc_fence_before();
@@ -424,16 +460,23 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
 }
 
 // grad[w_off + r * ld + col0 + n] += sum over the active CTAs' partials
-struct ReduceArgs { int n_items; WItem item[MAX_ITEMS]; int n_active; const float* partial; int64_t partial_stride; float* grad; };
-__global__ void __launch_bounds__(256) reduce_partials_kernel(ReduceArgs ra) {
-  const WItem im = ra.item[blockIdx.x];
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const __grid_constant__ WgradArgs ra) {
+  const int it = blockIdx.x;
+  const WItem& im = ra.item[it];
+  __shared__ int s_c[NERFB_SM_COUNT + 1];
+  __shared__ int s_n;
+  if (threadIdx.x == 0) {                    // the CTAs that own a non-empty tile range of this item
+    int n = 0;
+    for (int c = 0; c < ra.n_active; ++c) { int64_t t0, t1; seg_range(ra, c, it, t0, t1); if (t1 > t0) s_c[n++] = c; }
+    s_n = n;
+  }
+  __syncthreads();
   const int total = (im.m_hi - im.m_lo) * im.nvalid;
   for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < total; e += gridDim.y * blockDim.x) {
     const int r = im.m_lo + e / im.nvalid, n = e % im.nvalid;
-    const int64_t idx = im.w_off + (int64_t)r * im.ld + im.col0 + n;
     float s = 0.f;
-    for (int c = 0; c < ra.n_active; ++c) s += ra.partial[(int64_t)c * ra.partial_stride + idx];
-    ra.grad[idx] += s;
+    for (int k = 0; k < s_n; ++k) s += ra.partial[(int64_t)(s_c[k] + it) * W_SLOT + r * 256 + n];
+    ra.grad[im.w_off + (int64_t)r * im.ld + im.col0 + n] += s;
   }
 }
 
@@ -507,7 +550,8 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   pl.n_active = (int)(pl.n_tiles < NERFB_SM_COUNT ? pl.n_tiles : NERFB_SM_COUNT);
   pl.param_count = o.total;
   wg.fwd_tile_bytes = pg.fwd_tile_bytes; wg.bwd_tile_bytes = pg.bwd_tile_bytes; wg.n_tiles = pl.n_tiles; wg.n_active = pl.n_active;
-  wg.partial_stride = round_up64(o.total, 32);
+  wg.item_off[0] = 0;
+  for (int i = 0; i < ni; ++i) wg.item_off[i + 1] = wg.item_off[i] + (int64_t)item_cost(wg.item[i]) * pl.n_tiles;
   HeadArgs& h = pl.head;
   h.fwd_tile_bytes = pg.fwd_tile_bytes; h.hD_off = L.step_save_off[D - 1]; h.hd_off = L.step_save_off[D + 1];
   h.P = P; h.n_tiles = pl.n_tiles; h.n_active = pl.n_active;
@@ -516,7 +560,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   pl.off_wblob = off;   off += round_up64(wb, 1024);
   pl.off_heads = off;   off += 4096;
   pl.off_rec = off;     off += pl.n_tiles * (int64_t)pg.bwd_tile_bytes;
-  pl.off_partial = off; off += (int64_t)pl.n_active * wg.partial_stride * 4;
+  pl.off_partial = off; off += (int64_t)(pl.n_active + MAX_ITEMS) * W_SLOT * 4;
   pl.total = round_up64(off, 1024);
   return pl;
 }
@@ -564,10 +608,6 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   pl.wg.partial = reinterpret_cast<float*>(bb + pl.off_partial); pl.wg.grad = grad;
   NERFB_LAUNCH(mlp_tc_wgrad_kernel, pl.n_active, W_THREADS, smem_w, stream, pl.wg);
 
-  ReduceArgs ra{};
-  ra.n_items = pl.wg.n_items;
-  for (int i = 0; i < ra.n_items; ++i) ra.item[i] = pl.wg.item[i];
-  ra.n_active = pl.n_active; ra.partial = pl.wg.partial; ra.partial_stride = pl.wg.partial_stride; ra.grad = grad;
-  NERFB_LAUNCH(reduce_partials_kernel, dim3(ra.n_items, 32), 256, 0, stream, ra);
+  NERFB_LAUNCH(reduce_partials_kernel, dim3(pl.wg.n_items, 32), 256, 0, stream, pl.wg);
   return NERFB_OK;
 }

@@ -293,32 +293,42 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
     }
   } else if (warp == WARP_STORE) {
     // ===== store lane: published blocks -> the tile's record in HBM (training only) =====
+    // Up to 3 bulk stores stay in flight: after committing store k the lane waits only until store k-2 has been READ out
+    // of shared memory and releases that one's buffer (a_free / x_stored), so the ~1 us store latency is pipelined instead
+    // of serialising the 40 stores of a tile.  The release order is the issue order, which is also the order in which the
+    // epilogue / encoder need the buffers back, so the lag cannot deadlock (a buffer is needed again a whole layer later).
     if (lane == 0 && saving) {
       uint32_t a_par[4] = {0, 0, 0, 0}, s_par[2] = {0, 0}, xr_par[2] = {0, 0};
       uint32_t it = 0;
+      uint32_t pend[2] = {0u, 0u};              // barrier addresses of the two stores still unreleased (0 = none)
+      auto issued = [&](uint32_t bar) {         // store k committed: release store k-2
+        bulk_commit(); bulk_wait_read2();
+        if (pend[0]) mbar_arrive_addr(pend[0]);
+        pend[0] = pend[1]; pend[1] = bar;
+      };
       for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x, ++it) {
         const int b = it & 1;
         uint8_t* rec = args.save + tile * (int64_t)pg.tile_save_bytes;
         mbar_wait_relaxed(&sm.x_ready[b], xr_par[b]); xr_par[b] ^= 1;
-        bulk_s2g(rec + pg.save_x_off, sm.x[b], BLK_BYTES); bulk_commit(); bulk_wait_read0();
-        mbar_arrive(&sm.x_stored[b]);
+        bulk_s2g(rec + pg.save_x_off, sm.x[b], BLK_BYTES); issued(smem_u32(&sm.x_stored[b]));
         for (int s = 0; s < pg.n_steps; ++s) {
           const TcStep& st = pg.s[s];
           for (int j = 0; j < st.out_blocks; ++j) {
             if (st.store_only) { mbar_wait_relaxed(&sm.s_ready[j], s_par[j]); s_par[j] ^= 1; }
             else { mbar_wait_relaxed(&sm.a_ready[j], a_par[j]); a_par[j] ^= 1; }
             if (st.save_off >= 0) {
-              bulk_s2g(rec + st.save_off + j * BLK_BYTES, sm.a[j], BLK_BYTES); bulk_commit(); bulk_wait_read0();
-              mbar_arrive(&sm.a_free[j]);
+              bulk_s2g(rec + st.save_off + j * BLK_BYTES, sm.a[j], BLK_BYTES); issued(smem_u32(&sm.a_free[j]));
             }
           }
         }
         if (!pg.sigma_only) {
           mbar_wait_relaxed(&sm.x_ready[b], xr_par[b]); xr_par[b] ^= 1;
-          bulk_s2g(rec + pg.save_dir_off, sm.x[b], BLK_BYTES); bulk_commit(); bulk_wait_read0();
-          mbar_arrive(&sm.x_stored[b]);
+          bulk_s2g(rec + pg.save_dir_off, sm.x[b], BLK_BYTES); issued(smem_u32(&sm.x_stored[b]));
         }
       }
+      bulk_wait_read0();
+      if (pend[0]) mbar_arrive_addr(pend[0]);
+      if (pend[1]) mbar_arrive_addr(pend[1]);
       bulk_wait_all0();
     }
   } else if (warp >= WARP_ENC0 && warp < WARP_EPI0) {

@@ -58,6 +58,7 @@ struct TcStep {
   int save_off;        // byte offset of this step's output blocks in the tile's saved record (-1 = not saved)
   int store_only;      // the output blocks feed no later MMA (saved for the backward only): published on s_ready
   int film;            // SIREN: FiLM layer index of this step's frequency / phase vectors
+  int mask_off;        // byte offset of this step's ReLU gate bit-mask (128 rows x 32 B) in the tile's record, -1 = none
 };
 
 constexpr int MAX_OPS = 64;
@@ -114,6 +115,7 @@ struct __align__(1024) Smem {
   uint32_t tmem_base;
   uint4 ops[2][MAX_OPS];                 // per X buffer: {A descriptor low word, barrier address, flags, parity bit}
   uint32_t step_word[MAX_STEPS], step_bias[MAX_STEPS];
+  int step_mask[MAX_STEPS];
 };
 
 static_assert(sizeof(Smem) + 1024 <= 232448, "shared memory budget (227 KB per CTA)");
@@ -212,7 +214,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
     o.z = w;
     sm.ops[b][i] = o;
   }
-  if (threadIdx.x < pg.n_steps) { sm.step_word[threadIdx.x] = pg.step_word[threadIdx.x]; sm.step_bias[threadIdx.x] = (uint32_t)pg.s[threadIdx.x].bias_off; }
+  if (threadIdx.x < pg.n_steps) { sm.step_word[threadIdx.x] = pg.step_word[threadIdx.x]; sm.step_bias[threadIdx.x] = (uint32_t)pg.s[threadIdx.x].bias_off; sm.step_mask[threadIdx.x] = pg.s[threadIdx.x].mask_off; }
   if (threadIdx.x == 0) {
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
     for (int i = 0; i < 4; ++i) { mbar_init(&sm.a_ready[i], N_EPI_WARPS); mbar_init(&sm.a_free[i], 1); }
@@ -408,6 +410,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         tc_fence_after();
         NERFB_TRACE(const bool tr = args.trace && blockIdx.x == 0 && gs < 40 && lane == 0 && q == 0 && c4 == 0; if (tr) args.trace[gs * 32 + 20] = clock64();)
         float head_acc[3] = {0.f, 0.f, 0.f};
+        uint32_t gate_lo = 0u, gate_hi = 0u;       // ReLU gates of this thread's 4 x 16 columns, for the dgrad kernel
         uint32_t v[2][16];
         tmem_ld16(t_lane + a * 256u, v[0]);
 #pragma unroll
@@ -472,11 +475,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
               }
               const uint32_t blk = smem_u32(sm.a[0]) + (uint32_t)j * BLK_BYTES + row_off;
               if (st_relu) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) pk[i] = pack_bf16_relu(f[2 * i], f[2 * i + 1]);
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch)
-                  sts128(blk + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4), pack_bf16_relu(f[8 * ch + 0], f[8 * ch + 1]),
-                         pack_bf16_relu(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16_relu(f[8 * ch + 4], f[8 * ch + 5]),
-                         pack_bf16_relu(f[8 * ch + 6], f[8 * ch + 7]));
+                  sts128(blk + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4), pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+                if (st_saved) {                  // gate bit = the stored bf16 activation is non-zero (same rule the dgrad used to apply)
+                  uint32_t m = 0u;
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    const uint32_t ne = __vsetne2(pk[i], 0u);          // 0x0001 per non-zero half
+                    m |= ((ne & 1u) | ((ne >> 15) & 2u)) << (2 * i);
+                  }
+                  if (j < 2) gate_lo |= m << (16 * j); else gate_hi |= m << (16 * (j - 2));
+                }
               } else {
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch)
@@ -494,6 +507,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             if (j < st_out && lane == 0) mbar_arrive_addr(ready + 8u * (uint32_t)j);
             NERFB_TRACE(if (tr && j < 2) args.trace[gs * 32 + 24 + j] = clock64();)
           }
+        }
+        if (st_saved && st_relu) {
+          const int mo = sm.step_mask[s];
+          if (mo >= 0)
+            *reinterpret_cast<uint2*>(args.save + tile * (int64_t)pg.tile_save_bytes + mo + row * 32 + c4 * 8) = make_uint2(gate_lo, gate_hi);
         }
         if (st_head == 1) {       // combine the two groups' partial dot products
           sm.part[c4][0][row] = head_acc[0];
@@ -617,7 +635,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     for (int i = 0; i < d.D; ++i) {
       TcStep& st = pg.s[ns++];
       st = TcStep{};
-      st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1;
+      st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1; st.mask_off = -1;
       if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], 3, 0, 3, 256, 1); }
       else for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], 256, 64 * j, 64, 256); }
       st.bias_off = add_bias(o.b[i], 256, i);
@@ -625,7 +643,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     }
     if (!sigma_only) {
       TcStep& cl = pg.s[ns++]; cl = TcStep{};
-      cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = 0; cl.film = d.D; cl.save_off = -1;
+      cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = 0; cl.film = d.D; cl.save_off = -1; cl.mask_off = -1;
       for (int j = 0; j < 4; ++j) { cl.src[cl.n_kb++] = j; add_slab(o.w_dir, 259, 3 + 64 * j, 64, 256); }
       cl.src[cl.n_kb++] = SRC_X; cl.wait_x = 1; cl.x_done = 1; add_slab(o.w_dir, 259, 0, 3, 256, 1);
       cl.bias_off = add_bias(o.b_dir, 256, d.D);
@@ -643,9 +661,9 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
       for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], o.in[i], c0 + 64 * j, 64, 256); }
     }
     st.bias_off = add_bias(o.b[i], 256);
-    st.save_off = -1;
-    if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; }
-    if (sigma_only && i == d.D - 1) { st.out_blocks = 0; st.save_off = -1; }
+    st.save_off = -1; st.mask_off = -1;
+    if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; st.mask_off = sv; sv += TILE_M * 32; }
+    if (sigma_only && i == d.D - 1) { st.out_blocks = 0; st.save_off = -1; st.mask_off = -1; }
   }
   pg.s[last_x_reader].x_done = 1;
   if (!sigma_only && !siren) {
@@ -653,15 +671,15 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     fin.N = 256; fin.relu = 0; fin.out_blocks = 4;
     for (int j = 0; j < 4; ++j) { fin.src[fin.n_kb++] = j; add_slab(o.w_final, 256, 64 * j, 64, 256); }
     fin.bias_off = add_bias(o.b_final, 256);
-    fin.save_off = -1;
+    fin.save_off = -1; fin.mask_off = -1;
     if (save) { fin.save_off = sv; sv += 4 * BLK_BYTES; }
     TcStep& dr = pg.s[ns++]; dr = TcStep{};
     dr.N = 128; dr.relu = 1; dr.head = 2; dr.out_blocks = save ? 2 : 0; dr.store_only = 1;
     for (int j = 0; j < 4; ++j) { dr.src[dr.n_kb++] = j; add_slab(o.w_dir, 256 + o.in_dir, 64 * j, 64, 128); }
     dr.src[dr.n_kb++] = SRC_X; dr.wait_x = 1; dr.x_done = 1; add_slab(o.w_dir, 256 + o.in_dir, 256, o.in_dir, 128);
     dr.bias_off = add_bias(o.b_dir, 128);
-    dr.save_off = -1;
-    if (save) { dr.save_off = sv; sv += 2 * BLK_BYTES; pg.save_dir_off = sv; sv += BLK_BYTES; }
+    dr.save_off = -1; dr.mask_off = -1;
+    if (save) { dr.save_off = sv; sv += 2 * BLK_BYTES; dr.mask_off = sv; sv += TILE_M * 32; pg.save_dir_off = sv; sv += BLK_BYTES; }
   }
   pg.n_steps = ns; pg.n_bias = nb;
   pg.n_ops = 0;
@@ -750,7 +768,7 @@ TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P) {
   const TcPlan pl = tc_plan(d, P, false, true);
   TcFwdLayout L{};
   L.n_steps = pl.prog.n_steps;
-  for (int s = 0; s < pl.prog.n_steps; ++s) L.step_save_off[s] = pl.prog.s[s].save_off;
+  for (int s = 0; s < pl.prog.n_steps; ++s) { L.step_save_off[s] = pl.prog.s[s].save_off; L.step_mask_off[s] = pl.prog.s[s].mask_off; }
   L.save_x_off = pl.prog.save_x_off; L.save_dir_off = pl.prog.save_dir_off;
   L.tile_save_bytes = pl.prog.tile_save_bytes;
   L.off_save = pl.off_save; L.total = round_up64(pl.total, 1024);

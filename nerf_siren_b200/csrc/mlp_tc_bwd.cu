@@ -24,8 +24,10 @@ namespace {
 
 constexpr int N_STAGES = 4;
 constexpr int STAGE_BYTES = 256 * 128;
-constexpr int NUM_THREADS = 320;
-constexpr int EPI_THREADS = 256;
+// dgrad warp roles (same plan as the forward kernel: mostly-waiting roles get the low warp ids)
+constexpr int D_WARP_PRODUCER = 0, D_WARP_STORE = 1, D_WARP_EPI0 = 2, D_WARP_MMA = 18;
+constexpr int NUM_THREADS = 19 * 32;
+constexpr int D_EPI_WARPS = 16;
 constexpr int MAX_BSTEPS = 12;
 
 // ---- weight packing for the dgrad chain: slab (n, kk) = W[(row0 + kk) * ld + col0 + n]  (W^T, K-major) -----------
@@ -52,14 +54,14 @@ __global__ void __launch_bounds__(256) pack_weights_t_kernel(const float* __rest
 // ---- dgrad chain program -------------------------------------------------------------------------------------------
 struct BStep {
   int n_kb;          // K-blocks (64 upstream features each) of this step's A operand = blocks 0..n_kb-1
-  int mask_off;      // forward-record offset of the activation whose sign gates this step's output (-1: no gate)
+  int mask_off;      // forward-record offset of the gate bit-mask (128 rows x 32 B) of this step's output (-1: no gate)
   int add_sigma;     // output += d_sigma (x) w_sigma before gating (the sigma head reads the same activation)
   int save_off;      // backward-record offset of this step's output dZ (4 blocks)
 };
 struct BProgram {
   int n_steps;
   BStep s[MAX_BSTEPS];
-  int hd_off;        // forward-record offset of the direction layer's activations (2 blocks), gate of dZ_dir
+  int hd_off;        // forward-record offset of the direction layer's gate bit-mask, gate of dZ_dir
   int dzdir_off;     // backward-record offset of dZ_dir (2 blocks)
   int h_off;         // backward-record offset of the head block: columns 0..3 = [g_r g_g g_b d_sigma] per sample
   int fwd_tile_bytes, bwd_tile_bytes;
@@ -80,7 +82,8 @@ struct __align__(1024) SmemD {
   float w_sigma[256];
   float w_rgb[3 * 128];
   uint64_t w_full[N_STAGES], w_empty[N_STAGES];
-  uint64_t a_ready[4];
+  uint64_t a_ready[4];                   // block j holds a freshly written dZ block (16 epilogue warps arrive)
+  uint64_t g_free[4];                    // the store lane has read block j out to HBM
   uint64_t acc_full[2];
   uint32_t tmem_base;
 };
@@ -89,62 +92,51 @@ struct __align__(1024) SmemD {
 
 namespace {
 
-// 32 bf16 gate values (this thread's row, 32 consecutive columns) of a saved [128 x 64] block: 4 x 16 B
-__device__ __forceinline__ void load_gate(const uint8_t* blk, int row, int h, uint4 (&m)[4]) {
+// 16 gate bits -> zero the gated-off values
+__device__ __forceinline__ void apply_gate16(float (&f)[16], uint32_t bits) {
 #pragma unroll
-  for (int ch = 0; ch < 4; ++ch)
-    m[ch] = __ldg(reinterpret_cast<const uint4*>(blk + (uint32_t)row * 128u + ((((uint32_t)(4 * h + ch)) ^ ((uint32_t)row & 7u)) << 4)));
+  for (int i = 0; i < 16; ++i) f[i] = ((bits >> i) & 1u) ? f[i] : 0.f;
 }
-__device__ __forceinline__ void apply_gate(float (&f)[32], const uint4 (&m)[4]) {
+// this thread's 16 columns (chunks 2*c4, 2*c4+1) of row `row` of a [128 x 64] swizzled bf16 block
+__device__ __forceinline__ void store_block16(uint32_t blk, uint32_t row_off, uint32_t row_x, int c4, const float (&f)[16]) {
 #pragma unroll
-  for (int ch = 0; ch < 4; ++ch) {
-    const uint32_t w[4] = {m[ch].x, m[ch].y, m[ch].z, m[ch].w};
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {              // post-ReLU activations are >= +0: "h > 0" == "bits != 0"
-      if ((w[e] & 0xFFFFu) == 0u) f[8 * ch + 2 * e] = 0.f;
-      if ((w[e] >> 16) == 0u) f[8 * ch + 2 * e + 1] = 0.f;
-    }
-  }
-}
-__device__ __forceinline__ void store_block_row(uint32_t blk, int row, int h, const float (&f)[32]) {
-#pragma unroll
-  for (int ch = 0; ch < 4; ++ch) {
-    const uint32_t addr = blk + (uint32_t)row * 128u + ((((uint32_t)(4 * h + ch)) ^ ((uint32_t)row & 7u)) << 4);
-    sts128(addr, pack_bf16(f[8 * ch + 0], f[8 * ch + 1]), pack_bf16(f[8 * ch + 2], f[8 * ch + 3]),
-           pack_bf16(f[8 * ch + 4], f[8 * ch + 5]), pack_bf16(f[8 * ch + 6], f[8 * ch + 7]));
-  }
+  for (int ch = 0; ch < 2; ++ch)
+    sts128(blk + row_off + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4), pack_bf16(f[8 * ch + 0], f[8 * ch + 1]),
+           pack_bf16(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16(f[8 * ch + 4], f[8 * ch + 5]), pack_bf16(f[8 * ch + 6], f[8 * ch + 7]));
 }
 
+// v2: 16 epilogue warps (32 rows x 16 columns of every 64-column block each, double-buffered TMEM loads), ReLU gates
+// from the forward's bit-masks (8 B per thread per layer instead of the 64 KB activation image), the dZ stores on their
+// own lane with lagged buffer release, and an MMA thread that only waits and issues.
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __grid_constant__ DgradArgs args) {
-  extern __shared__ uint8_t smem_raw[];
-  SmemD& sm = *reinterpret_cast<SmemD*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  SmemD& sm = *reinterpret_cast<SmemD*>(smem_raw);
+  if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
   const BProgram& pg = args.prog;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __shared__ uint64_t g_free;
 
   for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.heads + i);
   for (int i = threadIdx.x; i < 384; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.heads + 256 + i);
   if (threadIdx.x == 0) {
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
-    for (int i = 0; i < 4; ++i) mbar_init(&sm.a_ready[i], 8);
+    for (int i = 0; i < 4; ++i) { mbar_init(&sm.a_ready[i], D_EPI_WARPS); mbar_init(&sm.g_free[i], 1); }
     mbar_init(&sm.acc_full[0], 1); mbar_init(&sm.acc_full[1], 1);
-    mbar_init(&g_free, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
+  if (warp == D_WARP_MMA) tmem_alloc(&sm.tmem_base, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sm.tmem_base;
 
-  if (warp == 0) {
+  if (warp == D_WARP_PRODUCER) {
     if (lane == 0) {                       // ===== weight producer: W^T slabs, 32 KB each =====
       int stage = 0; uint32_t phase = 0;
       for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
         const uint8_t* src = args.wblob;
         for (int s = 0; s < pg.n_steps; ++s)
           for (int kb = 0; kb < pg.s[s].n_kb; ++kb) {
-            mbar_wait(&sm.w_empty[stage], phase ^ 1);
+            mbar_wait_relaxed(&sm.w_empty[stage], phase ^ 1);
             mbar_expect_tx(&sm.w_full[stage], STAGE_BYTES);
             bulk_g2s(sm.ring[stage], src, STAGE_BYTES, &sm.w_full[stage]);
             src += STAGE_BYTES;
@@ -152,55 +144,73 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
           }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == D_WARP_MMA) {
     if (lane == 0) {                       // ===== MMA issuer =====
-      int stage = 0; uint32_t phase = 0;
-      uint32_t a_phase[4] = {0, 0, 0, 0};
-      uint32_t gs = 0;
+      uint32_t stage = 0, phase = 0, a_par = 0, gs = 0;
       const uint32_t idesc = umma_idesc_bf16(TILE_M, 256);
+      const uint32_t g_lo0 = ((smem_u32(sm.g[0]) >> 4) & 0x3FFFu) | (1u << 16);
+      const uint32_t ring_lo0 = ((smem_u32(sm.ring[0]) >> 4) & 0x3FFFu) | (1u << 16);
+      const uint32_t ar0 = smem_u32(&sm.a_ready[0]), wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]);
+      const uint32_t af0 = smem_u32(&sm.acc_full[0]);
       for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
-        uint8_t* rec = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes;
         for (int s = 0; s < pg.n_steps; ++s, ++gs) {
-          const BStep& st = pg.s[s];
-          const uint32_t d_tmem = tmem + (gs & 1) * 256;
-          const int in_off = (s == 0) ? pg.dzdir_off : pg.s[s - 1].save_off;
-          for (int kb = 0; kb < st.n_kb; ++kb) {
-            mbar_wait(&sm.a_ready[kb], a_phase[kb]); a_phase[kb] ^= 1;
-            bulk_s2g(rec + in_off + kb * BLK_BYTES, sm.g[kb], BLK_BYTES);        // dZ block -> HBM for the wgrad
-            mbar_wait(&sm.w_full[stage], phase);
+          const int n_kb = pg.s[s].n_kb;
+          for (int kb = 0; kb < n_kb; ++kb) {
+            const bool ok_a = mbar_try_wait_addr(ar0 + 8u * kb, (a_par >> kb) & 1u);
+            const bool ok_w = mbar_try_wait_addr(wf0 + 8u * stage, phase);
+            if (!ok_a) mbar_wait_addr(ar0 + 8u * kb, (a_par >> kb) & 1u);
+            a_par ^= 1u << kb;
+            if (!ok_w) mbar_wait_addr(wf0 + 8u * stage, phase);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(sm.g[kb]), b_addr = smem_u32(sm.ring[stage]);
-#pragma unroll
-            for (int k = 0; k < KBLK / 16; ++k)
-              umma_bf16(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
-                        (kb > 0 || k > 0) ? 1u : 0u);
-            umma_commit(&sm.w_empty[stage]);
+            umma_bf16_k64(tmem + (gs & 1u) * 256u, g_lo0 + (uint32_t)kb * (BLK_BYTES >> 4), ring_lo0 + stage * (STAGE_BYTES >> 4), idesc,
+                          kb > 0 ? 1u : 0u);
+            umma_commit_addr(we0 + 8u * stage);
             if (++stage == N_STAGES) { stage = 0; phase ^= 1; }
           }
-          bulk_commit(); bulk_wait_read0();
-          umma_commit(&sm.acc_full[gs & 1]);
+          umma_commit_addr(af0 + 8u * (gs & 1u));
         }
-        const int last_off = pg.s[pg.n_steps - 1].save_off;
-        for (int j = 0; j < 4; ++j) {
-          mbar_wait(&sm.a_ready[j], a_phase[j]); a_phase[j] ^= 1;
-          bulk_s2g(rec + last_off + j * BLK_BYTES, sm.g[j], BLK_BYTES);
+        for (int j = 0; j < 4; ++j) {           // the last step's output blocks feed no MMA: keep the phase count in step
+          mbar_wait_addr(ar0 + 8u * j, (a_par >> j) & 1u); a_par ^= 1u << j;
         }
-        bulk_commit(); bulk_wait_read0();
-        mbar_arrive(&g_free);                 // the next tile's prologue may overwrite the dZ blocks
       }
+    }
+  } else if (warp == D_WARP_STORE) {
+    if (lane == 0) {                       // ===== store lane: every published dZ block -> HBM for the wgrad =====
+      uint32_t a_par = 0, pend = 0;
+      auto issued = [&](uint32_t bar) {       // store k committed: release the buffer of store k-1 once it has been read
+        bulk_commit(); bulk_wait_read1();
+        if (pend) mbar_arrive_addr(pend);
+        pend = bar;
+      };
+      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+        uint8_t* rec = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes;
+        for (int s = -1; s < pg.n_steps; ++s) {
+          const int nb = s < 0 ? 2 : 4;
+          const int off = s < 0 ? pg.dzdir_off : pg.s[s].save_off;
+          for (int j = 0; j < nb; ++j) {
+            mbar_wait_relaxed(&sm.a_ready[j], (a_par >> j) & 1u); a_par ^= 1u << j;
+            bulk_s2g(rec + off + j * BLK_BYTES, sm.g[j], BLK_BYTES);
+            issued(smem_u32(&sm.g_free[j]));
+          }
+        }
+      }
+      bulk_wait_read0();
+      if (pend) mbar_arrive_addr(pend);
       bulk_wait_all0();
     }
-  } else {
+  } else if (warp >= D_WARP_EPI0 && warp < D_WARP_MMA) {
     // ===== prologue (rgb head + direction-layer gate) and per-step epilogues =====
-    const int ew = warp - 2, q = warp & 3, h = ew >> 2;
+    const int ew = warp - D_WARP_EPI0, q = warp & 3, c4 = ew >> 2;
     const int row = q * 32 + lane;
-    uint32_t acc_phase[2] = {0, 0}, free_phase = 0;
+    const uint32_t row_off = (uint32_t)row * 128u, row_x = (uint32_t)row & 7u;
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + 16u * (uint32_t)c4;
+    const uint32_t g0_addr = smem_u32(sm.g[0]);
+    uint32_t acc_par = 0, gf_par = 0, need_free = 0;
     uint32_t gs = 0;
-    bool first = true;
     for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
       const int64_t p = tile * TILE_M + row;
       const bool live = p < args.P;
-      const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes;
+      const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + row * 32 + c4 * 8;
       float g0 = 0.f, g1 = 0.f, g2 = 0.f, dsig = 0.f;
       if (live) {
         const float4 y = __ldg(reinterpret_cast<const float4*>(args.out + p * 4));
@@ -208,53 +218,57 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         g0 = dy.x * y.x * (1.f - y.x); g1 = dy.y * y.y * (1.f - y.y); g2 = dy.z * y.z * (1.f - y.z);   // sigmoid'
         dsig = dy.w;
       }
-      if (h == 0) {                           // head block for the wgrad kernel: 4 bf16 per sample, rest of the row unused
+      if (c4 == 0) {                          // head block for the wgrad kernel: 4 bf16 per sample, rest of the row unused
         uint2 hw; hw.x = pack_bf16(g0, g1); hw.y = pack_bf16(g2, dsig);
         *reinterpret_cast<uint2*>(args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off + swz_off(row, 0)) = hw;
       }
-      uint4 gate[4];
-      load_gate(frec + pg.hd_off, row, h, gate);
-      if (!first) { mbar_wait(&g_free, free_phase); free_phase ^= 1; }
-      first = false;
-#pragma unroll 1
-      for (int j = 0; j < 2; ++j) {           // dZ_dir = (g . W_rgb) (.) [hd > 0]     (models/nerf.py:119-120)
-        float f[32];
-        const int col0 = 64 * j + 32 * h;
+      uint2 mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
+      for (int j = 0; j < 2; ++j) {           // dZ_dir = (g . W_rgb) (.) [hd > 0]     (models/nerf.py:119-120)
+        float f[16];
+        const int col0 = 64 * j + 16 * c4;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
           f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[128 + col0 + i] + g2 * sm.w_rgb[256 + col0 + i];
-        apply_gate(f, gate);
-        if (j == 0) load_gate(frec + pg.hd_off + BLK_BYTES, row, h, gate);
-        store_block_row(smem_u32(sm.g[j]), row, h, f);
+        apply_gate16(f, (mk.x >> (16 * j)) & 0xFFFFu);
+        if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
+        need_free |= 1u << j;
+        store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.a_ready[j]);
       }
       for (int s = 0; s < pg.n_steps; ++s, ++gs) {
         const BStep& st = pg.s[s];
-        const int a = gs & 1;
+        const uint32_t a = gs & 1u;
         const bool gated = st.mask_off >= 0;
-        if (gated) load_gate(frec + st.mask_off, row, h, gate);
-        mbar_wait(&sm.acc_full[a], acc_phase[a]); acc_phase[a] ^= 1;
+        if (gated) mk = __ldg(reinterpret_cast<const uint2*>(frec + st.mask_off));
+        const bool add_sigma = st.add_sigma != 0;
+        mbar_wait(&sm.acc_full[a], (acc_par >> a) & 1u); acc_par ^= 1u << a;
         tc_fence_after();
-#pragma unroll 1
+        uint32_t v[2][16];
+        tmem_ld16(t_lane + a * 256u, v[0]);
+#pragma unroll
         for (int j = 0; j < 4; ++j) {
-          uint32_t v[32];
-          const int col0 = 64 * j + 32 * h;
-          tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * 256 + col0), v);
+          const int col0 = 64 * j + 16 * c4;
           tmem_ld_wait();
-          float f[32];
+          if (j + 1 < 4) tmem_ld16(t_lane + a * 256u + 64u * (uint32_t)(j + 1), v[(j + 1) & 1]);
+          float f[16];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-          if (st.add_sigma) {                 // sigma = <h8, w_sigma> + b reads the same activation (models/nerf.py:112)
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[j & 1][i]);
+          if (add_sigma) {                    // sigma = <h8, w_sigma> + b reads the same activation (models/nerf.py:112)
+            const uint32_t wb = smem_u32(sm.w_sigma) + (uint32_t)col0 * 4u;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = fmaf(dsig, sm.w_sigma[col0 + i], f[i]);
+            for (int i = 0; i < 4; ++i) {
+              const float4 w = lds128f(wb + 16u * i);
+              f[4 * i] = fmaf(dsig, w.x, f[4 * i]); f[4 * i + 1] = fmaf(dsig, w.y, f[4 * i + 1]);
+              f[4 * i + 2] = fmaf(dsig, w.z, f[4 * i + 2]); f[4 * i + 3] = fmaf(dsig, w.w, f[4 * i + 3]);
+            }
           }
-          if (gated) {
-            apply_gate(f, gate);
-            if (j < 3) load_gate(frec + st.mask_off + (j + 1) * BLK_BYTES, row, h, gate);
-          }
-          store_block_row(smem_u32(sm.g[j]), row, h, f);
+          if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (j & 1))) & 0xFFFFu);
+          if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
+          need_free |= 1u << j;
+          store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);
           fence_proxy_async();
           tc_fence_before();
           __syncwarp();
@@ -265,7 +279,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+  if (warp == D_WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
 }  // namespace
@@ -512,7 +526,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   const int dzdir = 0, dzfin = 2 * BLK_BYTES;
   auto dz_off = [&](int i) { return (6 + 4 * (D - i)) * BLK_BYTES; };          // dZ_i, i = D..1 (grad of trunk step i-1's pre-activation)
   BProgram& pg = pl.prog;
-  pg.hd_off = L.step_save_off[D + 1]; pg.dzdir_off = dzdir;
+  pg.hd_off = L.step_mask_off[D + 1]; pg.dzdir_off = dzdir;
   const int hblk = (6 + 4 * D) * BLK_BYTES;                     // head block (+ one never-written block behind it)
   pg.h_off = hblk;
   pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (8 + 4 * D) * BLK_BYTES;
@@ -521,10 +535,10 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
     for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
   };
   pg.s[ns++] = BStep{2, -1, 0, dzfin};                       slabs(o.w_dir, 256 + o.in_dir, 0, 2);
-  pg.s[ns++] = BStep{4, L.step_save_off[D - 1], 1, dz_off(D)}; slabs(o.w_final, 256, 0, 4);
+  pg.s[ns++] = BStep{4, L.step_mask_off[D - 1], 1, dz_off(D)}; slabs(o.w_final, 256, 0, 4);
   for (int i = D - 1; i >= 1; --i) {
     const bool skip = (d.skip_mask >> i) & 1;
-    pg.s[ns++] = BStep{4, L.step_save_off[i - 1], 0, dz_off(i)};
+    pg.s[ns++] = BStep{4, L.step_mask_off[i - 1], 0, dz_off(i)};
     slabs(o.w[i], o.in[i], skip ? o.in_xyz : 0, 4);
   }
   pg.n_steps = ns; pl.pack.n_slabs = nslab;

@@ -9,7 +9,7 @@
 
 // where the forward kernel parked each tile's activations (byte offsets inside one tile record)
 struct TcFwdLayout {
-  int n_steps; int step_save_off[12]; int save_x_off, save_dir_off; int tile_save_bytes;
+  int n_steps; int step_save_off[12]; int step_mask_off[12]; int save_x_off, save_dir_off; int tile_save_bytes;
   int64_t off_save, total;     // record array offset inside the workspace; end of the forward's workspace part
 };
 
@@ -149,6 +149,7 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint3
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read2() { asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // generic-proxy smem writes -> visible to the async proxy (UMMA operand fetch, bulk stores)

@@ -475,20 +475,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
               }
               const uint32_t blk = smem_u32(sm.a[0]) + (uint32_t)j * BLK_BYTES + row_off;
               if (st_relu) {
-                uint32_t pk[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) pk[i] = pack_bf16_relu(f[2 * i], f[2 * i + 1]);
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch)
-                  sts128(blk + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4), pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
-                if (st_saved) {                  // gate bit = the stored bf16 activation is non-zero (same rule the dgrad used to apply)
-                  uint32_t m = 0u;
+                  sts128(blk + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4), pack_bf16_relu(f[8 * ch + 0], f[8 * ch + 1]),
+                         pack_bf16_relu(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16_relu(f[8 * ch + 4], f[8 * ch + 5]),
+                         pack_bf16_relu(f[8 * ch + 6], f[8 * ch + 7]));
+                if (st_saved) {
+                  // gate mask for the dgrad: ONE funnel shift per element pulls the pre-activation's sign bit in
+                  // (1 = negative = gated off); element i of block j lands at bit 15 - i of its 16-bit field.
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) {
-                    const uint32_t ne = __vsetne2(pk[i], 0u);          // 0x0001 per non-zero half
-                    m |= ((ne & 1u) | ((ne >> 15) & 2u)) << (2 * i);
+                  for (int i = 0; i < 16; ++i) {
+                    if (j < 2) gate_lo = __funnelshift_l(__float_as_uint(f[i]), gate_lo, 1);
+                    else gate_hi = __funnelshift_l(__float_as_uint(f[i]), gate_hi, 1);
                   }
-                  if (j < 2) gate_lo |= m << (16 * j); else gate_hi |= m << (16 * (j - 2));
                 }
               } else {
 #pragma unroll

@@ -92,10 +92,10 @@ struct __align__(1024) SmemD {
 
 namespace {
 
-// 16 gate bits -> zero the gated-off values
+// 16 sign bits of the forward pre-activations (element i at bit 15 - i, 1 = negative): zero the gated-off values
 __device__ __forceinline__ void apply_gate16(float (&f)[16], uint32_t bits) {
 #pragma unroll
-  for (int i = 0; i < 16; ++i) f[i] = ((bits >> i) & 1u) ? f[i] : 0.f;
+  for (int i = 0; i < 16; ++i) f[i] = ((bits >> (15 - i)) & 1u) ? 0.f : f[i];
 }
 // this thread's 16 columns (chunks 2*c4, 2*c4+1) of row `row` of a [128 x 64] swizzled bf16 block
 __device__ __forceinline__ void store_block16(uint32_t blk, uint32_t row_off, uint32_t row_x, int c4, const float (&f)[16]) {
@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
 #pragma unroll
         for (int i = 0; i < 16; ++i)
           f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[128 + col0 + i] + g2 * sm.w_rgb[256 + col0 + i];
-        apply_gate16(f, (mk.x >> (16 * j)) & 0xFFFFu);
+        apply_gate16(f, (mk.x >> (16 * (1 - j))) & 0xFFFFu);      // block 0 was shifted in first: upper half
         if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
         need_free |= 1u << j;
         store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
               f[4 * i + 2] = fmaf(dsig, w.z, f[4 * i + 2]); f[4 * i + 3] = fmaf(dsig, w.w, f[4 * i + 3]);
             }
           }
-          if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (j & 1))) & 0xFFFFu);
+          if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu);
           if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
           need_free |= 1u << j;
           store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);

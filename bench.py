@@ -225,9 +225,13 @@ def kernel_rooflines(nb, trainer, rays, peaks):
         out.append({"kernel": "mlp_tc_bwd (dgrad chain + wgrad)" if tprec == _lib.PREC_BF16 else
                     "sgemm_strided_kernel (fp32 bwd chain)", "bound": "tensor", "achieved": fl / ms / 1e9,
                     "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "ms": ms, "flops": fl})
+    traffic = {}
+    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp))
     for r in out:
         r["frac"] = r["achieved"] / r["peak"]
-        r["traffic"] = None
+        r["traffic"] = traffic.get(r["kernel"])            # DRAM bytes of one launch from the committed ncu capture
         r["peak_source"] = peaks["source"] + (" burst (kernel timed alone)" if r["bound"] == "tensor" else " copy")
     return out
 
@@ -316,7 +320,7 @@ def run_ours(args):
     # the step runs coarse (64 samples) + fine (128 samples): MLP kernels were timed on the fine shape (2/3 of the rows)
     step_tensor_frac = FLOP_TRAIN_PER_RAY * N_RAYS / (ms_per_step * 1e-3) / 1e12 / peaks["bf16_sustained"]
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:           # the CPU baseline is reported at N = 1 only
         v, ms, cores = time_cpu(args.cpu_rays, 3, 1)
         cpu = {"value": v, "unit": "rays/s", "cores": cores, "kind": "port",
                "sample": f"{args.cpu_rays} rays x (64 + 128) samples, fwd+bwd+Adam, 3 timed steps after 1 warm-up "
@@ -362,6 +366,9 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1; the reference arm is meant to use every host core (set before torch loads)
+        for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ[k] = str(os.cpu_count() or 1)
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 and world == 1:

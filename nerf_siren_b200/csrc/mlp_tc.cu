@@ -59,13 +59,14 @@ struct TcStep {
   int store_only;      // the output blocks feed no later MMA (saved for the backward only): published on s_ready
   int film;            // SIREN: FiLM layer index of this step's frequency / phase vectors
   int mask_off;        // byte offset of this step's ReLU gate bit-mask (128 rows x 32 B) in the tile's record, -1 = none
+  int reuse_a;         // the activation blocks were already waited for by the previous step (class head before direction layer)
 };
 
 constexpr int MAX_OPS = 64;
 // One K-block of MMAs, pre-decoded for the issuing thread (indexed parameter-bank loads cost ~100 cycles each on the
 // critical path; the list is copied to shared memory once).  bits: 0 A = X tile, 1 wait before use, 2 first of step,
 // 3 last of step, 4 last reader of X, 5-6 activation block, 7 N = 128
-constexpr uint32_t OP_X = 1u, OP_WAIT = 2u, OP_FIRST = 4u, OP_LAST = 8u, OP_XDONE = 16u, OP_N128 = 128u;
+constexpr uint32_t OP_X = 1u, OP_WAIT = 2u, OP_FIRST = 4u, OP_LAST = 8u, OP_XDONE = 16u, OP_N128 = 128u, OP_N16 = 256u;
 // packed per-step word for the epilogue: N | relu << 9 | out_blocks << 10 | head << 13 | store_only << 15 | saved << 16
 struct TcProgram {
   int n_steps;
@@ -78,6 +79,7 @@ struct TcProgram {
   int tile_save_bytes;             // saved bytes per tile (0 = nothing saved)
   int n_freq_xyz, n_freq_dir, in_xyz, in_dir;
   int sigma_only, out_c;
+  int n_cls;                       // NeRF_3D class head width (models/nerf_cls.py:56-61), 0 = plain NeRF
   int siren, rgb_in;               // rgb head fan-in: 128 (NeRF direction layer) or 256 (SIREN colour layer)
   float xyz_scale;                 // SIREN: UniformBoxWarp 2 / sidelength (models/nerf.py:134-140)
 };
@@ -179,7 +181,7 @@ __device__ __forceinline__ void copy_row(const float* src, int width, uint32_t b
   store_row64(base, row, buf);
 }
 
-template <bool SIREN>
+template <bool SIREN, bool CLS>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid_constant__ TcFwdArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);            // keeps the shared address space: native LDS / STS
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
     } else {
       const uint32_t src = (w >> 5) & 3u;
       o.x = ((smem_u32(sm.a[src]) >> 4) & 0x3FFFu) | (1u << 16);
-      o.y = smem_u32(&sm.a_ready[src]);
+      o.y = (w & OP_WAIT) ? smem_u32(&sm.a_ready[src]) : 0u;      // a second reader of the same blocks does not wait again
       o.w = src;
     }
     if (!o.y) o.w = 31u;                  // no wait: flip a spare parity bit
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
       const uint32_t ring_lo0 = ((smem_u32(sm.ring[0]) >> 4) & 0x3FFFu) | (1u << 16);
       const uint32_t wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]);
       const uint32_t af0 = smem_u32(&sm.acc_full[0]), xc0 = smem_u32(&sm.x_consumed[0]);
-      const uint32_t idesc256 = umma_idesc_bf16(TILE_M, 256), idesc128 = umma_idesc_bf16(TILE_M, 128);
+      const uint32_t idesc256 = umma_idesc_bf16(TILE_M, 256), idesc128 = umma_idesc_bf16(TILE_M, 128), idesc16 = umma_idesc_bf16(TILE_M, 16);
       NERFB_TRACE(int kbi = 0;)
       for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x, ++it) {
         const uint32_t b = it & 1;
@@ -280,7 +282,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
           if (!ok_w) mbar_wait_addr(w_bar, phase);
           tc_fence_after();
           NERFB_TRACE(if (args.trace && blockIdx.x == 0 && gs < 40) args.trace[gs * 32 + kbi * 4 + 2] = clock64();)
-          umma_bf16_k64(tmem + (gs & 1u) * 256u, cur.x, ring_lo0 + stage * (STAGE_BYTES >> 4), (cur.z & OP_N128) ? idesc128 : idesc256,
+          umma_bf16_k64(tmem + (gs & 1u) * 256u, cur.x, ring_lo0 + stage * (STAGE_BYTES >> 4), (cur.z & OP_N16) ? idesc16 : (cur.z & OP_N128) ? idesc128 : idesc256,
                         (cur.z & OP_FIRST) ? 0u : 1u);
           umma_commit_addr(we0 + 8u * stage);            // slab free once these MMAs have read it
           NERFB_TRACE(if (args.trace && blockIdx.x == 0 && gs < 40) args.trace[gs * 32 + kbi * 4 + 3] = clock64(); ++kbi;)
@@ -512,6 +514,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
           if (mo >= 0)
             *reinterpret_cast<uint2*>(args.save + tile * (int64_t)pg.tile_save_bytes + mo + row * 32 + c4 * 8) = make_uint2(gate_lo, gate_hi);
         }
+        if (CLS && st_head == 3) {       // class head (models/nerf_cls.py:104): sigmoid of the merged parse.1 o parse.0 logits, 16-column step
+          tmem_ld_wait();
+          if (c4 == 0 && live) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              if (k < pg.n_cls) args.out[p * pg.out_c + 4 + k] = 1.f / (1.f + __expf(-(__uint_as_float(v[0][k]) + sm.bias[sb + k])));
+          }
+          tc_fence_before();
+        }
         if (st_head == 1) {       // combine the two groups' partial dot products
           sm.part[c4][0][row] = head_acc[0];
           named_bar_sync(1, EPI_THREADS);
@@ -529,7 +540,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             o.y = 1.f / (1.f + __expf(-(sm.part[0][1][row] + sm.part[1][1][row] + sm.part[2][1][row] + sm.part[3][1][row] + sm.b_heads[2])));
             o.z = 1.f / (1.f + __expf(-(sm.part[0][2][row] + sm.part[1][2][row] + sm.part[2][2][row] + sm.part[3][2][row] + sm.b_heads[3])));
             o.w = sm.sigma[row];
-            *reinterpret_cast<float4*>(args.out + p * 4) = o;
+            if (!CLS) *reinterpret_cast<float4*>(args.out + p * 4) = o;
+            else { float* dst = args.out + p * pg.out_c; dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
           }
         }
       }
@@ -544,12 +556,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
 }
 
 // ---- weight packing: fp32 nn.Linear weights -> bf16 slabs in the swizzled shared-memory image, schedule order ----
-struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; };   // W[n*ld + col0 + kk], kk < ncols
+struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; int aux; };   // aux: read the merged class-head matrix, not params   // W[n*ld + col0 + kk], kk < ncols
 // hilo: 3 source columns expanded to 9 K-columns [W_hi W_hi W_lo] (pairs with hilo_row's [x_hi x_lo x_hi])
 struct PackArgs { int n_slabs; PackSlab slab[48]; };
 
-__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params, PackArgs pa, uint8_t* __restrict__ blob) {
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params_in, PackArgs pa, uint8_t* __restrict__ blob,
+                                                           const float* __restrict__ aux) {
   const PackSlab sl = pa.slab[blockIdx.x];
+  const float* params = sl.aux ? aux : params_in;
   for (int idx = threadIdx.x; idx < sl.N * 8; idx += blockDim.x) {       // one 16-byte chunk per iteration
     const int n = idx >> 3, ch = idx & 7;
     float f[8];
@@ -573,14 +587,15 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 }
 
 // bias table: [step biases ...] | w_sigma | b_sigma | w_rgb | b_rgb, gathered from the flat parameter blob
-struct BiasSeg { int64_t src; int n; int dst; int film; };     // film >= 0: FiLM layer whose freq / phase fold into this bias
+struct BiasSeg { int64_t src; int n; int dst; int film; int aux; };     // film >= 0: FiLM layer whose freq / phase fold into this bias
 struct BiasArgs { int n_segs; BiasSeg seg[20]; int film_stride; };
 // film = [freq (L x W) | phase (L x W)]: table = freq * b + phase, scale = freq  (models/nerf.py:149-151)
 __global__ void __launch_bounds__(256) gather_bias_kernel(const float* __restrict__ params, BiasArgs ba, float* __restrict__ table,
-                                                          const float* __restrict__ film, float* __restrict__ scale) {
+                                                          const float* __restrict__ film, float* __restrict__ scale,
+                                                          const float* __restrict__ aux) {
   const BiasSeg sg = ba.seg[blockIdx.x];
   for (int i = threadIdx.x; i < sg.n; i += blockDim.x) {
-    const float b = __ldg(params + sg.src + i);
+    const float b = __ldg((sg.aux ? aux : params) + sg.src + i);
     if (sg.film >= 0 && film) {
       const float fr = __ldg(film + sg.film * sg.n + i), ph = __ldg(film + ba.film_stride + sg.film * sg.n + i);
       table[sg.dst + i] = fmaf(fr, b, ph);
@@ -591,19 +606,39 @@ __global__ void __launch_bounds__(256) gather_bias_kernel(const float* __restric
   }
 }
 
+// NeRF_3D class head (models/nerf_cls.py:56-61,104): parse = Linear(256,512) -> Linear(512,CLS) -> Sigmoid with NO activation
+// between the two Linears, so logits = W_eff feat + b_eff with W_eff = W_p1 W_p0 (CLS x 256), b_eff = W_p1 b_p0 + b_p1.
+// One block per output row k (16 rows, rows >= CLS zero); weff fp32 [16 x 256], beff [16] -> the bias table slot.
+__global__ void __launch_bounds__(256) merge_parse_kernel(const float* __restrict__ params, int64_t w_p0, int64_t b_p0, int64_t w_p1,
+                                                          int64_t b_p1, int n_cls, float* __restrict__ weff, float* __restrict__ beff) {
+  const int k = blockIdx.x, i = threadIdx.x;
+  float acc = 0.f, bacc = 0.f;
+  if (k < n_cls) {
+    for (int j = 0; j < 512; ++j) {
+      const float w1 = __ldg(params + w_p1 + (int64_t)k * 512 + j);
+      acc = fmaf(w1, __ldg(params + w_p0 + (int64_t)j * 256 + i), acc);
+      if (i == 0) bacc = fmaf(w1, __ldg(params + b_p0 + j), bacc);
+    }
+    if (i == 0) bacc += __ldg(params + b_p1 + k);
+  }
+  weff[k * 256 + i] = acc;
+  if (i == 0) beff[k] = bacc;
+}
+
 // ---- host side: program construction, workspace plan, launch ---------------------------------------------------
 struct TcPlan {
   TcProgram prog;
   PackArgs pack;
   BiasArgs bias;
   int64_t wblob_bytes, bias_floats;
-  int64_t off_wblob, off_bias, off_scale, off_save, total;
+  int64_t off_wblob, off_bias, off_scale, off_weff, off_save, total;
+  int cls_bias_off;                // slot of b_eff in the bias table (-1: no class head)
 };
 
 bool tc_supported(const nerfb_mlp_desc& d, int in_mode) {
   (void)in_mode;
   if (d.kind == NERFB_KIND_SIREN) return d.W == 256 && d.D >= 1 && d.D <= 9 && d.box > 0.f;   // forward only, see tc_bwd_supported
-  if (d.kind != NERFB_KIND_NERF || d.W != 256 || d.n_cls != 0) return false;
+  if (d.kind != NERFB_KIND_NERF || d.W != 256 || d.n_cls < 0 || d.n_cls > 8) return false;
   if (d.D < 1 || d.D > 9) return false;
   if (!d.logscale && d.in_xyz <= 0) return false;                 // in-kernel encoding is the power-of-two ladder
   if (nerfb_in_xyz(d) > 64 || nerfb_in_dir(d) > 32) return false;
@@ -617,13 +652,14 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   const NerfOffsets o = nerf_offsets(d);
   TcProgram& pg = pl.prog;
   pg.n_freq_xyz = d.n_freq_xyz; pg.n_freq_dir = d.n_freq_dir; pg.in_xyz = o.in_xyz; pg.in_dir = o.in_dir;
-  pg.sigma_only = sigma_only; pg.out_c = sigma_only ? 1 : 4;
+  pg.sigma_only = sigma_only; pg.out_c = sigma_only ? 1 : 4 + d.n_cls; pg.n_cls = sigma_only ? 0 : d.n_cls;
+  pl.cls_bias_off = -1;
   int64_t wb = 0; int nb = 0, ns = 0, nslab = 0, nseg = 0, sv = 0;
-  auto add_slab = [&](int64_t w_off, int ld, int col0, int ncols, int N, int hilo = 0) {
-    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb, hilo};
+  auto add_slab = [&](int64_t w_off, int ld, int col0, int ncols, int N, int hilo = 0, int aux = 0) {
+    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb, hilo, aux};
     wb += (int64_t)N * 128;
   };
-  auto add_bias = [&](int64_t src, int n, int film = -1) { pl.bias.seg[nseg++] = BiasSeg{src, n, nb, film}; nb += n; return nb - n; };
+  auto add_bias = [&](int64_t src, int n, int film = -1, int aux = 0) { pl.bias.seg[nseg++] = BiasSeg{src, n, nb, film, aux}; nb += n; return nb - n; };
   const bool siren = d.kind == NERFB_KIND_SIREN;
   pg.siren = siren; pg.rgb_in = siren ? 256 : 128; pg.xyz_scale = siren ? 2.0f / d.box : 1.0f;
   pl.bias.film_stride = (d.D + 1) * d.W;
@@ -672,8 +708,15 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     fin.bias_off = add_bias(o.b_final, 256);
     fin.save_off = -1; fin.mask_off = -1;
     if (save) { fin.save_off = sv; sv += 4 * BLK_BYTES; }
+    if (d.n_cls > 0) {      // class-head step: 16 output columns, A = the un-activated xyz_encoding_final blocks
+      TcStep& pc = pg.s[ns++]; pc = TcStep{};
+      pc.N = 16; pc.relu = 0; pc.out_blocks = 0; pc.head = 3; pc.save_off = -1; pc.mask_off = -1;
+      for (int j = 0; j < 4; ++j) { pc.src[pc.n_kb++] = j; add_slab(0, 256, 64 * j, 64, 16, 0, 1); }
+      pc.bias_off = add_bias(16 * 256, 16, -1, 1);                         // b_eff, written by merge_parse_kernel behind W_eff
+      pl.cls_bias_off = pc.bias_off;
+    }
     TcStep& dr = pg.s[ns++]; dr = TcStep{};
-    dr.N = 128; dr.relu = 1; dr.head = 2; dr.out_blocks = save ? 2 : 0; dr.store_only = 1;
+    dr.N = 128; dr.relu = 1; dr.head = 2; dr.out_blocks = save ? 2 : 0; dr.store_only = 1; dr.reuse_a = d.n_cls > 0;
     for (int j = 0; j < 4; ++j) { dr.src[dr.n_kb++] = j; add_slab(o.w_dir, 256 + o.in_dir, 64 * j, 64, 128); }
     dr.src[dr.n_kb++] = SRC_X; dr.wait_x = 1; dr.x_done = 1; add_slab(o.w_dir, 256 + o.in_dir, 256, o.in_dir, 128);
     dr.bias_off = add_bias(o.b_dir, 128);
@@ -687,10 +730,11 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     for (int kb = 0; kb < st.n_kb; ++kb) {
       uint32_t w = 0;
       if (st.src[kb] == SRC_X) w |= OP_X | (st.wait_x ? OP_WAIT : 0u);
-      else w |= OP_WAIT | ((uint32_t)st.src[kb] << 5);
+      else w |= (st.reuse_a ? 0u : OP_WAIT) | ((uint32_t)st.src[kb] << 5);
       if (kb == 0) w |= OP_FIRST;
       if (kb == st.n_kb - 1) w |= OP_LAST | (st.x_done ? OP_XDONE : 0u);
       if (st.N == 128) w |= OP_N128;
+      if (st.N == 16) w |= OP_N16;
       pg.ops[pg.n_ops++] = w;
     }
     pg.step_word[s] = (uint32_t)st.N | ((uint32_t)st.relu << 9) | ((uint32_t)st.out_blocks << 10) | ((uint32_t)st.head << 13) |
@@ -706,6 +750,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   pl.off_wblob = off; off += round_up64(wb, 1024);
   pl.off_bias = off;  off += round_up64(pl.bias_floats * 4, 1024);
   pl.off_scale = off; off += siren ? round_up64((int64_t)pg.n_bias * 4, 1024) : 0;
+  pl.off_weff = off;  off += d.n_cls > 0 ? 16 * 256 * 4 + 1024 : 0;        // merged class-head matrix (fp32) | b_eff
   pl.off_save = off;  off += save ? n_tiles * (int64_t)sv : 0;
   pl.total = off;
   return pl;
@@ -735,10 +780,15 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;
   if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return NERFB_E_BADARG;
   uint8_t* base = static_cast<uint8_t*>(ws);
-  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob);
+  float* weff = reinterpret_cast<float*>(base + pl.off_weff);
+  if (pl.cls_bias_off >= 0) {
+    const NerfOffsets o = nerf_offsets(d);
+    NERFB_LAUNCH(merge_parse_kernel, 16, 256, 0, stream, params, o.w_p0, o.b_p0, o.w_p1, o.b_p1, d.n_cls, weff, weff + 16 * 256);
+  }
+  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob, (const float*)weff);
   NERFB_LAUNCH(gather_bias_kernel, pl.bias.n_segs, 256, 0, stream, params, pl.bias,
                reinterpret_cast<float*>(base + pl.off_bias), siren ? film : (const float*)nullptr,
-               reinterpret_cast<float*>(base + pl.off_scale));
+               reinterpret_cast<float*>(base + pl.off_scale), (const float*)weff);
   TcFwdArgs a{};
   a.prog = pl.prog;
   a.wblob = base + pl.off_wblob;
@@ -752,13 +802,15 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   const size_t smem = sizeof(Smem) + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
-  if (siren) NERFB_LAUNCH(mlp_tc_fwd_kernel<true>, grid, NUM_THREADS, smem, stream, a);
-  else NERFB_LAUNCH(mlp_tc_fwd_kernel<false>, grid, NUM_THREADS, smem, stream, a);
+  if (siren) NERFB_LAUNCH((mlp_tc_fwd_kernel<true, false>), grid, NUM_THREADS, smem, stream, a);
+  else if (pl.prog.n_cls > 0) NERFB_LAUNCH((mlp_tc_fwd_kernel<false, true>), grid, NUM_THREADS, smem, stream, a);
+  else NERFB_LAUNCH((mlp_tc_fwd_kernel<false, false>), grid, NUM_THREADS, smem, stream, a);
   return NERFB_OK;
 }
 
@@ -771,5 +823,6 @@ TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P) {
   L.save_x_off = pl.prog.save_x_off; L.save_dir_off = pl.prog.save_dir_off;
   L.tile_save_bytes = pl.prog.tile_save_bytes;
   L.off_save = pl.off_save; L.total = round_up64(pl.total, 1024);
+  L.off_weff = pl.off_weff;
   return L;
 }

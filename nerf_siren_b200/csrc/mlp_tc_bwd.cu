@@ -57,6 +57,7 @@ struct BStep {
   int mask_off;      // forward-record offset of the gate bit-mask (128 rows x 32 B) of this step's output (-1: no gate)
   int add_sigma;     // output += d_sigma (x) w_sigma before gating (the sigma head reads the same activation)
   int save_off;      // backward-record offset of this step's output dZ (4 blocks)
+  int add_cls;       // output += g_cls W_eff before storing (NeRF_3D class head reads xyz_encoding_final, nerf_cls.py:104)
 };
 struct BProgram {
   int n_steps;
@@ -65,12 +66,14 @@ struct BProgram {
   int dzdir_off;     // backward-record offset of dZ_dir (2 blocks)
   int h_off;         // backward-record offset of the head block: columns 0..3 = [g_r g_g g_b d_sigma] per sample
   int fwd_tile_bytes, bwd_tile_bytes;
+  int n_cls, out_c;  // NeRF_3D: class-head width; floats per output row (4 + n_cls)
 };
 
 struct DgradArgs {
   BProgram prog;
   const uint8_t* wblob;            // transposed bf16 slabs in schedule order
   const float* heads;              // w_sigma[256] | w_rgb[3*128]
+  const float* weff;               // NeRF_3D: merged class-head matrix, fp32 [16 x 256] (forward workspace)
   const float* out; const float* d_out;
   const uint8_t* fwd_rec; uint8_t* bwd_rec;
   int64_t P; int64_t n_tiles;
@@ -81,6 +84,7 @@ struct __align__(1024) SmemD {
   uint8_t ring[N_STAGES][STAGE_BYTES];
   float w_sigma[256];
   float w_rgb[3 * 128];
+  float w_cls[8 * 256];                  // NeRF_3D: W_eff rows
   uint64_t w_full[N_STAGES], w_empty[N_STAGES];
   uint64_t a_ready[4];                   // block j holds a freshly written dZ block (16 epilogue warps arrive)
   uint64_t g_free[4];                    // the store lane has read block j out to HBM
@@ -117,6 +121,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
 
   for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.heads + i);
   for (int i = threadIdx.x; i < 384; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.heads + 256 + i);
+  for (int i = threadIdx.x; i < pg.n_cls * 256; i += NUM_THREADS) sm.w_cls[i] = __ldg(args.weff + i);
   if (threadIdx.x == 0) {
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
     for (int i = 0; i < 4; ++i) { mbar_init(&sm.a_ready[i], D_EPI_WARPS); mbar_init(&sm.g_free[i], 1); }
@@ -212,15 +217,31 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
       const bool live = p < args.P;
       const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + row * 32 + c4 * 8;
       float g0 = 0.f, g1 = 0.f, g2 = 0.f, dsig = 0.f;
+      float gc[8];                            // class-head logit gradients d_cls * s (1 - s)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) gc[k] = 0.f;
       if (live) {
-        const float4 y = __ldg(reinterpret_cast<const float4*>(args.out + p * 4));
-        const float4 dy = __ldg(reinterpret_cast<const float4*>(args.d_out + p * 4));
+        float4 y, dy;
+        if (pg.out_c == 4) {
+          y = __ldg(reinterpret_cast<const float4*>(args.out + p * 4));
+          dy = __ldg(reinterpret_cast<const float4*>(args.d_out + p * 4));
+        } else {
+          const float* yo = args.out + p * pg.out_c; const float* dyo = args.d_out + p * pg.out_c;
+          y = make_float4(__ldg(yo), __ldg(yo + 1), __ldg(yo + 2), __ldg(yo + 3));
+          dy = make_float4(__ldg(dyo), __ldg(dyo + 1), __ldg(dyo + 2), __ldg(dyo + 3));
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (k < pg.n_cls) { const float sv = __ldg(yo + 4 + k); gc[k] = __ldg(dyo + 4 + k) * sv * (1.f - sv); }
+        }
         g0 = dy.x * y.x * (1.f - y.x); g1 = dy.y * y.y * (1.f - y.y); g2 = dy.z * y.z * (1.f - y.z);   // sigmoid'
         dsig = dy.w;
       }
-      if (c4 == 0) {                          // head block for the wgrad kernel: 4 bf16 per sample, rest of the row unused
-        uint2 hw; hw.x = pack_bf16(g0, g1); hw.y = pack_bf16(g2, dsig);
-        *reinterpret_cast<uint2*>(args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off + swz_off(row, 0)) = hw;
+      if (c4 == 0) {                          // head block for the wgrad kernel: [g_rgb d_sigma g_cls(8) 0 0 0 0] bf16 per sample
+        uint8_t* hrow = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off;
+        *reinterpret_cast<uint4*>(hrow + swz_off(row, 0)) =
+            make_uint4(pack_bf16(g0, g1), pack_bf16(g2, dsig), pack_bf16(gc[0], gc[1]), pack_bf16(gc[2], gc[3]));
+        if (pg.n_cls > 0)
+          *reinterpret_cast<uint4*>(hrow + swz_off(row, 8)) = make_uint4(pack_bf16(gc[4], gc[5]), pack_bf16(gc[6], gc[7]), 0u, 0u);
       }
       uint2 mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
 #pragma unroll
@@ -265,6 +286,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
               f[4 * i + 2] = fmaf(dsig, w.z, f[4 * i + 2]); f[4 * i + 3] = fmaf(dsig, w.w, f[4 * i + 3]);
             }
           }
+          if (st.add_cls) {                   // d feat += g_cls W_eff
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              if (k < pg.n_cls) {
+                const uint32_t wb = smem_u32(sm.w_cls) + (uint32_t)(k * 256 + col0) * 4u;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float4 w = lds128f(wb + 16u * i);
+                  f[4 * i] = fmaf(gc[k], w.x, f[4 * i]); f[4 * i + 1] = fmaf(gc[k], w.y, f[4 * i + 1]);
+                  f[4 * i + 2] = fmaf(gc[k], w.z, f[4 * i + 2]); f[4 * i + 3] = fmaf(gc[k], w.w, f[4 * i + 3]);
+                }
+              }
+            }
+          }
           if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu);
           if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
           need_free |= 1u << j;
@@ -303,6 +338,7 @@ struct WItem {
   int64_t bias_off;          // destination of colsum(dZ), or -1
   int m_lo, m_hi;            // rows (out features) of the accumulator that are real: [m_lo, m_hi)
   int64_t bias_alt;          // head block only (>= 0): colsum of column 3 goes here (b_sigma), columns 0..2 to bias_off
+  int aux;                   // destination is the aux buffer (class-head dW_eff | column sums), not the gradient blob
 };
 struct WgradArgs {
   int n_items; WItem item[MAX_ITEMS];
@@ -311,6 +347,7 @@ struct WgradArgs {
   int64_t n_tiles; int n_active;
   float* partial;                      // [n_active + n_items slots][256 x 256] dense per-item partials
   float* grad;
+  float* aux;                          // NeRF_3D: dW_eff [16 x 256] | colsum of the head block [128]
 };
 constexpr int64_t W_SLOT = 256 * 256;  // floats per partial slot
 
@@ -437,8 +474,9 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
       }
       if (sum_here && n_chunks > 0) {
         if (im.bias_alt < 0) {
-          atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
-          atomicAdd(args.grad + im.bias_off + 2 * bt + 1, b1);
+          float* bdst = (im.aux ? args.aux : args.grad) + im.bias_off;
+          atomicAdd(bdst + 2 * bt, b0);
+          atomicAdd(bdst + 2 * bt + 1, b1);
         } else if (bt < 2) {               // head block: columns [g_r g_g g_b d_sigma]
           atomicAdd(args.grad + im.bias_off + 2 * bt, b0);
           atomicAdd(bt == 0 ? args.grad + im.bias_off + 1 : args.grad + im.bias_alt, b1);
@@ -490,8 +528,52 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const __grid_const
     const int r = im.m_lo + e / im.nvalid, n = e % im.nvalid;
     float s = 0.f;
     for (int k = 0; k < s_n; ++k) s += ra.partial[(int64_t)(s_c[k] + it) * W_SLOT + r * 256 + n];
-    ra.grad[im.w_off + (int64_t)r * im.ld + im.col0 + n] += s;
+    if (im.aux) ra.aux[im.w_off + (int64_t)r * im.ld + im.col0 + n] = s;
+    else ra.grad[im.w_off + (int64_t)r * im.ld + im.col0 + n] += s;
   }
+}
+
+// Class-head chain rule (logits = W_p1 (W_p0 feat + b_p0) + b_p1, models/nerf_cls.py:56-61):  with dWe = sum g feat^T
+// (n_cls x 256) and db = sum g (n_cls) from the wgrad:
+//   dW_p0[j][i] = sum_k W_p1[k][j] dWe[k][i]      db_p0[j] = sum_k W_p1[k][j] db[k]
+//   dW_p1[k][j] = sum_i dWe[k][i] W_p0[j][i] + db[k] b_p0[j]      db_p1[k] = db[k]
+// One block per hidden unit j (512), one thread per input i (256).  aux = dWe [16 x 256] (rows 4.. of the head item) | colsums.
+__global__ void __launch_bounds__(256) parse_chain_kernel(const float* __restrict__ params, const float* __restrict__ aux, int n_cls,
+                                                          int64_t w_p0, int64_t b_p0, int64_t w_p1, int64_t b_p1, float* __restrict__ grad) {
+  const int j = blockIdx.x, i = threadIdx.x;
+  __shared__ float red[8][8];
+  const float* dwe = aux;                       // row k at aux + k * 256
+  const float* db = aux + 16 * 256 + 4;         // head-block columns 4 .. 4 + n_cls
+  const float w0 = __ldg(params + w_p0 + (int64_t)j * 256 + i);
+  float acc = 0.f;
+  float part[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    part[k] = 0.f;
+    if (k < n_cls) {
+      const float d = dwe[k * 256 + i];
+      acc = fmaf(__ldg(params + w_p1 + (int64_t)k * 512 + j), d, acc);
+      part[k] = d * w0;
+    }
+  }
+  grad[w_p0 + (int64_t)j * 256 + i] += acc;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float v = warp_sum(part[k]);
+    if ((i & 31) == 0) red[k][i >> 5] = v;
+  }
+  __syncthreads();
+  if (i < n_cls) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += red[i][w];
+    grad[w_p1 + (int64_t)i * 512 + j] += s + db[i] * __ldg(params + b_p0 + j);
+  }
+  if (i == 32) {
+    float s = 0.f;
+    for (int k = 0; k < n_cls; ++k) s = fmaf(__ldg(params + w_p1 + (int64_t)k * 512 + j), db[k], s);
+    grad[b_p0 + j] += s;
+  }
+  if (j == 0 && i >= 64 && i < 64 + n_cls) grad[b_p1 + (i - 64)] += db[i - 64];
 }
 
 }  // namespace
@@ -514,7 +596,7 @@ __global__ void __launch_bounds__(256) gather_heads_kernel(const float* __restri
 
 struct BwdPlan {
   BProgram prog; PackTArgs pack; WgradArgs wg; HeadArgs head;
-  int64_t off_wblob, off_heads, off_rec, off_partial, total;
+  int64_t off_wblob, off_heads, off_rec, off_partial, off_aux, total;
   int n_active; int64_t n_tiles; int64_t param_count;
 };
 
@@ -526,7 +608,9 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   const int dzdir = 0, dzfin = 2 * BLK_BYTES;
   auto dz_off = [&](int i) { return (6 + 4 * (D - i)) * BLK_BYTES; };          // dZ_i, i = D..1 (grad of trunk step i-1's pre-activation)
   BProgram& pg = pl.prog;
-  pg.hd_off = L.step_mask_off[D + 1]; pg.dzdir_off = dzdir;
+  const int dr_idx = D + 1 + (d.n_cls > 0 ? 1 : 0);            // forward step order: trunk 0..D-1, final, [class head], direction
+  pg.hd_off = L.step_mask_off[dr_idx]; pg.dzdir_off = dzdir;
+  pg.n_cls = d.n_cls; pg.out_c = 4 + d.n_cls;
   const int hblk = (6 + 4 * D) * BLK_BYTES;                     // head block (+ one never-written block behind it)
   pg.h_off = hblk;
   pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (8 + 4 * D) * BLK_BYTES;
@@ -534,7 +618,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   auto slabs = [&](int64_t w_off, int ld, int col0, int n_kb) {
     for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
   };
-  pg.s[ns++] = BStep{2, -1, 0, dzfin};                       slabs(o.w_dir, 256 + o.in_dir, 0, 2);
+  pg.s[ns++] = BStep{2, -1, 0, dzfin, d.n_cls > 0 ? 1 : 0};                       slabs(o.w_dir, 256 + o.in_dir, 0, 2);
   pg.s[ns++] = BStep{4, L.step_mask_off[D - 1], 1, dz_off(D)}; slabs(o.w_final, 256, 0, 4);
   for (int i = D - 1; i >= 1; --i) {
     const bool skip = (d.skip_mask >> i) & 1;
@@ -557,8 +641,10 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   wg.item[ni++] = WItem{dzdir, 2, 1, L.save_dir_off, 1, 64, o.w_dir, 256 + o.in_dir, 256, o.in_dir, -1, 0, 128, -1};
   // heads (models/nerf.py:112,119-120): the head block H holds [g_r g_g g_b d_sigma] in columns 0..3, so rows 0..2 of
   // H^T hd are dW_rgb and row 3 of H^T h_D is dW_sigma; its column sums are the two head biases
-  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D + 1], 2, 128, o.w_rgb, 128, 0, 128, o.b_rgb, 0, 3, o.b_sigma};
+  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[dr_idx], 2, 128, o.w_rgb, 128, 0, 128, o.b_rgb, 0, 3, o.b_sigma};
   wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D - 1], 4, 256, o.w_sigma - 3 * 256, 256, 0, 256, -1, 3, 4, -1};
+  if (d.n_cls > 0)      // class head: rows 4 .. 4+n_cls of H^T feat are dW_eff; head-block column sums -> aux[4096 ..]
+    wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D], 4, 256, -4 * 256, 256, 0, 256, 16 * 256, 4, 4 + d.n_cls, -1, 1};
   wg.n_items = ni;
   pl.n_tiles = ceil_div64(P, TILE_M);
   pl.n_active = (int)(pl.n_tiles < NERFB_SM_COUNT ? pl.n_tiles : NERFB_SM_COUNT);
@@ -567,7 +653,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   wg.item_off[0] = 0;
   for (int i = 0; i < ni; ++i) wg.item_off[i + 1] = wg.item_off[i] + (int64_t)item_cost(wg.item[i]) * pl.n_tiles;
   HeadArgs& h = pl.head;
-  h.fwd_tile_bytes = pg.fwd_tile_bytes; h.hD_off = L.step_save_off[D - 1]; h.hd_off = L.step_save_off[D + 1];
+  h.fwd_tile_bytes = pg.fwd_tile_bytes; h.hD_off = L.step_save_off[D - 1]; h.hd_off = L.step_save_off[dr_idx];
   h.P = P; h.n_tiles = pl.n_tiles; h.n_active = pl.n_active;
   h.w_sigma = o.w_sigma; h.b_sigma = o.b_sigma; h.w_rgb = o.w_rgb; h.b_rgb = o.b_rgb;
   int64_t off = 0;
@@ -575,6 +661,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   pl.off_heads = off;   off += 4096;
   pl.off_rec = off;     off += pl.n_tiles * (int64_t)pg.bwd_tile_bytes;
   pl.off_partial = off; off += (int64_t)(pl.n_active + MAX_ITEMS) * W_SLOT * 4;
+  pl.off_aux = off;     off += (16 * 256 + 128) * 4;
   pl.total = round_up64(off, 1024);
   return pl;
 }
@@ -585,7 +672,7 @@ bool tc_bwd_supported(const nerfb_mlp_desc& d) {
   if (!tc_supported(d, 0) || d.kind != NERFB_KIND_NERF) return false;      // SIREN: tcgen05 arm is forward-only
   int skips = 0;
   for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
-  return d.D + skips + 5 <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
+  return d.D + skips + 5 + (d.n_cls > 0 ? 1 : 0) <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
 }
 int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) { return bwd_plan(d, P).total; }
 
@@ -616,12 +703,19 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   DgradArgs da{};
   da.prog = pl.prog; da.wblob = bb + pl.off_wblob; da.heads = heads; da.out = out; da.d_out = d_out;
   da.fwd_rec = fwd_rec; da.bwd_rec = bb + pl.off_rec; da.P = P; da.n_tiles = pl.n_tiles;
+  da.weff = reinterpret_cast<const float*>(base + L.off_weff);
   NERFB_LAUNCH(mlp_tc_dgrad_kernel, pl.n_active, NUM_THREADS, smem_d, stream, da);
 
   pl.wg.fwd_rec = fwd_rec; pl.wg.bwd_rec = bb + pl.off_rec;
   pl.wg.partial = reinterpret_cast<float*>(bb + pl.off_partial); pl.wg.grad = grad;
+  pl.wg.aux = reinterpret_cast<float*>(bb + pl.off_aux);
+  if (d.n_cls > 0) NERFB_CUDA(cudaMemsetAsync(pl.wg.aux + 16 * 256, 0, 128 * 4, (cudaStream_t)stream));
   NERFB_LAUNCH(mlp_tc_wgrad_kernel, pl.n_active, W_THREADS, smem_w, stream, pl.wg);
 
   NERFB_LAUNCH(reduce_partials_kernel, dim3(pl.wg.n_items, 32), 256, 0, stream, pl.wg);
+  if (d.n_cls > 0) {
+    const NerfOffsets o = nerf_offsets(d);
+    NERFB_LAUNCH(parse_chain_kernel, 512, 256, 0, stream, params, (const float*)pl.wg.aux, d.n_cls, o.w_p0, o.b_p0, o.w_p1, o.b_p1, grad);
+  }
   return NERFB_OK;
 }

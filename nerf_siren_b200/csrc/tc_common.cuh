@@ -11,6 +11,7 @@
 struct TcFwdLayout {
   int n_steps; int step_save_off[12]; int step_mask_off[12]; int save_x_off, save_dir_off; int tile_save_bytes;
   int64_t off_save, total;     // record array offset inside the workspace; end of the forward's workspace part
+  int64_t off_weff;            // NeRF_3D: merged class-head matrix W_eff (fp32 16 x 256) | b_eff (16) in the forward's workspace
 };
 
 namespace tc {

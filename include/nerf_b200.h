@@ -38,6 +38,10 @@ extern "C" {
                                      (replaces models/rendering.py:224,131-150 + models/nerf.py:33-38) */
 #define NERFB_IN_EMBEDDED 1       /* x (P, in_xyz [+ in_dir]) already embedded -- NeRF.forward(x) called
                                      directly, e.g. extract_color_mesh.py:136-139 */
+#define NERFB_IN_GRID     2       /* dense occupancy query of extract_color_mesh.py:117-144: in0 = SIX float64 values on the
+                                     device [xmin xmax ymin ymax zmin zmax], n_samples = N, n_rows = N^3; point p is row p of
+                                     np.stack(np.meshgrid(x, y, z), -1).reshape(-1, 3) with np.linspace axes, generated and
+                                     encoded in-kernel; sigma_only, bf16 arm; out (N^3) = max(sigma, 0) (:141) */
 
 typedef struct nerfb_mlp_desc {
   int32_t kind;        /* NERFB_KIND_* */
@@ -170,6 +174,19 @@ int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* dec
                           const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
                           float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
                           float* opacity_final, float* depths_fine_out, void* workspace, void* stream);
+
+/* ---- the steps either side of the path ----------------------------------
+ * nerfb_generate_rays: datasets/ray_utils.py:5-50 (get_ray_directions, get_rays) [+ :53-94 get_ndc_rays when ndc != 0,
+ *   near plane 1.0 and near/far = 0/1 as datasets/llff.py:234-239] -> rays (H*W, 8) = [o d near far], row-major pixels
+ *   (datasets/blender.py:103-108).  c2w: 12 floats in HOST memory (row-major 3x4 camera-to-world; passed by value to the
+ *   kernel, the only host pointer of this ABI).
+ * nerfb_finish_image: eval.py:163-193 on the device: rgb (H*W,3) -> uint8 (H*W,3) [(img*255).astype(uint8)], depth (H*W)
+ *   -> nan_to_num + rows flipped = the PFM payload of datasets/depth_utils.py:43-69, and sq_err = sum (rgb - gt)^2 (one
+ *   float64; metrics.py:4-14 psnr = -10 log10(sq_err / (3 H W))).  Any of rgb_u8 / depth+depth_pfm / gt+sq_err may be null. */
+int nerfb_generate_rays(const float* c2w_host, int H, int W, double focal, float near, float far, int ndc,
+                        float* rays, void* stream);
+int nerfb_finish_image(const float* rgb, const float* depth, const float* gt, int H, int W, uint8_t* rgb_u8,
+                       float* depth_pfm, double* sq_err, void* stream);
 
 /* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
 int64_t nerfb_launch_count(void);

@@ -22,7 +22,7 @@ class MlpDesc(C.Structure):
 
 KIND_NERF, KIND_SIREN = 0, 1
 PREC_FP32, PREC_BF16 = 0, 1
-IN_RAYS, IN_EMBEDDED = 0, 1
+IN_RAYS, IN_EMBEDDED, IN_GRID = 0, 1, 2
 E_UNSUPPORTED = -2
 
 _P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
@@ -51,6 +51,8 @@ SIGNATURES = {
     "nerfb_mip_march": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P]),
     "nerfb_triplane_render": (_I, [_P, _I, _I, _P, _F, _P, _P, _L, _I, _I, C.c_double, C.c_double, _P, _P, _I, _F, _I,
                                    _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "nerfb_generate_rays": (_I, [_P, _I, _I, C.c_double, _F, _F, _I, _P, _P]),
+    "nerfb_finish_image": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P]),
 }
 

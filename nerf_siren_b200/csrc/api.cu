@@ -62,7 +62,8 @@ extern "C" int nerfb_mlp_fwd(const nerfb_mlp_desc* d, int precision, int in_mode
                              const float* in0, const float* in1, int64_t n_rows, int n_samples, int sigma_only,
                              int save_for_backward, float* out, void* workspace, int64_t workspace_bytes, void* stream) {
   NERFB_CHECK_ARG(desc_ok(d) && params && in0 && out && n_rows >= 0 && n_samples >= 1);
-  NERFB_CHECK_ARG(in_mode == NERFB_IN_EMBEDDED || (in_mode == NERFB_IN_RAYS && in1));
+  NERFB_CHECK_ARG(in_mode == NERFB_IN_EMBEDDED || in_mode == NERFB_IN_GRID || (in_mode == NERFB_IN_RAYS && in1));
+  if (in_mode == NERFB_IN_GRID && precision != NERFB_PREC_BF16) return NERFB_E_UNSUPPORTED;
   NERFB_CHECK_ARG(workspace || workspace_bytes == 0);
   if (n_rows == 0) return NERFB_OK;
   if (precision == NERFB_PREC_FP32)

@@ -357,6 +357,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         px = __fadd_rn(__ldg(ray + 0), __fmul_rn(dirx, z));
         py = __fadd_rn(__ldg(ray + 1), __fmul_rn(diry, z));
         pz = __fadd_rn(__ldg(ray + 2), __fmul_rn(dirz, z));
+      } else if (args.in_mode == NERFB_IN_GRID) {          // dense query grid (extract_color_mesh.py:117-125): point
+        // p = (iy * N + ix) * N + iz of np.meshgrid(x, y, z) ('xy' indexing), axes = np.linspace in float64 -> float32
+        const double* rg = reinterpret_cast<const double*>(args.in0);
+        const int64_t N = args.S;
+        const int iz = (int)(pc % N), ix = (int)((pc / N) % N), iy = (int)(pc / (N * N));
+        const double den = (double)(N > 1 ? N - 1 : 1);
+        px = (float)(ix == N - 1 && N > 1 ? rg[1] : rg[0] + (double)ix * ((rg[1] - rg[0]) / den));
+        py = (float)(iy == N - 1 && N > 1 ? rg[3] : rg[2] + (double)iy * ((rg[3] - rg[2]) / den));
+        pz = (float)(iz == N - 1 && N > 1 ? rg[5] : rg[4] + (double)iz * ((rg[5] - rg[4]) / den));
       } else if (SIREN) {                                  // x = [xyz(3) | dir(3)] rows (SirenField.forward)
         const float* src = args.in0 + pc * (int64_t)(pg.sigma_only ? 3 : 6);
         px = __ldg(src); py = __ldg(src + 1); pz = __ldg(src + 2);
@@ -369,7 +378,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         if (saving) { mbar_wait_relaxed(&sm.x_stored[b], xs_par[b]); xs_par[b] ^= 1; }
       }
       if (SIREN) hilo_row(__fmul_rn(px, pg.xyz_scale), __fmul_rn(py, pg.xyz_scale), __fmul_rn(pz, pg.xyz_scale), x_base, row);
-      else if (args.in_mode == NERFB_IN_RAYS) encode_row(px, py, pz, pg.n_freq_xyz, x_base, row);
+      else if (args.in_mode != NERFB_IN_EMBEDDED) encode_row(px, py, pz, pg.n_freq_xyz, x_base, row);
       else copy_row(emb_src, pg.in_xyz, x_base, row);
       fence_proxy_async();
       __syncwarp();
@@ -531,7 +540,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
           if (c4 == 0) {
             const float sg = sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[0];
             sm.sigma[row] = sg;
-            if (pg.sigma_only && live) args.out[p] = sg;
+            if (pg.sigma_only && live) args.out[p] = (args.in_mode == NERFB_IN_GRID) ? fmaxf(sg, 0.f) : sg;   // grid: np.maximum(sigma, 0), extract_color_mesh.py:141
           }
         } else if (st_head == 2) { // rgb = sigmoid(W_rgb h_dir + b)  (models/nerf.py:119-120)
           sm.part[c4][0][row] = head_acc[0]; sm.part[c4][1][row] = head_acc[1]; sm.part[c4][2][row] = head_acc[2];
@@ -777,6 +786,7 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
                int64_t ws_bytes, void* stream) {
   const bool siren = d.kind == NERFB_KIND_SIREN;
   if (siren && (!film || save)) return siren && save ? NERFB_E_UNSUPPORTED : NERFB_E_BADARG;
+  if (in_mode == NERFB_IN_GRID && (!sigma_only || save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0);
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;

@@ -278,3 +278,39 @@ def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, 
         _req(u, "u", allow_none=True), int(seed) & 0xFFFFFFFFFFFFFFFF, *[o.data_ptr() for o in out],
         0 if fine is None else fine.data_ptr(), ws.data_ptr(), _stream()), "nerfb_triplane_render")
     return (*out, fine) if return_depths_fine else tuple(out)
+
+
+# ---- the steps either side of the path --------------------------------------------------------
+def generate_rays(c2w, h, w, focal, near=2.0, far=6.0, ndc=False, device="cuda"):
+    """(H*W, 8) rays of one view on the device: ray_utils.get_ray_directions + get_rays (+ get_ndc_rays when ndc)."""
+    c2w = torch.as_tensor(c2w, dtype=torch.float32, device="cpu").reshape(3, 4).contiguous()
+    rays = torch.empty(h * w, 8, device=device, dtype=torch.float32)
+    check(lib.nerfb_generate_rays(c2w.data_ptr(), int(h), int(w), float(focal), float(near), float(far), int(bool(ndc)),
+                                  rays.data_ptr(), _stream()), "nerfb_generate_rays")
+    return rays
+
+
+def finish_image(rgb, h, w, depth=None, gt=None):
+    """eval.py:163-193 on the device -> (uint8 image (H,W,3), PFM-ordered depth (H,W) or None, squared-error sum or None)."""
+    if rgb.shape != (h * w, 3):
+        raise ValueError(f"rgb must be ({h * w}, 3), got {tuple(rgb.shape)}")
+    u8 = torch.empty(h, w, 3, device=rgb.device, dtype=torch.uint8)
+    dp = torch.empty(h, w, device=rgb.device, dtype=torch.float32) if depth is not None else None
+    se = torch.zeros(1, device=rgb.device, dtype=torch.float64) if gt is not None else None
+    check(lib.nerfb_finish_image(_req(rgb, "rgb"), _req(depth, "depth", allow_none=True), _req(gt, "gt", allow_none=True), int(h),
+                                 int(w), u8.data_ptr(), 0 if dp is None else dp.data_ptr(), 0 if se is None else se.data_ptr(),
+                                 _stream()), "nerfb_finish_image")
+    return u8, dp, se
+
+
+def sigma_grid(desc, params, n_grid, x_range, y_range, z_range):
+    """Dense occupancy grid of extract_color_mesh.py:117-144 -> (N, N, N) max(sigma, 0), points generated in-kernel."""
+    dev = params.device
+    rg = torch.tensor([x_range[0], x_range[1], y_range[0], y_range[1], z_range[0], z_range[1]], dtype=torch.float64, device=dev)
+    n_pts = n_grid ** 3
+    ws = mlp_workspace(desc, _lib.PREC_BF16, n_pts, True, False, dev)
+    out = torch.empty(n_pts, 1, device=dev, dtype=torch.float32)
+    ws_ptr, ws_bytes = _aligned(ws)
+    check(lib.nerfb_mlp_fwd(C.byref(desc), _lib.PREC_BF16, _lib.IN_GRID, _req(params, "params"), 0, rg.data_ptr(), 0, n_pts,
+                            int(n_grid), 1, 0, out.data_ptr(), ws_ptr, ws_bytes, _stream()), "nerfb_mlp_fwd[grid]")
+    return out.view(n_grid, n_grid, n_grid)

@@ -1,0 +1,126 @@
+"""the steps either side of render_rays.  CPU: oracle vs the reference-produced fixture g11_io, the
+Lightning-free system's checkpoint layout / schedulers.  GPU: kernels through the C ABI against the oracle."""
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import io_oracle as IO
+from oracle import render_oracle as O
+from tests._util import gold
+
+DEV = "cuda"
+
+
+def hp(**kw):
+    base = dict(N_samples=16, N_importance=16, use_disp=False, perturb=1.0, noise_std=1.0, chunk=32768, batch_size=256,
+                lr=5e-4, optimizer="adam", lr_scheduler="steplr", decay_step=[2], decay_gamma=0.5, num_epochs=3, loss_type="mse")
+    base.update(kw)
+    return types.SimpleNamespace(**base)
+
+
+def test_oracle_rays_and_pfm_match_reference():
+    g = gold("g11_io")
+    for tag, ndc in (("blender", False), ("llff", True)):
+        H, W, focal = g[f"{tag}:hwf"].tolist()
+        rays = IO.image_rays(g[f"{tag}:c2w"], int(H), int(W), focal, 2.0, 6.0, ndc)
+        assert torch.equal(rays, g[f"{tag}:rays"])
+    depth = g["pfm:depth"].numpy()
+    assert IO.pfm_bytes(np.nan_to_num(depth)) == g["pfm:bytes"].numpy().tobytes()
+
+
+def test_grid_points_order():
+    p = IO.grid_points(3, (0, 1), (10, 11), (20, 21))
+    assert p.shape == (27, 3)
+    assert p[1].tolist() == [0.0, 10.0, 20.5] and p[3].tolist() == [0.5, 10.0, 20.0] and p[9].tolist() == [0.0, 10.5, 20.0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,ndc", [("blender", False), ("llff", True)])
+def test_generate_rays_matches_reference(tag, ndc):
+    import nerf_siren_b200 as nb
+    g = gold("g11_io")
+    H, W, focal = g[f"{tag}:hwf"].tolist()
+    rays = nb.ops.generate_rays(g[f"{tag}:c2w"], int(H), int(W), focal, 2.0, 6.0, ndc).cpu()
+    ref = g[f"{tag}:rays"]
+    # fp32; the 3-term rotation and the norm are summed in a fixed fma order here, in MKL's order in the reference
+    torch.testing.assert_close(rays, ref, rtol=2e-6, atol=2e-6)
+    assert torch.equal(rays[:, 6:], ref[:, 6:])
+
+
+@pytest.mark.gpu
+def test_finish_image_quantise_flip_psnr():
+    import nerf_siren_b200 as nb
+    from nerf_siren_b200 import evaluation as ev
+    g = gold("g11_io")
+    H, W = 37, 53
+    gen = torch.Generator().manual_seed(1)
+    rgb = torch.rand(H * W, 3, generator=gen)
+    rgb[0] = torch.tensor([0.0, 1.0, 0.999999])
+    gt = torch.rand(H * W, 3, generator=gen)
+    depth = g["pfm:depth"].reshape(-1).contiguous()
+    u8, dp, se = nb.ops.finish_image(rgb.to(DEV), H, W, depth.to(DEV), gt.to(DEV))
+    assert np.array_equal(u8.cpu().numpy(), IO.quantize(rgb.view(H, W, 3).numpy()))
+    psnr = float(-10 * torch.log10(se / (3 * H * W)))
+    assert abs(psnr - float(IO.psnr(rgb, gt))) < 1e-4
+    import tempfile
+    with tempfile.NamedTemporaryFile(suffix=".pfm") as f:
+        ev.save_pfm(f.name, dp.cpu().numpy(), already_flipped=True)
+        assert open(f.name, "rb").read() == g["pfm:bytes"].numpy().tobytes()          # byte-identical to the reference's file
+
+
+@pytest.mark.gpu
+def test_sigma_grid_matches_oracle():
+    """extract_color_mesh.py:117-141 on the tcgen05 arm; bf16 tolerance 3e-2 of the sigma scale, same ordering as np.meshgrid."""
+    import nerf_siren_b200 as nb
+    from nerf_siren_b200 import evaluation as ev
+    p = O.nerf_field(seed=21)
+    m = nb.NeRF().to(DEV); m.load_state_dict(p)
+    N, xr, yr, zr = 24, (-1.2, 1.2), (-1.0, 1.3), (-0.7, 1.1)
+    got = ev.sigma_grid(m, nb.Embedding(3, 10), N, xr, yr, zr).cpu()
+    pts = IO.grid_points(N, xr, yr, zr)
+    ref = np.maximum(O.nerf_mlp(p, O.embed(pts, 10), True)[:, 0].numpy(), 0).reshape(N, N, N)
+    assert got.shape == (N, N, N) and float(got.min()) >= 0
+    scale = float(np.abs(ref).max())
+    assert float(np.abs(got.numpy() - ref).max()) <= 3e-2 * scale
+
+
+def test_checkpoint_layout_and_schedulers(tmp_path):
+    """Lightning key layout (utils/__init__.py:56-86 reads it back), MultiStepLR / cosine / poly as utils/__init__.py:33-52."""
+    pytest.importorskip("nerf_siren_b200")
+    from nerf_siren_b200 import system as S
+    sd = {"state_dict": {"nerf_coarse.sigma.weight": torch.ones(1, 256), "nerf_fine.sigma.weight": torch.zeros(1, 256),
+                         "nerf_fine.extra.weight": torch.zeros(1)}}
+    path = os.path.join(tmp_path, "a.ckpt")
+    torch.save(sd, path)
+    got = S.extract_model_state_dict(path, "nerf_fine", prefixes_to_ignore=["extra"])
+    assert list(got) == ["sigma.weight"] and float(got["sigma.weight"].sum()) == 0
+    lin = torch.nn.Linear(2, 2)
+    for name, want in (("steplr", [1.0, 1.0, 0.5]), ("poly", [1.0, (1 - 1 / 3) ** 0.9, (1 - 2 / 3) ** 0.9])):
+        h = hp(lr=1.0, lr_scheduler=name)
+        opt = S.get_optimizer(h, [lin]); sch = S.get_scheduler(h, opt)
+        lrs = []
+        for _ in range(3):
+            lrs.append(S.get_learning_rate(opt)); opt.step(); sch.step()
+        assert np.allclose(lrs, want)
+
+
+@pytest.mark.gpu
+def test_system_fit_trains_and_checkpoints(tmp_path):
+    import nerf_siren_b200 as nb
+    from nerf_siren_b200 import system as S
+    torch.manual_seed(0)
+    sys_ = S.NeRFSystem(hp(num_epochs=2), white_back=True).to(DEV)
+    rays = O.blender_rays(512, seed=3).to(DEV)
+    rgbs = torch.full((512, 3), 0.25, device=DEV)
+    batches = [{"rays": rays[i:i + 256], "rgbs": rgbs[i:i + 256]} for i in (0, 256)] * 10
+    hist = sys_.fit(batches, val_batches=[{"rays": rays[None], "rgbs": rgbs[None]}], ckpt_dir=str(tmp_path))
+    assert len(hist) == 2 and hist[1]["val/loss"] < hist[0]["val/loss"] and hist[1]["val/psnr"] > hist[0]["val/psnr"]
+    fresh = nb.NeRF().to(DEV)
+    S.load_ckpt(fresh, os.path.join(tmp_path, "epoch=1.ckpt"), model_name="nerf_fine")
+    for a, b in zip(fresh.parameters(), sys_.nerf_fine.parameters()):
+        assert torch.equal(a, b)
+    out = sys_(rays)                                     # system.py:199-223 result keys
+    assert set(out) == {"rgb_coarse", "depth_coarse", "opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine"}

@@ -523,7 +523,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         if (st_saved && st_relu) {
           const int mo = sm.step_mask[s];
           if (mo >= 0)
-            *reinterpret_cast<uint2*>(args.save + tile * (int64_t)pg.tile_save_bytes + mo + row * 32 + c4 * 8) = make_uint2(gate_lo, gate_hi);
+            *reinterpret_cast<uint2*>(args.save + tile * (int64_t)pg.tile_save_bytes + mo + c4 * (TILE_M * 8) + row * 8) = make_uint2(gate_lo, gate_hi);   // [c4][row]: a warp writes 256 contiguous bytes
         }
         if (CLS && st_head == 3) {       // class head (models/nerf_cls.py:104): sigmoid of the merged parse.1 o parse.0 logits, 16-column step
           tmem_ld_wait();

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
     for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
       const int64_t p = tile * TILE_M + row;
       const bool live = p < args.P;
-      const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + row * 32 + c4 * 8;
+      const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + c4 * (TILE_M * 8) + row * 8;   // mask layout [c4][row]
       float g0 = 0.f, g1 = 0.f, g2 = 0.f, dsig = 0.f;
       float gc[8];                            // class-head logit gradients d_cls * s (1 - s)
 #pragma unroll
@@ -516,10 +516,16 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const __grid_const
   const int it = blockIdx.x;
   const WItem& im = ra.item[it];
   __shared__ int s_c[NERFB_SM_COUNT + 1];
+  __shared__ int s_flag[NERFB_SM_COUNT + 1];
   __shared__ int s_n;
-  if (threadIdx.x == 0) {                    // the CTAs that own a non-empty tile range of this item
+  if (threadIdx.x < ra.n_active) {           // the CTAs that own a non-empty tile range of this item (one thread per CTA)
+    int64_t t0, t1; seg_range(ra, threadIdx.x, it, t0, t1);
+    s_flag[threadIdx.x] = t1 > t0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
     int n = 0;
-    for (int c = 0; c < ra.n_active; ++c) { int64_t t0, t1; seg_range(ra, c, it, t0, t1); if (t1 > t0) s_c[n++] = c; }
+    for (int c = 0; c < ra.n_active; ++c) if (s_flag[c]) s_c[n++] = c;
     s_n = n;
   }
   __syncthreads();

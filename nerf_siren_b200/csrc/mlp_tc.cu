@@ -110,7 +110,7 @@ struct __align__(1024) Smem {
   float sigma[TILE_M];
   uint64_t w_full[N_STAGES], w_empty[N_STAGES];
   uint64_t a_ready[4];                   // block j holds the current step's output (16 epilogue warps arrive)
-  uint64_t s_ready[2];                   // training: block j of a store-only step (direction-layer activations)
+  uint64_t s_ready[4];                   // training: block j of a store-only step (direction / colour layer activations)
   uint64_t a_free[4];                    // training: the store lane has read block j out
   uint64_t x_ready[2], x_consumed[2], x_stored[2];
   uint64_t acc_full[2];
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
   if (threadIdx.x == 0) {
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
     for (int i = 0; i < 4; ++i) { mbar_init(&sm.a_ready[i], N_EPI_WARPS); mbar_init(&sm.a_free[i], 1); }
-    mbar_init(&sm.s_ready[0], N_EPI_WARPS); mbar_init(&sm.s_ready[1], N_EPI_WARPS);
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.s_ready[i], N_EPI_WARPS);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&sm.x_ready[i], 4); mbar_init(&sm.x_consumed[i], 1); mbar_init(&sm.x_stored[i], 1);
       mbar_init(&sm.acc_full[i], 1);
@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
     // of serialising the 40 stores of a tile.  The release order is the issue order, which is also the order in which the
     // epilogue / encoder need the buffers back, so the lag cannot deadlock (a buffer is needed again a whole layer later).
     if (lane == 0 && saving) {
-      uint32_t a_par[4] = {0, 0, 0, 0}, s_par[2] = {0, 0}, xr_par[2] = {0, 0};
+      uint32_t a_par[4] = {0, 0, 0, 0}, s_par[4] = {0, 0, 0, 0}, xr_par[2] = {0, 0};
       uint32_t it = 0;
       uint32_t pend[2] = {0u, 0u};              // barrier addresses of the two stores still unreleased (0 = none)
       auto issued = [&](uint32_t bar) {         // store k committed: release store k-2
@@ -444,13 +444,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 26] = clock64();)
             const uint32_t (&vv)[16] = v[j & 1];
             float f[16];
+            uint32_t gcos[8];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               float2 r0, r1;
               if (SIREN) {      // sin(freq * (acc + b) + phase) = sin(freq * acc + (freq * b + phase))   (models/nerf.py:149-151)
                 r0 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(sc[i].x, sc[i].y), make_float2(bb[i].x, bb[i].y));
                 r1 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(sc[i].z, sc[i].w), make_float2(bb[i].z, bb[i].w));
-                r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y);
+                if (SAVE) {       // training: d/dz sin(freq z + phase) = freq cos(.) is the dgrad kernel's multiplicative gate
+                  float c0, c1, c2, c3;
+                  __sincosf(r0.x, &r0.x, &c0); __sincosf(r0.y, &r0.y, &c1); __sincosf(r1.x, &r1.x, &c2); __sincosf(r1.y, &r1.y, &c3);
+                  gcos[2 * i] = pack_bf16(c0 * sc[i].x, c1 * sc[i].y); gcos[2 * i + 1] = pack_bf16(c2 * sc[i].z, c3 * sc[i].w);
+                } else {
+                  r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y);
+                }
               } else {
                 r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
                 r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
@@ -513,6 +520,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
               fence_proxy_async();
               NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 23] = clock64();)
               if (st_saved) need_free |= 1u << j;
+            }
+            if (SIREN && SAVE && st_saved) {       // cos image [block][column quarter][row][16 x bf16]: a warp writes 1 KB contiguous
+              uint4* dst = reinterpret_cast<uint4*>(args.save + tile * (int64_t)pg.tile_save_bytes + sm.step_mask[s] +
+                                                    ((j * 4 + c4) * TILE_M + row) * 32);
+              dst[0] = make_uint4(gcos[0], gcos[1], gcos[2], gcos[3]);
+              dst[1] = make_uint4(gcos[4], gcos[5], gcos[6], gcos[7]);
             }
             tc_fence_before();
             __syncwarp();
@@ -682,6 +695,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
       TcStep& st = pg.s[ns++];
       st = TcStep{};
       st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1; st.mask_off = -1;
+      if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; st.mask_off = sv; sv += 4 * BLK_BYTES; }      // activations | freq cos image
       if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], 3, 0, 3, 256, 1); }
       else for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], 256, 64 * j, 64, 256); }
       st.bias_off = add_bias(o.b[i], 256, i);
@@ -689,7 +703,8 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     }
     if (!sigma_only) {
       TcStep& cl = pg.s[ns++]; cl = TcStep{};
-      cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = 0; cl.film = d.D; cl.save_off = -1; cl.mask_off = -1;
+      cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = save ? 4 : 0; cl.store_only = 1; cl.film = d.D; cl.save_off = -1; cl.mask_off = -1;
+      if (save) { cl.save_off = sv; sv += 4 * BLK_BYTES; cl.mask_off = sv; sv += 4 * BLK_BYTES; pg.save_dir_off = sv; sv += BLK_BYTES; }
       for (int j = 0; j < 4; ++j) { cl.src[cl.n_kb++] = j; add_slab(o.w_dir, 259, 3 + 64 * j, 64, 256); }
       cl.src[cl.n_kb++] = SRC_X; cl.wait_x = 1; cl.x_done = 1; add_slab(o.w_dir, 259, 0, 3, 256, 1);
       cl.bias_off = add_bias(o.b_dir, 256, d.D);
@@ -785,7 +800,7 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
                const float* in1, int64_t n_rows, int n_samples, int sigma_only, int save, float* out, void* ws,
                int64_t ws_bytes, void* stream) {
   const bool siren = d.kind == NERFB_KIND_SIREN;
-  if (siren && (!film || save)) return siren && save ? NERFB_E_UNSUPPORTED : NERFB_E_BADARG;
+  if (siren && !film) return NERFB_E_BADARG;
   if (in_mode == NERFB_IN_GRID && (!sigma_only || save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0);
@@ -817,13 +832,15 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
   const bool sv = a.save != nullptr;
-  if (siren) NERFB_LAUNCH((mlp_tc_fwd_kernel<true, false, false>), grid, NUM_THREADS, smem, stream, a);
+  if (siren && sv) NERFB_LAUNCH((mlp_tc_fwd_kernel<true, false, true>), grid, NUM_THREADS, smem, stream, a);
+  else if (siren) NERFB_LAUNCH((mlp_tc_fwd_kernel<true, false, false>), grid, NUM_THREADS, smem, stream, a);
   else if (pl.prog.n_cls > 0 && sv) NERFB_LAUNCH((mlp_tc_fwd_kernel<false, true, true>), grid, NUM_THREADS, smem, stream, a);
   else if (pl.prog.n_cls > 0) NERFB_LAUNCH((mlp_tc_fwd_kernel<false, true, false>), grid, NUM_THREADS, smem, stream, a);
   else if (sv) NERFB_LAUNCH((mlp_tc_fwd_kernel<false, false, true>), grid, NUM_THREADS, smem, stream, a);

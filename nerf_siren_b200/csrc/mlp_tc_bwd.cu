@@ -67,6 +67,9 @@ struct BProgram {
   int h_off;         // backward-record offset of the head block: columns 0..3 = [g_r g_g g_b d_sigma] per sample
   int fwd_tile_bytes, bwd_tile_bytes;
   int n_cls, out_c;  // NeRF_3D: class-head width; floats per output row (4 + n_cls)
+  int siren;         // SIREN: gates are the forward's freq*cos images (multiplicative), colour layer is 256 wide
+  int n_pro;         // dZ blocks the prologue produces: 2 (NeRF direction layer, 128 wide) or 4 (SIREN colour layer)
+  int rgb_in;        // fan-in of the rgb head: 128 / 256
 };
 
 struct DgradArgs {
@@ -83,7 +86,7 @@ struct __align__(1024) SmemD {
   uint8_t g[4][BLK_BYTES];               // current dZ tile: 4 K-blocks
   uint8_t ring[N_STAGES][STAGE_BYTES];
   float w_sigma[256];
-  float w_rgb[3 * 128];
+  float w_rgb[3 * 256];
   float w_cls[8 * 256];                  // NeRF_3D: W_eff rows
   uint64_t w_full[N_STAGES], w_empty[N_STAGES];
   uint64_t a_ready[4];                   // block j holds a freshly written dZ block (16 epilogue warps arrive)
@@ -101,6 +104,16 @@ __device__ __forceinline__ void apply_gate16(float (&f)[16], uint32_t bits) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) f[i] = ((bits >> (15 - i)) & 1u) ? 0.f : f[i];
 }
+// SIREN gate: multiply by the 16 bf16 values freq * cos(freq z + phase) the forward kernel parked for this thread
+__device__ __forceinline__ void apply_cos16(float (&f)[16], const uint8_t* src) {
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)), b = __ldg(reinterpret_cast<const uint4*>(src) + 1);
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    f[2 * i] *= __uint_as_float(w[i] << 16);
+    f[2 * i + 1] *= __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
 // this thread's 16 columns (chunks 2*c4, 2*c4+1) of row `row` of a [128 x 64] swizzled bf16 block
 __device__ __forceinline__ void store_block16(uint32_t blk, uint32_t row_off, uint32_t row_x, int c4, const float (&f)[16]) {
 #pragma unroll
@@ -112,6 +125,7 @@ __device__ __forceinline__ void store_block16(uint32_t blk, uint32_t row_off, ui
 // v2: 16 epilogue warps (32 rows x 16 columns of every 64-column block each, double-buffered TMEM loads), ReLU gates
 // from the forward's bit-masks (8 B per thread per layer instead of the 64 KB activation image), the dZ stores on their
 // own lane with lagged buffer release, and an MMA thread that only waits and issues.
+template <bool SIREN>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __grid_constant__ DgradArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   SmemD& sm = *reinterpret_cast<SmemD*>(smem_raw);
@@ -120,7 +134,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.heads + i);
-  for (int i = threadIdx.x; i < 384; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.heads + 256 + i);
+  constexpr int RGB_IN = SIREN ? 256 : 128;
+  for (int i = threadIdx.x; i < 3 * RGB_IN; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.heads + 256 + i);
   for (int i = threadIdx.x; i < pg.n_cls * 256; i += NUM_THREADS) sm.w_cls[i] = __ldg(args.weff + i);
   if (threadIdx.x == 0) {
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
@@ -190,7 +205,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
       for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
         uint8_t* rec = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes;
         for (int s = -1; s < pg.n_steps; ++s) {
-          const int nb = s < 0 ? 2 : 4;
+          const int nb = s < 0 ? pg.n_pro : 4;
           const int off = s < 0 ? pg.dzdir_off : pg.s[s].save_off;
           for (int j = 0; j < nb; ++j) {
             mbar_wait_relaxed(&sm.a_ready[j], (a_par >> j) & 1u); a_par ^= 1u << j;
@@ -243,15 +258,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         if (pg.n_cls > 0)
           *reinterpret_cast<uint4*>(hrow + swz_off(row, 8)) = make_uint4(pack_bf16(gc[4], gc[5]), pack_bf16(gc[6], gc[7]), 0u, 0u);
       }
-      uint2 mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
+      // SIREN: the gate of block j is 16 bf16 values freq*cos(.) at [block][column quarter][row] of the step's cos image
+      const uint8_t* crec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + (c4 * TILE_M + row) * 32;
+      uint2 mk = make_uint2(0u, 0u);
+      if (!SIREN) mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {           // dZ_dir = (g . W_rgb) (.) [hd > 0]     (models/nerf.py:119-120)
+      for (int j = 0; j < (SIREN ? 4 : 2); ++j) {   // dZ_dir = (g . W_rgb) (.) gate     (models/nerf.py:119-120 / :213-215)
         float f[16];
         const int col0 = 64 * j + 16 * c4;
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-          f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[128 + col0 + i] + g2 * sm.w_rgb[256 + col0 + i];
-        apply_gate16(f, (mk.x >> (16 * (1 - j))) & 0xFFFFu);      // block 0 was shifted in first: upper half
+          f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[RGB_IN + col0 + i] + g2 * sm.w_rgb[2 * RGB_IN + col0 + i];
+        if (SIREN) apply_cos16(f, crec + pg.hd_off + j * (4 * TILE_M * 32));
+        else apply_gate16(f, (mk.x >> (16 * (1 - j))) & 0xFFFFu);      // block 0 was shifted in first: upper half
         if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
         need_free |= 1u << j;
         store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);
@@ -263,7 +282,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         const BStep& st = pg.s[s];
         const uint32_t a = gs & 1u;
         const bool gated = st.mask_off >= 0;
-        if (gated) mk = __ldg(reinterpret_cast<const uint2*>(frec + st.mask_off));
+        if (gated && !SIREN) mk = __ldg(reinterpret_cast<const uint2*>(frec + st.mask_off));
         const bool add_sigma = st.add_sigma != 0;
         mbar_wait(&sm.acc_full[a], (acc_par >> a) & 1u); acc_par ^= 1u << a;
         tc_fence_after();
@@ -300,7 +319,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
               }
             }
           }
-          if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu);
+          if (gated && SIREN) apply_cos16(f, crec + st.mask_off + j * (4 * TILE_M * 32));
+          else if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu);
           if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
           need_free |= 1u << j;
           store_block16(g0_addr + (uint32_t)j * BLK_BYTES, row_off, row_x, c4, f);
@@ -339,6 +359,7 @@ struct WItem {
   int m_lo, m_hi;            // rows (out features) of the accumulator that are real: [m_lo, m_hi)
   int64_t bias_alt;          // head block only (>= 0): colsum of column 3 goes here (b_sigma), columns 0..2 to bias_off
   int aux;                   // destination is the aux buffer (class-head dW_eff | column sums), not the gradient blob
+  int hilo;                  // SIREN 3-wide inputs ride as [x_hi x_lo x_hi]: dW[:, k] = column k + column 3 + k
 };
 struct WgradArgs {
   int n_items; WItem item[MAX_ITEMS];
@@ -533,7 +554,10 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const __grid_const
   for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < total; e += gridDim.y * blockDim.x) {
     const int r = im.m_lo + e / im.nvalid, n = e % im.nvalid;
     float s = 0.f;
-    for (int k = 0; k < s_n; ++k) s += ra.partial[(int64_t)(s_c[k] + it) * W_SLOT + r * 256 + n];
+    for (int k = 0; k < s_n; ++k) {
+      const float* pp = ra.partial + (int64_t)(s_c[k] + it) * W_SLOT + r * 256 + n;
+      s += im.hilo ? pp[0] + pp[3] : pp[0];
+    }
     if (im.aux) ra.aux[im.w_off + (int64_t)r * im.ld + im.col0 + n] = s;
     else ra.grad[im.w_off + (int64_t)r * im.ld + im.col0 + n] += s;
   }
@@ -596,8 +620,8 @@ struct HeadArgs {
 };
 
 __global__ void __launch_bounds__(256) gather_heads_kernel(const float* __restrict__ params, int64_t w_sigma, int64_t w_rgb,
-                                                           float* __restrict__ heads) {
-  for (int i = threadIdx.x; i < 640; i += blockDim.x) heads[i] = __ldg(params + (i < 256 ? w_sigma + i : w_rgb + (i - 256)));
+                                                           float* __restrict__ heads, int rgb_in) {
+  for (int i = threadIdx.x; i < 256 + 3 * rgb_in; i += blockDim.x) heads[i] = __ldg(params + (i < 256 ? w_sigma + i : w_rgb + (i - 256)));
 }
 
 struct BwdPlan {
@@ -606,7 +630,10 @@ struct BwdPlan {
   int n_active; int64_t n_tiles; int64_t param_count;
 };
 
+BwdPlan bwd_plan_siren(const nerfb_mlp_desc& d, int64_t P);
+
 BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
+  if (d.kind == NERFB_KIND_SIREN) return bwd_plan_siren(d, P);
   BwdPlan pl{};
   const NerfOffsets o = nerf_offsets(d);
   const TcFwdLayout L = tc_fwd_layout(d, P);
@@ -616,7 +643,7 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   BProgram& pg = pl.prog;
   const int dr_idx = D + 1 + (d.n_cls > 0 ? 1 : 0);            // forward step order: trunk 0..D-1, final, [class head], direction
   pg.hd_off = L.step_mask_off[dr_idx]; pg.dzdir_off = dzdir;
-  pg.n_cls = d.n_cls; pg.out_c = 4 + d.n_cls;
+  pg.n_cls = d.n_cls; pg.out_c = 4 + d.n_cls; pg.siren = 0; pg.n_pro = 2; pg.rgb_in = 128;
   const int hblk = (6 + 4 * D) * BLK_BYTES;                     // head block (+ one never-written block behind it)
   pg.h_off = hblk;
   pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (8 + 4 * D) * BLK_BYTES;
@@ -672,10 +699,61 @@ BwdPlan bwd_plan(const nerfb_mlp_desc& d, int64_t P) {
   return pl;
 }
 
+// SIREN / FiLM (models/nerf.py:201-216): forward steps 0..D-1 = FiLM layers (h_l saved at step_save_off[l], freq*cos image at
+// step_mask_off[l]), step D = colour FiLM layer on [dir | h_{D-1}] (hc, cos image), heads sigma <- h_{D-1}, rgb <- hc.
+// dgrad: prologue dZ_c = (g W_rgb) (.) cos_c (4 blocks); step 0: x W_dir[:, 3:]^T + d_sigma w_sigma, (.) cos_{D-1} -> dZ_{D-1};
+// step k: x W_{D-k}^T (.) cos_{D-1-k} -> dZ_{D-1-k}, k = 1..D-1.  Backward record: dZ_c | dZ_{D-1} .. dZ_0 | head block.
+BwdPlan bwd_plan_siren(const nerfb_mlp_desc& d, int64_t P) {
+  BwdPlan pl{};
+  const NerfOffsets o = nerf_offsets(d);
+  const TcFwdLayout L = tc_fwd_layout(d, P);
+  const int D = d.D;
+  auto dz_off = [&](int l) { return (4 + 4 * (D - 1 - l)) * BLK_BYTES; };       // dZ_l, l = D-1 .. 0
+  BProgram& pg = pl.prog;
+  pg.hd_off = L.step_mask_off[D]; pg.dzdir_off = 0;
+  pg.n_cls = 0; pg.out_c = 4; pg.siren = 1; pg.n_pro = 4; pg.rgb_in = 256;
+  const int hblk = (4 + 4 * D) * BLK_BYTES;
+  pg.h_off = hblk;
+  pg.fwd_tile_bytes = L.tile_save_bytes; pg.bwd_tile_bytes = (6 + 4 * D) * BLK_BYTES;
+  int ns = 0, nslab = 0; int64_t wb = 0;
+  auto slabs = [&](int64_t w_off, int ld, int col0, int n_kb) {
+    for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
+  };
+  pg.s[ns++] = BStep{4, L.step_mask_off[D - 1], 1, dz_off(D - 1), 0};  slabs(o.w_dir, 259, 3, 4);
+  for (int l = D - 1; l >= 1; --l) { pg.s[ns++] = BStep{4, L.step_mask_off[l - 1], 0, dz_off(l - 1), 0}; slabs(o.w[l], 256, 0, 4); }
+  pg.n_steps = ns; pl.pack.n_slabs = nslab;
+  WgradArgs& wg = pl.wg; int ni = 0;
+  wg.item[ni++] = WItem{dz_off(0), 4, 1, L.save_x_off, 1, 64, o.w[0], 3, 0, 3, o.b[0], 0, 256, -1, 0, 1};
+  for (int l = 1; l < D; ++l)
+    wg.item[ni++] = WItem{dz_off(l), 4, 1, L.step_save_off[l - 1], 4, 256, o.w[l], 256, 0, 256, o.b[l], 0, 256, -1, 0, 0};
+  wg.item[ni++] = WItem{0, 4, 1, L.step_save_off[D - 1], 4, 256, o.w_dir, 259, 3, 256, o.b_dir, 0, 256, -1, 0, 0};
+  wg.item[ni++] = WItem{0, 4, 1, L.save_dir_off, 1, 64, o.w_dir, 259, 0, 3, -1, 0, 256, -1, 0, 1};
+  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D], 4, 256, o.w_rgb, 256, 0, 256, o.b_rgb, 0, 3, o.b_sigma, 0, 0};
+  wg.item[ni++] = WItem{hblk, 2, 1, L.step_save_off[D - 1], 4, 256, o.w_sigma - 3 * 256, 256, 0, 256, -1, 3, 4, -1, 0, 0};
+  wg.n_items = ni;
+  pl.n_tiles = ceil_div64(P, TILE_M);
+  pl.n_active = (int)(pl.n_tiles < NERFB_SM_COUNT ? pl.n_tiles : NERFB_SM_COUNT);
+  pl.param_count = o.total;
+  wg.fwd_tile_bytes = pg.fwd_tile_bytes; wg.bwd_tile_bytes = pg.bwd_tile_bytes; wg.n_tiles = pl.n_tiles; wg.n_active = pl.n_active;
+  wg.item_off[0] = 0;
+  for (int i = 0; i < ni; ++i) wg.item_off[i + 1] = wg.item_off[i] + (int64_t)item_cost(wg.item[i]) * pl.n_tiles;
+  HeadArgs& h = pl.head;
+  h.w_sigma = o.w_sigma; h.b_sigma = o.b_sigma; h.w_rgb = o.w_rgb; h.b_rgb = o.b_rgb;
+  int64_t off = 0;
+  pl.off_wblob = off;   off += round_up64(wb, 1024);
+  pl.off_heads = off;   off += 8192;
+  pl.off_rec = off;     off += pl.n_tiles * (int64_t)pg.bwd_tile_bytes;
+  pl.off_partial = off; off += (int64_t)(pl.n_active + MAX_ITEMS) * W_SLOT * 4;
+  pl.off_aux = off;     off += (16 * 256 + 128) * 4;
+  pl.total = round_up64(off, 1024);
+  return pl;
+}
+
 }  // namespace
 
 bool tc_bwd_supported(const nerfb_mlp_desc& d) {
-  if (!tc_supported(d, 0) || d.kind != NERFB_KIND_NERF) return false;      // SIREN: tcgen05 arm is forward-only
+  if (!tc_supported(d, 0)) return false;
+  if (d.kind == NERFB_KIND_SIREN) return d.D >= 2 && d.D + 4 <= MAX_ITEMS;
   int skips = 0;
   for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
   return d.D + skips + 5 + (d.n_cls > 0 ? 1 : 0) <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
@@ -697,12 +775,13 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   const uint8_t* fwd_rec = base + L.off_save;
   float* heads = reinterpret_cast<float*>(bb + pl.off_heads);
   NERFB_LAUNCH(pack_weights_t_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, bb + pl.off_wblob);
-  NERFB_LAUNCH(gather_heads_kernel, 1, 256, 0, stream, params, pl.head.w_sigma, pl.head.w_rgb, heads);
+  NERFB_LAUNCH(gather_heads_kernel, 1, 256, 0, stream, params, pl.head.w_sigma, pl.head.w_rgb, heads, pl.prog.rgb_in);
 
   static bool attr_set = false;
   const size_t smem_d = sizeof(SmemD) + 1024, smem_w = sizeof(SmemW) + 1024;
   if (!attr_set) {
-    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
     NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w));
     attr_set = true;
   }
@@ -710,7 +789,8 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   da.prog = pl.prog; da.wblob = bb + pl.off_wblob; da.heads = heads; da.out = out; da.d_out = d_out;
   da.fwd_rec = fwd_rec; da.bwd_rec = bb + pl.off_rec; da.P = P; da.n_tiles = pl.n_tiles;
   da.weff = reinterpret_cast<const float*>(base + L.off_weff);
-  NERFB_LAUNCH(mlp_tc_dgrad_kernel, pl.n_active, NUM_THREADS, smem_d, stream, da);
+  if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_dgrad_kernel<true>, pl.n_active, NUM_THREADS, smem_d, stream, da);
+  else NERFB_LAUNCH(mlp_tc_dgrad_kernel<false>, pl.n_active, NUM_THREADS, smem_d, stream, da);
 
   pl.wg.fwd_rec = fwd_rec; pl.wg.bwd_rec = bb + pl.off_rec;
   pl.wg.partial = reinterpret_cast<float*>(bb + pl.off_partial); pl.wg.grad = grad;

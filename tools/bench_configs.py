@@ -105,11 +105,31 @@ def cls_train():
           "mlp_tflops": flops / ms / 1e9, "config": {"workload": "configs[3]: nerf_cls training, LLFF-shaped rays, batch 8192 / GPU"}})
 
 
-for what in (sys.argv[1:] or ["render", "siren", "cls"]):
+def siren_train():
+    """Not a BASELINE configuration: the SIREN variant through the same training step (kernel (1) backward with sine activations)."""
+    torch.manual_seed(0)
+    nb.set_precision("auto")
+    models = [nb.SirenField().to(dev), nb.SirenField().to(dev)]
+    emb = [nb.Embedding(3, 0), nb.Embedding(3, 0)]
+    n = 4096
+    trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, True)
+    rays = synth.blender_rays(n, seed=10 + rank).to(dev)
+    rgbs = synth.target_rgbs(n, seed=20 + rank).to(dev)
+    ms = timed(lambda: trainer.step(rays, rgbs), 5)
+    arm = "bf16 tcgen05" if nb.ops.mlp_supported(models[0]._desc(), nb._lib.PREC_BF16, True) else "fp32 CUDA cores"
+    flops = n * 192 * 3 * 2 * 526_848
+    emit({"metric": "rays/s, SIREN coarse+fine training step (64+64 samples)", "value": n * world / ms * 1e3, "unit": "rays/s",
+          "n_gpus": world, "rays_per_gpu": n, "ms_per_step": ms, "mlp_arm": arm, "mlp_tflops": flops / ms / 1e9,
+          "config": {"workload": "SIREN variant of configs[1]: 4096 rays / GPU, 64+64 samples"}})
+
+
+for what in (sys.argv[1:] or ["render", "siren", "cls", "siren_train"]):
     if what in ("render", "siren"):
         render(what)
     elif what == "cls":
         cls_train()
+    elif what == "siren_train":
+        siren_train()
 if world > 1:
     dist.barrier()
     dist.destroy_process_group()

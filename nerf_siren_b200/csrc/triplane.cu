@@ -9,7 +9,7 @@
 //     so each of the 12 bilinear taps of a sample is a single coalesced request served by L2 (the 25 MB of planes stay
 //     resident in the 126 MB L2).  Bound: L2 gather bandwidth, 1,536 B per sample.
 //   * decoder on CUDA cores with its 2 x 64 x 32 first-layer weights in registers (lane j owns hidden units j, j + 32),
-//     features broadcast by shuffles; 2,304 MACs per sample is far below the gather cost.
+//     features broadcast through shared memory (8 LDS.128); 2,304 MACs per sample is far below the gather cost.
 //   * marcher = warp product-scan over the S-1 intervals with a running carry (same scheme as composite.cu).
 //   * the chunk-global depth clamp (ray_marcher.py:49-50: torch.min / torch.max over ALL depths) is two ordered-int
 //     atomics per warp plus a tiny second kernel.
@@ -74,54 +74,64 @@ __device__ __forceinline__ float softplusf(float x) {
   return x > 20.f ? x : fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(x)));
 }
 
-// the 4 bilinear taps of one plane at normalised (gx -> W, gy -> H), zeros padding, align_corners=False
-// (F.grid_sample semantics, renderer.py:64).  Offsets are clamped in-bounds and out-of-range taps get weight 0, so the
-// loads are unconditional and all 12 of a sample are in flight together.  NaN coordinates fail every test -> no tap.
-__device__ __forceinline__ void plane_taps(int H, int W, float gx, float gy, int (&off)[4], float (&wt)[4]) {
+// One bilinear tap per lane (lanes 0..11 = plane * 4 + corner) at normalised (gx -> W, gy -> H), zeros padding,
+// align_corners=False (F.grid_sample semantics, renderer.py:64).  The offset is clamped in-bounds and an out-of-range tap
+// gets weight 0, so the loads are unconditional and all 12 of a sample are in flight together; NaN coordinates fail every
+// test -> no tap.  Computing the 12 taps on 12 lanes instead of all of them on every lane removes ~85 of the ~110 address
+// instructions per sample; the (offset, weight) pairs go through shared memory (1 STS + 6 broadcast LDS.128).
+__device__ __forceinline__ void tap_lane(int H, int W, float x, float y, float z, int lane, int& off, float& wt) {
+  const int p = min(lane >> 2, 2), corner = lane & 3;
+  // plane axes (renderer.py:29-39): projections (x, y), (x, z), (z, x)
+  const float gx = p == 2 ? z : x;
+  const float gy = p == 0 ? y : (p == 1 ? z : x);
   const float ix = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gx, 1.f), (float)W), 1.f), 0.5f);
   const float iy = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gy, 1.f), (float)H), 1.f), 0.5f);
   const float fx = floorf(ix), fy = floorf(iy);
   const float w = ix - fx, e = 1.f - w, n = iy - fy, s = 1.f - n;
-  const bool x0 = fx >= 0.f && fx < (float)W, x1 = fx >= -1.f && fx < (float)(W - 1);
-  const bool y0 = fy >= 0.f && fy < (float)H, y1 = fy >= -1.f && fy < (float)(H - 1);
-  const int xi = (int)fmaxf(fminf(fx, (float)W), -2.f), yi = (int)fmaxf(fminf(fy, (float)H), -2.f);
-  const int xa = min(max(xi, 0), W - 1), xb = min(max(xi + 1, 0), W - 1);
-  const int ya = min(max(yi, 0), H - 1) * W, yb = min(max(yi + 1, 0), H - 1) * W;
-  off[0] = (ya + xa) * TP_C; wt[0] = (y0 && x0) ? s * e : 0.f;
-  off[1] = (ya + xb) * TP_C; wt[1] = (y0 && x1) ? s * w : 0.f;
-  off[2] = (yb + xa) * TP_C; wt[2] = (y1 && x0) ? n * e : 0.f;
-  off[3] = (yb + xb) * TP_C; wt[3] = (y1 && x1) ? n * w : 0.f;
+  const bool right = corner & 1, down = corner & 2;
+  const float cx = right ? fx + 1.f : fx, cy = down ? fy + 1.f : fy;
+  const bool valid = cx >= 0.f && cx < (float)W && cy >= 0.f && cy < (float)H;
+  wt = valid ? (down ? n : s) * (right ? w : e) : 0.f;
+  const int xi = min(max((int)fmaxf(fminf(cx, (float)W), -2.f), 0), W - 1);
+  const int yi = min(max((int)fmaxf(fminf(cy, (float)H), -2.f), 0), H - 1);
+  off = ((p * H + yi) * W + xi) * TP_C;
 }
 
 // run_model for one point (renderer.py:144-151 + triplane.py:155-167).  Returns on lane 0: sigma, lane 8 / 16 / 24: r, g, b.
+// s_tap: 12 x (offset, weight) as int2, s_feat: 32 floats; the caller alternates two such buffers between consecutive samples.
 __device__ __forceinline__ float field_eval(const float* __restrict__ planes, int H, int W, float x, float y, float z,
-                                            const Dec& d, int lane) {
-  const int ps = H * W * TP_C;
-  // plane axes (renderer.py:29-39): projections (x, y), (x, z), (z, x)
-  int off[3][4]; float wt[3][4], v[3][4];
-  plane_taps(H, W, x, y, off[0], wt[0]);
-  plane_taps(H, W, x, z, off[1], wt[1]);
-  plane_taps(H, W, z, x, off[2], wt[2]);
+                                            const Dec& d, int lane, int2* s_tap, float* s_feat) {
+  int off; float wt;
+  tap_lane(H, W, x, y, z, lane, off, wt);
+  if (lane < 12) s_tap[lane] = make_int2(off, __float_as_int(wt));
+  __syncwarp();
   const float* pl = planes + lane;
+  float v[12], wts[12];
 #pragma unroll
-  for (int p = 0; p < 3; ++p)
-#pragma unroll
-    for (int t = 0; t < 4; ++t) v[p][t] = __ldg(pl + p * ps + off[p][t]);
+  for (int t = 0; t < 6; ++t) {
+    const int4 q = *reinterpret_cast<const int4*>(s_tap + 2 * t);
+    v[2 * t] = __ldg(pl + q.x); wts[2 * t] = __int_as_float(q.y);
+    v[2 * t + 1] = __ldg(pl + q.z); wts[2 * t + 1] = __int_as_float(q.w);
+  }
   float fp[3];
 #pragma unroll
   for (int p = 0; p < 3; ++p) {
-    float acc = v[p][0] * wt[p][0];
-    acc = fmaf(v[p][1], wt[p][1], acc);
-    acc = fmaf(v[p][2], wt[p][2], acc);
-    fp[p] = fmaf(v[p][3], wt[p][3], acc);
+    float acc = v[4 * p] * wts[4 * p];
+    acc = fmaf(v[4 * p + 1], wts[4 * p + 1], acc);
+    acc = fmaf(v[4 * p + 2], wts[4 * p + 2], acc);
+    fp[p] = fmaf(v[4 * p + 3], wts[4 * p + 3], acc);
   }
   const float f = __fdiv_rn(__fadd_rn(__fadd_rn(fp[0], fp[1]), fp[2]), 3.f);      // sampled_features.mean(1)
+  s_feat[lane] = f;
+  __syncwarp();
   float ha = d.b1a, hb = d.b1b;
 #pragma unroll
-  for (int c = 0; c < TP_C; ++c) {
-    const float fc = __shfl_sync(0xffffffffu, f, c);
-    ha = fmaf(d.w1a[c], fc, ha);
-    hb = fmaf(d.w1b[c], fc, hb);
+  for (int c4 = 0; c4 < TP_C / 4; ++c4) {                   // all 32 features: 8 broadcast LDS.128 instead of 32 shuffles
+    const float4 q = *reinterpret_cast<const float4*>(s_feat + 4 * c4);
+    ha = fmaf(d.w1a[4 * c4], q.x, ha); hb = fmaf(d.w1b[4 * c4], q.x, hb);
+    ha = fmaf(d.w1a[4 * c4 + 1], q.y, ha); hb = fmaf(d.w1b[4 * c4 + 1], q.y, hb);
+    ha = fmaf(d.w1a[4 * c4 + 2], q.z, ha); hb = fmaf(d.w1b[4 * c4 + 2], q.z, hb);
+    ha = fmaf(d.w1a[4 * c4 + 3], q.w, ha); hb = fmaf(d.w1b[4 * c4 + 3], q.w, hb);
   }
   ha = softplusf(ha); hb = softplusf(hb);
   float p0 = fmaf(d.w2a[0], ha, d.w2b[0] * hb), p1 = fmaf(d.w2a[1], ha, d.w2b[1] * hb);
@@ -246,12 +256,14 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int S = a.S, Si = a.Si, St = S + Si;
   // per warp: two sample sets of 5 arrays (depth, sigma, r, g, b) x St, weights St, bins / cdf 2 x S
-  float* base = smem + (size_t)wib * (11 * St + 2 * S);
+  const int scr_off = (11 * St + 2 * S + 3) & ~3;            // 16-byte aligned scratch behind the per-ray arrays
+  float* base = smem + (size_t)wib * (scr_off + 128);
   float* const A = base;               // sample set A: [depth | sigma | r | g | b] x St, coarse [0,S) then fine [S,St)
   float* const B = base + 5 * St;      // sample set B: the merged, sorted samples
   float* s_w = base + 10 * St;
   float* s_bins = s_w + St;
   float* s_cdf = s_bins + S;
+  float* s_scr = base + scr_off;               // 2 x [12 x (offset, weight) | 32 features]
   Dec dec;
   load_decoder(dec, a.dec, a.lr_mul, lane);
   for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < a.R; r += (int64_t)gridDim.x * TP_WARPS) {
@@ -284,7 +296,8 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
         const float t = A[s];
         const float v = field_eval(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
                                    __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
-                                   __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane);
+                                   __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), dec, lane,
+                                   reinterpret_cast<int2*>(s_scr + (s & 1) * 64), s_scr + (s & 1) * 64 + 32);
         if ((lane & 7) == 0) A[(1 + (lane >> 3)) * St + s] = v;
       }
       __syncwarp();
@@ -332,11 +345,15 @@ __global__ void __launch_bounds__(TP_WARPS * 32) triplane_field_kernel(const flo
     const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
     float* __restrict__ rgb, float* __restrict__ sigma) {
   const int lane = threadIdx.x & 31;
+  __shared__ __align__(16) float s_scr[TP_WARPS][64];
+  float* scr = s_scr[threadIdx.x >> 5];
   Dec dec;
   load_decoder(dec, decp, lr_mul, lane);
   for (int64_t p = (int64_t)blockIdx.x * TP_WARPS + (threadIdx.x >> 5); p < P; p += (int64_t)gridDim.x * TP_WARPS) {
     const float x = __ldg(coords + p * 3), y = __ldg(coords + p * 3 + 1), z = __ldg(coords + p * 3 + 2);
-    const float v = field_eval(planes, H, W, __fmul_rn(coord_scale, x), __fmul_rn(coord_scale, y), __fmul_rn(coord_scale, z), dec, lane);
+    const float v = field_eval(planes, H, W, __fmul_rn(coord_scale, x), __fmul_rn(coord_scale, y), __fmul_rn(coord_scale, z), dec, lane,
+                               reinterpret_cast<int2*>(scr), scr + 32);
+    __syncwarp();
     if (lane == 0) sigma[p] = v;
     else if ((lane & 7) == 0) rgb[p * 3 + (lane >> 3) - 1] = v;
   }
@@ -430,7 +447,7 @@ extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const
   a.rand_coarse = rand_coarse; a.u = u; a.seed = seed;
   a.rgb_c = rgb_coarse; a.depth_c = depth_coarse; a.opac_c = opacity_coarse; a.rgb_f = rgb_final; a.depth_f = depth_final;
   a.opac_f = opacity_final; a.depths_fine_out = depths_fine_out; a.mm = static_cast<uint32_t*>(workspace);
-  const size_t smem = (size_t)TP_WARPS * (11 * (n_samples + n_importance) + 2 * n_samples) * sizeof(float);
+  const size_t smem = (size_t)TP_WARPS * (((11 * (n_samples + n_importance) + 2 * n_samples + 3) & ~3) + 128) * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
   if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(triplane_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   NERFB_LAUNCH(minmax_init_kernel, 1, 32, 0, stream, a.mm);

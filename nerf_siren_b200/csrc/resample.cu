@@ -85,13 +85,14 @@ extern "C" int nerfb_sample_pdf(const float* bins, const float* weights, const f
 }
 
 // ---- the fused call site: z_mid -> sample_pdf(weights[1:-1]) -> cat -> sort ---------------------------
+template <int NPL>      // elements per lane of the in-register sort (n_pad / 32), 0 = shared-memory sort for other sizes
 __global__ void __launch_bounds__(RS_WARPS * 32)
 resample_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse, const float* __restrict__ u, int det,
-                int64_t N, int Sc, int Si, float* __restrict__ z_fine) {
+                int64_t N, int Sc, int Si, int n_pad, float* __restrict__ z_fine) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int nb = Sc - 1, St = Sc + Si;
-  float* s_bins = smem + (size_t)wib * (3 * Sc + St);
+  float* s_bins = smem + (size_t)wib * (3 * Sc + n_pad);
   float* s_w = s_bins + Sc;
   float* s_cdf = s_w + Sc;
   float* s_all = s_cdf + Sc;                               // [0,Sc) coarse z, [Sc,St) new samples
@@ -108,16 +109,63 @@ resample_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_
       s_all[Sc + j] = invert_cdf(s_bins, s_cdf, nb, uj, eps, nullptr);
     }
     __syncwarp();
-    // rank-by-counting: position of element k = #(x < x_k) + #(x == x_k with index < k)
-    for (int k = lane; k < St; k += 32) {
-      const float xk = s_all[k];
-      int rank = 0;
-      for (int m = 0; m < St; ++m) {
-        const float xm = s_all[m];
-        rank += (xm < xk) || (xm == xk && m < k);
+    // warp bitonic sort of the St values in shared memory, padded with +inf to the next power of two (values only, so the
+    // result is the exact multiset torch.sort returns; no assumption that the inverse-CDF output is monotone to the ulp).
+    // log2(n)(log2(n)+1)/2 compare-exchange sweeps of n/2 pairs: 28 sweeps x 2 pairs per lane at St = 128, against the
+    // 128 x 128 / 32 comparisons per lane of a rank-by-counting sort.
+    if (NPL > 0) {
+      // in-register bitonic network: element idx = q * 32 + lane lives in v[q] of lane `lane`; partners at distance j < 32
+      // are one shuffle away, at distance j >= 32 they are another register of the same lane.
+      float v[NPL > 0 ? NPL : 1];
+#pragma unroll
+      for (int q = 0; q < NPL; ++q) { const int idx = q * 32 + lane; v[q] = idx < St ? s_all[idx] : INFINITY; }
+#pragma unroll
+      for (int k = 2; k <= NPL * 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          if (j >= 32) {
+            const int dq = j >> 5;
+#pragma unroll
+            for (int q = 0; q < NPL; ++q) {
+              if ((q & dq) == 0) {
+                const bool up = (((q * 32) & k) == 0);
+                const float a = v[q], b = v[q | dq];
+                const bool sw = (a > b) == up;
+                v[q] = sw ? b : a; v[q | dq] = sw ? a : b;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < NPL; ++q) {
+              const int idx = q * 32 + lane;
+              const float o = __shfl_xor_sync(0xffffffffu, v[q], j);
+              const bool up = (idx & k) == 0, lower = (lane & j) == 0;
+              // the lower index keeps the min in an ascending block, the max in a descending one
+              v[q] = (lower == up) ? fminf(v[q], o) : fmaxf(v[q], o);
+            }
+          }
+        }
       }
-      z_fine[r * St + rank] = xk;
+#pragma unroll
+      for (int q = 0; q < NPL; ++q) { const int idx = q * 32 + lane; if (idx < St) z_fine[r * St + idx] = v[q]; }
+      __syncwarp();
+      continue;
     }
+    for (int i = St + lane; i < n_pad; i += 32) s_all[i] = INFINITY;
+    __syncwarp();
+    for (int k = 2; k <= n_pad; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < (n_pad >> 1); t += 32) {
+          const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));      // index with bit j clear
+          const int hi = lo | j;
+          const float a = s_all[lo], b = s_all[hi];
+          const bool up = (lo & k) == 0;                              // ascending block
+          if ((a > b) == up) { s_all[lo] = b; s_all[hi] = a; }
+        }
+        __syncwarp();
+      }
+    }
+    for (int i = lane; i < St; i += 32) z_fine[r * St + i] = s_all[i];
     __syncwarp();
   }
 }
@@ -127,13 +175,22 @@ extern "C" int nerfb_resample(const float* z_coarse, const float* weights_coarse
   NERFB_CHECK_ARG(z_coarse && weights_coarse && z_fine && n_rays >= 0 && n_coarse >= 3 && n_importance >= 1);
   NERFB_CHECK_ARG(det || u);
   if (n_rays == 0) return NERFB_OK;
-  const size_t smem = (size_t)RS_WARPS * (4 * n_coarse + n_importance) * sizeof(float);
+  int n_pad = 2;
+  while (n_pad < n_coarse + n_importance) n_pad <<= 1;
+  const size_t smem = (size_t)RS_WARPS * (3 * n_coarse + n_pad) * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
   if (smem > 48 * 1024)
-    NERFB_CUDA(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute(resample_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t want = ceil_div64(n_rays, RS_WARPS);
   const int grid = (int)(want < NERFB_SM_COUNT * 16 ? want : NERFB_SM_COUNT * 16);
-  NERFB_LAUNCH(resample_kernel, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
-               n_importance, z_fine);
+  if (n_pad == 128 && smem <= 48 * 1024)
+    NERFB_LAUNCH(resample_kernel<4>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
+                 n_importance, n_pad, z_fine);
+  else if (n_pad == 256 && smem <= 48 * 1024)
+    NERFB_LAUNCH(resample_kernel<8>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
+                 n_importance, n_pad, z_fine);
+  else
+    NERFB_LAUNCH(resample_kernel<0>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
+                 n_importance, n_pad, z_fine);
   return NERFB_OK;
 }

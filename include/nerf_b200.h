@@ -41,7 +41,8 @@ extern "C" {
 #define NERFB_IN_GRID     2       /* dense occupancy query of extract_color_mesh.py:117-144: in0 = SIX float64 values on the
                                      device [xmin xmax ymin ymax zmin zmax], n_samples = N, n_rows = N^3; point p is row p of
                                      np.stack(np.meshgrid(x, y, z), -1).reshape(-1, 3) with np.linspace axes, generated and
-                                     encoded in-kernel; sigma_only, bf16 arm; out (N^3) = max(sigma, 0) (:141) */
+                                     encoded in-kernel; bf16 arm.  sigma_only: out (N^3) = max(sigma, 0) (:141); else out
+                                     (N^3, 4) = [rgb sigma] with view direction 0 (extract_mesh.ipynb cell 4) */
 
 typedef struct nerfb_mlp_desc {
   int32_t kind;        /* NERFB_KIND_* */
@@ -187,6 +188,15 @@ int nerfb_generate_rays(const float* c2w_host, int H, int W, double focal, float
                         float* rays, void* stream);
 int nerfb_finish_image(const float* rgb, const float* depth, const float* gt, int H, int W, uint8_t* rgb_u8,
                        float* depth_pfm, double* sq_err, void* stream);
+
+/* ---- the sparse `.vol` volume of extract_mesh.ipynb cell 7 ---------------------
+ * rgbsigma (n_voxels, 4) fp32 = the dense-grid output of nerfb_mlp_fwd (NERFB_IN_GRID, sigma_only = 0), 16-byte aligned;
+ * neg_step = (float)(-(xmax - xmin) / N).  Writes uint32 pairs (voxel index, r<<24 | g<<16 | b<<8 | alpha) for every voxel
+ * with alpha = 1 - exp(neg_step * max(sigma, 0)) > 0, in index order, up to `capacity` pairs; *n_valid (device int64) =
+ * the number of such voxels (call with capacity 0 to size the buffer).  n_voxels < 2^32 (the file format's index width). */
+int64_t nerfb_pack_vol_workspace_bytes(int64_t n_voxels);
+int nerfb_pack_vol(const float* rgbsigma, int64_t n_voxels, float neg_step, uint32_t* pairs, int64_t capacity,
+                   int64_t* n_valid, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
 int64_t nerfb_launch_count(void);

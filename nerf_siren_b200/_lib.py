@@ -53,6 +53,8 @@ SIGNATURES = {
                                    _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_generate_rays": (_I, [_P, _I, _I, C.c_double, _F, _F, _I, _P, _P]),
     "nerfb_finish_image": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
+    "nerfb_pack_vol_workspace_bytes": (_L, [_L]),
+    "nerfb_pack_vol": (_I, [_P, _L, _F, _P, _L, _P, _P, _L, _P]),
     "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P]),
 }
 

@@ -387,7 +387,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         mbar_wait_relaxed(&sm.x_consumed[b], xc_par[b]); xc_par[b] ^= 1;
         if (saving) { mbar_wait_relaxed(&sm.x_stored[b], xs_par[b]); xs_par[b] ^= 1; }
         if (SIREN) hilo_row(dirx, diry, dirz, x_base, row);
-        else if (args.in_mode == NERFB_IN_RAYS) encode_row(dirx, diry, dirz, pg.n_freq_dir, x_base, row);
+        else if (args.in_mode != NERFB_IN_EMBEDDED) encode_row(dirx, diry, dirz, pg.n_freq_dir, x_base, row);   // grid: dir = 0 (extract_mesh.ipynb cell 4)
         else copy_row(emb_src + pg.in_xyz, pg.in_dir, x_base, row);
         fence_proxy_async();
         __syncwarp();
@@ -801,7 +801,7 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
                int64_t ws_bytes, void* stream) {
   const bool siren = d.kind == NERFB_KIND_SIREN;
   if (siren && !film) return NERFB_E_BADARG;
-  if (in_mode == NERFB_IN_GRID && (!sigma_only || save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
+  if (in_mode == NERFB_IN_GRID && (save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0);
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;

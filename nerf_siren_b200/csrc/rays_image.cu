@@ -5,7 +5,9 @@
 //   nerfb_finish_image  -- eval.py:163-193: uint8 quantisation of the rendered rgb, nan_to_num + vertical flip of the
 //     depth map into the PFM payload order (datasets/depth_utils.py:43-69 writes np.flipud(image)), and the squared-error
 //     sum behind metrics.psnr (metrics.py:4-14).
-// Both are pure streaming kernels (HBM-bound): 32 B per ray out; 12 + 4 (+12) B in, 3 + 4 B out per pixel.
+//   nerfb_pack_vol      -- extract_mesh.ipynb cell 7: the sparse `.vol` volume Unity renders, 8 bytes per
+//     voxel with alpha > 0, from the dense (N^3, 4) [rgb sigma] query of kernel (1).
+// All are pure streaming kernels (HBM-bound): 32 B per ray out; 12 + 4 (+12) B in, 3 + 4 B out per pixel; 16 B in per voxel.
 #include "common.cuh"
 
 namespace {
@@ -89,6 +91,112 @@ __global__ void __launch_bounds__(256) finish_image_kernel(const float* __restri
 
 __global__ void zero_double_kernel(double* p) { *p = 0.0; }
 
+// ---- .vol packing (extract_mesh.ipynb cell 7) --------------------------------------------------------------------
+//   a = 1 - np.exp(-(xmax - xmin) / N * sigma)       float32 throughout (the Python scalar is weak: cast to float32)
+//   rgb = (rgbsigma[:, :3] * 255).astype(np.uint32);  i = np.where(a > 0)[0]
+//   s = rgb . [1<<24, 1<<16, 1<<8] + (a * 255).astype(np.uint32);  file = uint32 pairs (i, s) in index order
+// sigma is clamped at 0 first (cell 4: np.maximum(sigma, 0)).  exp is evaluated in double and rounded once (numpy's float32
+// exp is within 1 ulp of that; the alpha byte can differ by one where a * 255 sits on an integer).
+constexpr int VOL_BLOCK = 256, VOL_PER_THREAD = 4, VOL_CHUNK = VOL_BLOCK * VOL_PER_THREAD;
+
+__device__ __forceinline__ bool vol_voxel(const float4 v, float k, uint32_t* packed) {
+  const float sg = fmaxf(v.w, 0.f);
+  const float a = __fsub_rn(1.f, (float)exp((double)__fmul_rn(k, sg)));
+  const uint32_t r = (uint32_t)__fmul_rn(v.x, 255.f), g = (uint32_t)__fmul_rn(v.y, 255.f), b = (uint32_t)__fmul_rn(v.z, 255.f);
+  *packed = (r << 24) + (g << 16) + (b << 8) + (uint32_t)__fmul_rn(a, 255.f);
+  return a > 0.f;
+}
+
+// pass 1: number of voxels with alpha > 0 in each chunk of 1024
+__global__ void __launch_bounds__(VOL_BLOCK) vol_count_kernel(const float4* __restrict__ rgbsigma, int64_t n, float k,
+                                                              uint32_t* __restrict__ chunk_count) {
+  __shared__ uint32_t warp_cnt[VOL_BLOCK / 32];
+  for (int64_t c = blockIdx.x; c * VOL_CHUNK < n; c += gridDim.x) {
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int t = 0; t < VOL_PER_THREAD; ++t) {
+      const int64_t i = c * VOL_CHUNK + t * VOL_BLOCK + threadIdx.x;
+      uint32_t pk;
+      if (i < n && vol_voxel(__ldg(rgbsigma + i), k, &pk)) ++cnt;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t tot = 0;
+#pragma unroll
+      for (int w = 0; w < VOL_BLOCK / 32; ++w) tot += warp_cnt[w];
+      chunk_count[c] = tot;
+    }
+    __syncthreads();
+  }
+}
+
+// pass 2 (one CTA): exclusive prefix sum of the chunk counts into int64 offsets; total -> *n_valid
+__global__ void __launch_bounds__(1024) vol_scan_kernel(const uint32_t* __restrict__ chunk_count, int64_t n_chunks,
+                                                        int64_t* __restrict__ chunk_off, int64_t* __restrict__ n_valid) {
+  __shared__ int64_t warp_sum[32];
+  __shared__ int64_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int64_t base = 0; base < n_chunks; base += 1024) {
+    const int64_t i = base + threadIdx.x;
+    const int64_t v = i < n_chunks ? (int64_t)chunk_count[i] : 0;
+    int64_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int64_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) warp_sum[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+      int64_t ws = warp_sum[lane], wi = ws;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int64_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+      warp_sum[lane] = wi - ws;                     // exclusive over warps
+    }
+    __syncthreads();
+    const int64_t c0 = carry;
+    if (i < n_chunks) chunk_off[i] = c0 + warp_sum[w] + inc - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = c0 + warp_sum[w] + inc;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *n_valid = carry;
+}
+
+// pass 3: ordered write of the (index, packed rgba) pairs
+__global__ void __launch_bounds__(VOL_BLOCK) vol_write_kernel(const float4* __restrict__ rgbsigma, int64_t n, float k,
+                                                              const int64_t* __restrict__ chunk_off, int64_t capacity,
+                                                              uint2* __restrict__ pairs) {
+  __shared__ uint32_t warp_cnt[VOL_PER_THREAD][VOL_BLOCK / 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int64_t c = blockIdx.x; c * VOL_CHUNK < n; c += gridDim.x) {
+    uint32_t pk[VOL_PER_THREAD], before[VOL_PER_THREAD];
+    bool ok[VOL_PER_THREAD];
+#pragma unroll
+    for (int t = 0; t < VOL_PER_THREAD; ++t) {
+      const int64_t i = c * VOL_CHUNK + t * VOL_BLOCK + threadIdx.x;
+      ok[t] = i < n && vol_voxel(__ldg(rgbsigma + i), k, &pk[t]);
+      const uint32_t m = __ballot_sync(0xffffffffu, ok[t]);
+      before[t] = __popc(m & ((1u << lane) - 1u));
+      if (lane == 0) warp_cnt[t][w] = __popc(m);
+    }
+    __syncthreads();
+    int64_t off = chunk_off[c];
+#pragma unroll
+    for (int t = 0; t < VOL_PER_THREAD; ++t) {
+      uint32_t pre = 0, row = 0;
+#pragma unroll
+      for (int x = 0; x < VOL_BLOCK / 32; ++x) { const uint32_t v = warp_cnt[t][x]; if (x < w) pre += v; row += v; }
+      const int64_t dst = off + pre + before[t];
+      if (ok[t] && dst < capacity) pairs[dst] = make_uint2((uint32_t)(c * VOL_CHUNK + t * VOL_BLOCK + threadIdx.x), pk[t]);
+      off += row;
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace
 
 extern "C" int nerfb_generate_rays(const float* c2w_host, int H, int W, double focal, float near, float far, int ndc,
@@ -103,6 +211,28 @@ extern "C" int nerfb_generate_rays(const float* c2w_host, int H, int W, double f
   const int64_t want = ceil_div64((int64_t)H * W, 256);
   const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
   NERFB_LAUNCH(generate_rays_kernel, grid, 256, 0, stream, a, rays);
+  return NERFB_OK;
+}
+
+extern "C" int64_t nerfb_pack_vol_workspace_bytes(int64_t n_voxels) {
+  const int64_t n_chunks = ceil_div64(n_voxels > 0 ? n_voxels : 1, VOL_CHUNK);
+  return ((n_chunks * 4 + 255) & ~(int64_t)255) + n_chunks * 8;
+}
+
+extern "C" int nerfb_pack_vol(const float* rgbsigma, int64_t n_voxels, float neg_step, uint32_t* pairs, int64_t capacity,
+                              int64_t* n_valid, void* workspace, int64_t workspace_bytes, void* stream) {
+  NERFB_CHECK_ARG(rgbsigma && n_valid && n_voxels >= 0 && n_voxels < ((int64_t)1 << 32) && capacity >= 0 && (pairs || capacity == 0) &&
+                  workspace && workspace_bytes >= nerfb_pack_vol_workspace_bytes(n_voxels));
+  NERFB_CHECK_ARG((reinterpret_cast<uintptr_t>(rgbsigma) & 15) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0 &&
+                  (reinterpret_cast<uintptr_t>(pairs) & 7) == 0);
+  const int64_t n_chunks = ceil_div64(n_voxels > 0 ? n_voxels : 1, VOL_CHUNK);
+  uint32_t* cnt = static_cast<uint32_t*>(workspace);
+  int64_t* off = reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + ((n_chunks * 4 + 255) & ~(int64_t)255));
+  const float4* v = reinterpret_cast<const float4*>(rgbsigma);
+  const int grid = (int)(n_chunks < NERFB_SM_COUNT * 8 ? n_chunks : NERFB_SM_COUNT * 8);
+  NERFB_LAUNCH(vol_count_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, cnt);
+  NERFB_LAUNCH(vol_scan_kernel, 1, 1024, 0, stream, cnt, n_chunks, off, n_valid);
+  if (capacity > 0) NERFB_LAUNCH(vol_write_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, off, capacity, reinterpret_cast<uint2*>(pairs));
   return NERFB_OK;
 }
 

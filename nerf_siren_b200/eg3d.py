@@ -182,3 +182,51 @@ class ImportanceRenderer(nn.Module):
                                             sample_coordinates[b].contiguous(), float(options["box_warp"]))
             rgbs.append(rgb); sigmas.append(sigma)
         return {"rgb": torch.stack(rgbs, 0), "sigma": torch.stack(sigmas, 0).unsqueeze(-1)}
+
+
+# rendering_kwargs the reference hard-codes for its Unity scenes (eg3d_training/eg3d_renderer.py:30-36); only the fields the
+# volume renderer reads
+DEFAULT_RENDERING_KWARGS = {
+    "depth_resolution": 64, "depth_resolution_importance": 64, "ray_start": 0.1, "ray_end": 10.0, "box_warp": 15.0,
+    "white_back": False, "disparity_space_sampling": False, "clamp_mode": "softplus", "decoder_lr_mul": 1.0,
+}
+
+
+class LearnedPlanes(nn.Module):
+    """Stand-in for the plane source: a directly optimisable (1, 96, H, W) feature image.  The reference produces the planes
+    with a StyleGAN2 backbone (``TriPlaneGenerator.backbone.synthesis``, eg3d_training/triplane.py:61), which is outside the
+    render_rays path (out of scope); any module / callable returning (B, 96, H, W) can take its place."""
+
+    def __init__(self, resolution=256, channels=96):
+        super().__init__()
+        self.planes = nn.Parameter(torch.randn(1, channels, resolution, resolution))
+
+    def forward(self, *_a, **_k):
+        return self.planes
+
+
+class EG3D_Renderer(nn.Module):
+    """eg3d_training/eg3d_renderer.py:6-67: the object ``NeRFSystem_eg3d`` renders with (system.py:22,75) and
+    ``extract_color_mesh_eg3d.py:171-190`` samples.  ``render`` returns the reference's six keys with the batch axis
+    squeezed; ``sample`` returns run_model's {'rgb', 'sigma'}.  ``plane_source``: module / callable -> (1, 96, H, W)."""
+
+    def __init__(self, plane_source=None, rendering_kwargs=None, decoder=None):
+        super().__init__()
+        self.rendering_kwargs = dict(DEFAULT_RENDERING_KWARGS if rendering_kwargs is None else rendering_kwargs)
+        self.plane_source = LearnedPlanes() if plane_source is None else plane_source
+        self.decoder = decoder if decoder is not None else OSGDecoder(
+            32, {"decoder_lr_mul": self.rendering_kwargs.get("decoder_lr_mul", 1.0), "decoder_output_dim": 3})
+        self.renderer = ImportanceRenderer()
+
+    def _planes(self, conditioning_params):
+        planes = self.plane_source(conditioning_params) if callable(self.plane_source) else self.plane_source
+        return planes.view(len(planes), 3, 32, planes.shape[-2], planes.shape[-1])       # triplane.py:65
+
+    def render(self, conditioning_params, ray_origins, ray_directions, **kw):
+        out = self.renderer(self._planes(conditioning_params), self.decoder, ray_origins.unsqueeze(0),
+                            ray_directions.unsqueeze(0), self.rendering_kwargs, **kw)
+        keys = ("rgb_coarse", "depth_coarse", "opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine")
+        return {k: v.squeeze(0) for k, v in zip(keys, out)}
+
+    def sample(self, coordinates, directions):
+        return self.renderer.run_model(self._planes(-1), self.decoder, coordinates, directions, self.rendering_kwargs)

@@ -79,3 +79,20 @@ def sigma_grid(nerf, embedding_xyz, N_grid, x_range, y_range, z_range):
     if not ops.mlp_supported(desc, _lib.PREC_BF16, False):
         raise RuntimeError("the dense-grid query runs on the tcgen05 arm: this model shape is outside it")
     return ops.sigma_grid(desc, _field.flat_params(nerf).detach(), int(N_grid), x_range, y_range, z_range)
+
+
+@torch.no_grad()
+def export_vol(filename, nerf, embedding_xyz, N_grid, x_range, y_range, z_range):
+    """extract_mesh.ipynb cells 4 + 7: the sparse ``.vol`` volume for Unity -- dense (N^3, 4) [rgb sigma] query with view
+    direction 0 (kernel (1), grid input), alpha = 1 - exp(-(xmax - xmin) / N * max(sigma, 0)), uint32 pairs
+    (index, r<<24 | g<<16 | b<<8 | alpha) of the voxels with alpha > 0.  Everything per-voxel runs on the device; the host
+    writes the bytes.  Returns the (n_valid, 2) uint32 CUDA tensor.  The reference asserts N == 512 for the Unity shader."""
+    desc = nerf._desc(False, embedding_xyz.N_freqs, 4, embedding_xyz.logscale)
+    if not ops.mlp_supported(desc, _lib.PREC_BF16, False):
+        raise RuntimeError("the dense-grid query runs on the tcgen05 arm: this model shape is outside it")
+    rgbsigma = ops.sigma_grid(desc, _field.flat_params(nerf).detach(), int(N_grid), x_range, y_range, z_range, sigma_only=False)
+    pairs = ops.pack_vol(rgbsigma, -(x_range[1] - x_range[0]) / N_grid)
+    if filename is not None:
+        with open(filename, "wb") as f:
+            f.write(pairs.cpu().numpy().tobytes())
+    return pairs

@@ -303,14 +303,33 @@ def finish_image(rgb, h, w, depth=None, gt=None):
     return u8, dp, se
 
 
-def sigma_grid(desc, params, n_grid, x_range, y_range, z_range):
-    """Dense occupancy grid of extract_color_mesh.py:117-144 -> (N, N, N) max(sigma, 0), points generated in-kernel."""
+def sigma_grid(desc, params, n_grid, x_range, y_range, z_range, sigma_only=True):
+    """Dense query grid of extract_color_mesh.py:117-144 / extract_mesh.ipynb cell 4, points generated in-kernel:
+    sigma_only -> (N, N, N) max(sigma, 0); else (N^3, 4) [rgb sigma] with view direction 0."""
     dev = params.device
     rg = torch.tensor([x_range[0], x_range[1], y_range[0], y_range[1], z_range[0], z_range[1]], dtype=torch.float64, device=dev)
     n_pts = n_grid ** 3
-    ws = mlp_workspace(desc, _lib.PREC_BF16, n_pts, True, False, dev)
-    out = torch.empty(n_pts, 1, device=dev, dtype=torch.float32)
+    ws = mlp_workspace(desc, _lib.PREC_BF16, n_pts, bool(sigma_only), False, dev)
+    out = torch.empty(n_pts, 1 if sigma_only else 4, device=dev, dtype=torch.float32)
     ws_ptr, ws_bytes = _aligned(ws)
     check(lib.nerfb_mlp_fwd(C.byref(desc), _lib.PREC_BF16, _lib.IN_GRID, _req(params, "params"), 0, rg.data_ptr(), 0, n_pts,
-                            int(n_grid), 1, 0, out.data_ptr(), ws_ptr, ws_bytes, _stream()), "nerfb_mlp_fwd[grid]")
-    return out.view(n_grid, n_grid, n_grid)
+                            int(n_grid), 1 if sigma_only else 0, 0, out.data_ptr(), ws_ptr, ws_bytes, _stream()), "nerfb_mlp_fwd[grid]")
+    return out.view(n_grid, n_grid, n_grid) if sigma_only else out
+
+
+def pack_vol(rgbsigma, neg_step):
+    """extract_mesh.ipynb cell 7: (n, 4) [rgb sigma] -> uint32 (n_valid, 2) pairs (voxel index, packed rgba), index order."""
+    n = rgbsigma.shape[0]
+    dev = rgbsigma.device
+    n_valid = torch.zeros(1, dtype=torch.int64, device=dev)
+    if n == 0:
+        return torch.empty(0, 2, dtype=torch.uint32, device=dev)
+    ws = torch.empty(int(lib.nerfb_pack_vol_workspace_bytes(n)) + 1024, dtype=torch.uint8, device=dev)
+    ws_ptr, ws_bytes = _aligned(ws)
+    src = _req(rgbsigma, "rgbsigma")
+    check(lib.nerfb_pack_vol(src, n, float(neg_step), 0, 0, n_valid.data_ptr(), ws_ptr, ws_bytes, _stream()), "nerfb_pack_vol[count]")
+    k = int(n_valid.item())
+    pairs = torch.empty(max(k, 1), 2, dtype=torch.uint32, device=dev)
+    check(lib.nerfb_pack_vol(src, n, float(neg_step), pairs.data_ptr(), k, n_valid.data_ptr(), ws_ptr, ws_bytes, _stream()),
+          "nerfb_pack_vol")
+    return pairs[:k]

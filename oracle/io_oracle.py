@@ -83,3 +83,18 @@ def grid_points(N, x_range, y_range, z_range) -> torch.Tensor:
     y = np.linspace(y_range[0], y_range[1], N)
     z = np.linspace(z_range[0], z_range[1], N)
     return torch.FloatTensor(np.stack(np.meshgrid(x, y, z), -1).reshape(-1, 3))
+
+
+def vol_pack(rgbsigma: np.ndarray, xmin: float, xmax: float, N: int) -> np.ndarray:
+    """extract_mesh.ipynb cells 4 + 7 (the `.vol` file Unity's volume renderer reads), the notebook's numpy statements on an
+    (N^3, 4) float32 [rgb sigma] array; returns the uint32 array whose bytes are the file.  (The notebook asserts N == 512;
+    the arithmetic does not depend on it.)"""
+    sigma = np.maximum(rgbsigma[:, -1], 0)                      # cell 4
+    a = 1 - np.exp(-(xmax - xmin) / N * sigma)
+    a = a.flatten()
+    rgb = (rgbsigma[:, :3] * 255).astype(np.uint32)
+    i = np.where(a > 0)[0]
+    rgb = rgb[i]
+    a = a[i]
+    s = rgb.dot(np.array([1 << 24, 1 << 16, 1 << 8])) + (a * 255).astype(np.uint32)
+    return np.stack([i, s], -1).astype(np.uint32).flatten()

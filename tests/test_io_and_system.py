@@ -87,6 +87,78 @@ def test_sigma_grid_matches_oracle():
     assert float(np.abs(got.numpy() - ref).max()) <= 3e-2 * scale
 
 
+def test_oracle_vol_pack_known_answers():
+    """extract_mesh.ipynb cell 7 by hand: voxel 1 (sigma <= 0) is dropped, rgb truncates, alpha = trunc(255 (1 - exp(-dx sigma)))."""
+    v = np.array([[0.5, 0.25, 1.0, 100.0], [0.9, 0.9, 0.9, -3.0], [0.0, 0.999, 0.2, 1e4]], np.float32)
+    got = IO.vol_pack(v, -1.2, 1.2, 512).reshape(-1, 2)
+    assert got.dtype == np.uint32 and got[:, 0].tolist() == [0, 2]
+    a0 = int(np.float32(255) * (np.float32(1) - np.exp(np.float32(-2.4 / 512) * np.float32(100.0))))
+    assert got[0, 1] == (127 << 24) + (63 << 16) + (255 << 8) + a0
+    assert got[1, 1] == (0 << 24) + (254 << 16) + (51 << 8) + 255
+
+
+@pytest.mark.gpu
+def test_vol_export_matches_oracle(tmp_path):
+    """Row f4, `.vol` packing: the device compaction against the notebook's numpy on the SAME (N^3, 4) grid output -- index
+    set and rgb bytes identical, alpha byte within 1 (numpy's float32 exp vs a correctly rounded one); and the grid's rgb /
+    sigma against the fp32 field at bf16 tolerance."""
+    import nerf_siren_b200 as nb
+    from nerf_siren_b200 import _field, evaluation as ev, ops
+    p = O.nerf_field(seed=22)
+    m = nb.NeRF().to(DEV); m.load_state_dict(p)
+    N, xr, yr, zr = 20, (-1.2, 1.2), (-1.2, 1.2), (-1.2, 1.2)
+    emb = nb.Embedding(3, 10)
+    rgbsigma = ops.sigma_grid(m._desc(False, 10, 4, True), _field.flat_params(m).detach(), N, xr, yr, zr, sigma_only=False)
+    pts = IO.grid_points(N, xr, yr, zr)
+    x = torch.cat([O.embed(pts, 10), O.embed(torch.zeros_like(pts), 4)], 1)
+    ref = O.nerf_mlp(p, x, False).numpy()
+    got = rgbsigma.cpu().numpy()
+    def logit(v):
+        v = np.clip(v.astype(np.float64), 1e-6, 1 - 1e-6)
+        return np.log(v / (1 - v))
+    lg, lr = logit(got[:, :3]), logit(ref[:, :3])                     # bf16 tolerance on the pre-sigmoid scale, as for sigma
+    assert np.abs(lg - lr).max() <= 3e-2 * np.abs(lr).max() and np.abs(got[:, :3] - ref[:, :3]).mean() <= 1e-2
+    assert np.abs(got[:, 3] - ref[:, 3]).max() <= 3e-2 * np.abs(ref[:, 3]).max()
+    path = os.path.join(tmp_path, "scene.vol")
+    pairs = ev.export_vol(path, m, emb, N, xr, yr, zr).cpu().numpy()
+    want = IO.vol_pack(got, xr[0], xr[1], N).reshape(-1, 2)
+    assert len(want) > 100 and len(want) < N ** 3                  # the case exercises both kept and dropped voxels
+    assert pairs.shape == want.shape and np.array_equal(pairs[:, 0], want[:, 0])
+    assert np.array_equal(pairs[:, 1] >> 8, want[:, 1] >> 8)
+    assert np.abs((pairs[:, 1] & 255).astype(np.int64) - (want[:, 1] & 255).astype(np.int64)).max() <= 1
+    assert open(path, "rb").read() == pairs.tobytes()
+    # ragged sizes: a voxel count that is not a multiple of the 1024-voxel chunk, all-empty and empty inputs
+    odd = rgbsigma[:1531].contiguous()
+    assert np.array_equal(ops.pack_vol(odd, -2.4 / N).cpu().numpy()[:, 0], IO.vol_pack(got[:1531], xr[0], xr[1], N).reshape(-1, 2)[:, 0])
+    none = rgbsigma.clone(); none[:, 3] = -1.0
+    assert ops.pack_vol(none, -2.4 / N).shape == (0, 2)
+    assert ops.pack_vol(rgbsigma[:0], -2.4 / N).shape == (0, 2)
+
+
+@pytest.mark.gpu
+def test_eg3d_renderer_glue():
+    """Row f3: eg3d_training/eg3d_renderer.py:47-67 -- render() returns the six reference keys with the batch axis squeezed,
+    sample() returns run_model's dict; both equal the ImportanceRenderer they wrap (same planes, decoder, random numbers)."""
+    from nerf_siren_b200 import eg3d
+    torch.manual_seed(5)
+    kw = dict(eg3d.DEFAULT_RENDERING_KWARGS, depth_resolution=12, depth_resolution_importance=12, ray_start=0.5, ray_end=4.0, box_warp=3.0)
+    r = eg3d.EG3D_Renderer(eg3d.LearnedPlanes(resolution=32), kw).to(DEV)
+    n = 300
+    o = torch.randn(n, 3, device=DEV) * 0.1 + torch.tensor([0.0, 0.0, -2.0], device=DEV)
+    d = torch.nn.functional.normalize(torch.randn(n, 3, device=DEV) * 0.2 + torch.tensor([0.0, 0.0, 1.0], device=DEV), dim=-1)
+    rc, u = torch.rand(1, n, 12, 1, device=DEV), torch.rand(1, n, 12, device=DEV)
+    with torch.no_grad():
+        out = r.render(-1, o, d, rand_coarse=rc, u=u)
+        planes = r.plane_source().view(1, 3, 32, 32, 32)
+        want = eg3d.ImportanceRenderer()(planes, r.decoder, o[None], d[None], kw, rand_coarse=rc, u=u)
+        smp = r.sample(o[None] * 0.3, d[None])
+    assert list(out) == ["rgb_coarse", "depth_coarse", "opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine"]
+    for k, w in zip(out, want):
+        assert out[k].shape == w.shape[1:] and torch.equal(out[k], w[0])
+    assert smp["rgb"].shape == (1, n, 3) and smp["sigma"].shape == (1, n, 1)
+    assert "plane_source.planes" in dict(r.named_parameters())       # checkpoint prefix 'eg3d_renderer.' loads like system.py:25
+
+
 def test_checkpoint_layout_and_schedulers(tmp_path):
     """Lightning key layout (utils/__init__.py:56-86 reads it back), MultiStepLR / cosine / poly as utils/__init__.py:33-52."""
     pytest.importorskip("nerf_siren_b200")

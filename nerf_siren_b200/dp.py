@@ -106,7 +106,7 @@ class DataParallelStep:
 
     def __init__(self, models: List[nn.Module], embeddings: List[nn.Module], N_samples=64, N_importance=64,
                  use_disp=False, perturb=1.0, noise_std=1.0, chunk=32 * 1024, white_back=True, lr=5e-4,
-                 betas=(0.9, 0.999), eps=1e-8, group=None, render_fn=None):
+                 betas=(0.9, 0.999), eps=1e-8, group=None, render_fn=None, cuda_graph=False):
         from .models.rendering import render_rays
         self.models, self.embeddings = list(models), list(embeddings)
         self.render_fn = render_fn or render_rays
@@ -117,6 +117,35 @@ class DataParallelStep:
         self.exp_avg = torch.zeros_like(self.params.flat.data)
         self.exp_avg_sq = torch.zeros_like(self.params.flat.data)
         self.steps = 0
+        # cuda_graph: forward + backward of one batch shape is captured once and replayed (the ~60 launches of a step
+        # cost more host time than the GPU needs for the small ones); the all-reduce and the Adam kernel stay outside,
+        # so the step counter and the collective are ordinary launches.
+        self.cuda_graph = bool(cuda_graph)
+        self._graphs = {}
+        self.graph_launches = 0            # kernels of this library launched by graph replays (ops.launch_count() only sees host calls)
+
+    def _captured(self, rays: torch.Tensor, rgbs: torch.Tensor):
+        key = (tuple(rays.shape), tuple(rgbs.shape))
+        st = self._graphs.get(key)
+        if st is None:
+            import types
+            dev = self.params.flat.device
+            st = types.SimpleNamespace(rays=torch.empty(rays.shape, device=dev, dtype=torch.float32),
+                                       rgbs=torch.empty(rgbs.shape, device=dev, dtype=torch.float32))
+            st.rays.copy_(rays); st.rgbs.copy_(rgbs)
+            side = torch.cuda.Stream(device=dev)             # warm-up off the capture stream (allocator, autograd, lazy inits)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    self.forward_backward(st.rays, st.rgbs)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            before = ops.launch_count()
+            st.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(st.graph):
+                st.loss = self.forward_backward(st.rays, st.rgbs)
+            st.launches = ops.launch_count() - before
+            self._graphs[key] = st
+        return st
 
     def forward_backward(self, rays: torch.Tensor, rgbs: torch.Tensor) -> torch.Tensor:
         self.params.zero_grad()
@@ -126,7 +155,15 @@ class DataParallelStep:
         return loss.detach()
 
     def step(self, rays: torch.Tensor, rgbs: torch.Tensor) -> torch.Tensor:
-        loss = self.forward_backward(rays, rgbs)
+        if self.cuda_graph and self.params.flat.is_cuda:
+            st = self._captured(rays, rgbs)
+            st.rays.copy_(rays, non_blocking=True)          # host (pinned) or device batch -> the graph's input buffers
+            st.rgbs.copy_(rgbs, non_blocking=True)
+            st.graph.replay()
+            self.graph_launches += st.launches
+            loss = st.loss.clone()
+        else:
+            loss = self.forward_backward(rays, rgbs)
         g = self.params.flat.grad
         allreduce_sum_(g, self.group)                       # the batch-boundary collective (4.77 MB for NeRF x2)
         self.steps += 1

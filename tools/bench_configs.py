@@ -93,7 +93,7 @@ def cls_train():
     models = [nb.NeRF_3D(CLS=6).to(dev), nb.NeRF_3D(CLS=6).to(dev)]
     emb = [nb.Embedding(3, 10), nb.Embedding(3, 4)]
     n = 8192
-    trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, False)
+    trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, False, cuda_graph=True)
     rays = synth.llff_rays(n, seed=10 + rank).to(dev)
     rgbs = synth.target_rgbs(n, seed=20 + rank).to(dev)
     ms = timed(lambda: trainer.step(rays, rgbs), 5)
@@ -112,7 +112,7 @@ def siren_train():
     models = [nb.SirenField().to(dev), nb.SirenField().to(dev)]
     emb = [nb.Embedding(3, 0), nb.Embedding(3, 0)]
     n = 4096
-    trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, True)
+    trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, True, cuda_graph=True)
     rays = synth.blender_rays(n, seed=10 + rank).to(dev)
     rgbs = synth.target_rgbs(n, seed=20 + rank).to(dev)
     ms = timed(lambda: trainer.step(rays, rgbs), 5)

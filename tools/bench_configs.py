@@ -8,7 +8,7 @@
 
 Timing: CUDA events around whole public-API calls (render_rays / DataParallelStep.step) on resident inputs, after warm-up,
 max over ranks when launched under torchrun.  MLP FLOPs per sample from SURVEY 8d.
-    python tools/bench_configs.py [render|siren|cls ...]
+    python tools/bench_configs.py [render|siren|cls|siren_train|render_e2e ...]
 """
 import json
 import os
@@ -123,7 +123,33 @@ def siren_train():
           "config": {"workload": "SIREN variant of configs[1]: 4096 rays / GPU, 64+64 samples"}})
 
 
-for what in (sys.argv[1:] or ["render", "siren", "cls", "siren_train"]):
+def render_e2e():
+    """The render arm end to end through the public eval-side API (rows f2 + path + f3): host camera pose in, uint8 image and
+    PFM depth payload on the host out -- rays generated on the device, 20 chunks of 32k rays, image finished on the device."""
+    from nerf_siren_b200 import evaluation as ev
+    torch.manual_seed(0)
+    nb.set_precision("auto")
+    models = [nb.NeRF().to(dev), nb.NeRF().to(dev)]
+    emb = [nb.Embedding(3, 10), nb.Embedding(3, 4)]
+    c2w = torch.tensor([[1.0, 0.0, 0.0, 0.0], [0.0, 0.0, -1.0, -4.0], [0.0, 1.0, 0.0, 0.0]])
+    H = W = 800
+    focal = 0.5 * W / 0.3604                                   # camera_angle_x = 0.6911 (lego)
+    gt = torch.rand(H * W, 3, device=dev)
+
+    def run():
+        r = ev.render_image(models, emb, c2w, H, W, focal, 2.0, 6.0, 64, 64, white_back=True, gt=gt, device=dev)
+        return r["img"].cpu(), r["depth_pfm"].cpu(), r["psnr"]
+    ms = timed(run, 3)
+    emit({"metric": "rays/s, NeRF 800x800 image end to end (pose in, uint8 image + PFM depth on the host out)",
+          "value": H * W / ms * 1e3, "unit": "rays/s", "n_gpus": 1, "ms_per_image": ms, "d2h_bytes_per_image": H * W * 7,
+          "config": {"workload": "eval.py:152-193 iteration: generate rays, 64+64 render (test_time), quantise / flip / PSNR"}})
+
+
+for what in (sys.argv[1:] or ["render", "siren", "cls", "siren_train", "render_e2e"]):
+    if what == "render_e2e":
+        if rank == 0:
+            render_e2e()
+        continue
     if what in ("render", "siren"):
         render(what)
     elif what == "cls":

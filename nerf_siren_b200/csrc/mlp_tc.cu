@@ -444,17 +444,24 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 26] = clock64();)
             const uint32_t (&vv)[16] = v[j & 1];
             float f[16];
-            uint32_t gcos[8];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               float2 r0, r1;
               if (SIREN) {      // sin(freq * (acc + b) + phase) = sin(freq * acc + (freq * b + phase))   (models/nerf.py:149-151)
                 r0 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(sc[i].x, sc[i].y), make_float2(bb[i].x, bb[i].y));
                 r1 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(sc[i].z, sc[i].w), make_float2(bb[i].z, bb[i].w));
-                if (SAVE) {       // training: d/dz sin(freq z + phase) = freq cos(.) is the dgrad kernel's multiplicative gate
+                if (SAVE) {       // training: d/dz sin(freq z + phase) = freq cos(.) is the dgrad kernel's multiplicative gate.
+                  // Only sign(cos) is saved (one bit per element, same mask record as the ReLU gates): the dgrad rebuilds
+                  // |cos| = sqrt(1 - sin^2) from the saved sine image it shares with the wgrad and multiplies by freq.
                   float c0, c1, c2, c3;
                   __sincosf(r0.x, &r0.x, &c0); __sincosf(r0.y, &r0.y, &c1); __sincosf(r1.x, &r1.x, &c2); __sincosf(r1.y, &r1.y, &c3);
-                  gcos[2 * i] = pack_bf16(c0 * sc[i].x, c1 * sc[i].y); gcos[2 * i + 1] = pack_bf16(c2 * sc[i].z, c3 * sc[i].w);
+                  if (j < 2) {
+                    gate_lo = __funnelshift_l(__float_as_uint(c0), gate_lo, 1); gate_lo = __funnelshift_l(__float_as_uint(c1), gate_lo, 1);
+                    gate_lo = __funnelshift_l(__float_as_uint(c2), gate_lo, 1); gate_lo = __funnelshift_l(__float_as_uint(c3), gate_lo, 1);
+                  } else {
+                    gate_hi = __funnelshift_l(__float_as_uint(c0), gate_hi, 1); gate_hi = __funnelshift_l(__float_as_uint(c1), gate_hi, 1);
+                    gate_hi = __funnelshift_l(__float_as_uint(c2), gate_hi, 1); gate_hi = __funnelshift_l(__float_as_uint(c3), gate_hi, 1);
+                  }
                 } else {
                   r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y);
                 }
@@ -521,19 +528,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
               NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 23] = clock64();)
               if (st_saved) need_free |= 1u << j;
             }
-            if (SIREN && SAVE && st_saved) {       // cos image [block][column quarter][row][16 x bf16]: a warp writes 1 KB contiguous
-              uint4* dst = reinterpret_cast<uint4*>(args.save + tile * (int64_t)pg.tile_save_bytes + sm.step_mask[s] +
-                                                    ((j * 4 + c4) * TILE_M + row) * 32);
-              dst[0] = make_uint4(gcos[0], gcos[1], gcos[2], gcos[3]);
-              dst[1] = make_uint4(gcos[4], gcos[5], gcos[6], gcos[7]);
-            }
             tc_fence_before();
             __syncwarp();
             if (j < st_out && lane == 0) mbar_arrive_addr(ready + 8u * (uint32_t)j);
             NERFB_TRACE(if (tr && j < 2) args.trace[gs * 32 + 24 + j] = clock64();)
           }
         }
-        if (st_saved && st_relu) {
+        if (st_saved && (st_relu || (SIREN && SAVE))) {
           const int mo = sm.step_mask[s];
           if (mo >= 0)
             *reinterpret_cast<uint2*>(args.save + tile * (int64_t)pg.tile_save_bytes + mo + c4 * (TILE_M * 8) + row * 8) = make_uint2(gate_lo, gate_hi);   // [c4][row]: a warp writes 256 contiguous bytes
@@ -695,7 +696,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
       TcStep& st = pg.s[ns++];
       st = TcStep{};
       st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1; st.mask_off = -1;
-      if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; st.mask_off = sv; sv += 4 * BLK_BYTES; }      // activations | freq cos image
+      if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; st.mask_off = sv; sv += TILE_M * 32; }      // activations (sine image) | sign(cos) bit mask
       if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], 3, 0, 3, 256, 1); }
       else for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], 256, 64 * j, 64, 256); }
       st.bias_off = add_bias(o.b[i], 256, i);
@@ -704,7 +705,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     if (!sigma_only) {
       TcStep& cl = pg.s[ns++]; cl = TcStep{};
       cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = save ? 4 : 0; cl.store_only = 1; cl.film = d.D; cl.save_off = -1; cl.mask_off = -1;
-      if (save) { cl.save_off = sv; sv += 4 * BLK_BYTES; cl.mask_off = sv; sv += 4 * BLK_BYTES; pg.save_dir_off = sv; sv += BLK_BYTES; }
+      if (save) { cl.save_off = sv; sv += 4 * BLK_BYTES; cl.mask_off = sv; sv += TILE_M * 32; pg.save_dir_off = sv; sv += BLK_BYTES; }
       for (int j = 0; j < 4; ++j) { cl.src[cl.n_kb++] = j; add_slab(o.w_dir, 259, 3 + 64 * j, 64, 256); }
       cl.src[cl.n_kb++] = SRC_X; cl.wait_x = 1; cl.x_done = 1; add_slab(o.w_dir, 259, 0, 3, 256, 1);
       cl.bias_off = add_bias(o.b_dir, 256, d.D);

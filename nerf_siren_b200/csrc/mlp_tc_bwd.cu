@@ -58,6 +58,8 @@ struct BStep {
   int add_sigma;     // output += d_sigma (x) w_sigma before gating (the sigma head reads the same activation)
   int save_off;      // backward-record offset of this step's output dZ (4 blocks)
   int add_cls;       // output += g_cls W_eff before storing (NeRF_3D class head reads xyz_encoding_final, nerf_cls.py:104)
+  int act_off;       // SIREN: forward-record offset of the gated layer's saved sine image (4 blocks); film_off: its FiLM row * 256
+  int film_off;
 };
 struct BProgram {
   int n_steps;
@@ -67,9 +69,10 @@ struct BProgram {
   int h_off;         // backward-record offset of the head block: columns 0..3 = [g_r g_g g_b d_sigma] per sample
   int fwd_tile_bytes, bwd_tile_bytes;
   int n_cls, out_c;  // NeRF_3D: class-head width; floats per output row (4 + n_cls)
-  int siren;         // SIREN: gates are the forward's freq*cos images (multiplicative), colour layer is 256 wide
+  int siren;         // SIREN: gates are freq * cos(.) rebuilt from sign(cos) masks + the saved sine images, colour layer is 256 wide
   int n_pro;         // dZ blocks the prologue produces: 2 (NeRF direction layer, 128 wide) or 4 (SIREN colour layer)
   int rgb_in;        // fan-in of the rgb head: 128 / 256
+  int hd_act_off, hd_film_off;   // SIREN: sine image / FiLM row of the colour layer (the prologue's gate)
 };
 
 struct DgradArgs {
@@ -77,6 +80,7 @@ struct DgradArgs {
   const uint8_t* wblob;            // transposed bf16 slabs in schedule order
   const float* heads;              // w_sigma[256] | w_rgb[3*128]
   const float* weff;               // NeRF_3D: merged class-head matrix, fp32 [16 x 256] (forward workspace)
+  const float* film;               // SIREN: [frequencies (D+1) x 256 | phase shifts], the forward's FiLM vector
   const float* out; const float* d_out;
   const uint8_t* fwd_rec; uint8_t* bwd_rec;
   int64_t P; int64_t n_tiles;
@@ -104,14 +108,31 @@ __device__ __forceinline__ void apply_gate16(float (&f)[16], uint32_t bits) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) f[i] = ((bits >> (15 - i)) & 1u) ? 0.f : f[i];
 }
-// SIREN gate: multiply by the 16 bf16 values freq * cos(freq z + phase) the forward kernel parked for this thread
-__device__ __forceinline__ void apply_cos16(float (&f)[16], const uint8_t* src) {
-  const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)), b = __ldg(reinterpret_cast<const uint4*>(src) + 1);
-  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+// SIREN gate freq * cos(freq z + phase) (models/nerf.py:149-151) for this thread's 16 columns of block j: sign(cos) from the
+// forward's bit mask (bit 15 - i, 1 = negative), |cos| = sqrt(1 - sin^2) from the saved bf16 sine image (the same swizzled
+// block the wgrad reads as its operand), freq from the FiLM vector.  The sine's bf16 rounding makes |cos| ill-conditioned
+// only where |cos| < ~0.06 (absolute error <= 0.06 there, <= 2e-3 / |cos| elsewhere).
+__device__ __forceinline__ void load_sine16(uint4 (&sv)[2], const uint8_t* act_blk, uint32_t row_off, uint32_t row_x, int c4) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    f[2 * i] *= __uint_as_float(w[i] << 16);
-    f[2 * i + 1] *= __uint_as_float(w[i] & 0xFFFF0000u);
+  for (int ch = 0; ch < 2; ++ch)
+    sv[ch] = __ldg(reinterpret_cast<const uint4*>(act_blk + row_off + ((((uint32_t)(2 * c4 + ch)) ^ row_x) << 4)));
+}
+__device__ __forceinline__ void apply_sine_gate16(float (&f)[16], const uint4 (&sv)[2], uint32_t bits, const float* freq) {
+  uint32_t sgn = bits << 16;                   // element i's bit (15 - i) moves to bit 31 as the loop shifts left
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    const float4 fa = __ldg(reinterpret_cast<const float4*>(freq + 8 * ch)), fb = __ldg(reinterpret_cast<const float4*>(freq + 8 * ch + 4));
+    const uint32_t w[4] = {sv[ch].x, sv[ch].y, sv[ch].z, sv[ch].w};
+    const float fr[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float sn = __uint_as_float((e & 1) ? (w[e >> 1] & 0xFFFF0000u) : (w[e >> 1] << 16));
+      float c;                                 // |sn| <= 1 (a rounded sine), so 1 - sn^2 >= 0
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(c) : "f"(fmaf(-sn, sn, 1.f)));
+      const float g = fr[e] * c;
+      f[8 * ch + e] *= __uint_as_float(__float_as_uint(g) ^ (sgn & 0x80000000u));
+      sgn <<= 1;
+    }
   }
 }
 // this thread's 16 columns (chunks 2*c4, 2*c4+1) of row `row` of a [128 x 64] swizzled bf16 block
@@ -258,18 +279,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         if (pg.n_cls > 0)
           *reinterpret_cast<uint4*>(hrow + swz_off(row, 8)) = make_uint4(pack_bf16(gc[4], gc[5]), pack_bf16(gc[6], gc[7]), 0u, 0u);
       }
-      // SIREN: the gate of block j is 16 bf16 values freq*cos(.) at [block][column quarter][row] of the step's cos image
-      const uint8_t* crec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + (c4 * TILE_M + row) * 32;
-      uint2 mk = make_uint2(0u, 0u);
-      if (!SIREN) mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
+      const uint8_t* arec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes;      // SIREN: saved sine images of this tile
+      uint2 mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
+      uint4 sv[2][2];                         // SIREN: this thread's 16 saved sines of the current / next block (one block ahead)
+      if (SIREN) load_sine16(sv[0], arec + pg.hd_act_off, row_off, row_x, c4);
 #pragma unroll
       for (int j = 0; j < (SIREN ? 4 : 2); ++j) {   // dZ_dir = (g . W_rgb) (.) gate     (models/nerf.py:119-120 / :213-215)
         float f[16];
         const int col0 = 64 * j + 16 * c4;
+        if (SIREN && j + 1 < 4) load_sine16(sv[(j + 1) & 1], arec + pg.hd_act_off + (j + 1) * BLK_BYTES, row_off, row_x, c4);
 #pragma unroll
         for (int i = 0; i < 16; ++i)
           f[i] = g0 * sm.w_rgb[col0 + i] + g1 * sm.w_rgb[RGB_IN + col0 + i] + g2 * sm.w_rgb[2 * RGB_IN + col0 + i];
-        if (SIREN) apply_cos16(f, crec + pg.hd_off + j * (4 * TILE_M * 32));
+        if (SIREN) apply_sine_gate16(f, sv[j & 1], ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu, args.film + pg.hd_film_off + col0);
         else apply_gate16(f, (mk.x >> (16 * (1 - j))) & 0xFFFFu);      // block 0 was shifted in first: upper half
         if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
         need_free |= 1u << j;
@@ -282,7 +304,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         const BStep& st = pg.s[s];
         const uint32_t a = gs & 1u;
         const bool gated = st.mask_off >= 0;
-        if (gated && !SIREN) mk = __ldg(reinterpret_cast<const uint2*>(frec + st.mask_off));
+        if (gated) mk = __ldg(reinterpret_cast<const uint2*>(frec + st.mask_off));
+        if (gated && SIREN) load_sine16(sv[0], arec + st.act_off, row_off, row_x, c4);
         const bool add_sigma = st.add_sigma != 0;
         mbar_wait(&sm.acc_full[a], (acc_par >> a) & 1u); acc_par ^= 1u << a;
         tc_fence_after();
@@ -293,6 +316,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
           const int col0 = 64 * j + 16 * c4;
           tmem_ld_wait();
           if (j + 1 < 4) tmem_ld16(t_lane + a * 256u + 64u * (uint32_t)(j + 1), v[(j + 1) & 1]);
+          if (gated && SIREN && j + 1 < 4) load_sine16(sv[(j + 1) & 1], arec + st.act_off + (j + 1) * BLK_BYTES, row_off, row_x, c4);
           float f[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[j & 1][i]);
@@ -319,7 +343,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
               }
             }
           }
-          if (gated && SIREN) apply_cos16(f, crec + st.mask_off + j * (4 * TILE_M * 32));
+          if (gated && SIREN) apply_sine_gate16(f, sv[j & 1], ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu, args.film + st.film_off + col0);
           else if (gated) apply_gate16(f, ((j < 2 ? mk.x : mk.y) >> (16 * (1 - (j & 1)))) & 0xFFFFu);
           if ((need_free >> j) & 1u) { mbar_wait(&sm.g_free[j], (gf_par >> j) & 1u); gf_par ^= 1u << j; }
           need_free |= 1u << j;
@@ -710,7 +734,7 @@ BwdPlan bwd_plan_siren(const nerfb_mlp_desc& d, int64_t P) {
   const int D = d.D;
   auto dz_off = [&](int l) { return (4 + 4 * (D - 1 - l)) * BLK_BYTES; };       // dZ_l, l = D-1 .. 0
   BProgram& pg = pl.prog;
-  pg.hd_off = L.step_mask_off[D]; pg.dzdir_off = 0;
+  pg.hd_off = L.step_mask_off[D]; pg.dzdir_off = 0; pg.hd_act_off = L.step_save_off[D]; pg.hd_film_off = D * 256;
   pg.n_cls = 0; pg.out_c = 4; pg.siren = 1; pg.n_pro = 4; pg.rgb_in = 256;
   const int hblk = (4 + 4 * D) * BLK_BYTES;
   pg.h_off = hblk;
@@ -719,8 +743,8 @@ BwdPlan bwd_plan_siren(const nerfb_mlp_desc& d, int64_t P) {
   auto slabs = [&](int64_t w_off, int ld, int col0, int n_kb) {
     for (int kb = 0; kb < n_kb; ++kb) { pl.pack.slab[nslab++] = PackTSlab{w_off, ld, kb * 64, 64, col0, wb}; wb += STAGE_BYTES; }
   };
-  pg.s[ns++] = BStep{4, L.step_mask_off[D - 1], 1, dz_off(D - 1), 0};  slabs(o.w_dir, 259, 3, 4);
-  for (int l = D - 1; l >= 1; --l) { pg.s[ns++] = BStep{4, L.step_mask_off[l - 1], 0, dz_off(l - 1), 0}; slabs(o.w[l], 256, 0, 4); }
+  pg.s[ns++] = BStep{4, L.step_mask_off[D - 1], 1, dz_off(D - 1), 0, L.step_save_off[D - 1], (D - 1) * 256};  slabs(o.w_dir, 259, 3, 4);
+  for (int l = D - 1; l >= 1; --l) { pg.s[ns++] = BStep{4, L.step_mask_off[l - 1], 0, dz_off(l - 1), 0, L.step_save_off[l - 1], (l - 1) * 256}; slabs(o.w[l], 256, 0, 4); }
   pg.n_steps = ns; pl.pack.n_slabs = nslab;
   WgradArgs& wg = pl.wg; int ni = 0;
   wg.item[ni++] = WItem{dz_off(0), 4, 1, L.save_x_off, 1, 64, o.w[0], 3, 0, 3, o.b[0], 0, 256, -1, 0, 1};
@@ -763,8 +787,9 @@ int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) { return bwd_
 int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, const float* out, const float* d_out, float* grad,
                float* d_in, void* ws, int64_t ws_bytes, void* stream) {
-  (void)film; (void)in0; (void)in1;
+  (void)in0; (void)in1;
   if (d_in || !tc_bwd_supported(d)) return NERFB_E_UNSUPPORTED;
+  if (d.kind == NERFB_KIND_SIREN && !film) return NERFB_E_BADARG;      // the dgrad gates need the FiLM frequencies
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcFwdLayout L = tc_fwd_layout(d, P);
   BwdPlan pl = bwd_plan(d, P);
@@ -789,6 +814,7 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   da.prog = pl.prog; da.wblob = bb + pl.off_wblob; da.heads = heads; da.out = out; da.d_out = d_out;
   da.fwd_rec = fwd_rec; da.bwd_rec = bb + pl.off_rec; da.P = P; da.n_tiles = pl.n_tiles;
   da.weff = reinterpret_cast<const float*>(base + L.off_weff);
+  da.film = film;
   if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_dgrad_kernel<true>, pl.n_active, NUM_THREADS, smem_d, stream, da);
   else NERFB_LAUNCH(mlp_tc_dgrad_kernel<false>, pl.n_active, NUM_THREADS, smem_d, stream, da);
 

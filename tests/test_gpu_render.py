@@ -187,9 +187,10 @@ def test_siren_module_tensor_core_forward(tag):
 
 
 def test_siren_tensor_core_backward_matches_fp32_arm():
-    """SIREN backward on the tcgen05 arm (sincos epilogue, freq*cos gate images, hi/lo first-layer wgrad) against the fp32
-    CUDA-core arm (itself pinned to the reference's autograd at 5e-4): every parameter gradient within 8e-2 relative L2
-    (bf16 operands; same bound as the NeRF bf16 arm), many tiles + ragged tail."""
+    """SIREN backward on the tcgen05 arm (sincos epilogue; gates freq * cos rebuilt in the dgrad from sign(cos) bit masks and
+    the saved bf16 sine images; hi/lo first-layer wgrad) against the fp32 CUDA-core arm (itself pinned to the reference's
+    autograd at 5e-4): every parameter gradient within 8e-2 relative L2 (bf16 operands; same bound as the NeRF bf16 arm;
+    measured 3.1e-2 .. 6.5e-2 on this random high-frequency field), many tiles + ragged tail."""
     g = gold("g4_siren_rand")
     gen = torch.Generator().manual_seed(11)
     n = 128 * 9 + 37

@@ -8,7 +8,7 @@ timeout 1500 python -m pytest tests -m gpu -q > $OUT/pytest_$TAG.log 2>&1; echo 
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke_$TAG.log 2>&1; echo "smoke exit $?"; tail -2 $OUT/smoke_$TAG.log
 timeout 900 python bench.py --steps 20 --warmup 3 > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench exit $?"
 timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err; echo "bench ref exit $?"
-timeout 600 python tools/bench_configs.py render siren cls siren_train > $OUT/bench_configs_$TAG.json 2> $OUT/bench_configs_$TAG.err; echo "configs exit $?"
+timeout 600 python tools/bench_configs.py render siren cls siren_train render_e2e > $OUT/bench_configs_$TAG.json 2> $OUT/bench_configs_$TAG.err; echo "configs exit $?"
 timeout 600 python tools/bench_eg3d.py > $OUT/bench_eg3d_$TAG.json 2> $OUT/bench_eg3d_$TAG.err; echo "eg3d exit $?"
 timeout 600 python tools/bench_stream_kernels.py > $OUT/stream_$TAG.json 2> $OUT/stream_$TAG.err; echo "stream exit $?"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_$TAG.csv \

@@ -102,7 +102,6 @@ struct __align__(1024) Smem {
   uint8_t x[2][BLK_BYTES];               // encoding tiles (double buffer: tile t uses x[t & 1])
   uint8_t ring[N_STAGES][STAGE_BYTES];   // weight slabs
   float bias[10 * 256 + 128];
-  float scale[9 * 256];                  // SIREN frequencies
   float w_sigma[256];
   float w_rgb[3 * 256];
   float b_heads[4];                      // b_sigma, b_rgb[3]
@@ -199,7 +198,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
   constexpr int RGB_IN = SIREN ? 256 : 128;
   for (int i = threadIdx.x; i < 3 * RGB_IN; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.bias + pg.n_bias + 257 + i);
   if (threadIdx.x < 3) sm.b_heads[1 + threadIdx.x] = __ldg(args.bias + pg.n_bias + 257 + 3 * RGB_IN + threadIdx.x);
-  if (SIREN) for (int i = threadIdx.x; i < pg.n_bias; i += NUM_THREADS) sm.scale[i] = __ldg(args.scale + i);
   if (threadIdx.x < 2 * pg.n_ops) {       // decode the MMA op list once, for both X buffers
     const int b = threadIdx.x / pg.n_ops, i = threadIdx.x % pg.n_ops;
     const uint32_t w = pg.ops[i];
@@ -417,7 +415,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
         const bool st_saved = saving && ((sw >> 16) & 1u);
         const uint32_t ready = ((sw >> 15) & 1u) ? smem_u32(sm.s_ready) : smem_u32(sm.a_ready);
         const uint32_t bias_base = smem_u32(sm.bias) + sb * 4u + 64u * (uint32_t)c4;
-        const uint32_t scale_base = smem_u32(sm.scale) + sb * 4u + 64u * (uint32_t)c4;
         const uint32_t a = gs & 1;
         mbar_wait(&sm.acc_full[a], (acc_par >> a) & 1u); acc_par ^= 1u << a;
         tc_fence_after();
@@ -433,11 +430,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
             float4 bb[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) bb[i] = lds128f(bias_base + 256u * (uint32_t)j + 16u * i);
-            float4 sc[4];
-            if (SIREN) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) sc[i] = lds128f(scale_base + 256u * (uint32_t)j + 16u * i);
-            }
             tmem_ld_wait();
             NERFB_TRACE(if (tr && j == 0) args.trace[gs * 32 + 21] = clock64();)
             if (j + 1 < nb) tmem_ld16(t_lane + a * 256u + 64u * (uint32_t)(j + 1), v[(j + 1) & 1]);
@@ -447,9 +439,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               float2 r0, r1;
-              if (SIREN) {      // sin(freq * (acc + b) + phase) = sin(freq * acc + (freq * b + phase))   (models/nerf.py:149-151)
-                r0 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(sc[i].x, sc[i].y), make_float2(bb[i].x, bb[i].y));
-                r1 = __ffma2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(sc[i].z, sc[i].w), make_float2(bb[i].z, bb[i].w));
+              r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
+              r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
+              if (SIREN) {      // sin(freq (W x + b) + phase) = sin((freq W) x + (freq b + phase)): both folds are done when packing (models/nerf.py:149-151)
                 if (SAVE) {       // training: d/dz sin(freq z + phase) = freq cos(.) is the dgrad kernel's multiplicative gate.
                   // Only sign(cos) is saved (one bit per element, same mask record as the ReLU gates): the dgrad rebuilds
                   // |cos| = sqrt(1 - sin^2) from the saved sine image it shares with the wgrad and multiplies by freq.
@@ -465,9 +457,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
                 } else {
                   r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y);
                 }
-              } else {
-                r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
-                r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
               }
               f[4 * i] = r0.x; f[4 * i + 1] = r0.y; f[4 * i + 2] = r1.x; f[4 * i + 3] = r1.y;
             }
@@ -581,16 +570,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
 }
 
 // ---- weight packing: fp32 nn.Linear weights -> bf16 slabs in the swizzled shared-memory image, schedule order ----
-struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; int aux; };   // aux: read the merged class-head matrix, not params   // W[n*ld + col0 + kk], kk < ncols
+struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; int aux; int film; };   // aux: read the merged class-head matrix, not params   // W[n*ld + col0 + kk], kk < ncols
 // hilo: 3 source columns expanded to 9 K-columns [W_hi W_hi W_lo] (pairs with hilo_row's [x_hi x_lo x_hi])
+// film >= 0 (SIREN): row n is scaled by the FiLM frequency of that layer, sin(freq (W x + b) + phase) = sin((freq W) x + (freq b + phase)),
+// so the epilogue only adds the folded bias; bf16(freq W) carries the same relative rounding as bf16(W)
 struct PackArgs { int n_slabs; PackSlab slab[48]; };
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params_in, PackArgs pa, uint8_t* __restrict__ blob,
-                                                           const float* __restrict__ aux) {
+                                                           const float* __restrict__ aux, const float* __restrict__ film) {
   const PackSlab sl = pa.slab[blockIdx.x];
   const float* params = sl.aux ? aux : params_in;
   for (int idx = threadIdx.x; idx < sl.N * 8; idx += blockDim.x) {       // one 16-byte chunk per iteration
     const int n = idx >> 3, ch = idx & 7;
+    const float fq = (sl.film >= 0 && film) ? __ldg(film + sl.film * sl.N + n) : 1.f;
     float f[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -598,12 +590,12 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
       if (sl.hilo) {
         f[e] = 0.f;
         if (kk < 9) {
-          const float w = __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk % 3);
+          const float w = __fmul_rn(fq, __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk % 3));
           const float hi = __bfloat162float(__float2bfloat16_rn(w));
           f[e] = kk < 6 ? hi : w - hi;
         }
       } else
-      f[e] = (kk < sl.ncols) ? __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk) : 0.f;
+      f[e] = (kk < sl.ncols) ? __fmul_rn(fq, __ldg(params + sl.w_off + (int64_t)n * sl.ld + sl.col0 + kk)) : 0.f;
     }
     uint4 o;
     o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
@@ -680,8 +672,9 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   pg.sigma_only = sigma_only; pg.out_c = sigma_only ? 1 : 4 + d.n_cls; pg.n_cls = sigma_only ? 0 : d.n_cls;
   pl.cls_bias_off = -1;
   int64_t wb = 0; int nb = 0, ns = 0, nslab = 0, nseg = 0, sv = 0;
+  int slab_film = -1;            // SIREN: FiLM layer whose frequencies scale the slabs being added
   auto add_slab = [&](int64_t w_off, int ld, int col0, int ncols, int N, int hilo = 0, int aux = 0) {
-    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb, hilo, aux};
+    pl.pack.slab[nslab++] = PackSlab{w_off, ld, col0, ncols, N, wb, hilo, aux, slab_film};
     wb += (int64_t)N * 128;
   };
   auto add_bias = [&](int64_t src, int n, int film = -1, int aux = 0) { pl.bias.seg[nseg++] = BiasSeg{src, n, nb, film, aux}; nb += n; return nb - n; };
@@ -696,6 +689,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
       TcStep& st = pg.s[ns++];
       st = TcStep{};
       st.N = 256; st.relu = 0; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0; st.film = i; st.save_off = -1; st.mask_off = -1;
+      slab_film = i;
       if (save) { st.save_off = sv; sv += 4 * BLK_BYTES; st.mask_off = sv; sv += TILE_M * 32; }      // activations (sine image) | sign(cos) bit mask
       if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], 3, 0, 3, 256, 1); }
       else for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], 256, 64 * j, 64, 256); }
@@ -705,6 +699,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     if (!sigma_only) {
       TcStep& cl = pg.s[ns++]; cl = TcStep{};
       cl.N = 256; cl.relu = 0; cl.head = 2; cl.out_blocks = save ? 4 : 0; cl.store_only = 1; cl.film = d.D; cl.save_off = -1; cl.mask_off = -1;
+      slab_film = d.D;
       if (save) { cl.save_off = sv; sv += 4 * BLK_BYTES; cl.mask_off = sv; sv += TILE_M * 32; pg.save_dir_off = sv; sv += BLK_BYTES; }
       for (int j = 0; j < 4; ++j) { cl.src[cl.n_kb++] = j; add_slab(o.w_dir, 259, 3 + 64 * j, 64, 256); }
       cl.src[cl.n_kb++] = SRC_X; cl.wait_x = 1; cl.x_done = 1; add_slab(o.w_dir, 259, 0, 3, 256, 1);
@@ -813,7 +808,8 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     const NerfOffsets o = nerf_offsets(d);
     NERFB_LAUNCH(merge_parse_kernel, 16, 256, 0, stream, params, o.w_p0, o.b_p0, o.w_p1, o.b_p1, d.n_cls, weff, weff + 16 * 256);
   }
-  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob, (const float*)weff);
+  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob, (const float*)weff,
+               siren ? film : (const float*)nullptr);
   NERFB_LAUNCH(gather_bias_kernel, pl.bias.n_segs, 256, 0, stream, params, pl.bias,
                reinterpret_cast<float*>(base + pl.off_bias), siren ? film : (const float*)nullptr,
                reinterpret_cast<float*>(base + pl.off_scale), (const float*)weff);

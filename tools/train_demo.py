@@ -1,7 +1,7 @@
 """Convergence check of the whole training path on a scene with a closed-form image: a shaded unit sphere on a white
 background (Blender-shaped cameras, near 2 / far 6).  Trains the coarse + fine NeRF pair with the captured data-parallel
 step for --steps iterations of 4096 random rays and reports training loss and held-out-view PSNR (through
-evaluation.batched_inference) as JSON lines.     python tools/train_demo.py [--steps 2000]"""
+evaluation.batched_inference) as JSON lines.     python tools/train_demo.py [--steps 2000] [--model nerf|siren]"""
 import argparse
 import json
 import os
@@ -32,13 +32,20 @@ def sphere_rgb(rays):
 ap = argparse.ArgumentParser()
 ap.add_argument("--steps", type=int, default=2000)
 ap.add_argument("--rays", type=int, default=4096)
+ap.add_argument("--model", default="nerf", choices=["nerf", "siren"])
+ap.add_argument("--precision", default="auto", choices=["auto", "fp32"])
+ap.add_argument("--lr", type=float, default=5e-4)
 args = ap.parse_args()
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
-nb.set_precision("auto")
-models = [nb.NeRF().to(dev), nb.NeRF().to(dev)]
-emb = [nb.Embedding(3, 10), nb.Embedding(3, 4)]
-trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, True, cuda_graph=True)
+nb.set_precision(args.precision)
+if args.model == "siren":
+    models = [nb.SirenField().to(dev), nb.SirenField().to(dev)]
+    emb = [nb.Embedding(3, 0), nb.Embedding(3, 0)]
+else:
+    models = [nb.NeRF().to(dev), nb.NeRF().to(dev)]
+    emb = [nb.Embedding(3, 10), nb.Embedding(3, 4)]
+trainer = nb.dp.DataParallelStep(models, emb, 64, 64, False, 1.0, 1.0, 32768, True, lr=args.lr, cuda_graph=True)
 pool = [synth.blender_rays(args.rays, seed=100 + i).to(dev) for i in range(64)]
 targets = [sphere_rgb(r) for r in pool]
 held = synth.blender_image_rays(200, 200, seed=987654).to(dev)          # a view no training batch draws from

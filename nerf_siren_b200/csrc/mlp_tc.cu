@@ -18,8 +18,9 @@
 // l are still in the epilogue, into the other accumulator.  Skip / direction concatenations are extra K-blocks (the
 // resident X tile), never a cat.  sigma (256->1) and rgb (128->3, sigmoid) heads are fp32 dot products in the epilogue.
 //
-// SIREN / FiLM variant (models/nerf.py:142-216, forward only): same kernel, template parameter SIREN.  The epilogue is
-// sin(freq (.) acc + (freq (.) b + phase)) -- one packed FMA against two per-column tables, then MUFU.SIN; the 3-wide
+// SIREN / FiLM variant (models/nerf.py:142-216): same kernel, template parameter SIREN.  sin(freq (W x + b) + phase) =
+// sin((freq W) x + (freq b + phase)): both folds happen when the weights / biases are packed, so the epilogue is a bias
+// add and MUFU.SIN; with SAVE it also records sign(cos) as the backward's gate mask (mlp_tc_bwd.cu).  The 3-wide
 // first layer (and the 3 direction columns of the colour layer) are carried as 9 K-columns [x_hi x_lo x_hi] against
 // [W_hi W_hi W_lo], which restores ~16 mantissa bits where the first-layer frequency scale w0 = 30 amplifies input
 // rounding; the colour layer is N = 256 and its 256->3 sigmoid head rides in the epilogue like NeRF's.
@@ -654,7 +655,7 @@ struct TcPlan {
 
 bool tc_supported(const nerfb_mlp_desc& d, int in_mode) {
   (void)in_mode;
-  if (d.kind == NERFB_KIND_SIREN) return d.W == 256 && d.D >= 1 && d.D <= 9 && d.box > 0.f;   // forward only, see tc_bwd_supported
+  if (d.kind == NERFB_KIND_SIREN) return d.W == 256 && d.D >= 1 && d.D <= 9 && d.box > 0.f;   // backward: see tc_bwd_supported
   if (d.kind != NERFB_KIND_NERF || d.W != 256 || d.n_cls < 0 || d.n_cls > 8) return false;
   if (d.D < 1 || d.D > 9) return false;
   if (!d.logscale && d.in_xyz <= 0) return false;                 // in-kernel encoding is the power-of-two ladder

@@ -9,7 +9,7 @@ package falls back to torch ops or to the CPU.
 import sys as _sys
 
 from . import _lib  # noqa: F401  (raises ImportError when libnerf_b200.so is missing)
-from . import config, dp, eg3d, evaluation, ops, synth, system  # noqa: F401
+from . import config, dp, eg3d, evaluation, losses, ops, synth, system  # noqa: F401
 from .config import get_precision, set_precision  # noqa: F401
 from .models import nerf, nerf_cls, rendering  # noqa: F401
 from .models.nerf import Embedding, NeRF, SemanticNeRF, SirenField  # noqa: F401
@@ -27,6 +27,11 @@ def install_as_models() -> None:
     _sys.modules["models.rendering"] = rendering
     _sys.modules["models.nerf"] = nerf
     _sys.modules["models.nerf_cls"] = nerf_cls
+
+
+def install_as_losses() -> None:
+    """Make ``from losses import loss_dict`` (system.py:10, train.py in the reference) resolve to this package."""
+    _sys.modules["losses"] = losses
 
 
 def install_as_eg3d() -> None:

@@ -102,15 +102,23 @@ def mse_loss(results: dict, rgbs: torch.Tensor) -> torch.Tensor:
 
 
 class DataParallelStep:
-    """render_rays -> MSELoss -> backward -> ONE flat all-reduce -> Adam, for this rank's shard of rays."""
+    """render_rays -> loss -> backward -> ONE flat all-reduce -> Adam, for this rank's shard of rays.
+
+    ``loss_fn(results, rgbs)`` defaults to MSELoss (losses.py:10-20).  For the semantic head (BASELINE configs[3]) pass
+    ``render_fn=render_rays_3d, render_kwargs={"no_grad_on_nerf": False}`` and ``loss_fn=losses.MSECELoss()`` /
+    ``MSENLLLoss()``: ``step(rays, rgbs, labels)`` then calls ``loss_fn(results, rgbs, labels)`` the way
+    system.py:351 does and back-propagates its ``"sum"`` entry."""
 
     def __init__(self, models: List[nn.Module], embeddings: List[nn.Module], N_samples=64, N_importance=64,
                  use_disp=False, perturb=1.0, noise_std=1.0, chunk=32 * 1024, white_back=True, lr=5e-4,
-                 betas=(0.9, 0.999), eps=1e-8, group=None, render_fn=None, cuda_graph=False):
+                 betas=(0.9, 0.999), eps=1e-8, group=None, render_fn=None, cuda_graph=False, loss_fn=None,
+                 render_kwargs=None, loss_kwargs=None):
         from .models.rendering import render_rays
         self.models, self.embeddings = list(models), list(embeddings)
         self.render_fn = render_fn or render_rays
         self.render_args = (N_samples, use_disp, perturb, noise_std, N_importance, chunk, white_back)
+        self.render_kwargs = dict(render_kwargs or {})
+        self.loss_fn, self.loss_kwargs = loss_fn, dict(loss_kwargs or {})
         self.group = group
         self.lr, self.betas, self.eps = lr, betas, eps
         self.params = FlatParameters(self.models)
@@ -124,46 +132,58 @@ class DataParallelStep:
         self._graphs = {}
         self.graph_launches = 0            # kernels of this library launched by graph replays (ops.launch_count() only sees host calls)
 
-    def _captured(self, rays: torch.Tensor, rgbs: torch.Tensor):
-        key = (tuple(rays.shape), tuple(rgbs.shape))
+    def _captured(self, rays: torch.Tensor, rgbs: torch.Tensor, labels: Optional[torch.Tensor]):
+        key = (tuple(rays.shape), tuple(rgbs.shape), None if labels is None else tuple(labels.shape))
         st = self._graphs.get(key)
         if st is None:
             import types
             dev = self.params.flat.device
             st = types.SimpleNamespace(rays=torch.empty(rays.shape, device=dev, dtype=torch.float32),
-                                       rgbs=torch.empty(rgbs.shape, device=dev, dtype=torch.float32))
+                                       rgbs=torch.empty(rgbs.shape, device=dev, dtype=torch.float32),
+                                       labels=None if labels is None else torch.empty(labels.shape, device=dev, dtype=labels.dtype))
             st.rays.copy_(rays); st.rgbs.copy_(rgbs)
+            if labels is not None:
+                st.labels.copy_(labels)
             side = torch.cuda.Stream(device=dev)             # warm-up off the capture stream (allocator, autograd, lazy inits)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
                 for _ in range(2):
-                    self.forward_backward(st.rays, st.rgbs)
+                    self.forward_backward(st.rays, st.rgbs, st.labels)
             torch.cuda.current_stream(dev).wait_stream(side)
             before = ops.launch_count()
             st.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(st.graph):
-                st.loss = self.forward_backward(st.rays, st.rgbs)
+                st.loss = self.forward_backward(st.rays, st.rgbs, st.labels)
             st.launches = ops.launch_count() - before
             self._graphs[key] = st
         return st
 
-    def forward_backward(self, rays: torch.Tensor, rgbs: torch.Tensor) -> torch.Tensor:
+    def forward_backward(self, rays: torch.Tensor, rgbs: torch.Tensor, labels: Optional[torch.Tensor] = None) -> torch.Tensor:
         self.params.zero_grad()
-        results = self.render_fn(self.models, self.embeddings, rays, *self.render_args)
-        loss = mse_loss(results, rgbs)
+        results = self.render_fn(self.models, self.embeddings, rays, *self.render_args, **self.render_kwargs)
+        if self.loss_fn is None:
+            loss = mse_loss(results, rgbs)
+        elif labels is None:
+            loss = self.loss_fn(results, rgbs, **self.loss_kwargs)
+        else:
+            loss = self.loss_fn(results, rgbs, labels, **self.loss_kwargs)
+        if isinstance(loss, dict):                            # MSECELoss / MSENLLLoss: {"sum", "rgb", "cls"}, system.py:352
+            loss = loss["sum"]
         loss.backward()
         return loss.detach()
 
-    def step(self, rays: torch.Tensor, rgbs: torch.Tensor) -> torch.Tensor:
+    def step(self, rays: torch.Tensor, rgbs: torch.Tensor, labels: Optional[torch.Tensor] = None) -> torch.Tensor:
         if self.cuda_graph and self.params.flat.is_cuda:
-            st = self._captured(rays, rgbs)
+            st = self._captured(rays, rgbs, labels)
             st.rays.copy_(rays, non_blocking=True)          # host (pinned) or device batch -> the graph's input buffers
             st.rgbs.copy_(rgbs, non_blocking=True)
+            if labels is not None:
+                st.labels.copy_(labels, non_blocking=True)
             st.graph.replay()
             self.graph_launches += st.launches
             loss = st.loss.clone()
         else:
-            loss = self.forward_backward(rays, rgbs)
+            loss = self.forward_backward(rays, rgbs, labels)
         g = self.params.flat.grad
         allreduce_sum_(g, self.group)                       # the batch-boundary collective (4.77 MB for NeRF x2)
         self.steps += 1

@@ -282,13 +282,20 @@ def render_rays(models, embeddings, rays, N_samples=64, use_disp=False, perturb=
 
 
 def render_rays_3d(models, embeddings, rays, N_samples=64, use_disp=False, perturb=0, noise_std=1, N_importance=0,
-                   chunk=1024 * 32, white_back=False, test_time=False, _cls_num=6, no_grad_on_nerf=True):
+                   chunk=1024 * 32, white_back=False, test_time=False, _cls_num=6, no_grad_on_nerf=True, network=None):
     """The class-rendering entry (models/rendering.py:265-472): adds 'cls_coarse' / 'cls_fine' = sum_i w_i cls_i
     (:379).  The per-sample class scores are the NeRF_3D head's channels 4: (BASELINE config 4); the reference's
-    PointNet-over-thresholded-points branch (:350-377) is outside the hot path and not provided."""
+    PointNet-over-thresholded-points branch (:350-377) is outside the hot path and not provided (``network`` is
+    accepted and ignored).  ``no_grad_on_nerf=True`` -- the reference's default -- runs the NeRF models under
+    ``torch.no_grad()`` exactly as :306-308 does, so no gradient reaches them (in the reference only the PointNet
+    trains in that mode); pass ``no_grad_on_nerf=False`` to train the NeRF_3D trunk and class head."""
     if not hasattr(models[0], "CLS") or models[0].CLS == 0:
         raise NotImplementedError("render_rays_3d here composites the NeRF_3D class head; the reference's PointNet "
                                   "branch (models/rendering.py:350-377) is out of scope")
+    if no_grad_on_nerf:
+        with torch.no_grad():
+            return _render(models[:2], embeddings, rays, N_samples, use_disp, perturb, noise_std, N_importance, chunk,
+                           white_back, test_time, want_cls=True)
     return _render(models[:2], embeddings, rays, N_samples, use_disp, perturb, noise_std, N_importance, chunk,
                    white_back, test_time, want_cls=True)
 

@@ -96,3 +96,33 @@ def test_shard_bounds_partition():
             assert b[0][0] == 0 and b[-1][1] == n and all(b[k][1] == b[k + 1][0] for k in range(world - 1))
             sizes = [hi - lo for lo, hi in b]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_loss_hook_receives_labels_and_dict_losses_backprop_their_sum():
+    """configs[3] host logic: DataParallelStep(loss_fn=MSECELoss()) calls loss_fn(results, rgbs, labels) as system.py:351
+    does and back-propagates the dict's "sum"; render_kwargs reach the render function."""
+    nb = pytest.importorskip("nerf_siren_b200")
+    from nerf_siren_b200 import dp, losses
+    seen = {}
+
+    class _ClsField(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.rgb, self.cls = torch.nn.Linear(8, 3), torch.nn.Linear(8, 6)
+
+    def render(models, embeddings, rays, *args, **kw):
+        seen.update(kw)
+        out = {}
+        for m, t in zip(models, ("coarse", "fine")):
+            out["rgb_" + t], out["cls_" + t] = torch.sigmoid(m.rgb(rays)), m.cls(rays)
+        return out
+    torch.manual_seed(3)
+    step = dp.DataParallelStep([_ClsField(), _ClsField()], [None, None], render_fn=render, loss_fn=losses.MSECELoss(),
+                               render_kwargs={"no_grad_on_nerf": False}, loss_kwargs={"weight": 0.25})
+    rays, rgbs = _batch(40)
+    labels = torch.randint(0, 6, (40, 1), generator=torch.Generator().manual_seed(5))
+    loss = step.forward_backward(rays, rgbs, labels)
+    assert seen == {"no_grad_on_nerf": False}
+    want = losses.MSECELoss()(render(step.models, None, rays), rgbs, labels, weight=0.25)["sum"]
+    assert float(loss) == pytest.approx(float(want), rel=1e-6)
+    assert all(float(m.cls.weight.grad.abs().sum()) > 0 and float(m.rgb.weight.grad.abs().sum()) > 0 for m in step.models)

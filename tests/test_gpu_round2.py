@@ -1,0 +1,338 @@
+"""Round-2 parity additions ("Next round" item 3/4): the optimizer step against torch.optim.Adam, two NCCL
+ranks against one process, tight bf16 GRADIENT bounds on a smooth field against the fp32 reference algorithm, parity at
+the headline shape (4096 rays, 64+64), SIREN 64+128 end to end with random FiLM vectors, and the semantic-head losses."""
+import os
+import socket
+
+import pytest
+import torch
+
+from oracle import render_oracle as O
+from tests._util import fields, gold, rng_of
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def nb():
+    import nerf_siren_b200
+    return nerf_siren_b200
+
+
+def _load(cls, params, **kw):
+    m = cls(**kw).to(DEV)
+    m.load_state_dict(params)
+    return m
+
+
+# ------------------------------------------------------------------------------------------------------
+# (i) nerfb_adam_step == torch.optim.Adam(lr, eps=1e-8)   (reference: utils/__init__.py:20)
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [4096 + 3, 1_191_688, 5])
+@pytest.mark.parametrize("grad_scale", [1.0, 0.125])
+def test_adam_step_matches_torch_optim_adam(n, grad_scale):
+    """5 steps on random gradients, n not a multiple of 4 (scalar tail) and the flat size of two NeRFs; grad_scale is the
+    1/world of the DDP mean folded into the kernel.  Bound: 1e-6 relative to the parameter scale (fp32 round-off of the
+    differently associated but algebraically identical update)."""
+    g = torch.Generator().manual_seed(n)
+    p0 = torch.randn(n, generator=g)
+    ours = p0.clone().to(DEV)
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    ref = torch.nn.Parameter(p0.clone().to(DEV))
+    opt = torch.optim.Adam([ref], lr=5e-4, eps=1e-8)
+    for step in range(1, 6):
+        grad = (torch.randn(n, generator=g) * (10.0 ** torch.randint(-4, 1, (n,), generator=g).float())).to(DEV)
+        ref.grad = grad * grad_scale
+        opt.step()
+        nb().ops.adam_step(ours, grad, m, v, step, 5e-4, (0.9, 0.999), 1e-8, grad_scale=grad_scale)
+        err = (ours - ref.detach()).abs().max().item()
+        assert err <= 1e-6 * max(1.0, p0.abs().max().item()), (step, err)
+    st = opt.state[ref]
+    assert (m - st["exp_avg"]).abs().max().item() <= 1e-6 * st["exp_avg"].abs().max().item()
+    assert (v - st["exp_avg_sq"]).abs().max().item() <= 1e-6 * st["exp_avg_sq"].abs().max().item()
+
+
+# ------------------------------------------------------------------------------------------------------
+# (ii) two NCCL ranks on the halves of a batch == one process on the whole batch   (train.py:48-49, DDP mean)
+# ------------------------------------------------------------------------------------------------------
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _dp_batch(n, i):
+    return O.blender_rays(n, seed=300 + i), torch.rand(n, 3, generator=torch.Generator().manual_seed(400 + i))
+
+
+def _dp_trainer(n_mod, group=None):
+    torch.manual_seed(0)
+    models = [n_mod.NeRF().to(DEV), n_mod.NeRF().to(DEV)]
+    emb = [n_mod.Embedding(3, 10), n_mod.Embedding(3, 4)]
+    return n_mod.dp.DataParallelStep(models, emb, 32, 32, False, 0.0, 0.0, 32768, True, group=group)
+
+
+def _nccl_worker(rank, world, port, n_rays, steps, out_dir, precision):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import nerf_siren_b200 as n_mod
+        n_mod.set_precision(precision)
+        tr = _dp_trainer(n_mod)
+        losses, grad0 = [], None
+        for i in range(steps):
+            rays, rgbs = _dp_batch(n_rays, i)
+            lo, hi = n_mod.dp.shard_bounds(n_rays, rank, world)
+            losses.append(float(tr.step(rays[lo:hi].cuda(), rgbs[lo:hi].cuda())))
+            if i == 0:
+                grad0 = tr.params.flat.grad.detach().cpu().clone()      # the all-reduced SUM of step 0
+        torch.cuda.synchronize()
+        torch.save({"flat": tr.params.flat.detach().cpu(), "losses": losses, "grad0": grad0},
+                   os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "auto"])
+def test_two_nccl_ranks_equal_one_process_on_the_whole_batch(tmp_path, precision):
+    """3 DataParallelStep steps (perturb = noise = 0) on the two halves of each batch over NCCL.  (a) Both ranks end with
+    BIT-IDENTICAL parameters.  (b) DDP mean semantics: the all-reduced SUM of step 0 divided by the world size equals the
+    gradient of one process on the whole batch (equal shards: mean of the per-rank mean losses == whole-batch mean) to
+    1e-5 relative L2 -- shards are whole 128-sample tiles, so only the fp32 summation order differs, on both arms.
+    (c) After 3 Adam steps the parameters agree to 1e-7 mean-abs and 1e-4 max-abs (Adam divides by sqrt(v) + 1e-8, so
+    round-off in a near-zero gradient entry can move that one parameter by a fraction of lr = 5e-4)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    n_rays, steps, world = 256, 3, 2
+    mp.spawn(_nccl_worker, args=(world, _free_port(), n_rays, steps, str(tmp_path), precision), nprocs=world, join=True)
+    r = [torch.load(os.path.join(tmp_path, f"rank{k}.pt")) for k in range(world)]
+    assert torch.equal(r[0]["flat"], r[1]["flat"]), "ranks diverged"
+    assert torch.equal(r[0]["grad0"], r[1]["grad0"])
+    nb().set_precision(precision)
+    tr = _dp_trainer(nb())
+    for i in range(steps):
+        rays, rgbs = _dp_batch(n_rays, i)
+        tr.step(rays.to(DEV), rgbs.to(DEV))
+        if i == 0:
+            g_one = tr.params.flat.grad.detach().cpu().double()
+            g_two = r[0]["grad0"].double() / world
+            rel = ((g_one - g_two).norm() / g_one.norm()).item()
+            assert rel <= 1e-5, rel
+    d = (tr.params.flat.detach().cpu() - r[0]["flat"]).abs()
+    assert d.mean().item() <= 1e-7 and d.max().item() <= 1e-4, (d.mean().item(), d.max().item())
+
+
+# ------------------------------------------------------------------------------------------------------
+# (iii) bf16 tensor-core GRADIENTS on a smooth (gain 1) field against the fp32 reference algorithm, full tensors
+# ------------------------------------------------------------------------------------------------------
+def _oracle_grads(p, x, up, **kw):
+    pr = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+    (O.nerf_mlp(pr, x, **kw) * up).sum().backward()
+    return {k: v.grad for k, v in pr.items()}
+
+
+@pytest.mark.parametrize("n_cls", [0, 6])
+def test_bf16_gradients_smooth_field_against_fp32_reference(n_cls):
+    """Default-init (gain 1) NeRF / NeRF_3D, 2048 + 77 rows (17 tiles, ragged tail), random upstream gradient: EVERY
+    parameter's FULL gradient tensor from the tcgen05 arm (bf16 operands, fp32 accumulation) within 2e-2 relative L2 of
+    the fp32 autograd of the reference algorithm (oracle, pinned bit-exact to the reference modules by
+    oracle/make_goldens.py).  A systematic scale error of a few percent in any layer fails this."""
+    n = nb()
+    n.set_precision("bf16")
+    p = O.nerf_init(seed=61 + n_cls, gain=1.0, n_cls=n_cls)
+    rows = 2048 + 77
+    g = torch.Generator().manual_seed(17)
+    x = torch.randn(rows, 90, generator=g)
+    x[:, :3] *= 2
+    up = torch.randn(rows, 4 + n_cls, generator=g)
+    ref = _oracle_grads(p, x, up)
+    m = _load(n.NeRF_3D, p, CLS=n_cls) if n_cls else _load(n.NeRF, p)
+    assert n.ops.mlp_supported(m._desc(False), n._lib.PREC_BF16, True)
+    y = m(x.to(DEV))
+    yr = O.nerf_mlp(p, x)
+    assert (y.detach().cpu() - yr).abs().max().item() <= 2e-2 * yr.abs().max().item()
+    (y * up.to(DEV)).sum().backward()
+    worst = {}
+    for k, prm in m.named_parameters():
+        got, want = prm.grad.detach().cpu().double(), ref[k].double()
+        rel = ((got - want).norm() / (want.norm() + 1e-30)).item()
+        worst[k] = rel
+        assert rel <= 2e-2, (k, rel)
+    print("bf16 grad rel-L2 vs fp32 reference: max %.3e (%s)" % (max(worst.values()), max(worst, key=worst.get)))
+
+
+# ------------------------------------------------------------------------------------------------------
+# (iv) parity at the headline shape: 4096 rays, 64 + 64, bf16 arm, against the oracle run on this box's CPU
+# ------------------------------------------------------------------------------------------------------
+def test_headline_shape_render_against_oracle():
+    """BASELINE configs[1] shape (4096 rays, 64 coarse + 64 importance samples; 2048 + 4096 MLP tiles = 14 / 28 tiles per SM,
+    several waves), smooth calibrated field, deterministic sampling: every output of the tcgen05 arm against the fp32
+    oracle (2.4 s of CPU).  Then the same call split into three ragged `rays_per_call` chunks (models/rendering.py's
+    MAX_POINTS loop; 1500 rays x 128 samples is not a multiple of the 128-sample tile x SM count) must reproduce the
+    single-call result bit for bit.  Tolerances = test_bf16_smooth_field_end_to_end's."""
+    n = nb()
+    n.set_precision("bf16")
+    pc, pf = O.nerf_field(seed=51, gain=1.0), O.nerf_field(seed=52, gain=1.0)
+    rays = O.blender_rays(4096, seed=77)
+    torch.set_num_threads(os.cpu_count() or 1)
+    ref = O.render_rays(fields(pc, pf), rays, 64, False, 0.0, 0.0, 64, 32768, True, False)
+    mc, mf = _load(n.NeRF, pc), _load(n.NeRF, pf)
+    emb = [n.Embedding(3, 10), n.Embedding(3, 4)]
+    with torch.no_grad():
+        out = n.render_rays([mc, mf], emb, rays.to(DEV), 64, False, 0, 0, 64, 32768, True)
+    for k in ("rgb_coarse", "opacity_coarse", "rgb_fine", "opacity_fine"):
+        e = (out[k].cpu() - ref[k]).abs()
+        assert e.max().item() <= 1.5e-2 and e.mean().item() <= 1.5e-3, (k, e.max().item(), e.mean().item())
+    for k in ("depth_coarse", "depth_fine"):
+        e = (out[k].cpu() - ref[k]).abs()
+        assert e.mean().item() <= 5e-2 and e.max().item() <= 0.8, (k, e.mean().item(), e.max().item())
+    mse = ((out["rgb_fine"].cpu() - ref["rgb_fine"]) ** 2).mean().item()
+    assert -10 * torch.log10(torch.tensor(mse + 1e-12)).item() >= 40.0
+    old = n.config.MAX_POINTS_BF16
+    try:
+        n.config.MAX_POINTS_BF16 = 1500 * 128
+        with torch.no_grad():
+            split = n.render_rays([mc, mf], emb, rays.to(DEV), 64, False, 0, 0, 64, 32768, True)
+    finally:
+        n.config.MAX_POINTS_BF16 = old
+    for k in out:
+        assert torch.equal(out[k], split[k]), k
+
+
+# ------------------------------------------------------------------------------------------------------
+# (v) BASELINE configs[2]: SIREN, 64 + 128 samples, test_time, RANDOM FiLM vectors, depth included
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_siren_render_64_128_random_film_against_oracle(prec):
+    """2048 + 5 rays, N(0, 0.3^2) FiLM frequencies (-> 30 + 15 f in [~16, ~44]) and N(0,1) phase shifts so every layer's
+    sine argument is non-trivial (zeros give a flat field); sigma head re-calibrated on a probe set so the
+    scene is not empty (depth is then a real weighted mean).  Rays are Blender-shaped but scaled into SIREN's
+    UniformBoxWarp(51) box.  Stated tolerances: fp32 arm rgb / opacity 2e-3, depth 2e-2 (sine layers amplify fp32
+    summation-order noise; resampled depths move); bf16 arm rgb / opacity mean-abs 1e-2 and PSNR >= 30 dB, depth mean-abs
+    8e-2."""
+    n = nb()
+    n.set_precision(prec)
+    ps = O.siren_init(seed=19)
+    g = torch.Generator().manual_seed(23)
+    freq = torch.randn(1, 9 * 256, generator=g) * 0.3
+    phase = torch.randn(1, 9 * 256, generator=g)
+    rays = O.blender_rays(2048 + 5, seed=29)
+
+    def raw_field(p, x, sigma_only):
+        y = O.siren_mlp(p, x[None, :, :3], freq, phase, x[None, :, 3:6] if not sigma_only else x[None, :, :3])[0]
+        return y[:, 3:4] if sigma_only else y
+    # calibrate the sigma head (final_layer) so raw sigma ~ N(0.5, 3^2) on a probe set, as O.nerf_field does for NeRF
+    probe = O.blender_rays(32, seed=99)
+    z = O.stratified_z(probe, 16)
+    xyz = (probe[:, None, :3] + probe[:, None, 3:6] * z[..., None]).reshape(-1, 3)
+    with torch.no_grad():
+        s = raw_field(ps, xyz, True)
+        k = 3.0 / float(s.std())
+        ps["final_layer.weight"] = ps["final_layer.weight"] * k
+        ps["final_layer.bias"] = (ps["final_layer.bias"] - float(s.mean())) * k + 0.5
+    m = n.SirenField(frequencies=freq, phase_shifts=phase).to(DEV)
+    if prec == "bf16" and not n.ops.mlp_supported(m._desc(), n._lib.PREC_BF16, False):
+        pytest.skip("SIREN not on the tensor-core arm")
+    m.load_state_dict({**ps, "frequencies": freq.reshape(-1), "phase_shifts": phase.reshape(-1)})
+    torch.set_num_threads(os.cpu_count() or 1)
+    with torch.no_grad():
+        ref = O.render_rays([lambda x, so: raw_field(ps, x, so)] * 2, rays, 64, False, 0.0, 0.0, 128, 32768, True, True,
+                            n_freq_xyz=0, n_freq_dir=0)
+        out = n.render_rays([m, m], [n.Embedding(3, 0), n.Embedding(3, 0)], rays.to(DEV), 64, False, 0, 0, 128, 32768,
+                            True, test_time=True)
+    assert set(out) == {"opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine"}
+    assert float(ref["opacity_fine"].mean()) > 0.2, "test scene is empty"
+    stats = {}
+    for key in ("rgb_fine", "opacity_fine", "opacity_coarse", "depth_fine"):
+        e = (out[key].cpu() - ref[key]).abs()
+        stats[key] = (e.max().item(), e.mean().item())
+    print(prec, stats)
+    if prec == "fp32":
+        for key in ("rgb_fine", "opacity_fine", "opacity_coarse"):
+            assert stats[key][0] <= 2e-3, (key, stats[key])
+        assert stats["depth_fine"][0] <= 2e-2, stats["depth_fine"]
+    else:
+        for key in ("rgb_fine", "opacity_fine", "opacity_coarse"):
+            assert stats[key][1] <= 1e-2, (key, stats[key])
+        assert stats["depth_fine"][1] <= 8e-2, stats["depth_fine"]
+        mse = ((out["rgb_fine"].cpu() - ref["rgb_fine"]) ** 2).mean().item()
+        assert -10 * torch.log10(torch.tensor(mse + 1e-12)).item() >= 30.0, mse
+
+
+# ------------------------------------------------------------------------------------------------------
+# (vi) BASELINE configs[3]: class compositing + MSECELoss / MSENLLLoss, losses and training gradients (golden G11)
+# ------------------------------------------------------------------------------------------------------
+class _Replay:
+    def __init__(self, g):
+        self.rand, self.randn = [g["rng:perturb_rand"], g["rng:u"]], [g["rng:noise_coarse"], g["rng:noise_fine"]]
+
+    def __enter__(self):
+        self.orig = (torch.rand, torch.randn)
+        ri, rn = iter(self.rand), iter(self.randn)
+        torch.rand = lambda *s, **kw: next(ri).to(kw.get("device", "cpu"))
+        torch.randn = lambda *s, **kw: next(rn).to(kw.get("device", "cpu"))
+
+    def __exit__(self, *a):
+        torch.rand, torch.randn = self.orig
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("tag", ["ce_default", "ce_half", "nll"])
+def test_semantic_head_losses_and_gradients(prec, tag):
+    """render_rays_3d(no_grad_on_nerf=False) [+ log_softmax for the NLL variant] -> this package's MSECELoss / MSENLLLoss ->
+    backward, against golden G11 = the reference's own loss modules and NeRF_3D autograd (oracle/make_goldens_cls.py).
+    fp32 arm: losses 2e-4 relative, gradients 3e-2 of their norm (end to end through resampled depths, as
+    test_training_step_gradients).  bf16 arm: losses 5e-2, gradient norms within a factor 2 (adversarial gain-3 field)."""
+    n = nb()
+    n.set_precision(prec)
+    g = gold("g11_cls_loss")
+    pc, pf = O.nerf_field(seed=31, n_cls=6), O.nerf_field(seed=32, n_cls=6)
+    mc, mf = _load(n.NeRF_3D, pc, CLS=6), _load(n.NeRF_3D, pf, CLS=6)
+    if prec == "bf16" and not n.ops.mlp_supported(mc._desc(False), n._lib.PREC_BF16, True):
+        pytest.skip("NeRF_3D backward not on the tensor-core arm")
+    emb = [n.Embedding(3, 10), n.Embedding(3, 4)]
+    fn = n.render_rays_3d_conv if tag == "nll" else n.render_rays_3d
+    with _Replay(g):
+        out = fn([mc, mf], emb, g["rays"].to(DEV), 64, False, 1.0, 1.0, 64, 32768, False, no_grad_on_nerf=False)
+    assert {"cls_coarse", "cls_fine"} <= set(out)
+    if tag == "ce_default":
+        for k in ("cls_coarse", "cls_fine"):
+            tol = 5e-5 if (prec == "fp32" and k.endswith("coarse")) else (5e-3 if prec == "fp32" else 6e-2)
+            assert (out[k].detach().cpu() - g["out:" + k]).abs().max().item() <= tol, k
+    labels = (g["labels_nll"] if tag == "nll" else g["labels"]).to(DEV)
+    target = g["target"].to(DEV)
+    if tag == "nll":
+        loss = n.losses.MSENLLLoss()(out, target, labels)
+    elif tag == "ce_half":
+        loss = n.losses.MSECELoss()(out, target, labels, 0.5)
+    else:
+        loss = n.losses.MSECELoss()(out, target, labels)            # weight = 0., as system.py:351 calls it
+    ltol = 2e-4 if prec == "fp32" else 5e-2
+    for k in ("sum", "rgb", "cls"):
+        want = float(g[f"{tag}:loss_{k}"])
+        assert abs(float(loss[k]) - want) <= ltol * abs(want) + 1e-7, (k, float(loss[k]), want)
+    loss["sum"].backward()
+    gtol = 3e-2 if prec == "fp32" else 1.0
+    for pre, m in (("gradc:", mc), ("gradf:", mf)):
+        for k, p in m.named_parameters():
+            ref_norm = float(g[f"{tag}:{pre}{k}@norm"])
+            got = float(p.grad.double().norm()) if p.grad is not None else 0.0
+            assert abs(got - ref_norm) <= gtol * ref_norm + 1e-9, (pre, k, got, ref_norm)
+            if prec == "fp32" and f"{tag}:{pre}{k}" in g:
+                err = (p.grad.cpu() - g[f"{tag}:{pre}{k}"]).double().norm().item()
+                assert err <= gtol * ref_norm + 1e-9, (pre, k, err, ref_norm)
+    # the class head itself must be trained by this loss (VERDICT r1 missing 1)
+    assert float(mf.parse[0].weight.grad.abs().sum()) > 0 and float(mc.parse[1].weight.grad.abs().sum()) > 0
+
+
+def test_render_rays_3d_default_freezes_the_nerf():
+    """models/rendering.py:306-308: with the reference's default no_grad_on_nerf=True the NeRF runs under no_grad."""
+    n = nb()
+    n.set_precision("auto")
+    mc, mf = n.NeRF_3D(CLS=6).to(DEV), n.NeRF_3D(CLS=6).to(DEV)
+    out = n.render_rays_3d([mc, mf], [n.Embedding(3, 10), n.Embedding(3, 4)], O.llff_rays(32, seed=1).to(DEV), 16, False,
+                           0, 0, 16, 32768, False)
+    assert not out["cls_fine"].requires_grad and not out["rgb_fine"].requires_grad

@@ -34,7 +34,25 @@ def pick_precision(desc: MlpDesc, need_grad: bool) -> int:
     if want == "bf16" and not ok:
         raise RuntimeError("precision 'bf16' requested but this model shape (or its backward) is outside the "
                            "tcgen05 kernels")
+    if not ok:
+        _warn_fp32_once(desc, need_grad)
     return _lib.PREC_BF16 if ok else _lib.PREC_FP32
+
+
+_warned = set()
+
+
+def _warn_fp32_once(desc: MlpDesc, need_grad: bool) -> None:
+    """'auto' silently taking the fp32 CUDA-core arm is a ~30x cliff (W != 256, CLS > 8, D > 9, ...): say so once per shape."""
+    key = (desc.kind, desc.D, desc.W, desc.n_cls, bool(need_grad))
+    if key in _warned:
+        return
+    _warned.add(key)
+    import warnings
+    warnings.warn(f"nerf_siren_b200: model shape (kind={desc.kind}, D={desc.D}, W={desc.W}, CLS={desc.n_cls}, "
+                  f"grad={bool(need_grad)}) is outside the tcgen05 tensor-core kernels; precision 'auto' falls back to the "
+                  "fp32 CUDA-core arm, which is roughly 30x slower. Supported: W=256, D<=9, CLS<=8.", RuntimeWarning,
+                  stacklevel=3)
 
 
 def max_points(precision: int) -> int:
@@ -47,6 +65,11 @@ class MLPFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, flat, x, film, desc, precision, sigma_only):
         need = bool(ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) and not sigma_only
+        if ctx.needs_input_grad[2]:
+            raise RuntimeError("gradients w.r.t. the FiLM frequencies / phase shifts are not implemented (the reference's "
+                               "mapping network is commented out, models/nerf.py:185): detach them")
+        if ctx.needs_input_grad[1] and desc.kind == _lib.KIND_SIREN:
+            raise RuntimeError("gradients w.r.t. the SIREN input (points / directions) are not implemented")
         if ctx.needs_input_grad[1] and precision != _lib.PREC_FP32:
             raise RuntimeError("gradients w.r.t. the embedded input are only implemented by the fp32 arm")
         ws = ops.mlp_workspace(desc, precision, x.shape[0], sigma_only, need, x.device)

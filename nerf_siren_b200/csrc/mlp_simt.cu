@@ -417,6 +417,7 @@ int simt_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, cons
   const NerfOffsets o = nerf_offsets(d);
   const int W = d.W;
   const bool siren = d.kind == NERFB_KIND_SIREN;
+  if (siren && d_in) return NERFB_E_UNSUPPORTED;      // SIREN input gradients (d xyz, d dir) are not implemented: refuse, never return zeros
   const int C = 4 + d.n_cls;
   const float* freq = film;
   const float* phase = film ? film + (int64_t)(d.D + 1) * W : nullptr;

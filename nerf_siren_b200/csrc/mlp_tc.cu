@@ -825,15 +825,17 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   a.save = save ? base + pl.off_save : nullptr;
   a.trace = g_trace;
   const size_t smem = sizeof(Smem) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
+  int dev = 0;
+  NERFB_CUDA(cudaGetDevice(&dev));
+  static bool attr_set[64] = {};          // cudaFuncSetAttribute is per device
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
   const bool sv = a.save != nullptr;

@@ -86,6 +86,28 @@ struct DgradArgs {
   int64_t P; int64_t n_tiles;
 };
 
+// Fused backward (mlp_tc_bwd_fused_kernel): the dgrad chain CTAs hand every dZ packet (one step's 2 / 4 blocks) to the
+// wgrad CTAs of the SAME launch through a small per-chain-CTA ring in global memory that stays resident in the 126 MB L2,
+// so dZ is neither written to nor re-read from HBM.  Flags are monotonic counters in global memory (tc_common.cuh).
+constexpr int F_HQ = 4;                    // head-block ring slots per chain CTA
+constexpr int F_PKT_BYTES = 4 * BLK_BYTES; // one packet slot
+constexpr int F_FLAG_STRIDE = 32;          // uint32 words between per-CTA counters (one 128 B line each)
+constexpr int F_MAX_Q = 32;
+struct FusedCtl {
+  int Nc;                          // chain CTAs = blocks [0, Nc); wgrad CTAs = blocks [Nc, Nc + n_units * G)
+  int G;                           // wgrad CTAs per unit: CTA j of a unit owns tiles t = j (mod G)
+  int q;                           // packet ring slots per chain CTA
+  int PK;                          // packets per tile: prologue + n_steps
+  int m_head;                      // items that read the head block
+  int pk_need[MAX_BSTEPS + 1];     // items that read packet i of a tile
+  uint8_t* ring;                   // [Nc][q][F_PKT_BYTES]
+  uint8_t* hring;                  // [Nc][F_HQ][2 * BLK_BYTES]
+  uint32_t* produced;              // [Nc * F_FLAG_STRIDE]  packets published by chain CTA c
+  uint32_t* hprod;                 // [Nc * F_FLAG_STRIDE]  head-block warps (4 per tile) done
+  uint32_t* consumed;              // [Nc][q]      cumulative item reads of the slot
+  uint32_t* hcons;                 // [Nc][F_HQ]
+};
+
 struct __align__(1024) SmemD {
   uint8_t g[4][BLK_BYTES];               // current dZ tile: 4 K-blocks
   uint8_t ring[N_STAGES][STAGE_BYTES];
@@ -146,9 +168,11 @@ __device__ __forceinline__ void store_block16(uint32_t blk, uint32_t row_off, ui
 // v2: 16 epilogue warps (32 rows x 16 columns of every 64-column block each, double-buffered TMEM loads), ReLU gates
 // from the forward's bit-masks (8 B per thread per layer instead of the 64 KB activation image), the dZ stores on their
 // own lane with lagged buffer release, and an MMA thread that only waits and issues.
-template <bool SIREN>
-__global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __grid_constant__ DgradArgs args) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
+// The chain role of one CTA: `cta` of `n_cta` chain CTAs walks tiles cta, cta + n_cta, ...  FUSED = false: the stand-alone
+// dgrad kernel (dZ to the backward record in HBM, wgrad is a later launch).  FUSED = true: dZ packets go to this CTA's
+// L2-resident ring and are published to the wgrad CTAs of the same grid (FusedCtl).
+template <bool SIREN, bool FUSED>
+__device__ __forceinline__ void dgrad_role(const DgradArgs& args, const FusedCtl& fc, uint8_t* smem_raw, const int cta, const int n_cta) {
   SmemD& sm = *reinterpret_cast<SmemD*>(smem_raw);
   if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
   const BProgram& pg = args.prog;
@@ -173,7 +197,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
   if (warp == D_WARP_PRODUCER) {
     if (lane == 0) {                       // ===== weight producer: W^T slabs, 32 KB each =====
       int stage = 0; uint32_t phase = 0;
-      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+      for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta) {
         const uint8_t* src = args.wblob;
         for (int s = 0; s < pg.n_steps; ++s)
           for (int kb = 0; kb < pg.s[s].n_kb; ++kb) {
@@ -193,7 +217,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
       const uint32_t ring_lo0 = ((smem_u32(sm.ring[0]) >> 4) & 0x3FFFu) | (1u << 16);
       const uint32_t ar0 = smem_u32(&sm.a_ready[0]), wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]);
       const uint32_t af0 = smem_u32(&sm.acc_full[0]);
-      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+      for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta) {
         for (int s = 0; s < pg.n_steps; ++s, ++gs) {
           const int n_kb = pg.s[s].n_kb;
           for (int kb = 0; kb < n_kb; ++kb) {
@@ -216,14 +240,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
       }
     }
   } else if (warp == D_WARP_STORE) {
-    if (lane == 0) {                       // ===== store lane: every published dZ block -> HBM for the wgrad =====
+    if (lane == 0 && !FUSED) {             // ===== store lane: every published dZ block -> HBM for the wgrad =====
       uint32_t a_par = 0, pend = 0;
       auto issued = [&](uint32_t bar) {       // store k committed: release the buffer of store k-1 once it has been read
         bulk_commit(); bulk_wait_read1();
         if (pend) mbar_arrive_addr(pend);
         pend = bar;
       };
-      for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+      for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta) {
         uint8_t* rec = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes;
         for (int s = -1; s < pg.n_steps; ++s) {
           const int nb = s < 0 ? pg.n_pro : 4;
@@ -239,6 +263,50 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
       if (pend) mbar_arrive_addr(pend);
       bulk_wait_all0();
     }
+    if (lane == 0 && FUSED) {
+      // ===== store lane, fused: packet n of this CTA (tile-local order: prologue, step 0, ...) -> ring slot n % q.  Before
+      // the first block of a packet the slot's previous occupant (packet n - q) must have been read by all its items;
+      // a packet is PUBLISHED (produced[cta] = n + 1, release) once its stores have completed, which is checked lazily --
+      // F_LAG bulk groups later -- so the lane never sits on the ~1 us store latency.  q >= 3 keeps the wait chain
+      // well-founded: the packet whose slot is awaited was published at least one packet ago.
+      constexpr uint32_t F_LAG = 3;
+      uint32_t a_par = 0, pend = 0;
+      uint32_t n = 0, grp = 0, pub = 0;          // packets fully issued, bulk groups committed, packets published
+      uint32_t last_grp[4] = {0, 0, 0, 0};       // index of the last bulk group of packet (n & 3)
+      uint32_t expect[F_MAX_Q];
+      for (int i = 0; i < F_MAX_Q; ++i) expect[i] = 0;
+      uint32_t* const prod = fc.produced + (size_t)cta * F_FLAG_STRIDE;
+      const uint32_t* const cons = fc.consumed + (size_t)cta * fc.q;
+      uint8_t* const ring = fc.ring + (size_t)cta * fc.q * F_PKT_BYTES;
+      uint32_t slot = 0;
+      for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta) {
+        for (int s = -1; s < pg.n_steps; ++s) {
+          const int nb = s < 0 ? pg.n_pro : 4;
+          gflag_wait_ge(cons + slot, expect[slot]);
+          expect[slot] += (uint32_t)fc.pk_need[s + 1];
+          uint8_t* dst = ring + (size_t)slot * F_PKT_BYTES;
+          for (int j = 0; j < nb; ++j) {
+            mbar_wait_relaxed(&sm.a_ready[j], (a_par >> j) & 1u); a_par ^= 1u << j;
+            bulk_s2g(dst + j * BLK_BYTES, sm.g[j], BLK_BYTES);
+            bulk_commit(); ++grp; bulk_wait_read1();
+            if (pend) mbar_arrive_addr(pend);
+            pend = smem_u32(&sm.g_free[j]);
+            if (j == nb - 1) { last_grp[n & 3u] = grp - 1; ++n; }
+            if (pub < n && grp - 1 - last_grp[pub & 3u] >= F_LAG) {      // the oldest unpublished packet's stores are >= F_LAG groups back
+              bulk_wait_all3();
+              fence_proxy_async_all();
+              ++pub; st_release_gpu(prod, pub);
+            }
+          }
+          if (++slot == (uint32_t)fc.q) slot = 0;
+        }
+      }
+      bulk_wait_read0();
+      if (pend) mbar_arrive_addr(pend);
+      bulk_wait_all0();
+      fence_proxy_async_all();
+      st_release_gpu(prod, n);
+    }
   } else if (warp >= D_WARP_EPI0 && warp < D_WARP_MMA) {
     // ===== prologue (rgb head + direction-layer gate) and per-step epilogues =====
     const int ew = warp - D_WARP_EPI0, q = warp & 3, c4 = ew >> 2;
@@ -247,8 +315,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + 16u * (uint32_t)c4;
     const uint32_t g0_addr = smem_u32(sm.g[0]);
     uint32_t acc_par = 0, gf_par = 0, need_free = 0;
-    uint32_t gs = 0;
-    for (int64_t tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x) {
+    uint32_t gs = 0, tile_k = 0;               // tile_k: this CTA's local tile counter
+    for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta, ++tile_k) {
       const int64_t p = tile * TILE_M + row;
       const bool live = p < args.P;
       const uint8_t* frec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes + c4 * (TILE_M * 8) + row * 8;   // mask layout [c4][row]
@@ -273,11 +341,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
         dsig = dy.w;
       }
       if (c4 == 0) {                          // head block for the wgrad kernel: [g_rgb d_sigma g_cls(8) 0 0 0 0] bf16 per sample
-        uint8_t* hrow = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off;
+        uint8_t* hrow;
+        if (FUSED) {                          // this CTA's head ring: slot k % F_HQ, free once the head items of tile k - F_HQ have read it
+          const uint32_t hs = tile_k % F_HQ;
+          if (lane == 0) gflag_wait_ge(fc.hcons + (size_t)cta * F_HQ + hs, (uint32_t)fc.m_head * (tile_k / F_HQ));
+          __syncwarp();
+          hrow = fc.hring + ((size_t)cta * F_HQ + hs) * (2 * BLK_BYTES);
+        } else {
+          hrow = args.bwd_rec + tile * (int64_t)pg.bwd_tile_bytes + pg.h_off;
+        }
         *reinterpret_cast<uint4*>(hrow + swz_off(row, 0)) =
             make_uint4(pack_bf16(g0, g1), pack_bf16(g2, dsig), pack_bf16(gc[0], gc[1]), pack_bf16(gc[2], gc[3]));
         if (pg.n_cls > 0)
           *reinterpret_cast<uint4*>(hrow + swz_off(row, 8)) = make_uint4(pack_bf16(gc[4], gc[5]), pack_bf16(gc[6], gc[7]), 0u, 0u);
+        if (FUSED) {                          // generic-proxy global writes of this warp -> visible to the consumers' bulk reads
+          __threadfence();
+          fence_proxy_async_all();
+          __syncwarp();
+          if (lane == 0) red_release_gpu_add(fc.hprod + (size_t)cta * F_FLAG_STRIDE, 1u);
+        }
       }
       const uint8_t* arec = args.fwd_rec + tile * (int64_t)pg.fwd_tile_bytes;      // SIREN: saved sine images of this tile
       uint2 mk = __ldg(reinterpret_cast<const uint2*>(frec + pg.hd_off));
@@ -359,6 +441,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __gr
   tc_fence_before();
   __syncthreads();
   if (warp == D_WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+template <bool SIREN>
+__global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_dgrad_kernel(const __grid_constant__ DgradArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  dgrad_role<SIREN, false>(args, FusedCtl{}, smem_raw, (int)blockIdx.x, (int)gridDim.x);
 }
 
 }  // namespace
@@ -554,6 +642,213 @@ __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid
   tc_fence_before();
   __syncthreads();
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// ---- fused backward: the wgrad role ---------------------------------------------------------------------------------
+// A "unit" is a set of <= 4 items whose accumulators fit the 512 TMEM columns together (one 256 x 256 matrix, or e.g.
+// {direction layer, sigma head}); G CTAs serve a unit, CTA j taking tiles t = j (mod G) in increasing order and, inside a
+// tile, its items in the order the chain produces their dZ packets (head block first).  Every wait therefore points at a
+// lexicographically smaller (tile, packet), which is what makes the chain <-> wgrad hand-off deadlock-free.
+constexpr int F_MAX_UNITS = 16;
+constexpr int F_UNIT_ITEMS = 4;
+struct FusedWArgs {
+  int n_items; WItem item[MAX_ITEMS];
+  int item_pk[MAX_ITEMS];                    // packet index inside a tile (0 = prologue, s + 1 = step s), -1 = head block
+  int item_col[MAX_ITEMS][2];                // TMEM column of the accumulator half mh
+  int item_pslot[MAX_ITEMS];                 // partial slot of wgrad CTA w: item_pslot[i] + w_in_unit * unit_n[u]  (+ unit_pbase[u])
+  int item_unit[MAX_ITEMS];
+  int n_units; int unit_n[F_MAX_UNITS]; int unit_item[F_MAX_UNITS][F_UNIT_ITEMS]; int unit_pbase[F_MAX_UNITS];
+  const uint8_t* fwd_rec; int fwd_tile_bytes;
+  int64_t n_tiles;
+  float* partial; float* grad; float* aux;
+};
+
+__device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const FusedCtl& fc, uint8_t* smem_raw) {
+  SmemW& sm = *reinterpret_cast<SmemW*>(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int w = (int)blockIdx.x - fc.Nc, u = w / fc.G, jg = w % fc.G;
+  const int n_it = args.unit_n[u];
+  const int my_tiles = (int)((args.n_tiles - jg + fc.G - 1) / fc.G);       // tiles jg, jg + G, ... (n_tiles >= G is guaranteed by the host)
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < W_STAGES; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 5); }
+    mbar_init(&sm.acc_done, 1); mbar_init(&sm.acc_free, 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {                         // ===== producer: dZ halves from the chain CTAs' rings (L2), input halves from the forward record (HBM) =====
+      int st = 0; uint32_t ph = 0;
+      const uint64_t stream_once = l2_policy_evict_first();
+      for (int ti = 0; ti < my_tiles; ++ti) {
+        const int64_t tile = jg + (int64_t)ti * fc.G;
+        const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+        for (int li = 0; li < n_it; ++li) {
+          const int it = args.unit_item[u][li];
+          const WItem& im = args.item[it];
+          const int pk = args.item_pk[it];
+          const uint8_t* dzp;
+          if (pk >= 0) {
+            const uint32_t n = k * (uint32_t)fc.PK + (uint32_t)pk;
+            gflag_wait_ge(fc.produced + (size_t)c * F_FLAG_STRIDE, n + 1);
+            dzp = fc.ring + ((size_t)c * fc.q + n % (uint32_t)fc.q) * F_PKT_BYTES;
+          } else {
+            gflag_wait_ge(fc.hprod + (size_t)c * F_FLAG_STRIDE, 4u * (k + 1));
+            dzp = fc.hring + ((size_t)c * F_HQ + k % F_HQ) * (2 * BLK_BYTES);
+          }
+          fence_proxy_async_all();
+          const uint8_t* ap = args.fwd_rec + tile * (int64_t)args.fwd_tile_bytes + im.a_off;
+          for (int half = 0; half < 2; ++half) {
+            mbar_wait(&sm.empty[st], ph ^ 1);
+            mbar_expect_tx(&sm.full[st], (uint32_t)(im.nM + im.nN) * W_HALF);
+            for (int j = 0; j < im.nM; ++j) bulk_g2s(sm.stage[st] + j * W_HALF, dzp + j * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st]);
+            for (int j = 0; j < im.nN; ++j)
+              bulk_g2s_hint(sm.stage[st] + (4 + j) * W_HALF, ap + j * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st], stream_once);
+            if (++st == W_STAGES) { st = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {                         // ===== MMA issuer =====
+      int st = 0; uint32_t ph = 0;
+      for (int ti = 0; ti < my_tiles; ++ti) {
+        for (int li = 0; li < n_it; ++li) {
+          const int it = args.unit_item[u][li];
+          const WItem& im = args.item[it];
+          const uint32_t idesc = umma_idesc_bf16(128, im.N, 1, 1);
+          const uint32_t col0 = (uint32_t)args.item_col[it][0], col1 = (uint32_t)args.item_col[it][1];
+          for (int half = 0; half < 2; ++half) {
+            mbar_wait(&sm.full[st], ph);
+            tc_fence_after();
+            const uint32_t base = smem_u32(sm.stage[st]);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)       // 16 samples per UMMA
+              for (int mh = 0; mh < (im.nM >> 1); ++mh)
+                umma_bf16(tmem + (mh ? col1 : col0), umma_desc_mn128(base + mh * 2 * W_HALF + ks * 2048, W_HALF),
+                          umma_desc_mn128(base + 4 * W_HALF + ks * 2048, W_HALF), idesc, (ti > 0 || half > 0 || ks > 0) ? 1u : 0u);
+            umma_commit(&sm.empty[st]);
+            if (++st == W_STAGES) { st = 0; ph ^= 1; }
+          }
+        }
+      }
+      umma_commit(&sm.acc_done);
+    }
+  } else if (warp < 6) {
+    // ===== bias column sums (from shared memory), slot release, accumulator flush =====
+    const int q = warp & 3, bt = (warp - 2) * 32 + lane;
+    const int blk = bt >> 5, c2 = bt & 31;
+    int st = 0; uint32_t ph = 0;
+    float b0[F_UNIT_ITEMS], b1[F_UNIT_ITEMS];
+#pragma unroll
+    for (int li = 0; li < F_UNIT_ITEMS; ++li) { b0[li] = 0.f; b1[li] = 0.f; }
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      const int64_t tile = jg + (int64_t)ti * fc.G;
+      const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+#pragma unroll
+      for (int li = 0; li < F_UNIT_ITEMS; ++li) {
+        if (li < n_it) {
+          const int it = args.unit_item[u][li];
+          const WItem& im = args.item[it];
+          const bool sum_here = im.bias_off >= 0 && blk < im.nM;
+          for (int half = 0; half < 2; ++half) {
+            mbar_wait(&sm.full[st], ph);
+            if (half == 1 && bt == 0) {        // both halves of the packet are in shared memory: hand the ring slot back
+              const int pk = args.item_pk[it];
+              if (pk >= 0) red_release_gpu_add(fc.consumed + (size_t)c * fc.q + (k * (uint32_t)fc.PK + (uint32_t)pk) % (uint32_t)fc.q, 1u);
+              else red_release_gpu_add(fc.hcons + (size_t)c * F_HQ + k % F_HQ, 1u);
+            }
+            if (sum_here) {
+              const uint8_t* src = sm.stage[st] + blk * W_HALF + ((c2 & 3) << 2);
+#pragma unroll 8
+              for (int r = 0; r < 64; ++r) {
+                const uint32_t wd = *reinterpret_cast<const uint32_t*>(src + r * 128 + ((((uint32_t)c2 >> 2) ^ ((uint32_t)r & 7u)) << 4));
+                b0[li] += __uint_as_float(wd << 16); b1[li] += __uint_as_float(wd & 0xFFFF0000u);
+              }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[st]);
+            if (++st == W_STAGES) { st = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+    mbar_wait(&sm.acc_done, 0);
+    tc_fence_after();
+#pragma unroll
+    for (int li = 0; li < F_UNIT_ITEMS; ++li) {
+      if (li < n_it) {
+        const int it = args.unit_item[u][li];
+        const WItem& im = args.item[it];
+        if (im.bias_off >= 0 && blk < im.nM) {
+          if (im.bias_alt < 0) {
+            float* bdst = (im.aux ? args.aux : args.grad) + im.bias_off;
+            atomicAdd(bdst + 2 * bt, b0[li]);
+            atomicAdd(bdst + 2 * bt + 1, b1[li]);
+          } else if (bt < 2) {               // head block: columns [g_r g_g g_b d_sigma]
+            atomicAdd(args.grad + im.bias_off + 2 * bt, b0[li]);
+            atomicAdd(bt == 0 ? args.grad + im.bias_off + 1 : args.grad + im.bias_alt, b1[li]);
+          }
+        }
+        float* part = args.partial + (int64_t)(args.unit_pbase[u] + jg * n_it + args.item_pslot[it]) * W_SLOT;
+        for (int mh = 0; mh < (im.nM >> 1); ++mh) {
+          const int m = mh * 128 + q * 32 + lane;
+          if (mh * 128 + q * 32 >= im.m_hi || mh * 128 + q * 32 + 32 <= im.m_lo) continue;      // warp-uniform
+          float* dst = part + (int64_t)m * 256;
+          const bool real = m >= im.m_lo && m < im.m_hi;
+          for (int c0 = 0; c0 < im.N; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(args.item_col[it][mh] + c0), v);
+            tmem_ld_wait();
+            if (real && c0 < im.nvalid) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4)
+                *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                                                                      __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+struct FusedArgs { DgradArgs d; FusedCtl fc; FusedWArgs w; };
+
+template <bool SIREN>
+__global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_bwd_fused_kernel(const __grid_constant__ FusedArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  if ((int)blockIdx.x < args.fc.Nc) dgrad_role<SIREN, true>(args.d, args.fc, smem_raw, (int)blockIdx.x, args.fc.Nc);
+  else wgrad_fused_role(args.w, args.fc, smem_raw);
+}
+
+// grad[w_off + r * ld + col0 + n] += sum over the G partials of the item's unit
+__global__ void __launch_bounds__(256) reduce_partials_fused_kernel(const __grid_constant__ FusedWArgs ra, int G) {
+  const int it = blockIdx.x;
+  const WItem& im = ra.item[it];
+  const int u = ra.item_unit[it];
+  const int n_it = ra.unit_n[u];
+  const float* base = ra.partial + (int64_t)(ra.unit_pbase[u] + ra.item_pslot[it]) * W_SLOT;
+  const int total = (im.m_hi - im.m_lo) * im.nvalid;
+  for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < total; e += gridDim.y * blockDim.x) {
+    const int r = im.m_lo + e / im.nvalid, n = e % im.nvalid;
+    float s = 0.f;
+    for (int j = 0; j < G; ++j) {
+      const float* pp = base + (int64_t)j * n_it * W_SLOT + r * 256 + n;
+      s += im.hilo ? pp[0] + pp[3] : pp[0];
+    }
+    if (im.aux) ra.aux[im.w_off + (int64_t)r * im.ld + im.col0 + n] = s;
+    else ra.grad[im.w_off + (int64_t)r * im.ld + im.col0 + n] += s;
+  }
 }
 
 // grad[w_off + r * ld + col0 + n] += sum over the active CTAs' partials
@@ -782,7 +1077,115 @@ bool tc_bwd_supported(const nerfb_mlp_desc& d) {
   for (int i = 1; i < d.D; ++i) skips += (d.skip_mask >> i) & 1;
   return d.D + skips + 5 + (d.n_cls > 0 ? 1 : 0) <= MAX_ITEMS && d.D + 1 <= MAX_BSTEPS;
 }
-int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) { return bwd_plan(d, P).total; }
+
+namespace {
+
+// ---- fused launch plan: units (bin packing of the wgrad items under the 512-column TMEM budget), SM split, ring sizes -------
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+struct FusedPlan {
+  bool on;
+  FusedCtl fc; FusedWArgs w;
+  int n_units, grid;
+  int64_t off_ring, off_hring, off_flags, flags_bytes, off_partial, off_aux, total;   // relative to the backward workspace part
+};
+
+// MMA issue cost of one item per tile in clocks: 8 K-steps x M-halves x N/2 (tcgen05 floor), small-N shapes are bound by the
+// shared-memory operand fetch instead (A 4 KB + B N*32 B per instruction at 128 B/clk)
+int item_clk(const WItem& im) {
+  const int per = im.N / 2 > (4096 + im.N * 32) / 128 ? im.N / 2 : (4096 + im.N * 32) / 128;
+  return 8 * (im.nM >> 1) * per;
+}
+
+FusedPlan fused_plan(const BwdPlan& pl) {
+  FusedPlan fp{};
+  fp.on = false;
+  if (env_int("NERFB_BWD_FUSED", 1) == 0) return fp;
+  const BProgram& pg = pl.prog;
+  const WgradArgs& wg = pl.wg;
+  FusedWArgs& w = fp.w;
+  w.n_items = wg.n_items;
+  int order[MAX_ITEMS];
+  for (int i = 0; i < wg.n_items; ++i) {
+    w.item[i] = wg.item[i];
+    const int dz = wg.item[i].dz_off;
+    int pk = -2;
+    if (dz == pg.h_off) pk = -1;
+    else if (dz == pg.dzdir_off) pk = 0;
+    else for (int s = 0; s < pg.n_steps; ++s) if (pg.s[s].save_off == dz) pk = s + 1;
+    if (pk == -2 || !wg.item[i].a_fwd) return fp;                       // not expressible as packets: keep the 3-launch path
+    w.item_pk[i] = pk;
+    order[i] = i;
+  }
+  // first-fit decreasing on cost; capacity: 512 TMEM columns, F_UNIT_ITEMS items, ~1.2 x the cost of a full 256 x 256 item
+  for (int a = 0; a < wg.n_items; ++a)
+    for (int b = a + 1; b < wg.n_items; ++b)
+      if (item_clk(wg.item[order[b]]) > item_clk(wg.item[order[a]])) { const int t = order[a]; order[a] = order[b]; order[b] = t; }
+  int ucost[F_MAX_UNITS] = {0}, ucols[F_MAX_UNITS] = {0};
+  const int cap = (int)(2048 * 1.2);
+  int nu = 0;
+  for (int a = 0; a < wg.n_items; ++a) {
+    const int i = order[a];
+    const WItem& im = wg.item[i];
+    const int cols = (im.nM >> 1) * im.N, clk = item_clk(im);
+    int u = 0;
+    for (; u < nu; ++u)
+      if (ucols[u] + cols <= 512 && w.unit_n[u] < F_UNIT_ITEMS && ucost[u] + clk <= cap) break;
+    if (u == nu) { if (nu == F_MAX_UNITS) return fp; ++nu; w.unit_n[u] = 0; }
+    w.unit_item[u][w.unit_n[u]++] = i;
+    w.item_unit[i] = u;
+    ucols[u] += cols; ucost[u] += clk;
+  }
+  w.n_units = nu; fp.n_units = nu;
+  // inside a unit: packet order (head block first), then TMEM columns and partial slots in that order
+  for (int u = 0; u < nu; ++u) {
+    int* li = w.unit_item[u];
+    for (int a = 0; a < w.unit_n[u]; ++a)
+      for (int b = a + 1; b < w.unit_n[u]; ++b)
+        if (w.item_pk[li[b]] < w.item_pk[li[a]]) { const int t = li[a]; li[a] = li[b]; li[b] = t; }
+    int col = 0;
+    for (int a = 0; a < w.unit_n[u]; ++a) {
+      const WItem& im = w.item[li[a]];
+      w.item_pslot[li[a]] = a;
+      for (int mh = 0; mh < (im.nM >> 1); ++mh) { w.item_col[li[a]][mh] = col; col += im.N; }
+    }
+  }
+  FusedCtl& fc = fp.fc;
+  fc.G = env_int("NERFB_FUSED_G", 6);
+  fc.q = env_int("NERFB_FUSED_Q", 8);
+  if (fc.G < 1 || fc.q < 3 || fc.q > F_MAX_Q) return fp;
+  fc.Nc = NERFB_SM_COUNT - nu * fc.G;
+  fc.PK = pg.n_steps + 1;
+  // the fused grid needs every wgrad CTA to own tiles and the chain CTAs several rounds each; small problems keep the 3-launch path
+  if (fc.Nc < 16 || pl.n_tiles < 4 * (int64_t)NERFB_SM_COUNT) return fp;
+  fc.m_head = 0;
+  for (int i = 0; i <= MAX_BSTEPS; ++i) fc.pk_need[i] = 0;
+  for (int i = 0; i < w.n_items; ++i) { if (w.item_pk[i] < 0) ++fc.m_head; else ++fc.pk_need[w.item_pk[i]]; }
+  int pbase = 0;
+  for (int u = 0; u < nu; ++u) { w.unit_pbase[u] = pbase; pbase += fc.G * w.unit_n[u]; }
+  fp.grid = fc.Nc + nu * fc.G;
+  int64_t off = 0;
+  fp.off_ring = off;    off += (int64_t)fc.Nc * fc.q * F_PKT_BYTES;
+  fp.off_hring = off;   off += (int64_t)fc.Nc * F_HQ * 2 * BLK_BYTES;
+  fp.off_flags = off;   fp.flags_bytes = ((int64_t)fc.Nc * (2 * F_FLAG_STRIDE + fc.q + F_HQ)) * 4; off += round_up64(fp.flags_bytes, 1024);
+  fp.off_partial = off; off += (int64_t)pbase * W_SLOT * 4;
+  fp.off_aux = off;     off += (16 * 256 + 128) * 4;
+  fp.total = round_up64(off, 1024);
+  fp.on = true;
+  return fp;
+}
+
+}  // namespace
+
+// The backward workspace follows the forward's: packed W^T slabs | head vectors | then EITHER the 3-launch path's per-tile dZ
+// record + partials, OR the fused path's rings + flags + partials (decided by the same plan function in both entry points).
+int64_t tc_bwd_workspace_bytes(const nerfb_mlp_desc& d, int64_t P) {
+  const BwdPlan pl = bwd_plan(d, P);
+  const FusedPlan fp = fused_plan(pl);
+  return fp.on ? pl.off_rec + fp.total : pl.total;
+}
 
 int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, const float* out, const float* d_out, float* grad,
@@ -793,7 +1196,8 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
   const TcFwdLayout L = tc_fwd_layout(d, P);
   BwdPlan pl = bwd_plan(d, P);
-  if (ws_bytes < L.total + pl.total) return NERFB_E_WORKSPACE;
+  FusedPlan fp = fused_plan(pl);
+  if (ws_bytes < L.total + (fp.on ? pl.off_rec + fp.total : pl.total)) return NERFB_E_WORKSPACE;
   if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return NERFB_E_BADARG;
   uint8_t* base = static_cast<uint8_t*>(ws);
   uint8_t* bb = base + L.total;
@@ -802,19 +1206,53 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   NERFB_LAUNCH(pack_weights_t_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, bb + pl.off_wblob);
   NERFB_LAUNCH(gather_heads_kernel, 1, 256, 0, stream, params, pl.head.w_sigma, pl.head.w_rgb, heads, pl.prog.rgb_in);
 
-  static bool attr_set = false;
+  int dev = 0;
+  NERFB_CUDA(cudaGetDevice(&dev));
+  static bool attr_set[64] = {};          // the attribute is per device
   const size_t smem_d = sizeof(SmemD) + 1024, smem_w = sizeof(SmemW) + 1024;
-  if (!attr_set) {
+  const size_t smem_f = smem_d > smem_w ? smem_d : smem_w;
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
     NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_d));
     NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w));
-    attr_set = true;
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_bwd_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+    NERFB_CUDA(cudaFuncSetAttribute(mlp_tc_bwd_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   DgradArgs da{};
   da.prog = pl.prog; da.wblob = bb + pl.off_wblob; da.heads = heads; da.out = out; da.d_out = d_out;
   da.fwd_rec = fwd_rec; da.bwd_rec = bb + pl.off_rec; da.P = P; da.n_tiles = pl.n_tiles;
   da.weff = reinterpret_cast<const float*>(base + L.off_weff);
   da.film = film;
+
+  if (fp.on) {
+    // ONE launch: chain CTAs [0, Nc) and wgrad CTAs [Nc, grid) of a co-resident grid (<= 1 CTA per SM) exchange dZ through L2
+    uint8_t* fb = bb + pl.off_rec;
+    FusedArgs fa{};
+    fa.d = da; fa.d.bwd_rec = nullptr;
+    fa.fc = fp.fc;
+    fa.fc.ring = fb + fp.off_ring; fa.fc.hring = fb + fp.off_hring;
+    uint32_t* flags = reinterpret_cast<uint32_t*>(fb + fp.off_flags);
+    fa.fc.produced = flags;
+    fa.fc.hprod = flags + (size_t)fp.fc.Nc * F_FLAG_STRIDE;
+    fa.fc.consumed = flags + (size_t)fp.fc.Nc * 2 * F_FLAG_STRIDE;
+    fa.fc.hcons = fa.fc.consumed + (size_t)fp.fc.Nc * fp.fc.q;
+    fa.w = fp.w;
+    fa.w.fwd_rec = fwd_rec; fa.w.fwd_tile_bytes = pl.prog.fwd_tile_bytes; fa.w.n_tiles = pl.n_tiles;
+    fa.w.partial = reinterpret_cast<float*>(fb + fp.off_partial); fa.w.grad = grad;
+    fa.w.aux = reinterpret_cast<float*>(fb + fp.off_aux);
+    NERFB_CUDA(cudaMemsetAsync(flags, 0, (size_t)fp.flags_bytes, (cudaStream_t)stream));
+    if (d.n_cls > 0) NERFB_CUDA(cudaMemsetAsync(fa.w.aux + 16 * 256, 0, 128 * 4, (cudaStream_t)stream));
+    if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<true>, fp.grid, NUM_THREADS, smem_f, stream, fa);
+    else NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<false>, fp.grid, NUM_THREADS, smem_f, stream, fa);
+    NERFB_LAUNCH(reduce_partials_fused_kernel, dim3(fa.w.n_items, 32), 256, 0, stream, fa.w, fp.fc.G);
+    if (d.n_cls > 0) {
+      const NerfOffsets o = nerf_offsets(d);
+      NERFB_LAUNCH(parse_chain_kernel, 512, 256, 0, stream, params, (const float*)fa.w.aux, d.n_cls, o.w_p0, o.b_p0, o.w_p1, o.b_p1, grad);
+    }
+    return NERFB_OK;
+  }
+
   if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_dgrad_kernel<true>, pl.n_active, NUM_THREADS, smem_d, stream, da);
   else NERFB_LAUNCH(mlp_tc_dgrad_kernel<false>, pl.n_active, NUM_THREADS, smem_d, stream, da);
 

@@ -159,6 +159,48 @@ __device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.w
 // generic-proxy smem writes -> visible to the async proxy (UMMA operand fetch, bulk stores)
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// same copy with an L2 eviction-priority hint (streamed-once operands must not push the L2-resident ring out)
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all3() { asm volatile("cp.async.bulk.wait_group 3;" ::: "memory"); }
+// generic <-> async proxy ordering for ALL state spaces (global data written / read by bulk copies and by ld/st)
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// ---- cross-CTA flags in global memory (co-resident CTAs of ONE persistent grid: producer / consumer hand-off through L2) ----
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// bounded spin until *p >= target (monotonic counters; wrap-safe compare); traps instead of hanging the GPU
+__device__ __forceinline__ void gflag_wait_ge(const uint32_t* p, uint32_t target) {
+  if ((int32_t)(ld_acquire_gpu(p) - target) >= 0) return;
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_gpu(p) - target) < 0) {
+    __nanosleep(64);
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: global flag timeout (block %d thread %d flag %p target %u have %u)\n", (int)blockIdx.x, (int)threadIdx.x,
+             (const void*)p, target, ld_acquire_gpu(p));
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
+      __trap();
+    }
+  }
+}
+
 // ---- tcgen05 ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }

@@ -72,17 +72,35 @@ class OSGDecoder(nn.Module):
 
 
 class _Planes:
-    """Channels-last copy of one batch element's planes, cached on the source tensor's identity + version."""
+    """Channels-last copy of one batch element's planes.  The copy is reused only for a PERSISTENT source -- the very same
+    root tensor object (held by weak reference: a leaf / nn.Parameter such as ``LearnedPlanes.planes``) at the same
+    ``_version``.  A generator backbone returns a fresh tensor per call, usually at the address the caching allocator just
+    freed, so an address-based key would serve the previous call's planes: anything not provably the same object is
+    re-laid out (one streaming kernel)."""
 
     def __init__(self):
-        self.key, self.cl = None, None
+        self.ref, self.version, self.index, self.cl = None, None, None, None
 
-    def get(self, planes: torch.Tensor) -> torch.Tensor:
-        key = (planes.data_ptr(), planes._version, tuple(planes.shape))
-        if key != self.key:
-            self.cl = ops.triplane_relayout(planes)
-            self.key = key
+    def get(self, planes: torch.Tensor, b: int) -> torch.Tensor:
+        import weakref
+        root = planes._base if planes._base is not None else planes
+        persistent = root.is_leaf and not (root.grad_fn is not None)
+        if (persistent and self.ref is not None and self.ref() is root and self.version == root._version
+                and self.index == (b, planes.data_ptr(), tuple(planes.shape))):
+            return self.cl
+        self.cl = ops.triplane_relayout(planes[b])
+        self.ref, self.version = (weakref.ref(root), root._version) if persistent else (None, None)
+        self.index = (b, planes.data_ptr(), tuple(planes.shape))
         return self.cl
+
+
+def _refuse_grad(planes, decoder, what):
+    """Kernel (6) is the render path (the reference renders through it under no_grad, eval_eg3d.py:63-75); there is no
+    backward kernel, so a call that autograd would expect to differentiate must fail loudly instead of training nothing."""
+    if torch.is_grad_enabled() and (planes.requires_grad or any(p.requires_grad for p in decoder.parameters())):
+        raise RuntimeError(f"{what}: the EG3D tri-plane path of nerf_siren_b200 is forward-only (no backward kernel for the "
+                           "plane gather / decoder / marcher); call it under torch.no_grad(). EG3D training "
+                           "(system.py:111-120 of the reference) is not provided.")
 
 
 class MipRayMarcher2(nn.Module):
@@ -135,6 +153,7 @@ class ImportanceRenderer(nn.Module):
 
     def forward(self, planes, decoder, ray_origins, ray_directions, rendering_options, rand_coarse=None, u=None):
         opts = rendering_options
+        _refuse_grad(planes, decoder, "ImportanceRenderer.forward")
         if opts.get("clamp_mode", "softplus") != "softplus":
             assert False, "MipRayMarcher only supports `clamp_mode`=`softplus`!"
         if opts.get("density_noise", 0) > 0:
@@ -159,7 +178,7 @@ class ImportanceRenderer(nn.Module):
         for b in range(B):                          # planes differ per batch element; rays of one element form one launch
             self.seed += 1
             res = ops.triplane_render(
-                self._cache.get(planes[b]) if B == 1 else ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
+                self._cache.get(planes, b) if B == 1 else ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
                 ray_origins[b].contiguous(), ray_directions[b].contiguous(), opts["depth_resolution"], n_imp, float(rs), float(re),
                 None if start_arr is None else start_arr[b].reshape(-1).contiguous(),
                 None if end_arr is None else end_arr[b].reshape(-1).contiguous(),
@@ -175,6 +194,7 @@ class ImportanceRenderer(nn.Module):
         """renderer.py:144-151 -> {'rgb': (N, M, 3), 'sigma': (N, M, 1)}."""
         if options.get("density_noise", 0) > 0:
             raise NotImplementedError("density_noise > 0 is not on the render path")
+        _refuse_grad(planes, decoder, "ImportanceRenderer.run_model")
         N, M, _ = sample_coordinates.shape
         rgbs, sigmas = [], []
         for b in range(N):
@@ -193,7 +213,9 @@ DEFAULT_RENDERING_KWARGS = {
 
 
 class LearnedPlanes(nn.Module):
-    """Stand-in for the plane source: a directly optimisable (1, 96, H, W) feature image.  The reference produces the planes
+    """Stand-in for the plane source: a (1, 96, H, W) feature image held as a parameter (so it moves with ``.to()`` and
+    lands in checkpoints).  It is NOT trainable through this package: kernel (6) has no backward, and the renderer refuses
+    grad-enabled calls.  The reference produces the planes
     with a StyleGAN2 backbone (``TriPlaneGenerator.backbone.synthesis``, eg3d_training/triplane.py:61), which is outside the
     render_rays path (out of scope); any module / callable returning (B, 96, H, W) can take its place."""
 

@@ -333,3 +333,35 @@ def pack_vol(rgbsigma, neg_step):
     check(lib.nerfb_pack_vol(src, n, float(neg_step), pairs.data_ptr(), k, n_valid.data_ptr(), ws_ptr, ws_bytes, _stream()),
           "nerfb_pack_vol")
     return pairs[:k]
+
+
+# ---- device guard ---------------------------------------------------------------------------------------------
+# Kernels launch on the CUDA runtime's CURRENT device and on that device's current stream.  When the tensors of a call
+# live on another GPU (evaluation on cuda:1 from a process whose current device is cuda:0), enter that device for the call.
+def _on_tensor_device(fn):
+    import functools
+
+    @functools.wraps(fn)
+    def guarded(*args, **kwargs):
+        dev = None
+        for a in args:
+            if isinstance(a, torch.Tensor) and a.is_cuda:
+                dev = a.device
+                break
+        if dev is None:
+            for a in kwargs.values():
+                if isinstance(a, torch.Tensor) and a.is_cuda:
+                    dev = a.device
+                    break
+        if dev is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return guarded
+
+
+for _name in ("sample_coarse", "embed", "composite_fwd", "composite_bwd", "searchsorted", "sample_pdf", "resample",
+              "adam_step", "mlp_fwd", "mlp_bwd", "triplane_relayout", "triplane_field", "mip_march", "triplane_render",
+              "finish_image", "sigma_grid", "pack_vol"):
+    globals()[_name] = _on_tensor_device(globals()[_name])
+del _name

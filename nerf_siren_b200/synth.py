@@ -71,3 +71,40 @@ def llff_rays(n: int, seed: int = 0, w: int = 504, h: int = 378, focal: float = 
 
 def target_rgbs(n: int, seed: int = 0) -> torch.Tensor:
     return torch.rand(n, 3, generator=torch.Generator().manual_seed(seed + 7919))
+
+
+# ---- EG3D-shaped inputs (BASELINE config 5) -------------------------------------------------------------------
+def eg3d_planes(res: int = 256, channels: int = 32, seed: int = 0) -> torch.Tensor:
+    """(3, C, res, res) tri-planes: smooth low-frequency noise plus white noise, so densities vary along a ray (the
+    reference's planes come out of a StyleGAN2 backbone, eg3d_training/triplane.py:61, which is out of scope)."""
+    g = torch.Generator().manual_seed(seed)
+    lo = torch.randn(3, channels, max(res // 16, 2), max(res // 16, 2), generator=g)
+    up = torch.nn.functional.interpolate(lo, size=(res, res), mode="bilinear", align_corners=False)
+    return (up * 2.0 + 0.3 * torch.randn(3, channels, res, res, generator=g)).contiguous()
+
+
+def eg3d_decoder(seed: int = 0) -> torch.Tensor:
+    """OSGDecoder weights (eg3d_training/triplane.py:144-167, randn init of networks_stylegan2.py:109) as the flat vector
+    the kernel takes: W1 (64 x 32) | b1 (64) | W2 (4 x 64) | b2 (4)."""
+    g = torch.Generator().manual_seed(seed)
+    return torch.cat([torch.randn(64 * 32, generator=g), torch.randn(64, generator=g) * 0.1,
+                      torch.randn(4 * 64, generator=g), torch.randn(4, generator=g) * 0.1]).contiguous()
+
+
+def eg3d_camera_rays(n: int, seed: int = 0, radius: float = 2.7, fov_deg: float = 18.8, res: int = 128):
+    """n rays of a res x res pinhole camera on a sphere of `radius` looking at the origin (eg3d_renderer.py:30-32 shapes)
+    -> (origins (n, 3), directions (n, 3)), row-major pixel order when n == res * res."""
+    g = torch.Generator().manual_seed(seed)
+    th, ph = float(torch.rand(1, generator=g)) * 2 * math.pi, 1.2 + 0.6 * float(torch.rand(1, generator=g))
+    cam = torch.tensor([radius * math.sin(ph) * math.cos(th), radius * math.cos(ph), radius * math.sin(ph) * math.sin(th)])
+    fwd = -cam / cam.norm()
+    right = torch.linalg.cross(fwd, torch.tensor([0.0, 1.0, 0.0]))
+    right = right / right.norm()
+    upv = torch.linalg.cross(right, fwd)
+    pix = torch.arange(n) % (res * res) if n >= res * res else torch.randint(0, res * res, (n,), generator=g)
+    i, j = (pix % res).float(), (pix // res).float()
+    t = math.tan(math.radians(fov_deg) / 2)
+    x, y = ((i + 0.5) / res * 2 - 1) * t, (1 - (j + 0.5) / res * 2) * t
+    d = fwd[None] + x[:, None] * right[None] + y[:, None] * upv[None]
+    d = d / d.norm(dim=-1, keepdim=True)
+    return cam.expand(n, 3).contiguous(), d.contiguous()

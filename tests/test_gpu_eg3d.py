@@ -113,7 +113,8 @@ def test_renderer_module_is_a_drop_in():
     for got, key in zip(out, KEYS):
         torch.testing.assert_close(got.cpu(), g[key], rtol=0, atol=1e-3 if "depth" in key else 2e-4)
     coords = (ro.unsqueeze(-2) + g["depths_coarse"] * rd.unsqueeze(-2)).reshape(1, -1, 3)
-    rm = ren.run_model(planes.to(DEV), decoder, coords.to(DEV), None, opts)
+    with torch.no_grad():
+        rm = ren.run_model(planes.to(DEV), decoder, coords.to(DEV), None, opts)
     torch.testing.assert_close(rm["rgb"].cpu(), g["field_rgb"], rtol=0, atol=2e-5)
     assert rm["sigma"].shape == g["field_sigma"].shape
     mm = m.MipRayMarcher2()(g["field_rgb"].reshape(1, R, S, 3).to(DEV), g["field_sigma"].reshape(1, R, S, 1).to(DEV),
@@ -160,3 +161,48 @@ def test_empty_and_bad_arguments():
         nb().ops.triplane_relayout(torch.zeros(3, 16, 8, 8, device=DEV))          # 16 channels: NERFB_E_UNSUPPORTED
     with pytest.raises(RuntimeError):
         nb().ops.triplane_field(torch.zeros(3, 8, 8, 32), dec, 1.0, torch.zeros(4, 3), 1.0)   # CPU tensors are refused
+
+
+def test_fresh_plane_tensors_are_never_served_from_the_cache():
+    """a plane source that returns a FRESH tensor per call (generator backbone) usually gets the address the
+    caching allocator just freed, version 0, same shape.  Two different plane sets rendered back to back through one
+    renderer must give two different images, each equal to a fresh renderer's; a persistent Parameter updated in place
+    (version bump) must be re-laid out too."""
+    g = gold("g10_eg3d_small")
+    planes, dec, ro, rd, opts = setup(g)
+    m = nb().eg3d
+    decoder = m.OSGDecoder(32, {"decoder_lr_mul": 1, "decoder_output_dim": 3}).to(DEV)
+    decoder.load_state_dict(dec)
+    kw = dict(rand_coarse=g["rand_coarse"].to(DEV), u=g["u"].to(DEV))
+    ren = m.ImportanceRenderer()
+    outs = []
+    with torch.no_grad():
+        for scale in (1.0, -0.5):
+            fresh = (planes * scale).to(DEV)                       # new tensor object; freed before the next one is made
+            outs.append(ren(fresh, decoder, ro.to(DEV), rd.to(DEV), opts, **kw)[3].clone())
+            want = m.ImportanceRenderer()(fresh, decoder, ro.to(DEV), rd.to(DEV), opts, **kw)[3]
+            assert torch.equal(outs[-1], want), scale
+            del fresh, want
+        assert not torch.equal(outs[0], outs[1])
+        p = torch.nn.Parameter(planes.clone().to(DEV))
+        a = ren(p, decoder, ro.to(DEV), rd.to(DEV), opts, **kw)[3].clone()
+        a2 = ren(p, decoder, ro.to(DEV), rd.to(DEV), opts, **kw)[3]
+        assert torch.equal(a, a2)
+        p.mul_(0.25)                                                # in-place update: same object, new _version
+        b = ren(p, decoder, ro.to(DEV), rd.to(DEV), opts, **kw)[3]
+        assert not torch.equal(a, b)
+
+
+def test_grad_enabled_calls_are_refused():
+    """Kernel (6) has no backward: a grad-enabled call on trainable planes / decoder raises instead of silently training
+    nothing."""
+    g = gold("g10_eg3d_small")
+    planes, dec, ro, rd, opts = setup(g)
+    m = nb().eg3d
+    decoder = m.OSGDecoder(32, {"decoder_lr_mul": 1, "decoder_output_dim": 3}).to(DEV)
+    with pytest.raises(RuntimeError, match="forward-only"):
+        m.ImportanceRenderer()(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts)
+    for p in decoder.parameters():
+        p.requires_grad_(False)
+    out = m.ImportanceRenderer()(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts)      # nothing trainable: allowed
+    assert torch.isfinite(out[3]).all()

@@ -128,6 +128,17 @@ int nerfb_composite_bwd(const float* raw, int channels, const float* z, const fl
  *   cat, sort -> z_fine (N, S_c+S_i) ascending. */
 int nerfb_searchsorted(const float* a, int64_t rows_a, int64_t len_a, const float* v, int64_t rows_v,
                        int64_t len_v, int side_left, int64_t* out, void* stream);
+/* The same contract for every scalar type the reference's kernel is dispatched on (AT_DISPATCH_ALL_TYPES,
+ * src/cuda/searchsorted_cuda_kernel.cu:134): a and v share `dtype`, out stays int64. */
+#define NERFB_DT_F32 0
+#define NERFB_DT_F64 1
+#define NERFB_DT_I64 2
+#define NERFB_DT_I32 3
+#define NERFB_DT_I16 4
+#define NERFB_DT_I8 5
+#define NERFB_DT_U8 6
+int nerfb_searchsorted_typed(const void* a, int64_t rows_a, int64_t len_a, const void* v, int64_t rows_v,
+                             int64_t len_v, int dtype, int side_left, int64_t* out, void* stream);
 int nerfb_sample_pdf(const float* bins, const float* weights, const float* u, int det, float eps,
                      int64_t n_rays, int n_bins, int n_importance, float* samples, float* cdf_out,
                      int64_t* inds_out, void* stream);

@@ -44,6 +44,7 @@ SIGNATURES = {
     "nerfb_composite_fwd": (_I, [_P, _I, _P, _P, _P, _F, _I, _L, _I, _P, _P, _P, _P, _P, _P]),
     "nerfb_composite_bwd": (_I, [_P, _I, _P, _P, _P, _F, _I, _L, _I, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_searchsorted": (_I, [_P, _L, _L, _P, _L, _L, _I, _P, _P]),
+    "nerfb_searchsorted_typed": (_I, [_P, _L, _L, _P, _L, _L, _I, _I, _P, _P]),
     "nerfb_sample_pdf": (_I, [_P, _P, _P, _I, _F, _L, _I, _I, _P, _P, _P, _P]),
     "nerfb_resample": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P]),
     "nerfb_triplane_relayout": (_I, [_P, _I, _I, _I, _P, _P]),

@@ -10,19 +10,21 @@
 #define RS_WARPS 4
 
 // ---- searchsorted: out = #(a[row] <  v) (left)  or  #(a[row] <= v) (right) ---------------------------
+// Instantiated for every scalar type of the reference's AT_DISPATCH_ALL_TYPES (searchsorted_cuda_kernel.cu:134).
+template <typename T>
 __global__ void __launch_bounds__(256)
-searchsorted_kernel(const float* __restrict__ a, int64_t rows_a, int64_t A, const float* __restrict__ v, int64_t rows_v,
+searchsorted_kernel(const T* __restrict__ a, int64_t rows_a, int64_t A, const T* __restrict__ v, int64_t rows_v,
                     int64_t V, int side_left, int64_t rows, int64_t* __restrict__ out) {
   const int64_t total = rows * V;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = idx / V, c = idx - r * V;
-    const float* ar = a + (rows_a == 1 ? 0 : r) * A;
-    const float val = __ldg(v + (rows_v == 1 ? 0 : r) * V + c);
+    const T* ar = a + (rows_a == 1 ? 0 : r) * A;
+    const T val = __ldg(v + (rows_v == 1 ? 0 : r) * V + c);
     int64_t lo = 0, hi = A;                                  // first position whose element fails the test
     while (lo < hi) {
       const int64_t mid = (lo + hi) >> 1;
-      const float x = __ldg(ar + mid);
+      const T x = __ldg(ar + mid);
       const bool go_right = side_left ? (x < val) : (x <= val);
       if (go_right) lo = mid + 1; else hi = mid;
     }
@@ -30,16 +32,38 @@ searchsorted_kernel(const float* __restrict__ a, int64_t rows_a, int64_t A, cons
   }
 }
 
-extern "C" int nerfb_searchsorted(const float* a, int64_t rows_a, int64_t len_a, const float* v, int64_t rows_v,
-                                  int64_t len_v, int side_left, int64_t* out, void* stream) {
+template <typename T>
+static int searchsorted_launch(const void* a, int64_t rows_a, int64_t len_a, const void* v, int64_t rows_v, int64_t len_v,
+                               int side_left, int64_t* out, void* stream) {
+  const int64_t rows = rows_a > rows_v ? rows_a : rows_v;
+  const int64_t want = ceil_div64(rows * len_v, 256);
+  const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
+  NERFB_LAUNCH(searchsorted_kernel<T>, grid, 256, 0, stream, static_cast<const T*>(a), rows_a, len_a, static_cast<const T*>(v),
+               rows_v, len_v, side_left, rows, out);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_searchsorted_typed(const void* a, int64_t rows_a, int64_t len_a, const void* v, int64_t rows_v,
+                                        int64_t len_v, int dtype, int side_left, int64_t* out, void* stream) {
   NERFB_CHECK_ARG(a && v && out && rows_a >= 1 && rows_v >= 1 && len_a >= 0 && len_v >= 0);
   NERFB_CHECK_ARG(rows_a == rows_v || rows_a == 1 || rows_v == 1);
   const int64_t rows = rows_a > rows_v ? rows_a : rows_v;
   if (rows * len_v == 0) return NERFB_OK;
-  const int64_t want = ceil_div64(rows * len_v, 256);
-  const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
-  NERFB_LAUNCH(searchsorted_kernel, grid, 256, 0, stream, a, rows_a, len_a, v, rows_v, len_v, side_left, rows, out);
-  return NERFB_OK;
+  switch (dtype) {
+    case NERFB_DT_F32: return searchsorted_launch<float>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_F64: return searchsorted_launch<double>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_I64: return searchsorted_launch<long long>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_I32: return searchsorted_launch<int>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_I16: return searchsorted_launch<short>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_I8: return searchsorted_launch<signed char>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    case NERFB_DT_U8: return searchsorted_launch<unsigned char>(a, rows_a, len_a, v, rows_v, len_v, side_left, out, stream);
+    default: return NERFB_E_UNSUPPORTED;
+  }
+}
+
+extern "C" int nerfb_searchsorted(const float* a, int64_t rows_a, int64_t len_a, const float* v, int64_t rows_v,
+                                  int64_t len_v, int side_left, int64_t* out, void* stream) {
+  return nerfb_searchsorted_typed(a, rows_a, len_a, v, rows_v, len_v, NERFB_DT_F32, side_left, out, stream);
 }
 
 __global__ void __launch_bounds__(RS_WARPS * 32)

@@ -109,10 +109,16 @@ def searchsorted(a, v, side="left", out=None):
         out = torch.empty(shape, device=v.device, dtype=torch.long)
     elif out.dtype != torch.long or tuple(out.shape) != shape or out.device != a.device:
         raise ValueError("out must be a torch.long tensor of the result shape on the same device")
-    check(lib.nerfb_searchsorted(_req(a, "a"), a.shape[0], a.shape[1], _req(v, "v"), v.shape[0], v.shape[1],
-                                 1 if side == "left" else 0, _req(out, "out", dtype=torch.long), _stream()),
-          "nerfb_searchsorted")
+    if a.dtype != v.dtype or a.dtype not in _SS_DTYPES:
+        raise ValueError(f"`a` and `v` must share one of {sorted(str(d) for d in _SS_DTYPES)}; got {a.dtype}, {v.dtype}")
+    check(lib.nerfb_searchsorted_typed(_req(a, "a", dtype=a.dtype), a.shape[0], a.shape[1], _req(v, "v", dtype=a.dtype),
+                                       v.shape[0], v.shape[1], _SS_DTYPES[a.dtype], 1 if side == "left" else 0,
+                                       _req(out, "out", dtype=torch.long), _stream()), "nerfb_searchsorted_typed")
     return out
+
+
+# the scalar types of the reference's AT_DISPATCH_ALL_TYPES (searchsorted_cuda_kernel.cu:134) -> NERFB_DT_*
+_SS_DTYPES = {torch.float32: 0, torch.float64: 1, torch.int64: 2, torch.int32: 3, torch.int16: 4, torch.int8: 5, torch.uint8: 6}
 
 
 def sample_pdf(bins, weights, n_importance, det=False, eps=1e-5, u=None, return_aux=False):

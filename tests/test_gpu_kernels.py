@@ -118,6 +118,29 @@ def test_searchsorted_bit_exact_reference_test_grid(side):
         nb().ops.searchsorted(torch.zeros(3, 4, device=DEV), torch.zeros(2, 4, device=DEV))
 
 
+@pytest.mark.parametrize("dtype", ["float64", "int64", "int32", "int16", "int8", "uint8"])
+@pytest.mark.parametrize("side", ["left", "right"])
+def test_searchsorted_every_dispatched_dtype(dtype, side):
+    """The reference kernel is AT_DISPATCH_ALL_TYPES (searchsorted_cuda_kernel.cu:134): the same grid of the reference's own
+    test (Ba, Bv, A, V incl. 1-row broadcast, test_searchsorted.py:26-44) for every other scalar type, against numpy.
+    Integer inputs are drawn from a small range so that ties exercise left / right."""
+    rs = np.random.RandomState(3)
+    npd = np.dtype(dtype)
+    for Ba, Bv, A, V in [(1, 1, 1, 1), (1, 100, 50, 12), (100, 1, 500, 120), (200, 200, 1, 12), (100, 100, 500, 1),
+                         (200, 200, 50, 120)]:
+        if npd.kind == "f":
+            a, v = rs.rand(Ba, A).astype(npd), rs.rand(Bv, V).astype(npd)
+        else:
+            lo, hi = (0, 100) if npd.kind == "u" else (-60, 60)
+            a, v = rs.randint(lo, hi, (Ba, A)).astype(npd), rs.randint(lo, hi, (Bv, V)).astype(npd)
+        a = np.sort(a, 1)
+        v[:, :1] = a[:1, :1]
+        got = nb().ops.searchsorted(torch.from_numpy(a).to(DEV), torch.from_numpy(v).to(DEV), side=side)
+        assert got.dtype == torch.long and np.array_equal(got.cpu().numpy(), O.searchsorted_rows(a, v, side)), (Ba, Bv, A, V)
+    with pytest.raises(ValueError):
+        nb().ops.searchsorted(torch.zeros(2, 4, device=DEV), torch.zeros(2, 4, device=DEV, dtype=torch.float64))
+
+
 @pytest.mark.parametrize("name", ["peaky", "flat", "zero", "rand"])
 @pytest.mark.parametrize("ni", [64, 128])
 def test_resampling_indices_bit_exact_on_identical_cdf(name, ni):

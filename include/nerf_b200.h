@@ -187,6 +187,37 @@ int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* dec
                           float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
                           float* opacity_final, float* depths_fine_out, void* workspace, void* stream);
 
+/* ---- the whole inference render behind ONE call (SURVEY 8b `nerfb_render_fused_fwd`, 7 step 4) ----------------
+ * Replaces models/rendering.py:193-262 for inference (eval.py:85-96 with test_time=True, system.py:207-216 under no_grad):
+ * sampling (:206-222) -> coarse embedding + MLP (:129-159) -> compositing (:161-190) -> sample_pdf + sort (:241-247) ->
+ * fine embedding + MLP -> compositing, queued back to back on `stream`.  On the bf16 tensor-core arm, when n_samples
+ * (resp. n_samples + n_importance) is 32, 64 or 128 and the model has no class head, compositing runs in the MLP kernel's
+ * epilogue: per-sample [rgb sigma] never reaches HBM and the pass is one launch; other shapes use kernels (1) + (4).
+ * cfg.test_time: the coarse pass is sigma-only and only opacity_coarse is produced (:230-231).  Random inputs (perturb_rand,
+ * u when perturb > 0; noise_* when noise_std != 0) are supplied by the caller in the reference's draw order.
+ * Outputs that the configuration does not produce may be NULL.  Nothing is kept for a backward pass. */
+typedef struct nerfb_render_cfg {
+  int32_t precision;         /* NERFB_PREC_* */
+  int32_t n_samples, n_importance;
+  int32_t use_disp, white_back, test_time;
+  float perturb, noise_std;
+} nerfb_render_cfg;
+typedef struct nerfb_render_io {
+  const float* rays;          /* (N,8) [o d near far] */
+  const float* perturb_rand;  /* (N,S)      U[0,1), perturb > 0 */
+  const float* noise_coarse;  /* (N,S)      N(0,1), noise_std != 0 */
+  const float* u;             /* (N,S_i)    U[0,1), perturb > 0 and n_importance > 0 */
+  const float* noise_fine;    /* (N,S+S_i)  N(0,1), noise_std != 0 and n_importance > 0 */
+  float* rgb_coarse; float* depth_coarse; float* opacity_coarse; float* cls_coarse;   /* (N,3) (N) (N) (N,CLS) */
+  float* rgb_fine; float* depth_fine; float* opacity_fine; float* cls_fine;
+} nerfb_render_io;
+int64_t nerfb_render_fused_workspace_bytes(const nerfb_mlp_desc* coarse, const nerfb_mlp_desc* fine,
+                                           const nerfb_render_cfg* cfg, int64_t n_rays);
+int nerfb_render_fused_fwd(const nerfb_mlp_desc* coarse, const nerfb_mlp_desc* fine, const nerfb_render_cfg* cfg,
+                           const float* params_coarse, const float* film_coarse, const float* params_fine,
+                           const float* film_fine, const nerfb_render_io* io, int64_t n_rays, void* workspace,
+                           int64_t workspace_bytes, void* stream);
+
 /* ---- the steps either side of the path ----------------------------------
  * nerfb_generate_rays: datasets/ray_utils.py:5-50 (get_ray_directions, get_rays) [+ :53-94 get_ndc_rays when ndc != 0,
  *   near plane 1.0 and near/far = 0/1 as datasets/llff.py:234-239] -> rays (H*W, 8) = [o d near far], row-major pixels

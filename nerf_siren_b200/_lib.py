@@ -20,6 +20,19 @@ class MlpDesc(C.Structure):
                 ("logscale", C.c_int32), ("box", C.c_float), ("in_xyz", C.c_int32), ("in_dir", C.c_int32)]
 
 
+class RenderCfg(C.Structure):
+    """Mirror of ``nerfb_render_cfg``."""
+    _fields_ = [("precision", C.c_int32), ("n_samples", C.c_int32), ("n_importance", C.c_int32), ("use_disp", C.c_int32),
+                ("white_back", C.c_int32), ("test_time", C.c_int32), ("perturb", C.c_float), ("noise_std", C.c_float)]
+
+
+class RenderIO(C.Structure):
+    """Mirror of ``nerfb_render_io`` (device pointers, 0 = NULL)."""
+    _fields_ = [(k, C.c_void_p) for k in ("rays", "perturb_rand", "noise_coarse", "u", "noise_fine", "rgb_coarse",
+                                          "depth_coarse", "opacity_coarse", "cls_coarse", "rgb_fine", "depth_fine",
+                                          "opacity_fine", "cls_fine")]
+
+
 KIND_NERF, KIND_SIREN = 0, 1
 PREC_FP32, PREC_BF16 = 0, 1
 IN_RAYS, IN_EMBEDDED, IN_GRID = 0, 1, 2
@@ -41,6 +54,8 @@ SIGNATURES = {
     "nerfb_mlp_workspace_bytes": (_L, [_D, _I, _L, _I, _I]),
     "nerfb_mlp_fwd": (_I, [_D, _I, _I, _P, _P, _P, _P, _L, _I, _I, _I, _P, _P, _L, _P]),
     "nerfb_mlp_bwd": (_I, [_D, _I, _I, _P, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P, _L, _P]),
+    "nerfb_render_fused_workspace_bytes": (_L, [_D, _D, C.POINTER(RenderCfg), _L]),
+    "nerfb_render_fused_fwd": (_I, [_D, _D, C.POINTER(RenderCfg), _P, _P, _P, _P, C.POINTER(RenderIO), _L, _P, _L, _P]),
     "nerfb_composite_fwd": (_I, [_P, _I, _P, _P, _P, _F, _I, _L, _I, _P, _P, _P, _P, _P, _P]),
     "nerfb_composite_bwd": (_I, [_P, _I, _P, _P, _P, _F, _I, _L, _I, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_searchsorted": (_I, [_P, _L, _L, _P, _L, _L, _I, _P, _P]),

@@ -14,9 +14,10 @@ int simt_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, cons
                  float* d_in, float* ws, int64_t ws_bytes, void* stream);
 int64_t tc_workspace_bytes(const nerfb_mlp_desc& d, int64_t P, int sigma_only, int save);
 bool tc_supported(const nerfb_mlp_desc& d, int in_mode);
+struct TcComposite;
 int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, int sigma_only, int save, float* out, void* ws,
-               int64_t ws_bytes, void* stream);
+               int64_t ws_bytes, void* stream, const TcComposite* comp);
 int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, const float* out, const float* d_out, float* grad,
                float* d_in, void* ws, int64_t ws_bytes, void* stream);
@@ -72,7 +73,7 @@ extern "C" int nerfb_mlp_fwd(const nerfb_mlp_desc* d, int precision, int in_mode
   if (precision == NERFB_PREC_BF16) {
     if (!tc_supported(*d, in_mode)) return NERFB_E_UNSUPPORTED;
     return tc_mlp_fwd(*d, in_mode, params, film, in0, in1, n_rows, n_samples, sigma_only, save_for_backward, out,
-                      workspace, workspace_bytes, stream);
+                      workspace, workspace_bytes, stream, nullptr);
   }
   return NERFB_E_BADARG;
 }

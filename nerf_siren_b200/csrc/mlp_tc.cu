@@ -87,6 +87,7 @@ struct TcProgram {
 
 struct TcFwdArgs {
   TcProgram prog;
+  TcComposite comp;
   const uint8_t* wblob;            // packed bf16 weight slabs in schedule order
   const float* bias;               // fp32 bias table [n_bias] | w_sigma[256] | b_sigma | w_rgb[3*rgb_in] | b_rgb[3]
   const float* scale;              // SIREN: per-column frequency table [n_bias] (bias table then holds freq*b + phase)
@@ -108,6 +109,8 @@ struct __align__(1024) Smem {
   float b_heads[4];                      // b_sigma, b_rgb[3]
   float part[4][3][TILE_M];              // head partial sums [column quarter][channel][row]
   float sigma[TILE_M];
+  float comp[5][TILE_M];                 // epilogue compositing: w, w r, w g, w b, w z per row
+  float comp_tot[4];                     // transmittance product of each 32-row chunk
   uint64_t w_full[N_STAGES], w_empty[N_STAGES];
   uint64_t a_ready[4];                   // block j holds the current step's output (16 epilogue warps arrive)
   uint64_t s_ready[4];                   // training: block j of a store-only step (direction / colour layer activations)
@@ -179,6 +182,77 @@ __device__ __forceinline__ void copy_row(const float* src, int width, uint32_t b
 #pragma unroll
   for (int i = 0; i < 64; ++i) buf[i] = (src && i < width) ? __ldg(src + i) : 0.f;
   store_row64(base, row, buf);
+}
+
+// ---- compositing in the epilogue (the 4 epilogue warps that own column quarter 0; warp q holds rows 32 q .. 32 q + 31) ----
+// Same operations in the same order as composite_fwd_kernel (composite.cu): 32-sample chunks, inclusive warp product, running
+// carry over the chunks of a ray, per-lane accumulation over chunks, butterfly sum -- so the result is bit-identical to
+// running kernel (4) on the raw values this epilogue would have stored.
+struct CompTerms { float alpha, t; };
+__device__ __forceinline__ CompTerms comp_terms(float sigma, float noise, float noise_std, float z_i, float z_next, bool last, float dnorm) {
+  CompTerms s;
+  const float d = last ? 1e10f : __fsub_rn(z_next, z_i);                     // models/rendering.py:162-163
+  const float delta = __fmul_rn(d, dnorm);                                   // :168
+  const float pre = __fadd_rn(sigma, __fmul_rn(noise, noise_std));           // :170-173
+  const float a = pre > 0.f ? pre : 0.f;
+  s.alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, a)));
+  s.t = __fadd_rn(__fsub_rn(1.0f, s.alpha), 1e-10f);                         // :175
+  return s;
+}
+template <typename SmemT>
+__device__ __forceinline__ void epilogue_composite(SmemT& sm, const TcComposite& cp, const float* __restrict__ rays,
+                                                   const float* __restrict__ zbuf, int64_t p, int64_t P, bool live, int q, int lane,
+                                                   float cr, float cg, float cb, float sigma, bool has_rgb) {
+  const int S = cp.S, row = q * 32 + lane;
+  const int i = row % S;
+  const int64_t ray = p / S;
+  const float zi = live ? __ldg(zbuf + p) : 0.f;
+  float zn = __shfl_down_sync(0xffffffffu, zi, 1);
+  if (lane == 31 && live && i + 1 < S) zn = __ldg(zbuf + p + 1);
+  float dnorm = 0.f, nz = 0.f;
+  if (live) {
+    const float dx = __ldg(rays + ray * 8 + 3), dy = __ldg(rays + ray * 8 + 4), dz = __ldg(rays + ray * 8 + 5);
+    dnorm = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (cp.noise) nz = __ldg(cp.noise + p);
+  }
+  const CompTerms st = comp_terms(sigma, nz, cp.noise_std, zi, zn, i == S - 1, dnorm);
+  float incl = live ? st.t : 1.0f;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const float t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl *= t;
+  }
+  float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane == 0) excl = 1.0f;
+  if (lane == 31) sm.comp_tot[q] = incl;
+  named_bar_sync(3, 128);
+  float carry = 1.0f;
+  for (int k = q - (i >> 5); k < q; ++k) carry *= sm.comp_tot[k];             // chunks of this ray before mine, in order
+  const float w = live ? st.alpha * (carry * excl) : 0.f;                    // :176-177
+  if (live && cp.weights) cp.weights[p] = w;
+  sm.comp[0][row] = w;
+  if (has_rgb) { sm.comp[1][row] = w * cr; sm.comp[2][row] = w * cg; sm.comp[3][row] = w * cb; sm.comp[4][row] = w * zi; }
+  named_bar_sync(3, 128);
+  if (q < TILE_M / S) {                                                      // warp q reduces ray q of this tile
+    const int64_t r = (p - row) / S + q;
+    float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < S; c += 32) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k)
+        if (k == 0 || has_rgb) acc[k] += (lane + c < S) ? sm.comp[k][q * S + c + lane] : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+      if (k == 0 || has_rgb) acc[k] = warp_sum(acc[k]);
+    if (lane == 0 && r * S < P) {
+      if (cp.opacity) cp.opacity[r] = acc[0];
+      if (has_rgb) {
+        const float bg = cp.white_back ? (1.0f - acc[0]) : 0.f;              // :187-188
+        cp.rgb[r * 3 + 0] = acc[1] + bg; cp.rgb[r * 3 + 1] = acc[2] + bg; cp.rgb[r * 3 + 2] = acc[3] + bg;
+        cp.depth[r] = acc[4];
+      }
+    }
+  }
 }
 
 template <bool SIREN, bool CLS, bool SAVE>
@@ -544,18 +618,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
           if (c4 == 0) {
             const float sg = sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[0];
             sm.sigma[row] = sg;
-            if (pg.sigma_only && live) args.out[p] = (args.in_mode == NERFB_IN_GRID) ? fmaxf(sg, 0.f) : sg;   // grid: np.maximum(sigma, 0), extract_color_mesh.py:141
+            if (pg.sigma_only && args.comp.on)      // weights-only coarse pass of test_time (models/rendering.py:230-231) composited in place
+              epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, 0.f, 0.f, 0.f, sg, false);
+            else if (pg.sigma_only && live) args.out[p] = (args.in_mode == NERFB_IN_GRID) ? fmaxf(sg, 0.f) : sg;   // grid: np.maximum(sigma, 0), extract_color_mesh.py:141
           }
         } else if (st_head == 2) { // rgb = sigmoid(W_rgb h_dir + b)  (models/nerf.py:119-120)
           sm.part[c4][0][row] = head_acc[0]; sm.part[c4][1][row] = head_acc[1]; sm.part[c4][2][row] = head_acc[2];
           named_bar_sync(1, EPI_THREADS);
-          if (c4 == 0 && live) {
+          if (c4 == 0 && (live || args.comp.on)) {
             float4 o;
             o.x = 1.f / (1.f + __expf(-(sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[1])));
             o.y = 1.f / (1.f + __expf(-(sm.part[0][1][row] + sm.part[1][1][row] + sm.part[2][1][row] + sm.part[3][1][row] + sm.b_heads[2])));
             o.z = 1.f / (1.f + __expf(-(sm.part[0][2][row] + sm.part[1][2][row] + sm.part[2][2][row] + sm.part[3][2][row] + sm.b_heads[3])));
             o.w = sm.sigma[row];
-            if (!CLS) *reinterpret_cast<float4*>(args.out + p * 4) = o;
+            if (!CLS && args.comp.on) epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, o.x, o.y, o.z, o.w, true);
+            else if (!CLS) *reinterpret_cast<float4*>(args.out + p * 4) = o;
             else { float* dst = args.out + p * pg.out_c; dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
           }
         }
@@ -793,10 +870,16 @@ int64_t tc_workspace_bytes(const nerfb_mlp_desc& d, int64_t P, int sigma_only, i
   return total;
 }
 
+bool tc_composite_supported(const nerfb_mlp_desc& d, int in_mode, int n_samples, int save) {
+  return tc_supported(d, in_mode) && in_mode == NERFB_IN_RAYS && !save && d.n_cls == 0 &&
+         (n_samples == 32 || n_samples == 64 || n_samples == 128);
+}
+
 int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const float* film, const float* in0,
                const float* in1, int64_t n_rows, int n_samples, int sigma_only, int save, float* out, void* ws,
-               int64_t ws_bytes, void* stream) {
+               int64_t ws_bytes, void* stream, const TcComposite* comp) {
   const bool siren = d.kind == NERFB_KIND_SIREN;
+  if (comp && comp->on && !tc_composite_supported(d, in_mode, n_samples, save)) return NERFB_E_UNSUPPORTED;
   if (siren && !film) return NERFB_E_BADARG;
   if (in_mode == NERFB_IN_GRID && (save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
@@ -822,6 +905,7 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   a.in0 = in0; a.in1 = in1; a.in_mode = in_mode; a.S = n_samples;
   a.P = P; a.n_tiles = ceil_div64(P, TILE_M);
   a.out = out;
+  if (comp) a.comp = *comp;
   a.save = save ? base + pl.off_save : nullptr;
   a.trace = g_trace;
   const size_t smem = sizeof(Smem) + 1024;

@@ -14,6 +14,16 @@ struct TcFwdLayout {
   int64_t off_weff;            // NeRF_3D: merged class-head matrix W_eff (fp32 16 x 256) | b_eff (16) in the forward's workspace
 };
 
+// Compositing in the forward kernel's epilogue (models/rendering.py:161-190 without `raw` ever reaching HBM):
+// valid when a 128-sample tile holds whole rays (S in {32, 64, 128}), input mode RAYS, no class channels, inference.
+// Arithmetic = kernel (4)'s, operation for operation.
+struct TcComposite {
+  int on, S, white_back; float noise_std;
+  const float* noise;              // (N, S) or null
+  float* weights;                  // (N, S) or null
+  float* rgb; float* depth; float* opacity;   // (N,3) (N) (N); rgb / depth unused for a sigma-only pass
+};
+
 namespace tc {
 
 constexpr int TILE_M = 128;                 // samples per tile = TMEM lanes

@@ -183,8 +183,20 @@ def _render_fused(models, embeddings, rays, S, use_disp, perturb, noise_std, Si,
 
     rays_per_call = max(1, _field.max_points(cfg.precision) // (S + Si))
     pieces = []
+    e = torch.empty(0, device=dev)
     for i in range(0, n, rays_per_call):
         sl = slice(i, i + rays_per_call)
+        if not need_grad:
+            # inference: the whole chain behind one library call (nerfb_render_fused_fwd), compositing in the MLP epilogue
+            # where the sample counts allow it
+            piece = ops.render_fused(cfg.desc_c, cfg.desc_f, cfg.precision, flat_c.detach(), cfg.film_c,
+                                     None if flat_f is None else flat_f.detach(), cfg.film_f, rays[sl], S, Si, cfg.use_disp,
+                                     cfg.perturb, cfg.noise_std, cfg.white_back, cfg.test_time,
+                                     perturb_rand[sl] if perturb_rand is not None else None,
+                                     noise_c[sl] if cfg.noise_std != 0 else None, u[sl] if u is not None else None,
+                                     noise_f[sl] if (noise_f is not None and cfg.noise_std != 0) else None)
+            pieces.append(tuple(o if o is not None else e for o in piece))
+            continue
         pieces.append(_RenderFn.apply(flat_c, flat_f, rays[sl], cfg,
                                       perturb_rand[sl] if perturb_rand is not None else None, noise_c[sl],
                                       u[sl] if u is not None else None, noise_f[sl] if noise_f is not None else None))

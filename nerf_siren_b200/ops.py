@@ -208,6 +208,52 @@ def mlp_bwd(desc, precision, in_mode, params, film, in0, in1, n_rows, n_samples,
     return grad, d_in
 
 
+def render_fused(desc_c, desc_f, precision, params_c, film_c, params_f, film_f, rays, n_samples, n_importance, use_disp,
+                 perturb, noise_std, white_back, test_time, perturb_rand=None, noise_coarse=None, u=None, noise_fine=None):
+    """The whole inference render_rays in ONE library call (nerfb_render_fused_fwd): returns the tuple
+    (rgb_c, depth_c, opacity_c, cls_c, rgb_f, depth_f, opacity_f, cls_f), entries the configuration does not produce = None."""
+    n = rays.shape[0]
+    dev = rays.device
+    cfg = _lib.RenderCfg(precision=int(precision), n_samples=int(n_samples), n_importance=int(n_importance),
+                         use_disp=int(bool(use_disp)), white_back=int(bool(white_back)), test_time=int(bool(test_time)),
+                         perturb=float(perturb), noise_std=float(noise_std))
+    fine = n_importance > 0
+    dfp = C.byref(desc_f) if fine else None
+    nbytes = int(lib.nerfb_render_fused_workspace_bytes(C.byref(desc_c), dfp, C.byref(cfg), n))
+    if nbytes < 0:
+        check(nbytes, "nerfb_render_fused_workspace_bytes")
+    ws = torch.empty(nbytes + 1024, device=dev, dtype=torch.uint8)
+    ws_ptr, ws_bytes = _aligned(ws)
+    n_cls_c = int(lib.nerfb_out_channels(C.byref(desc_c))) - 4
+    n_cls_f = int(lib.nerfb_out_channels(C.byref(desc_f))) - 4 if fine else 0
+
+    def new(*shape):
+        return torch.empty(*shape, device=dev, dtype=torch.float32)
+    rgb_c = depth_c = cls_c = rgb_f = depth_f = op_f = cls_f = None
+    op_c = new(n)
+    if not test_time:
+        rgb_c, depth_c = new(n, 3), new(n)
+        cls_c = new(n, n_cls_c) if n_cls_c > 0 else None
+    if fine:
+        rgb_f, depth_f, op_f = new(n, 3), new(n), new(n)
+        cls_f = new(n, n_cls_f) if n_cls_f > 0 else None
+
+    def ptr(t):
+        return 0 if t is None else t.data_ptr()
+    io = _lib.RenderIO(rays=_req(rays, "rays"), perturb_rand=_req(perturb_rand, "perturb_rand", allow_none=not perturb > 0),
+                       noise_coarse=_req(noise_coarse, "noise_coarse", allow_none=noise_std == 0),
+                       u=_req(u, "u", allow_none=not (perturb > 0 and fine)),
+                       noise_fine=_req(noise_fine, "noise_fine", allow_none=(noise_std == 0 or not fine)),
+                       rgb_coarse=ptr(rgb_c), depth_coarse=ptr(depth_c), opacity_coarse=ptr(op_c), cls_coarse=ptr(cls_c),
+                       rgb_fine=ptr(rgb_f), depth_fine=ptr(depth_f), opacity_fine=ptr(op_f), cls_fine=ptr(cls_f))
+    check(lib.nerfb_render_fused_fwd(C.byref(desc_c), dfp, C.byref(cfg), _req(params_c, "params_coarse"),
+                                     _req(film_c, "film_coarse", allow_none=True),
+                                     _req(params_f, "params_fine", allow_none=not fine),
+                                     _req(film_f, "film_fine", allow_none=True), C.byref(io), n, ws_ptr, ws_bytes, _stream()),
+          "nerfb_render_fused_fwd")
+    return rgb_c, depth_c, op_c, cls_c, rgb_f, depth_f, op_f, cls_f
+
+
 # ---- kernel (6): EG3D tri-plane renderer ------------------------------------------------------------------
 def triplane_relayout(planes):
     """(3, 32, H, W) reference layout -> channels-last (3, H, W, 32)."""
@@ -367,7 +413,7 @@ def _on_tensor_device(fn):
 
 
 for _name in ("sample_coarse", "embed", "composite_fwd", "composite_bwd", "searchsorted", "sample_pdf", "resample",
-              "adam_step", "mlp_fwd", "mlp_bwd", "triplane_relayout", "triplane_field", "mip_march", "triplane_render",
+              "adam_step", "mlp_fwd", "mlp_bwd", "render_fused", "triplane_relayout", "triplane_field", "mip_march", "triplane_render",
               "finish_image", "sigma_grid", "pack_vol"):
     globals()[_name] = _on_tensor_device(globals()[_name])
 del _name

@@ -336,3 +336,55 @@ def test_render_rays_3d_default_freezes_the_nerf():
     out = n.render_rays_3d([mc, mf], [n.Embedding(3, 10), n.Embedding(3, 4)], O.llff_rays(32, seed=1).to(DEV), 16, False,
                            0, 0, 16, 32768, False)
     assert not out["cls_fine"].requires_grad and not out["rgb_fine"].requires_grad
+
+
+# ------------------------------------------------------------------------------------------------------
+# (vii) row N1: nerfb_render_fused_fwd -- one call, compositing in the MLP epilogue -- against the separate kernels
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("S,Si,test_time,noise_std,perturb", [(64, 64, True, 0.0, 0.0), (64, 64, False, 1.0, 1.0),
+                                                              (32, 32, False, 0.0, 0.0), (64, 128, True, 0.0, 0.0),
+                                                              (64, 0, False, 0.5, 1.0), (128, 0, True, 0.0, 0.0)])
+@pytest.mark.parametrize("prec", ["bf16", "fp32"])
+def test_render_fused_entry_equals_separate_kernels(S, Si, test_time, noise_std, perturb, prec):
+    """The single-call inference render (compositing in the tcgen05 kernel's epilogue when S is 32 / 64 / 128, kernels (1) + (4)
+    otherwise, e.g. 64 + 128 = 192 fine samples) must be BIT-IDENTICAL to the chain of separate library calls: the epilogue
+    composites the very registers the separate path would have stored as `raw`, with kernel (4)'s operations in kernel
+    (4)'s order.  1000 + 37 rays: many tiles, ragged last tile, whole dead rays in the padding."""
+    n_mod = nb()
+    n_mod.set_precision(prec)
+    from nerf_siren_b200 import _field, _lib, ops
+    pc, pf = O.nerf_field(seed=71, gain=2.0), O.nerf_field(seed=72, gain=2.0)
+    mc, mf = _load(n_mod.NeRF, pc), _load(n_mod.NeRF, pf)
+    n = 1037
+    rays = O.blender_rays(n, seed=41).to(DEV)
+    g = torch.Generator(device=DEV).manual_seed(9)
+    pr = torch.rand(n, S, device=DEV, generator=g) if perturb > 0 else None
+    nc = torch.randn(n, S, device=DEV, generator=g) if noise_std != 0 else None
+    u = torch.rand(n, Si, device=DEV, generator=g) if (perturb > 0 and Si > 0) else None
+    nf = torch.randn(n, S + Si, device=DEV, generator=g) if (noise_std != 0 and Si > 0) else None
+    precision = _lib.PREC_BF16 if prec == "bf16" else _lib.PREC_FP32
+    desc = mc._desc(False, 10, 4, True)
+    fc, ff = _field.flat_params(mc).detach(), _field.flat_params(mf).detach()
+    with torch.no_grad():
+        got = ops.render_fused(desc, desc, precision, fc, None, ff, None, rays, S, Si, False, perturb, noise_std, True, test_time,
+                               pr, nc, u, nf)
+        z = ops.sample_coarse(rays, S, False, perturb, pr)
+        ws = ops.mlp_workspace(desc, precision, n * S, test_time, False, DEV)
+        raw = ops.mlp_fwd(desc, precision, _lib.IN_RAYS, fc, None, rays, z, n, S, test_time, False, ws).view(n, S, -1)
+        w, rgb_c, depth_c, op_c, _ = ops.composite_fwd(raw, z, rays, nc, noise_std, True)
+        want = [None if test_time else rgb_c, None if test_time else depth_c, op_c, None, None, None, None, None]
+        if Si > 0:
+            zf = ops.resample(z, w, Si, det=(perturb == 0), u=u)
+            ws = ops.mlp_workspace(desc, precision, n * (S + Si), False, False, DEV)
+            rawf = ops.mlp_fwd(desc, precision, _lib.IN_RAYS, ff, None, rays, zf, n, S + Si, False, False, ws).view(n, S + Si, 4)
+            _, want[4], want[5], want[6], _ = ops.composite_fwd(rawf, zf, rays, nf, noise_std, True)
+    for k, (a, b) in enumerate(zip(got, want)):
+        assert (a is None) == (b is None), k
+        if a is not None:
+            assert torch.equal(a, b), (k, float((a - b).abs().max()))
+    # and through the public API: render_rays under no_grad takes this path
+    with torch.no_grad():
+        torch.manual_seed(3)
+        out = n_mod.render_rays([mc, mf], [n_mod.Embedding(3, 10), n_mod.Embedding(3, 4)], rays, S, False, 0, 0, Si, 32768, True,
+                                test_time=test_time)
+    assert "opacity_coarse" in out and (("rgb_fine" in out) == (Si > 0))

@@ -19,3 +19,7 @@ def set_precision(p: str) -> None:
 
 def get_precision() -> str:
     return _PRECISION
+
+# inference render through the single-call entry nerfb_render_fused_fwd (compositing in the MLP epilogue); 0 = the chain of
+# separate library calls
+RENDER_FUSED = int(os.environ.get("NERFB_RENDER_FUSED", "0")) != 0

@@ -1085,6 +1085,9 @@ int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v && *v) ? atoi(v) : dflt;
 }
+#ifndef NERFB_BWD_FUSED_DEFAULT
+#define NERFB_BWD_FUSED_DEFAULT 0          // flipped to 1 once the fused launch is validated on the B200 (tools/check_fused_bwd.py)
+#endif
 struct FusedPlan {
   bool on;
   FusedCtl fc; FusedWArgs w;
@@ -1102,7 +1105,7 @@ int item_clk(const WItem& im) {
 FusedPlan fused_plan(const BwdPlan& pl) {
   FusedPlan fp{};
   fp.on = false;
-  if (env_int("NERFB_BWD_FUSED", 1) == 0) return fp;
+  if (env_int("NERFB_BWD_FUSED", NERFB_BWD_FUSED_DEFAULT) == 0) return fp;
   const BProgram& pg = pl.prog;
   const WgradArgs& wg = pl.wg;
   FusedWArgs& w = fp.w;

@@ -18,7 +18,7 @@ from __future__ import annotations
 
 import torch
 
-from .. import _field, _lib, ops
+from .. import _field, _lib, config, ops
 from .nerf import Embedding, NeRF, SirenField
 
 __all__ = ["render_rays", "render_rays_3d", "render_rays_3d_conv", "sample_pdf"]
@@ -186,7 +186,7 @@ def _render_fused(models, embeddings, rays, S, use_disp, perturb, noise_std, Si,
     e = torch.empty(0, device=dev)
     for i in range(0, n, rays_per_call):
         sl = slice(i, i + rays_per_call)
-        if not need_grad:
+        if not need_grad and config.RENDER_FUSED:
             # inference: the whole chain behind one library call (nerfb_render_fused_fwd), compositing in the MLP epilogue
             # where the sample counts allow it
             piece = ops.render_fused(cfg.desc_c, cfg.desc_f, cfg.precision, flat_c.detach(), cfg.film_c,

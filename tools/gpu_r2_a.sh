@@ -21,4 +21,16 @@ for t in ("unfused", "fused"):
     except Exception as e:
         print(t, "failed", e)
 PY
-timeout 1500 python -m pytest tests -m gpu -q -x 2>&1 | tail -15 > $OUT/r2a_pytest_all.log; echo "all gpu tests: $(tail -1 $OUT/r2a_pytest_all.log)"
+timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -25 > $OUT/r2a_pytest_all.log; echo "all gpu tests (defaults): $(tail -1 $OUT/r2a_pytest_all.log)"
+NERFB_BWD_FUSED=1 NERFB_RENDER_FUSED=1 timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -25 > $OUT/r2a_pytest_all_fused.log; echo "all gpu tests (fused backward + fused render ON): $(tail -1 $OUT/r2a_pytest_all_fused.log)"
+NERFB_RENDER_FUSED=0 timeout 300 python bench.py --config render --steps 3 --warmup 3 --no-cpu-baseline --sustain 0 > $OUT/r2a_render_sep.json 2> $OUT/r2a_render_sep.err
+NERFB_RENDER_FUSED=1 timeout 300 python bench.py --config render --steps 3 --warmup 3 --no-cpu-baseline --sustain 0 > $OUT/r2a_render_fused.json 2> $OUT/r2a_render_fused.err
+python - <<'PY'
+import json
+for t in ("sep", "fused"):
+    try:
+        d = json.loads(open(f"gpurun_out/r2a_render_{t}.json").read().strip().splitlines()[-1])
+        print("render", t, "ms", round(d["ms_per_step"], 3), "rays/s", round(d["value"]), "e2e", round(d["e2e"]["value"]), "launches", d["gpu_launches"])
+    except Exception as e:
+        print("render", t, "failed", e)
+PY

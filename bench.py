@@ -178,7 +178,7 @@ def cpu_step_factory(config: str, n_rays: int):
             loss.backward()
             opt.step()
         return step, n_rays, f"{n_rays} rays x (64 + 128) samples, fwd+bwd+Adam, per step"
-    if config == "cls_train":
+    if config in ("cls_train", "cls_train_strong"):
         pc = {k: v.clone().requires_grad_(True) for k, v in O.nerf_init(seed=1, n_cls=6).items()}
         pf = {k: v.clone().requires_grad_(True) for k, v in O.nerf_init(seed=2, n_cls=6).items()}
         opt = torch.optim.Adam(list(pc.values()) + list(pf.values()), lr=5e-4, eps=1e-8)
@@ -287,6 +287,7 @@ METRICS = {
     "siren_render": "rays/s, SIREN full-image render 800x800 (64+128 samples, test_time)",
     "cls_train": "rays/s, NeRF_3D (CLS=6) semantic-head coarse+fine training step (64+64 samples)",
     "eg3d": "rays/s, EG3D tri-plane renderer (3x32x256^2 planes, 48+48 samples)",
+    "cls_train_strong": "rays/s, NeRF_3D (CLS=6) semantic-head training step, 8192 rays GLOBAL batch (64+64 samples)",
 }
 WORKLOADS = {
     "train": "configs[1]: NeRF coarse+fine training step, 4096 rays/GPU, 64+64 samples, bf16",
@@ -294,9 +295,11 @@ WORKLOADS = {
     "siren_render": "configs[2]: SIREN-MLP variant full-image render 800x800, 64+128 samples, ray-sharded over the GPUs",
     "cls_train": "configs[3]: nerf_cls semantic-head training, LLFF-shaped 504x378 rays, batch 8192 per GPU",
     "eg3d": "configs[4]: EG3D triplane renderer (volumetric_rendering ray_marcher), 3x32x256^2 planes, 96 samples/ray, 128x128 rays",
+    "cls_train_strong": "configs[3], strong scaling: nerf_cls semantic-head training, LLFF-shaped rays, 8192 rays global batch split over the GPUs",
 }
-CPU_SAMPLE_RAYS = {"train": 256, "cls_train": 256, "render": 1024, "siren_render": 1024, "eg3d": 1024}
-SCALING = {"train": "weak", "cls_train": "weak", "render": "strong", "siren_render": "strong", "eg3d": "weak"}
+CPU_SAMPLE_RAYS = {"train": 256, "cls_train": 256, "cls_train_strong": 256, "render": 1024, "siren_render": 1024, "eg3d": 1024}
+SCALING = {"train": "weak", "cls_train": "weak", "cls_train_strong": "strong", "render": "strong", "siren_render": "strong",
+           "eg3d": "weak"}
 
 
 def run_reference(args):
@@ -373,11 +376,13 @@ class Ctx:
 class TrainWorkload:
     """configs[1] (NeRF) / configs[3] (NeRF_3D semantic head): DataParallelStep on this rank's shard of rays."""
 
-    def __init__(self, cx: Ctx, cls: bool, no_graph: bool):
+    def __init__(self, cx: Ctx, cls: bool, no_graph: bool, strong: bool = False):
         torch, nb = cx.torch, cx.nb
         from nerf_siren_b200 import synth
         self.cx, self.cls = cx, cls
         self.n = 8192 if cls else N_RAYS
+        if strong:                                             # SURVEY 8d: configs[3] also at a FIXED global batch of 8192 rays
+            self.n = self.n // cx.world
         torch.manual_seed(0)                                   # identical init on every rank (DDP broadcast equivalent)
         if cls:
             models = [nb.NeRF_3D(CLS=6).to(cx.dev), nb.NeRF_3D(CLS=6).to(cx.dev)]
@@ -650,6 +655,8 @@ def make_workload(cx: Ctx, config: str, args):
         return TrainWorkload(cx, False, args.no_graph)
     if config == "cls_train":
         return TrainWorkload(cx, True, args.no_graph)
+    if config == "cls_train_strong":
+        return TrainWorkload(cx, True, args.no_graph, strong=True)
     if config == "render":
         return RenderWorkload(cx, False)
     if config == "siren_render":

@@ -150,9 +150,10 @@ int nerfb_resample(const float* z_coarse, const float* weights_coarse, const flo
  * system.py:257-275).  Here the host all-reduces ONE flat gradient buffer over NCCL (SUM) and this entry applies
  * the Adam update (torch.optim.Adam semantics: lr, betas, eps, no weight decay, no amsgrad) to the flat
  * parameter buffer in one launch; grad_scale (= 1/world_size) turns the SUM into the DDP mean.  step >= 1 is
- * the 1-based update count (bias correction).  All four buffers hold n floats, 16-byte aligned. */
+ * the 1-based update count (bias correction).  lr / betas / eps are doubles, as torch.optim.Adam holds them: 1 - beta
+ * and the bias corrections are formed in double and rounded once.  All four buffers hold n floats, 16-byte aligned. */
 int nerfb_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
-                    float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
+                    double lr, double beta1, double beta2, double eps, int64_t step, float grad_scale,
                     void* stream);
 
 /* ---- (6) EG3D tri-plane renderer --------------------------------------------

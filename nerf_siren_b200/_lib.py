@@ -71,7 +71,7 @@ SIGNATURES = {
     "nerfb_finish_image": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "nerfb_pack_vol_workspace_bytes": (_L, [_L]),
     "nerfb_pack_vol": (_I, [_P, _L, _F, _P, _L, _P, _P, _L, _P]),
-    "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P]),
+    "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, C.c_double, C.c_double, C.c_double, C.c_double, _L, _F, _P]),
 }
 
 if not os.path.exists(LIB_PATH):

@@ -7,7 +7,8 @@
 
 __global__ void __launch_bounds__(256)
 adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                 int64_t n, float grad_scale, float beta1, float beta2, float eps, float step_size, float inv_sqrt_bc2) {
+                 int64_t n, float grad_scale, float beta1, float beta2, float omb1, float omb2, float eps, float step_size,
+                 float inv_sqrt_bc2) {
   const int64_t n4 = n >> 2;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -19,8 +20,8 @@ adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float gk = ge[k] * grad_scale;
-      me[k] = beta1 * me[k] + (1.0f - beta1) * gk;                    // torch.optim.Adam: exp_avg.lerp_(grad, 1-beta1)
-      ve[k] = beta2 * ve[k] + (1.0f - beta2) * gk * gk;               // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1-beta2)
+      me[k] = me[k] + omb1 * (gk - me[k]);                            // torch.optim.Adam: exp_avg.lerp_(grad, 1-beta1), weight < 0.5 form
+      ve[k] = beta2 * ve[k] + omb2 * (gk * gk);                       // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1-beta2)
       const float denom = sqrtf(ve[k]) * inv_sqrt_bc2 + eps;          // (sqrt(v) / sqrt(1-beta2^t)) + eps
       pe[k] = pe[k] - step_size * (me[k] / denom);                    // step_size = lr / (1-beta1^t)
     }
@@ -31,27 +32,27 @@ adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
   // tail (n not a multiple of 4)
   for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const float gk = g[i] * grad_scale;
-    const float mk = beta1 * m[i] + (1.0f - beta1) * gk;
-    const float vk = beta2 * v[i] + (1.0f - beta2) * gk * gk;
+    const float mk = m[i] + omb1 * (gk - m[i]);
+    const float vk = beta2 * v[i] + omb2 * (gk * gk);
     m[i] = mk; v[i] = vk;
     p[i] = p[i] - step_size * (mk / (sqrtf(vk) * inv_sqrt_bc2 + eps));
   }
 }
 
 extern "C" int nerfb_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
-                               float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
+                               double lr, double beta1, double beta2, double eps, int64_t step, float grad_scale,
                                void* stream) {
   NERFB_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && n >= 0 && step >= 1);
   NERFB_CHECK_ARG((reinterpret_cast<uintptr_t>(params) & 15) == 0 && (reinterpret_cast<uintptr_t>(grads) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(exp_avg) & 15) == 0 && (reinterpret_cast<uintptr_t>(exp_avg_sq) & 15) == 0);
   if (n == 0) return NERFB_OK;
-  const double bc1 = 1.0 - pow((double)beta1, (double)step);
-  const double bc2 = 1.0 - pow((double)beta2, (double)step);
-  const float step_size = (float)((double)lr / bc1);
+  const double bc1 = 1.0 - pow(beta1, (double)step);
+  const double bc2 = 1.0 - pow(beta2, (double)step);
+  const float step_size = (float)(lr / bc1);
   const float inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
   const int64_t want = ceil_div64((n >> 2) + 1, 256);
   const int grid = (int)(want < NERFB_SM_COUNT * 8 ? want : NERFB_SM_COUNT * 8);
-  NERFB_LAUNCH(adam_step_kernel, grid, 256, 0, stream, params, grads, exp_avg, exp_avg_sq, n, grad_scale, beta1, beta2,
-               eps, step_size, inv_sqrt_bc2);
+  NERFB_LAUNCH(adam_step_kernel, grid, 256, 0, stream, params, grads, exp_avg, exp_avg_sq, n, grad_scale, (float)beta1,
+               (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps, step_size, inv_sqrt_bc2);
   return NERFB_OK;
 }

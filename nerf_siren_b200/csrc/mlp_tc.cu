@@ -24,6 +24,7 @@
 // first layer (and the 3 direction columns of the colour layer) are carried as 9 K-columns [x_hi x_lo x_hi] against
 // [W_hi W_hi W_lo], which restores ~16 mantissa bits where the first-layer frequency scale w0 = 30 amplifies input
 // rounding; the colour layer is N = 256 and its 256->3 sigmoid head rides in the epilogue like NeRF's.
+#include <cstdlib>
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -647,12 +648,452 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_kernel(const __grid
   if (warp == WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
+
+// =====================================================================================================================
+// Tile-pair forward (round 2, inference instantiations): TWO tiles in flight per SM, one accumulator each.
+//
+// The single-tile kernel above pipelines a layer's MMAs behind the previous layer's epilogue block by block, so a
+// tile-layer costs epilogue + MMA tail (~4200 clk measured, the tensor pipe needing 2048).  Here the event sequence is
+//   A.s, B.s, A.s+1, B.s+1, ...   (A, B = the two tiles of the pair, s = layer step)
+// and every role walks it: while the 16 epilogue warps drain accumulator A (TMEM columns [0,256)) into A's activation
+// blocks, the tensor pipe runs B's layer into columns [256,512) and vice versa.  MMA(slot, s+1) starts only when
+// epilogue(slot, s) has drained the whole accumulator, so a thread can own 64 CONTIGUOUS columns of its row (warp =
+// lane quarter x 64-column block) and publish ONCE per layer: one fence.proxy.async and one mbarrier arrive instead of
+// four (tools/ubench/epi2.cu: 1900 clk per 128 x 256 drain under full-rate MMAs against 2760 for the per-block split).
+// Shared memory: activations 2 x 4 x 16 KB; ONE 16 KB X block shared by the skip / direction K-blocks of both tiles
+// (step 0's encoding is written straight into the tile's own activation block 0, which is free at that point); weight
+// ring = 2 x 32 KB slabs (bulk copies below ~32 KB are op-rate-bound: ~350-500 clk per cp.async.bulk whatever its size,
+// tools/ubench/l2_stream.cu), and the bias table is read through L1 (ld.global.nc, 10.5 KB) to make room for it.
+// =====================================================================================================================
+constexpr int P_STAGES = 2;
+constexpr uint32_t OP_SX = 1u << 10, OP_SXDONE = 1u << 11, OP_TILE_LAST = 1u << 12;
+
+struct __align__(1024) SmemP {
+  uint8_t a[2][4][BLK_BYTES];            // activation tiles of the two slots
+  uint8_t x[BLK_BYTES];                  // shared X block: skip / direction encodings, one use at a time
+  uint8_t ring[P_STAGES][STAGE_BYTES];   // weight slabs
+  float w_sigma[256];
+  float w_rgb[3 * 256];
+  float b_heads[4];
+  float part[4][3][TILE_M];              // head partial sums [64-column block][channel][row]
+  float sigma[2][TILE_M];                // per slot: lives from the sigma-head step to the rgb step
+  float comp[5][TILE_M];
+  float comp_tot[4];
+  uint64_t w_full[P_STAGES], w_empty[P_STAGES];
+  uint64_t acc_full[2];                  // MMAs of the slot's current step have completed
+  uint64_t epi_done[2];                  // the slot's accumulator has been drained and its activation blocks published
+  uint64_t enc_ready[2];                 // step 0's encoding sits in a[slot][0]
+  uint64_t a0_free[2];                   // the slot's last step has read its activation blocks
+  uint64_t x_ready, x_free;
+  uint32_t tmem_base;
+  uint4 ops[2][MAX_OPS];                 // per slot: {A descriptor low word, -, flags, -}
+  uint32_t step_word[MAX_STEPS], step_bias[MAX_STEPS];
+  uint32_t step_woff[MAX_STEPS];         // byte offset of the step's first slab in the packed blob
+  uint32_t step_nkb[MAX_STEPS];          // K-blocks | N << 8
+  int use_step[4], use_kind[4], n_uses;  // X uses of a tile in step order: kind 0 = xyz encoding, 1 = direction encoding
+};
+static_assert(sizeof(SmemP) + 1024 <= 232448, "shared memory budget (227 KB per CTA)");
+
+__device__ __forceinline__ void pack_row64(const float (&buf)[64], uint32_t (&pk)[32]) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) pk[i] = pack_bf16(buf[2 * i], buf[2 * i + 1]);
+}
+__device__ __forceinline__ void store_pk64(uint32_t base, int row, const uint32_t (&pk)[32]) {
+#pragma unroll
+  for (int ch = 0; ch < 8; ++ch)
+    sts128(base + (uint32_t)row * 128u + ((((uint32_t)ch) ^ ((uint32_t)row & 7u)) << 4), pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+}
+// encode_row / hilo_row / copy_row into registers (same values, same rounding): the row is computed BEFORE the encoder waits
+// for its buffer and stored right after, so the hand-off costs eight st.shared.v4 instead of the sincos ladder
+__device__ __forceinline__ void encode_pk(float vx, float vy, float vz, int n_freq, uint32_t (&pk)[32]) {
+  float s[3], c[3];
+  const float v[3] = {vx, vy, vz};
+#pragma unroll
+  for (int j = 0; j < 3; ++j) sincosf(v[j], &s[j], &c[j]);
+  float buf[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) buf[i] = 0.f;
+#pragma unroll
+  for (int j = 0; j < 3; ++j) buf[j] = v[j];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) {
+    const bool on = k < n_freq;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      buf[3 + 6 * k + j] = on ? s[j] : 0.f;
+      buf[6 + 6 * k + j] = on ? c[j] : 0.f;
+      const float s2 = 2.f * s[j] * c[j];
+      const float c2 = 1.f - 2.f * s[j] * s[j];
+      s[j] = s2; c[j] = c2;
+    }
+  }
+  pack_row64(buf, pk);
+}
+__device__ __forceinline__ void hilo_pk(float vx, float vy, float vz, uint32_t (&pk)[32]) {
+  float buf[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) buf[i] = 0.f;
+  const float v[3] = {vx, vy, vz};
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float hi = __bfloat162float(__float2bfloat16_rn(v[j]));
+    buf[j] = hi; buf[3 + j] = v[j] - hi; buf[6 + j] = hi;
+  }
+  pack_row64(buf, pk);
+}
+__device__ __forceinline__ void copy_pk(const float* src, int width, uint32_t (&pk)[32]) {
+  float buf[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) buf[i] = (src && i < width) ? __ldg(src + i) : 0.f;
+  pack_row64(buf, pk);
+}
+
+template <bool SIREN, bool CLS>
+__global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const __grid_constant__ TcFwdArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  SmemP& sm = *reinterpret_cast<SmemP*>(smem_raw);
+  if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
+  const TcProgram& pg = args.prog;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t n_pairs = (args.n_tiles + 1) >> 1;
+
+  // ---- one-time setup -----------------------------------------------------------------------------------
+  for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.bias + pg.n_bias + i);
+  if (threadIdx.x == 0) sm.b_heads[0] = __ldg(args.bias + pg.n_bias + 256);
+  constexpr int RGB_IN = SIREN ? 256 : 128;
+  for (int i = threadIdx.x; i < 3 * RGB_IN; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.bias + pg.n_bias + 257 + i);
+  if (threadIdx.x < 3) sm.b_heads[1 + threadIdx.x] = __ldg(args.bias + pg.n_bias + 257 + 3 * RGB_IN + threadIdx.x);
+  if (threadIdx.x < 2) {                  // decode the MMA op list for slot b (sequential: the step index is needed)
+    const int b = threadIdx.x;
+    int s = 0; bool sx = false;
+    for (int i = 0; i < pg.n_ops; ++i) {
+      uint32_t w = pg.ops[i] & ~(OP_SX | OP_SXDONE | OP_TILE_LAST);
+      uint4 o;
+      if (w & OP_X) {
+        if (s == 0) o.x = ((smem_u32(sm.a[b][0]) >> 4) & 0x3FFFu) | (1u << 16);
+        else { o.x = ((smem_u32(sm.x) >> 4) & 0x3FFFu) | (1u << 16); w |= OP_SX; sx = true; }
+      } else {
+        o.x = ((smem_u32(sm.a[b][(w >> 5) & 3u]) >> 4) & 0x3FFFu) | (1u << 16);
+      }
+      if (w & OP_LAST) {
+        if (sx) w |= OP_SXDONE;
+        if (s == pg.n_steps - 1) w |= OP_TILE_LAST;
+        ++s; sx = false;
+      }
+      o.y = 0u; o.z = w; o.w = 0u;
+      sm.ops[b][i] = o;
+    }
+  }
+  if (threadIdx.x == 32) {                // per-step tables for the producer / epilogue, X uses for the encoder
+    uint32_t off = 0; int nu = 0; bool dir_now = false;
+    for (int s = 0; s < pg.n_steps; ++s) {
+      const TcStep& st = pg.s[s];
+      sm.step_word[s] = pg.step_word[s]; sm.step_bias[s] = (uint32_t)st.bias_off;
+      sm.step_woff[s] = off; sm.step_nkb[s] = (uint32_t)st.n_kb | ((uint32_t)st.N << 8);
+      off += (uint32_t)st.n_kb * (uint32_t)st.N * 128u;
+      bool uses_x = false;
+      for (int kb = 0; kb < st.n_kb; ++kb) uses_x |= (st.src[kb] == SRC_X);
+      if (uses_x && nu < 4) { sm.use_step[nu] = s; sm.use_kind[nu] = dir_now ? 1 : 0; ++nu; }
+      if (st.x_done) dir_now = true;      // the xyz encoding's last reader: later X contents are the direction encoding
+    }
+    sm.n_uses = nu;
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.epi_done[i], N_EPI_WARPS);
+      mbar_init(&sm.enc_ready[i], 4); mbar_init(&sm.a0_free[i], 1);
+    }
+    mbar_init(&sm.x_ready, 4); mbar_init(&sm.x_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == WARP_MMA) tmem_alloc(&sm.tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == WARP_PRODUCER) {
+    // ===== weight producer: slabs in event order (step s of slot 0, step s of slot 1, step s + 1 ...) =====
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+        for (int s = 0; s < pg.n_steps; ++s) {
+          const uint32_t nk = sm.step_nkb[s];
+          const uint32_t bytes = (nk >> 8) * 128u;
+          const int n_kb = (int)(nk & 255u);
+          for (int slot = 0; slot < 2; ++slot) {
+            const uint8_t* src = args.wblob + sm.step_woff[s];
+            for (int kb = 0; kb < n_kb; ++kb) {
+              mbar_wait_relaxed(&sm.w_empty[stage], phase ^ 1);
+              mbar_expect_tx(&sm.w_full[stage], bytes);
+              bulk_g2s(sm.ring[stage], src, bytes, &sm.w_full[stage]);
+              src += bytes;
+              if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == WARP_MMA) {
+    // ===== MMA issuer (single thread) =====
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0, ed_par = 0, en_par = 0, xr_par = 0, it = 0;
+      const int n_ops = pg.n_ops;
+      const uint32_t ring_lo0 = ((smem_u32(sm.ring[0]) >> 4) & 0x3FFFu) | (1u << 16);
+      const uint32_t wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]);
+      const uint32_t af0 = smem_u32(&sm.acc_full[0]), ed0 = smem_u32(&sm.epi_done[0]), en0 = smem_u32(&sm.enc_ready[0]);
+      const uint32_t a0f0 = smem_u32(&sm.a0_free[0]), xr = smem_u32(&sm.x_ready), xf = smem_u32(&sm.x_free);
+      const uint32_t idesc256 = umma_idesc_bf16(TILE_M, 256), idesc128 = umma_idesc_bf16(TILE_M, 128), idesc16 = umma_idesc_bf16(TILE_M, 16);
+      for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x, ++it) {
+        int i0 = 0;                           // first op of the current step
+        while (i0 < n_ops) {
+          int i1 = i0;
+          for (uint32_t slot = 0; slot < 2; ++slot) {
+            const uint32_t ops_base = smem_u32(sm.ops[slot]);
+            const uint32_t d_tmem = tmem + slot * 256u;
+            int i = i0;
+            for (;;) {
+              const uint4 cur = lds128u(ops_base + 16u * (uint32_t)i);
+              if (cur.z & OP_FIRST) {         // the slot's previous event has been drained (accumulator free, activations published)
+                if (!(it == 0 && i == 0)) { mbar_wait_addr(ed0 + 8u * slot, (ed_par >> slot) & 1u); ed_par ^= 1u << slot; }
+              }
+              if (cur.z & OP_X) {
+                if (cur.z & OP_SX) { mbar_wait_addr(xr, xr_par); xr_par ^= 1u; }
+                else { mbar_wait_addr(en0 + 8u * slot, (en_par >> slot) & 1u); en_par ^= 1u << slot; }
+              }
+              const uint32_t idesc = (cur.z & OP_N16) ? idesc16 : (cur.z & OP_N128) ? idesc128 : idesc256;
+              mbar_wait_addr(wf0 + 8u * stage, phase);
+              tc_fence_after();
+              umma_bf16_k64(d_tmem, cur.x, ring_lo0 + stage * (STAGE_BYTES >> 4), idesc, (cur.z & OP_FIRST) ? 0u : 1u);
+              umma_commit_addr(we0 + 8u * stage);            // slab free once these MMAs have read it
+              if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+              ++i;
+              if (cur.z & OP_LAST) {
+                umma_commit_addr(af0 + 8u * slot);
+                if (cur.z & OP_SXDONE) umma_commit_addr(xf);
+                if (cur.z & OP_TILE_LAST) umma_commit_addr(a0f0 + 8u * slot);
+                break;
+              }
+            }
+            i1 = i;
+          }
+          i0 = i1;
+        }
+      }
+    }
+  } else if (warp >= WARP_ENC0 && warp < WARP_EPI0) {
+    // ===== encoder warps: one row per thread; a row is computed into registers, then stored as soon as its buffer is free =====
+    const int row = (warp - WARP_ENC0) * 32 + lane;
+    uint32_t a0_par = 0, xf_par = 0, it = 0;
+    bool first_shared = true;
+    const int n_uses = sm.n_uses;
+    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x, ++it) {
+      float pos[2][3], dir[2][3];
+      const float* emb[2] = {nullptr, nullptr};
+#pragma unroll
+      for (int slot = 0; slot < 2; ++slot) {
+        const int64_t p = (2 * pair + slot) * TILE_M + row;
+        const int64_t pc = p < args.P ? p : args.P - 1;      // padded rows recompute the last point (never stored)
+        pos[slot][0] = pos[slot][1] = pos[slot][2] = 0.f; dir[slot][0] = dir[slot][1] = dir[slot][2] = 0.f;
+        if (args.in_mode == NERFB_IN_RAYS) {                 // x = o + d z  (models/rendering.py:224)
+          const int64_t r = pc / args.S;
+          const float* ray = args.in0 + r * 8;
+          const float z = __ldg(args.in1 + pc);
+          dir[slot][0] = __ldg(ray + 3); dir[slot][1] = __ldg(ray + 4); dir[slot][2] = __ldg(ray + 5);
+          pos[slot][0] = __fadd_rn(__ldg(ray + 0), __fmul_rn(dir[slot][0], z));
+          pos[slot][1] = __fadd_rn(__ldg(ray + 1), __fmul_rn(dir[slot][1], z));
+          pos[slot][2] = __fadd_rn(__ldg(ray + 2), __fmul_rn(dir[slot][2], z));
+        } else if (args.in_mode == NERFB_IN_GRID) {          // dense query grid (extract_color_mesh.py:117-125), see the single-tile kernel
+          const double* rg = reinterpret_cast<const double*>(args.in0);
+          const int64_t N = args.S;
+          const int iz = (int)(pc % N), ix = (int)((pc / N) % N), iy = (int)(pc / (N * N));
+          const double den = (double)(N > 1 ? N - 1 : 1);
+          pos[slot][0] = (float)(ix == N - 1 && N > 1 ? rg[1] : rg[0] + (double)ix * ((rg[1] - rg[0]) / den));
+          pos[slot][1] = (float)(iy == N - 1 && N > 1 ? rg[3] : rg[2] + (double)iy * ((rg[3] - rg[2]) / den));
+          pos[slot][2] = (float)(iz == N - 1 && N > 1 ? rg[5] : rg[4] + (double)iz * ((rg[5] - rg[4]) / den));
+        } else if (SIREN) {                                  // x = [xyz(3) | dir(3)] rows (SirenField.forward)
+          const float* src = args.in0 + pc * (int64_t)(pg.sigma_only ? 3 : 6);
+          pos[slot][0] = __ldg(src); pos[slot][1] = __ldg(src + 1); pos[slot][2] = __ldg(src + 2);
+          if (!pg.sigma_only) { dir[slot][0] = __ldg(src + 3); dir[slot][1] = __ldg(src + 4); dir[slot][2] = __ldg(src + 5); }
+        } else {
+          emb[slot] = args.in0 + pc * (int64_t)(pg.in_xyz + (pg.sigma_only ? 0 : pg.in_dir));
+        }
+      }
+      for (int u = 0; u < n_uses; ++u) {
+        const int us = sm.use_step[u], kind = sm.use_kind[u];
+#pragma unroll
+        for (int slot = 0; slot < 2; ++slot) {
+          uint32_t pk[32];
+          if (kind == 0) {
+            if (SIREN) hilo_pk(__fmul_rn(pos[slot][0], pg.xyz_scale), __fmul_rn(pos[slot][1], pg.xyz_scale), __fmul_rn(pos[slot][2], pg.xyz_scale), pk);
+            else if (args.in_mode != NERFB_IN_EMBEDDED) encode_pk(pos[slot][0], pos[slot][1], pos[slot][2], pg.n_freq_xyz, pk);
+            else copy_pk(emb[slot], pg.in_xyz, pk);
+          } else {
+            if (SIREN) hilo_pk(dir[slot][0], dir[slot][1], dir[slot][2], pk);
+            else if (args.in_mode != NERFB_IN_EMBEDDED) encode_pk(dir[slot][0], dir[slot][1], dir[slot][2], pg.n_freq_dir, pk);   // grid: dir = 0
+            else copy_pk(emb[slot] + pg.in_xyz, pg.in_dir, pk);
+          }
+          uint32_t base;
+          if (us == 0) {                       // the tile's own block 0: free once the slot's previous tile has been multiplied out
+            if (it > 0) { mbar_wait_relaxed(&sm.a0_free[slot], (a0_par >> slot) & 1u); a0_par ^= 1u << slot; }
+            base = smem_u32(sm.a[slot][0]);
+          } else {                             // shared X block: free once the previous use's step has completed
+            if (!first_shared) { mbar_wait_relaxed(&sm.x_free, xf_par); xf_par ^= 1u; }
+            first_shared = false;
+            base = smem_u32(sm.x);
+          }
+          store_pk64(base, row, pk);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(us == 0 ? &sm.enc_ready[slot] : &sm.x_ready);
+        }
+      }
+    }
+  } else if (warp >= WARP_EPI0 && warp < WARP_END) {
+    // ===== epilogue warps (16): warp = (TMEM lane quarter q, 64-column block g); a thread drains 64 contiguous columns of
+    // its row as four pipelined tcgen05.ld.x16, writes its 128-byte row of activation block g, and the warp publishes once =====
+    const int ew = warp - WARP_EPI0;         // 0..15
+    const int q = warp & 3;                  // TMEM lane quarter this warp may access (warp id mod 4)
+    const int g = ew >> 2;                   // 64-column block
+    const int row = q * 32 + lane;
+    const uint32_t row_off = (uint32_t)row * 128u, row_x = (uint32_t)row & 7u;
+    uint32_t acc_par = 0;
+    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      for (int s = 0; s < pg.n_steps; ++s) {
+        const uint32_t sw = lds32(smem_u32(sm.step_word) + 4u * (uint32_t)s);
+        const uint32_t sb = lds32(smem_u32(sm.step_bias) + 4u * (uint32_t)s);
+        const int st_relu = (sw >> 9) & 1, st_out = (sw >> 10) & 7, st_head = (sw >> 13) & 3;
+        const int nb = (sw & 511u) >> 6;     // 64-column blocks of this step's accumulator
+#pragma unroll 1
+        for (int slot = 0; slot < 2; ++slot) {
+          const int64_t p = (2 * pair + slot) * TILE_M + row;
+          const bool live = p < args.P;
+          mbar_wait(&sm.acc_full[slot], (acc_par >> slot) & 1u); acc_par ^= 1u << slot;
+          tc_fence_after();
+          float head_acc[3] = {0.f, 0.f, 0.f};
+          const uint32_t t_addr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)slot * 256u + 64u * (uint32_t)g;
+          if (g < nb) {
+            const float4* bias4 = reinterpret_cast<const float4*>(args.bias + sb) + 16 * g;      // L1-resident table, warp-uniform address
+            const uint32_t blk = smem_u32(sm.a[slot][g]) + row_off;
+            uint32_t v[2][16];
+            tmem_ld16(t_addr, v[0]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              float4 bb[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) bb[i] = __ldg(bias4 + 4 * c + i);
+              tmem_ld_wait();
+              if (c + 1 < 4) tmem_ld16(t_addr + 16u * (uint32_t)(c + 1), v[(c + 1) & 1]);
+              const uint32_t (&vv)[16] = v[c & 1];
+              float f[16];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                float2 r0, r1;
+                r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
+                r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
+                if (SIREN) { r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y); }   // frequency / phase folded when packing
+                f[4 * i] = r0.x; f[4 * i + 1] = r0.y; f[4 * i + 2] = r1.x; f[4 * i + 3] = r1.y;
+              }
+              const uint32_t col0 = 64u * (uint32_t)g + 16u * (uint32_t)c;
+              if (st_head == 1) {               // sigma = <relu(h_D), w_sigma> + b on the un-rounded activations (nerf.py:112)
+                const uint32_t wb = smem_u32(sm.w_sigma) + col0 * 4u;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float4 w = lds128f(wb + 16u * i);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[0]);
+                }
+              } else if (st_head == 2) {        // rgb pre-activations on the un-rounded direction-layer activations
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                  const uint32_t wb = smem_u32(sm.w_rgb) + (uint32_t)(ch * RGB_IN) * 4u + col0 * 4u;
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const float4 w = lds128f(wb + 16u * i);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[ch]);
+                  }
+                }
+              }
+              if (g < st_out) {
+                if (st_relu) {
+#pragma unroll
+                  for (int ch = 0; ch < 2; ++ch)
+                    sts128(blk + ((((uint32_t)(2 * c + ch)) ^ row_x) << 4), pack_bf16_relu(f[8 * ch + 0], f[8 * ch + 1]),
+                           pack_bf16_relu(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16_relu(f[8 * ch + 4], f[8 * ch + 5]),
+                           pack_bf16_relu(f[8 * ch + 6], f[8 * ch + 7]));
+                } else {
+#pragma unroll
+                  for (int ch = 0; ch < 2; ++ch)
+                    sts128(blk + ((((uint32_t)(2 * c + ch)) ^ row_x) << 4), pack_bf16(f[8 * ch + 0], f[8 * ch + 1]),
+                           pack_bf16(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16(f[8 * ch + 4], f[8 * ch + 5]),
+                           pack_bf16(f[8 * ch + 6], f[8 * ch + 7]));
+                }
+              }
+            }
+            if (g < st_out) fence_proxy_async();
+          }
+          if (CLS && st_head == 3 && g == 0) {       // class head (models/nerf_cls.py:104): sigmoid of the merged parse.1 o parse.0 logits, 16-column step
+            uint32_t v[16];
+            tmem_ld16(t_addr, v);
+            tmem_ld_wait();
+            if (live) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (k < pg.n_cls) args.out[p * pg.out_c + 4 + k] = 1.f / (1.f + __expf(-(__uint_as_float(v[k]) + __ldg(args.bias + sb + k))));
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.epi_done[slot]);    // accumulator drained, activation blocks published: the slot's next step may be issued
+          if (st_head == 1) {       // combine the four blocks' partial dot products
+            sm.part[g][0][row] = head_acc[0];
+            named_bar_sync(1, EPI_THREADS);
+            if (g == 0) {
+              const float sg = sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[0];
+              sm.sigma[slot][row] = sg;
+              if (pg.sigma_only && args.comp.on)      // weights-only coarse pass of test_time (models/rendering.py:230-231) composited in place
+                epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, 0.f, 0.f, 0.f, sg, false);
+              else if (pg.sigma_only && live) args.out[p] = (args.in_mode == NERFB_IN_GRID) ? fmaxf(sg, 0.f) : sg;   // grid: np.maximum(sigma, 0), extract_color_mesh.py:141
+            }
+            named_bar_sync(2, EPI_THREADS);          // head scratch is reused by the other slot's event right after
+          } else if (st_head == 2) { // rgb = sigmoid(W_rgb h_dir + b)  (models/nerf.py:119-120)
+            sm.part[g][0][row] = head_acc[0]; sm.part[g][1][row] = head_acc[1]; sm.part[g][2][row] = head_acc[2];
+            named_bar_sync(1, EPI_THREADS);
+            if (g == 0 && (live || args.comp.on)) {
+              float4 o;
+              o.x = 1.f / (1.f + __expf(-(sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[1])));
+              o.y = 1.f / (1.f + __expf(-(sm.part[0][1][row] + sm.part[1][1][row] + sm.part[2][1][row] + sm.part[3][1][row] + sm.b_heads[2])));
+              o.z = 1.f / (1.f + __expf(-(sm.part[0][2][row] + sm.part[1][2][row] + sm.part[2][2][row] + sm.part[3][2][row] + sm.b_heads[3])));
+              o.w = sm.sigma[slot][row];
+              if (!CLS && args.comp.on) epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, o.x, o.y, o.z, o.w, true);
+              else if (!CLS) *reinterpret_cast<float4*>(args.out + p * 4) = o;
+              else { float* dst = args.out + p * pg.out_c; dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
+            }
+            named_bar_sync(2, EPI_THREADS);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- teardown ------------------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
 // ---- weight packing: fp32 nn.Linear weights -> bf16 slabs in the swizzled shared-memory image, schedule order ----
 struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; int aux; int film; };   // aux: read the merged class-head matrix, not params   // W[n*ld + col0 + kk], kk < ncols
 // hilo: 3 source columns expanded to 9 K-columns [W_hi W_hi W_lo] (pairs with hilo_row's [x_hi x_lo x_hi])
 // film >= 0 (SIREN): row n is scaled by the FiLM frequency of that layer, sin(freq (W x + b) + phase) = sin((freq W) x + (freq b + phase)),
 // so the epilogue only adds the folded bias; bf16(freq W) carries the same relative rounding as bf16(W)
-struct PackArgs { int n_slabs; PackSlab slab[48]; };
+struct PackArgs { int n_slabs; PackSlab slab[48]; int sw64; };   // sw64: tile-pair kernel's image, two [N x 32] halves per slab, SWIZZLE_64B
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params_in, PackArgs pa, uint8_t* __restrict__ blob,
                                                            const float* __restrict__ aux, const float* __restrict__ film) {
@@ -677,6 +1118,9 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
     }
     uint4 o;
     o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+    if (pa.sw64)      // half (ch >> 2) of the slab, 64-byte rows, 16-byte chunk XOR ((row >> 1) & 3)  (Swizzle<2,4,3>)
+      *reinterpret_cast<uint4*>(blob + sl.dst_off + (int64_t)(ch >> 2) * sl.N * 64 + (int64_t)n * 64 + (((ch & 3) ^ ((n >> 1) & 3)) << 4)) = o;
+    else
     *reinterpret_cast<uint4*>(blob + sl.dst_off + (int64_t)n * 128 + ((ch ^ (n & 7)) << 4)) = o;
   }
 }
@@ -742,7 +1186,7 @@ bool tc_supported(const nerfb_mlp_desc& d, int in_mode) {
 }
 
 TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P);
-static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool save) {
+static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool save, bool pair = false) {
   TcPlan pl{};
   const NerfOffsets o = nerf_offsets(d);
   TcProgram& pg = pl.prog;
@@ -791,9 +1235,11 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
     st.N = 256; st.relu = 1; st.out_blocks = 4; st.head = (i == d.D - 1) ? 1 : 0;
     if (i == 0) { st.src[st.n_kb++] = SRC_X; st.wait_x = 1; add_slab(o.w[0], o.in[0], 0, o.in_xyz, 256); }
     else {
-      if (skip) { st.src[st.n_kb++] = SRC_X; add_slab(o.w[i], o.in[i], 0, o.in_xyz, 256); last_x_reader = i; }
+      // skip layer: the tile-pair kernel takes the X K-block LAST (the shared X block is handed over while the other four run)
+      if (skip && !pair) { st.src[st.n_kb++] = SRC_X; add_slab(o.w[i], o.in[i], 0, o.in_xyz, 256); last_x_reader = i; }
       const int c0 = skip ? o.in_xyz : 0;
       for (int j = 0; j < 4; ++j) { st.src[st.n_kb++] = j; add_slab(o.w[i], o.in[i], c0 + 64 * j, 64, 256); }
+      if (skip && pair) { st.src[st.n_kb++] = SRC_X; add_slab(o.w[i], o.in[i], 0, o.in_xyz, 256); last_x_reader = i; }
     }
     st.bias_off = add_bias(o.b[i], 256);
     st.save_off = -1; st.mask_off = -1;
@@ -842,7 +1288,7 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   }
   add_bias(o.w_sigma, 256); add_bias(o.b_sigma, 1);
   if (!sigma_only) { add_bias(o.w_rgb, 3 * pg.rgb_in); add_bias(o.b_rgb, 3); }
-  pl.pack.n_slabs = nslab; pl.bias.n_segs = nseg;
+  pl.pack.n_slabs = nslab; pl.bias.n_segs = nseg; pl.pack.sw64 = 0;
   pg.tile_save_bytes = save ? sv : 0;
   pl.wblob_bytes = wb; pl.bias_floats = pg.n_bias + 256 + 1 + 768 + 3;
   const int64_t n_tiles = ceil_div64(P, TILE_M);
@@ -856,6 +1302,13 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
   return pl;
 }
 
+#ifndef NERFB_FWD_PAIR_DEFAULT
+#define NERFB_FWD_PAIR_DEFAULT 0
+#endif
+static bool fwd_pair_enabled() {          // NERFB_FWD_PAIR=0/1 overrides the build default (read per call: tests flip it)
+  const char* e = getenv("NERFB_FWD_PAIR");
+  return e && *e ? atoi(e) != 0 : NERFB_FWD_PAIR_DEFAULT != 0;
+}
 static long long* g_trace = nullptr;
 extern "C" void nerfb_debug_trace(long long* device_buf) { g_trace = device_buf; }   // diagnostics only (40 x 16 slots)
 
@@ -883,7 +1336,8 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   if (siren && !film) return NERFB_E_BADARG;
   if (in_mode == NERFB_IN_GRID && (save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
-  const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0);
+  const bool pair = !save && fwd_pair_enabled();        // inference: two tiles in flight per SM (mlp_tc_fwd_pair_kernel)
+  const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0, pair);
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;
   if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return NERFB_E_BADARG;
   uint8_t* base = static_cast<uint8_t*>(ws);
@@ -908,11 +1362,14 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   if (comp) a.comp = *comp;
   a.save = save ? base + pl.off_save : nullptr;
   a.trace = g_trace;
-  const size_t smem = sizeof(Smem) + 1024;
+  const size_t smem = sizeof(Smem) + 1024, smem_p = sizeof(SmemP) + 1024;
   int dev = 0;
   NERFB_CUDA(cudaGetDevice(&dev));
   static bool attr_set[64] = {};          // cudaFuncSetAttribute is per device
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -920,6 +1377,14 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  if (pair) {
+    const int64_t n_pairs = (a.n_tiles + 1) >> 1;
+    const int pgrid = (int)(n_pairs < NERFB_SM_COUNT ? n_pairs : NERFB_SM_COUNT);
+    if (siren) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<true, false>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else if (pl.prog.n_cls > 0) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, true>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, false>), pgrid, NUM_THREADS, smem_p, stream, a);
+    return NERFB_OK;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);
   const bool sv = a.save != nullptr;

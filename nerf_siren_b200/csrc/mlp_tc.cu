@@ -671,7 +671,10 @@ constexpr uint32_t OP_SX = 1u << 10, OP_SXDONE = 1u << 11, OP_TILE_LAST = 1u << 
 struct __align__(1024) SmemP {
   uint8_t a[2][4][BLK_BYTES];            // activation tiles of the two slots
   uint8_t x[BLK_BYTES];                  // shared X block: skip / direction encodings, one use at a time
-  uint8_t ring[P_STAGES][STAGE_BYTES];   // weight slabs
+  union {
+    uint8_t ring[P_STAGES][STAGE_BYTES];   // weight slabs (single-CTA pair kernel)
+    uint8_t ring2[4][128 * 128];           // this CTA's slab halves (CTA-pair kernel, cta_group::2)
+  };
   float w_sigma[256];
   float w_rgb[3 * 256];
   float b_heads[4];
@@ -679,7 +682,8 @@ struct __align__(1024) SmemP {
   float sigma[2][TILE_M];                // per slot: lives from the sigma-head step to the rgb step
   float comp[5][TILE_M];
   float comp_tot[4];
-  uint64_t w_full[P_STAGES], w_empty[P_STAGES];
+  uint64_t w_full[4], w_empty[4];
+  uint64_t w_peer[4];                    // CTA-pair kernel, leader: the peer's half of the slab in this stage has landed
   uint64_t acc_full[2];                  // MMAs of the slot's current step have completed
   uint64_t epi_done[2];                  // the slot's accumulator has been drained and its activation blocks published
   uint64_t enc_ready[2];                 // step 0's encoding sits in a[slot][0]
@@ -691,6 +695,8 @@ struct __align__(1024) SmemP {
   uint32_t step_woff[MAX_STEPS];         // byte offset of the step's first slab in the packed blob
   uint32_t step_nkb[MAX_STEPS];          // K-blocks | N << 8
   int use_step[4], use_kind[4], n_uses;  // X uses of a tile in step order: kind 0 = xyz encoding, 1 = direction encoding
+  int step_mask[MAX_STEPS];
+  uint32_t st_cnt[2], sx_cnt;            // training: events the store lane has finished with per slot / shared-X uses it has seen
 };
 static_assert(sizeof(SmemP) + 1024 <= 232448, "shared memory budget (227 KB per CTA)");
 
@@ -748,7 +754,12 @@ __device__ __forceinline__ void copy_pk(const float* src, int width, uint32_t (&
   pack_row64(buf, pk);
 }
 
-template <bool SIREN, bool CLS>
+// SAVE (training): a store lane bulk-stores every published activation tile (one 64 KB copy per event) and the encodings to
+// the tile's record for the backward, and counts the events it has finished with per slot (st_cnt) / the shared-X uses
+// (sx_cnt); the epilogue and the encoder wait on those monotonic counters before they overwrite a buffer -- a whole event of
+// slack, so they practically never block.  ReLU gates / sign(cos) go out as the same [column quarter][row] bit-mask record
+// the dgrad kernel reads (mlp_tc_bwd.cu), here as four 16-bit stores per thread and layer.
+template <bool SIREN, bool CLS, bool SAVE>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const __grid_constant__ TcFwdArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   SmemP& sm = *reinterpret_cast<SmemP*>(smem_raw);
@@ -756,6 +767,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
   const TcProgram& pg = args.prog;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t n_pairs = (args.n_tiles + 1) >> 1;
+  const bool saving = SAVE ? (args.save != nullptr) : false;
 
   // ---- one-time setup -----------------------------------------------------------------------------------
   for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.bias + pg.n_bias + i);
@@ -789,7 +801,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
     for (int s = 0; s < pg.n_steps; ++s) {
       const TcStep& st = pg.s[s];
       sm.step_word[s] = pg.step_word[s]; sm.step_bias[s] = (uint32_t)st.bias_off;
-      sm.step_woff[s] = off; sm.step_nkb[s] = (uint32_t)st.n_kb | ((uint32_t)st.N << 8);
+      sm.step_woff[s] = off; sm.step_nkb[s] = (uint32_t)st.n_kb | ((uint32_t)st.N << 8); sm.step_mask[s] = st.mask_off;
       off += (uint32_t)st.n_kb * (uint32_t)st.N * 128u;
       bool uses_x = false;
       for (int kb = 0; kb < st.n_kb; ++kb) uses_x |= (st.src[kb] == SRC_X);
@@ -805,6 +817,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
       mbar_init(&sm.enc_ready[i], 4); mbar_init(&sm.a0_free[i], 1);
     }
     mbar_init(&sm.x_ready, 4); mbar_init(&sm.x_free, 1);
+    sm.st_cnt[0] = 0u; sm.st_cnt[1] = 0u; sm.sx_cnt = 0u;
     fence_barrier_init();
   }
   if (warp == WARP_MMA) tmem_alloc(&sm.tmem_base, 512);
@@ -839,6 +852,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
     // ===== MMA issuer (single thread) =====
     if (lane == 0) {
       uint32_t stage = 0, phase = 0, ed_par = 0, en_par = 0, xr_par = 0, it = 0;
+      NERFB_TRACE(int tev = 0;)
       const int n_ops = pg.n_ops;
       const uint32_t ring_lo0 = ((smem_u32(sm.ring[0]) >> 4) & 0x3FFFu) | (1u << 16);
       const uint32_t wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]);
@@ -853,17 +867,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
             const uint32_t ops_base = smem_u32(sm.ops[slot]);
             const uint32_t d_tmem = tmem + slot * 256u;
             int i = i0;
+            NERFB_TRACE(const bool tr = args.trace && blockIdx.x == 0 && tev < 64; long long tw = 0; if (tr) args.trace[tev * 16 + 0] = clock64();)
             for (;;) {
               const uint4 cur = lds128u(ops_base + 16u * (uint32_t)i);
               if (cur.z & OP_FIRST) {         // the slot's previous event has been drained (accumulator free, activations published)
                 if (!(it == 0 && i == 0)) { mbar_wait_addr(ed0 + 8u * slot, (ed_par >> slot) & 1u); ed_par ^= 1u << slot; }
+                NERFB_TRACE(if (tr) args.trace[tev * 16 + 1] = clock64();)
               }
               if (cur.z & OP_X) {
                 if (cur.z & OP_SX) { mbar_wait_addr(xr, xr_par); xr_par ^= 1u; }
                 else { mbar_wait_addr(en0 + 8u * slot, (en_par >> slot) & 1u); en_par ^= 1u << slot; }
               }
               const uint32_t idesc = (cur.z & OP_N16) ? idesc16 : (cur.z & OP_N128) ? idesc128 : idesc256;
+              NERFB_TRACE(const long long tw0 = clock64();)
               mbar_wait_addr(wf0 + 8u * stage, phase);
+              NERFB_TRACE(tw += clock64() - tw0;)
               tc_fence_after();
               umma_bf16_k64(d_tmem, cur.x, ring_lo0 + stage * (STAGE_BYTES >> 4), idesc, (cur.z & OP_FIRST) ? 0u : 1u);
               umma_commit_addr(we0 + 8u * stage);            // slab free once these MMAs have read it
@@ -873,6 +891,493 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
                 umma_commit_addr(af0 + 8u * slot);
                 if (cur.z & OP_SXDONE) umma_commit_addr(xf);
                 if (cur.z & OP_TILE_LAST) umma_commit_addr(a0f0 + 8u * slot);
+                NERFB_TRACE(if (tr) { args.trace[tev * 16 + 2] = tw; args.trace[tev * 16 + 3] = clock64(); } ++tev;)
+                break;
+              }
+            }
+            i1 = i;
+          }
+          i0 = i1;
+        }
+      }
+    }
+  } else if (warp == WARP_STORE) {
+    // ===== store lane (training): published tiles / encodings -> the tile's record in HBM =====
+    if (lane == 0 && saving) {
+      uint32_t ed_par = 0, en_par = 0, xr_par = 0;
+      const uint32_t cnt0 = smem_u32(&sm.st_cnt[0]), cntx = smem_u32(&sm.sx_cnt);
+      for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+        int u = 0;                                  // next X use of the tile (same for both slots)
+        for (int s = 0; s < pg.n_steps; ++s) {
+          const TcStep& st = pg.s[s];
+          const bool uses_x = u < sm.n_uses && sm.use_step[u] == s;
+          const int kind = uses_x ? sm.use_kind[u] : 0;
+          for (uint32_t slot = 0; slot < 2; ++slot) {
+            const int64_t tile = 2 * pair + slot;
+            const bool live_tile = tile < args.n_tiles;
+            uint8_t* rec = args.save + tile * (int64_t)pg.tile_save_bytes;
+            if (uses_x && s == 0) {                 // xyz encoding of step 0, in the tile's own block 0
+              mbar_wait_relaxed(&sm.enc_ready[slot], (en_par >> slot) & 1u); en_par ^= 1u << slot;
+              if (live_tile) { bulk_s2g(rec + pg.save_x_off, sm.a[slot][0], BLK_BYTES); bulk_commit(); bulk_wait_read0(); }
+              cnt_publish(cnt0 + 4u * slot);
+            } else if (uses_x) {                    // shared X block: the direction encoding is part of the record, the skip copy is not
+              mbar_wait_relaxed(&sm.x_ready, xr_par); xr_par ^= 1u;
+              if (kind == 1 && pg.save_dir_off >= 0 && live_tile) { bulk_s2g(rec + pg.save_dir_off, sm.x, BLK_BYTES); bulk_commit(); bulk_wait_read0(); }
+              cnt_publish(cntx);
+            }
+            mbar_wait_relaxed(&sm.epi_done[slot], (ed_par >> slot) & 1u); ed_par ^= 1u << slot;
+            if (st.save_off >= 0 && st.out_blocks > 0 && live_tile) {
+              bulk_s2g(rec + st.save_off, sm.a[slot][0], (uint32_t)st.out_blocks * BLK_BYTES); bulk_commit(); bulk_wait_read0();
+            }
+            cnt_publish(cnt0 + 4u * slot);
+          }
+          if (uses_x) ++u;
+        }
+      }
+      bulk_wait_all0();
+    }
+  } else if (warp >= WARP_ENC0 && warp < WARP_EPI0) {
+    // ===== encoder warps: one row per thread; a row is computed into registers, then stored as soon as its buffer is free =====
+    const int row = (warp - WARP_ENC0) * 32 + lane;
+    uint32_t a0_par = 0, xf_par = 0, it = 0, n_shared = 0;
+    bool first_shared = true;
+    const int n_uses = sm.n_uses;
+    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x, ++it) {
+      float pos[2][3], dir[2][3];
+      const float* emb[2] = {nullptr, nullptr};
+#pragma unroll
+      for (int slot = 0; slot < 2; ++slot) {
+        const int64_t p = (2 * pair + slot) * TILE_M + row;
+        const int64_t pc = p < args.P ? p : args.P - 1;      // padded rows recompute the last point (never stored)
+        pos[slot][0] = pos[slot][1] = pos[slot][2] = 0.f; dir[slot][0] = dir[slot][1] = dir[slot][2] = 0.f;
+        if (args.in_mode == NERFB_IN_RAYS) {                 // x = o + d z  (models/rendering.py:224)
+          const int64_t r = pc / args.S;
+          const float* ray = args.in0 + r * 8;
+          const float z = __ldg(args.in1 + pc);
+          dir[slot][0] = __ldg(ray + 3); dir[slot][1] = __ldg(ray + 4); dir[slot][2] = __ldg(ray + 5);
+          pos[slot][0] = __fadd_rn(__ldg(ray + 0), __fmul_rn(dir[slot][0], z));
+          pos[slot][1] = __fadd_rn(__ldg(ray + 1), __fmul_rn(dir[slot][1], z));
+          pos[slot][2] = __fadd_rn(__ldg(ray + 2), __fmul_rn(dir[slot][2], z));
+        } else if (args.in_mode == NERFB_IN_GRID) {          // dense query grid (extract_color_mesh.py:117-125), see the single-tile kernel
+          const double* rg = reinterpret_cast<const double*>(args.in0);
+          const int64_t N = args.S;
+          const int iz = (int)(pc % N), ix = (int)((pc / N) % N), iy = (int)(pc / (N * N));
+          const double den = (double)(N > 1 ? N - 1 : 1);
+          pos[slot][0] = (float)(ix == N - 1 && N > 1 ? rg[1] : rg[0] + (double)ix * ((rg[1] - rg[0]) / den));
+          pos[slot][1] = (float)(iy == N - 1 && N > 1 ? rg[3] : rg[2] + (double)iy * ((rg[3] - rg[2]) / den));
+          pos[slot][2] = (float)(iz == N - 1 && N > 1 ? rg[5] : rg[4] + (double)iz * ((rg[5] - rg[4]) / den));
+        } else if (SIREN) {                                  // x = [xyz(3) | dir(3)] rows (SirenField.forward)
+          const float* src = args.in0 + pc * (int64_t)(pg.sigma_only ? 3 : 6);
+          pos[slot][0] = __ldg(src); pos[slot][1] = __ldg(src + 1); pos[slot][2] = __ldg(src + 2);
+          if (!pg.sigma_only) { dir[slot][0] = __ldg(src + 3); dir[slot][1] = __ldg(src + 4); dir[slot][2] = __ldg(src + 5); }
+        } else {
+          emb[slot] = args.in0 + pc * (int64_t)(pg.in_xyz + (pg.sigma_only ? 0 : pg.in_dir));
+        }
+      }
+      for (int u = 0; u < n_uses; ++u) {
+        const int us = sm.use_step[u], kind = sm.use_kind[u];
+#pragma unroll
+        for (int slot = 0; slot < 2; ++slot) {
+          uint32_t pk[32];
+          if (kind == 0) {
+            if (SIREN) hilo_pk(__fmul_rn(pos[slot][0], pg.xyz_scale), __fmul_rn(pos[slot][1], pg.xyz_scale), __fmul_rn(pos[slot][2], pg.xyz_scale), pk);
+            else if (args.in_mode != NERFB_IN_EMBEDDED) encode_pk(pos[slot][0], pos[slot][1], pos[slot][2], pg.n_freq_xyz, pk);
+            else copy_pk(emb[slot], pg.in_xyz, pk);
+          } else {
+            if (SIREN) hilo_pk(dir[slot][0], dir[slot][1], dir[slot][2], pk);
+            else if (args.in_mode != NERFB_IN_EMBEDDED) encode_pk(dir[slot][0], dir[slot][1], dir[slot][2], pg.n_freq_dir, pk);   // grid: dir = 0
+            else copy_pk(emb[slot] + pg.in_xyz, pg.in_dir, pk);
+          }
+          uint32_t base;
+          if (us == 0) {                       // the tile's own block 0: free once the slot's previous tile has been multiplied out
+            if (it > 0) { mbar_wait_relaxed(&sm.a0_free[slot], (a0_par >> slot) & 1u); a0_par ^= 1u << slot; }
+            if (saving) cnt_wait_relaxed(smem_u32(&sm.st_cnt[slot]), it * (uint32_t)(pg.n_steps + 1));   // the previous tile's stores have been read out
+            base = smem_u32(sm.a[slot][0]);
+          } else {                             // shared X block: free once the previous use's step has completed
+            if (!first_shared) { mbar_wait_relaxed(&sm.x_free, xf_par); xf_par ^= 1u; }
+            first_shared = false;
+            if (saving) cnt_wait_relaxed(smem_u32(&sm.sx_cnt), n_shared);      // the store lane has seen (and stored) every earlier use
+            ++n_shared;
+            base = smem_u32(sm.x);
+          }
+          store_pk64(base, row, pk);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(us == 0 ? &sm.enc_ready[slot] : &sm.x_ready);
+        }
+      }
+    }
+  } else if (warp >= WARP_EPI0 && warp < WARP_END) {
+    // ===== epilogue warps (16): warp = (TMEM lane quarter q, 64-column block g); a thread drains 64 contiguous columns of
+    // its row as four pipelined tcgen05.ld.x16, writes its 128-byte row of activation block g, and the warp publishes once =====
+    const int ew = warp - WARP_EPI0;         // 0..15
+    const int q = warp & 3;                  // TMEM lane quarter this warp may access (warp id mod 4)
+    const int g = ew >> 2;                   // 64-column block
+    const int row = q * 32 + lane;
+    const uint32_t row_off = (uint32_t)row * 128u, row_x = (uint32_t)row & 7u;
+    uint32_t acc_par = 0, it = 0;
+    NERFB_TRACE(int tev = 0;)
+    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x, ++it) {
+      for (int s = 0; s < pg.n_steps; ++s) {
+        const uint32_t sw = lds32(smem_u32(sm.step_word) + 4u * (uint32_t)s);
+        const uint32_t sb = lds32(smem_u32(sm.step_bias) + 4u * (uint32_t)s);
+        const int st_relu = (sw >> 9) & 1, st_out = (sw >> 10) & 7, st_head = (sw >> 13) & 3;
+        const int nb = (sw & 511u) >> 6;     // 64-column blocks of this step's accumulator
+        const bool st_saved = saving && ((sw >> 16) & 1u);
+        const int mo = SAVE ? sm.step_mask[s] : -1;
+#pragma unroll 1
+        for (int slot = 0; slot < 2; ++slot) {
+          const int64_t p = (2 * pair + slot) * TILE_M + row;
+          const bool live = p < args.P;
+          NERFB_TRACE(const bool tr = args.trace && blockIdx.x == 0 && tev < 64 && ew == 0 && lane == 0; if (tr) args.trace[tev * 16 + 8] = clock64();)
+          mbar_wait(&sm.acc_full[slot], (acc_par >> slot) & 1u); acc_par ^= 1u << slot;
+          tc_fence_after();
+          NERFB_TRACE(if (tr) args.trace[tev * 16 + 9] = clock64();)
+          float head_acc[3] = {0.f, 0.f, 0.f};
+          // training: the store lane has read out everything this slot's blocks held before (X copy + s earlier events of this tile)
+          if (SAVE && saving && g < st_out) cnt_wait(smem_u32(&sm.st_cnt[slot]), it * (uint32_t)(pg.n_steps + 1) + 1u + (uint32_t)s);
+          const uint32_t t_addr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)slot * 256u + 64u * (uint32_t)g;
+          if (g < nb) {
+            const float4* bias4 = reinterpret_cast<const float4*>(args.bias + sb) + 16 * g;      // L1-resident table, warp-uniform address
+            const uint32_t blk = smem_u32(sm.a[slot][g]) + row_off;
+            uint32_t v[2][16];
+            tmem_ld16(t_addr, v[0]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              float4 bb[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) bb[i] = __ldg(bias4 + 4 * c + i);
+              tmem_ld_wait();
+              if (c + 1 < 4) tmem_ld16(t_addr + 16u * (uint32_t)(c + 1), v[(c + 1) & 1]);
+              const uint32_t (&vv)[16] = v[c & 1];
+              float f[16];
+              uint32_t gate = 0u;          // this chunk's 16 gate bits (element i at bit 15 - i), for the dgrad kernel
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                float2 r0, r1;
+                r0 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i]), __uint_as_float(vv[4 * i + 1])), make_float2(bb[i].x, bb[i].y));
+                r1 = __fadd2_rn(make_float2(__uint_as_float(vv[4 * i + 2]), __uint_as_float(vv[4 * i + 3])), make_float2(bb[i].z, bb[i].w));
+                if (SIREN) {      // frequency / phase folded when packing
+                  if (SAVE) {       // training: sign(cos) is the saved gate (the dgrad rebuilds |cos| from the sine image)
+                    float c0, c1, c2, c3;
+                    __sincosf(r0.x, &r0.x, &c0); __sincosf(r0.y, &r0.y, &c1); __sincosf(r1.x, &r1.x, &c2); __sincosf(r1.y, &r1.y, &c3);
+                    gate = __funnelshift_l(__float_as_uint(c0), gate, 1); gate = __funnelshift_l(__float_as_uint(c1), gate, 1);
+                    gate = __funnelshift_l(__float_as_uint(c2), gate, 1); gate = __funnelshift_l(__float_as_uint(c3), gate, 1);
+                  } else { r0.x = __sinf(r0.x); r0.y = __sinf(r0.y); r1.x = __sinf(r1.x); r1.y = __sinf(r1.y); }
+                }
+                f[4 * i] = r0.x; f[4 * i + 1] = r0.y; f[4 * i + 2] = r1.x; f[4 * i + 3] = r1.y;
+              }
+              const uint32_t col0 = 64u * (uint32_t)g + 16u * (uint32_t)c;
+              if (st_head == 1) {               // sigma = <relu(h_D), w_sigma> + b on the un-rounded activations (nerf.py:112)
+                const uint32_t wb = smem_u32(sm.w_sigma) + col0 * 4u;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float4 w = lds128f(wb + 16u * i);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[0]);
+                  head_acc[0] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[0]);
+                }
+              } else if (st_head == 2) {        // rgb pre-activations on the un-rounded direction-layer activations
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                  const uint32_t wb = smem_u32(sm.w_rgb) + (uint32_t)(ch * RGB_IN) * 4u + col0 * 4u;
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const float4 w = lds128f(wb + 16u * i);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i] : fmaxf(f[4 * i], 0.f), w.x, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 1] : fmaxf(f[4 * i + 1], 0.f), w.y, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 2] : fmaxf(f[4 * i + 2], 0.f), w.z, head_acc[ch]);
+                    head_acc[ch] = fmaf(SIREN ? f[4 * i + 3] : fmaxf(f[4 * i + 3], 0.f), w.w, head_acc[ch]);
+                  }
+                }
+              }
+              if (g < st_out) {
+                if (st_relu) {
+#pragma unroll
+                  for (int ch = 0; ch < 2; ++ch)
+                    sts128(blk + ((((uint32_t)(2 * c + ch)) ^ row_x) << 4), pack_bf16_relu(f[8 * ch + 0], f[8 * ch + 1]),
+                           pack_bf16_relu(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16_relu(f[8 * ch + 4], f[8 * ch + 5]),
+                           pack_bf16_relu(f[8 * ch + 6], f[8 * ch + 7]));
+                  if (SAVE && st_saved) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) gate = __funnelshift_l(__float_as_uint(f[i]), gate, 1);     // sign bit: 1 = gated off
+                  }
+                } else {
+#pragma unroll
+                  for (int ch = 0; ch < 2; ++ch)
+                    sts128(blk + ((((uint32_t)(2 * c + ch)) ^ row_x) << 4), pack_bf16(f[8 * ch + 0], f[8 * ch + 1]),
+                           pack_bf16(f[8 * ch + 2], f[8 * ch + 3]), pack_bf16(f[8 * ch + 4], f[8 * ch + 5]),
+                           pack_bf16(f[8 * ch + 6], f[8 * ch + 7]));
+                }
+                // bit-mask record [column quarter c][row] = {blocks 0|1, blocks 2|3}, block g's 16 bits in the upper (even g) / lower half
+                if (SAVE && st_saved && mo >= 0 && (st_relu || SIREN) && (2 * pair + slot) < args.n_tiles)
+                  *reinterpret_cast<uint16_t*>(args.save + (2 * pair + slot) * (int64_t)pg.tile_save_bytes + mo + c * (TILE_M * 8) + row * 8 +
+                                               (g >> 1) * 4 + ((g & 1) ? 0 : 2)) = (uint16_t)(gate & 0xFFFFu);
+              }
+            }
+            if (g < st_out) fence_proxy_async();
+          }
+          if (CLS && st_head == 3 && g == 0) {       // class head (models/nerf_cls.py:104): sigmoid of the merged parse.1 o parse.0 logits, 16-column step
+            uint32_t v[16];
+            tmem_ld16(t_addr, v);
+            tmem_ld_wait();
+            if (live) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (k < pg.n_cls) args.out[p * pg.out_c + 4 + k] = 1.f / (1.f + __expf(-(__uint_as_float(v[k]) + __ldg(args.bias + sb + k))));
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          NERFB_TRACE(if (tr) args.trace[tev * 16 + 10] = clock64(); ++tev;)
+          if (lane == 0) mbar_arrive(&sm.epi_done[slot]);    // accumulator drained, activation blocks published: the slot's next step may be issued
+          if (st_head == 1) {       // combine the four blocks' partial dot products
+            sm.part[g][0][row] = head_acc[0];
+            named_bar_sync(1, EPI_THREADS);
+            if (g == 0) {
+              const float sg = sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[0];
+              sm.sigma[slot][row] = sg;
+              if (pg.sigma_only && args.comp.on)      // weights-only coarse pass of test_time (models/rendering.py:230-231) composited in place
+                epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, 0.f, 0.f, 0.f, sg, false);
+              else if (pg.sigma_only && live) args.out[p] = (args.in_mode == NERFB_IN_GRID) ? fmaxf(sg, 0.f) : sg;   // grid: np.maximum(sigma, 0), extract_color_mesh.py:141
+            }
+            named_bar_sync(2, EPI_THREADS);          // head scratch is reused by the other slot's event right after
+          } else if (st_head == 2) { // rgb = sigmoid(W_rgb h_dir + b)  (models/nerf.py:119-120)
+            sm.part[g][0][row] = head_acc[0]; sm.part[g][1][row] = head_acc[1]; sm.part[g][2][row] = head_acc[2];
+            named_bar_sync(1, EPI_THREADS);
+            if (g == 0 && (live || args.comp.on)) {
+              float4 o;
+              o.x = 1.f / (1.f + __expf(-(sm.part[0][0][row] + sm.part[1][0][row] + sm.part[2][0][row] + sm.part[3][0][row] + sm.b_heads[1])));
+              o.y = 1.f / (1.f + __expf(-(sm.part[0][1][row] + sm.part[1][1][row] + sm.part[2][1][row] + sm.part[3][1][row] + sm.b_heads[2])));
+              o.z = 1.f / (1.f + __expf(-(sm.part[0][2][row] + sm.part[1][2][row] + sm.part[2][2][row] + sm.part[3][2][row] + sm.b_heads[3])));
+              o.w = sm.sigma[slot][row];
+              if (!CLS && args.comp.on) epilogue_composite(sm, args.comp, args.in0, args.in1, p, args.P, live, q, lane, o.x, o.y, o.z, o.w, true);
+              else if (!CLS) *reinterpret_cast<float4*>(args.out + p * 4) = o;
+              else { float* dst = args.out + p * pg.out_c; dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
+            }
+            named_bar_sync(2, EPI_THREADS);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- teardown ------------------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// ---- the same schedule on a CTA PAIR (cluster of 2, tcgen05 cta_group::2) -----------------------------------------------------
+// One UMMA is 256 x N x 16: rows 0..127 are the leader CTA's tile, rows 128..255 the peer's, and each CTA holds HALF of the
+// weight slab (N / 2 rows), so an SM streams 16 KB per K-block instead of 32 KB -- the single-CTA pair kernel is bound by
+// that stream (ring bytes / L2 latency).  Four tiles are in flight per cluster (two slots x two CTAs).  Only the leader's
+// elected thread issues MMAs; it waits on barriers in ITS shared memory on which the peer's roles arrive remotely
+// (mapa + mbarrier.arrive.shared::cluster), and its tcgen05.commit multicasts to the same barrier in both CTAs.
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
+}
+// arrive on the barrier at `bar` (a shared::cta address valid in both CTAs) in the LEADER's shared memory
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar, uint32_t rank) {
+  // default semantics (release, CTA scope) as CUTLASS's ClusterBarrier::arrive: an explicit .release.cluster costs a
+  // cluster-scope fence per arrival (measured: the CTA-pair kernel 0.82 ms with it)
+  if (rank == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+  else asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(bar, 0)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait_cluster(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait_cluster(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("nerf_b200: cluster mbarrier timeout (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, bar, parity);
+      const long long t1 = clock64();
+      while (clock64() - t1 < 400000000LL) { }
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void umma_commit_mc2(uint32_t bar) {     // arrive on `bar` in both CTAs once all prior UMMAs have completed
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_slot, uint32_t cols) {    // one full warp in EACH CTA of the pair
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// one 64-wide K-block = four K = 16 UMMAs of 256 x N x 16 on the CTA pair (descriptors as umma_bf16_k64; B = this CTA's N / 2 rows)
+__device__ __forceinline__ void umma2_bf16_k64(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 a0, b0, a1, b1, a2, b2, a3, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\tsetp.eq.b32 t, 0, 0;\n\t"
+      "mov.b64 a0, {%1, 0x40004040};\n\tmov.b64 b0, {%2, 0x40004040};\n\t"
+      "add.u64 a1, a0, 2;\n\tadd.u64 b1, b0, 2;\n\tadd.u64 a2, a0, 4;\n\tadd.u64 b2, b0, 4;\n\tadd.u64 a3, a0, 6;\n\tadd.u64 b3, b0, 6;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a0, b0, %3, p;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a1, b1, %3, t;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a2, b2, %3, t;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a3, b3, %3, t;\n\t}"
+      ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+constexpr int P2_STAGES = 4;
+constexpr int P2_STAGE_BYTES = 128 * 128;       // this CTA's half (N / 2 rows) of a [256 x 64] slab
+
+template <bool SIREN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair2_kernel(const __grid_constant__ TcFwdArgs args) {
+  constexpr bool CLS = false;
+  const uint32_t rank = cluster_ctarank();
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  SmemP& sm = *reinterpret_cast<SmemP*>(smem_raw);
+  if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
+  const TcProgram& pg = args.prog;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t n_quads = (args.n_tiles + 3) >> 2;          // a cluster walks quads of tiles: tile = 4 quad + 2 rank + slot
+  const int64_t cl0 = blockIdx.x >> 1, n_cl = gridDim.x >> 1;
+
+  // ---- one-time setup -----------------------------------------------------------------------------------
+  for (int i = threadIdx.x; i < 256; i += NUM_THREADS) sm.w_sigma[i] = __ldg(args.bias + pg.n_bias + i);
+  if (threadIdx.x == 0) sm.b_heads[0] = __ldg(args.bias + pg.n_bias + 256);
+  constexpr int RGB_IN = SIREN ? 256 : 128;
+  for (int i = threadIdx.x; i < 3 * RGB_IN; i += NUM_THREADS) sm.w_rgb[i] = __ldg(args.bias + pg.n_bias + 257 + i);
+  if (threadIdx.x < 3) sm.b_heads[1 + threadIdx.x] = __ldg(args.bias + pg.n_bias + 257 + 3 * RGB_IN + threadIdx.x);
+  if (threadIdx.x < 2) {                  // decode the MMA op list for slot b (sequential: the step index is needed)
+    const int b = threadIdx.x;
+    int s = 0; bool sx = false;
+    for (int i = 0; i < pg.n_ops; ++i) {
+      uint32_t w = pg.ops[i] & ~(OP_SX | OP_SXDONE | OP_TILE_LAST);
+      uint4 o;
+      if (w & OP_X) {
+        if (s == 0) o.x = ((smem_u32(sm.a[b][0]) >> 4) & 0x3FFFu) | (1u << 16);
+        else { o.x = ((smem_u32(sm.x) >> 4) & 0x3FFFu) | (1u << 16); w |= OP_SX; sx = true; }
+      } else {
+        o.x = ((smem_u32(sm.a[b][(w >> 5) & 3u]) >> 4) & 0x3FFFu) | (1u << 16);
+      }
+      if (w & OP_LAST) {
+        if (sx) w |= OP_SXDONE;
+        if (s == pg.n_steps - 1) w |= OP_TILE_LAST;
+        ++s; sx = false;
+      }
+      o.y = 0u; o.z = w; o.w = 0u;
+      sm.ops[b][i] = o;
+    }
+  }
+  if (threadIdx.x == 32) {                // per-step tables for the producer / epilogue, X uses for the encoder
+    uint32_t off = 0; int nu = 0; bool dir_now = false;
+    for (int s = 0; s < pg.n_steps; ++s) {
+      const TcStep& st = pg.s[s];
+      sm.step_word[s] = pg.step_word[s]; sm.step_bias[s] = (uint32_t)st.bias_off;
+      sm.step_woff[s] = off; sm.step_nkb[s] = (uint32_t)st.n_kb | ((uint32_t)st.N << 8); sm.step_mask[s] = st.mask_off;
+      off += (uint32_t)st.n_kb * (uint32_t)st.N * 128u;
+      bool uses_x = false;
+      for (int kb = 0; kb < st.n_kb; ++kb) uses_x |= (st.src[kb] == SRC_X);
+      if (uses_x && nu < 4) { sm.use_step[nu] = s; sm.use_kind[nu] = dir_now ? 1 : 0; ++nu; }
+      if (st.x_done) dir_now = true;      // the xyz encoding's last reader: later X contents are the direction encoding
+    }
+    sm.n_uses = nu;
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P2_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); mbar_init(&sm.w_peer[i], 1); }
+    for (int i = 0; i < 2; ++i) {                         // leader-side barriers collect the arrivals of BOTH CTAs
+      mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.epi_done[i], 2 * N_EPI_WARPS);
+      mbar_init(&sm.enc_ready[i], 8); mbar_init(&sm.a0_free[i], 1);
+    }
+    mbar_init(&sm.x_ready, 8); mbar_init(&sm.x_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == WARP_MMA) tmem_alloc2(&sm.tmem_base, 512);
+  tc_fence_before();
+  cluster_sync_all();                     // barriers of both CTAs initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == WARP_PRODUCER) {
+    // ===== weight producer: slabs in event order (step s of slot 0, step s of slot 1, step s + 1 ...) =====
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t quad = cl0; quad < n_quads; quad += n_cl) {
+        for (int s = 0; s < pg.n_steps; ++s) {
+          const uint32_t nk = sm.step_nkb[s];
+          const uint32_t bytes = (nk >> 8) * 64u;           // rows [rank N/2, (rank + 1) N/2) of every slab: a contiguous half of the swizzled image
+          const int n_kb = (int)(nk & 255u);
+          for (int slot = 0; slot < 2; ++slot) {
+            const uint8_t* src = args.wblob + sm.step_woff[s] + rank * bytes;
+            for (int kb = 0; kb < n_kb; ++kb) {
+              mbar_wait_relaxed(&sm.w_empty[stage], phase ^ 1);
+              mbar_expect_tx(&sm.w_full[stage], bytes);
+              bulk_g2s(sm.ring2[stage], src, bytes, &sm.w_full[stage]);
+              src += 2 * bytes;
+              if (++stage == P2_STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == WARP_STORE) {
+    // ===== peer CTA only: forward "my half of the slab has landed" to the leader's w_peer barrier; lane k owns ring stage k
+    // so the remote arrivals (a cross-SM round trip each) of consecutive slabs overlap =====
+    if (lane < P2_STAGES && rank == 1) {
+      int per_quad = 0;
+      for (int s = 0; s < pg.n_steps; ++s) per_quad += 2 * (int)(sm.step_nkb[s] & 255u);
+      const int64_t my_quads = cl0 < n_quads ? (n_quads - cl0 + n_cl - 1) / n_cl : 0;
+      const int64_t total = my_quads * per_quad;
+      const uint32_t remote = mapa_u32(smem_u32(&sm.w_peer[lane]), 0);
+      uint32_t phase = 0;
+      for (int64_t j = lane; j < total; j += P2_STAGES) {
+        mbar_wait(&sm.w_full[lane], phase); phase ^= 1;
+        asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+      }
+    }
+  } else if (warp == WARP_MMA) {
+    // ===== MMA issuer (single thread of the LEADER CTA) =====
+    if (lane == 0 && rank == 0) {
+      uint32_t stage = 0, phase = 0, ed_par = 0, en_par = 0, xr_par = 0, it = 0;
+      const int n_ops = pg.n_ops;
+      const uint32_t ring_lo0 = ((smem_u32(sm.ring2[0]) >> 4) & 0x3FFFu) | (1u << 16);
+      const uint32_t wf0 = smem_u32(&sm.w_full[0]), we0 = smem_u32(&sm.w_empty[0]), wp0 = smem_u32(&sm.w_peer[0]);
+      const uint32_t af0 = smem_u32(&sm.acc_full[0]), ed0 = smem_u32(&sm.epi_done[0]), en0 = smem_u32(&sm.enc_ready[0]);
+      const uint32_t a0f0 = smem_u32(&sm.a0_free[0]), xr = smem_u32(&sm.x_ready), xf = smem_u32(&sm.x_free);
+      const uint32_t idesc256 = umma_idesc_bf16(2 * TILE_M, 256), idesc128 = umma_idesc_bf16(2 * TILE_M, 128), idesc16 = umma_idesc_bf16(2 * TILE_M, 16);
+      for (int64_t quad = cl0; quad < n_quads; quad += n_cl, ++it) {
+        int i0 = 0;                           // first op of the current step
+        while (i0 < n_ops) {
+          int i1 = i0;
+          for (uint32_t slot = 0; slot < 2; ++slot) {
+            const uint32_t ops_base = smem_u32(sm.ops[slot]);
+            const uint32_t d_tmem = tmem + slot * 256u;
+            int i = i0;
+            for (;;) {
+              const uint4 cur = lds128u(ops_base + 16u * (uint32_t)i);
+              if (cur.z & OP_FIRST) {         // the slot's previous event has been drained (accumulator free, activations published)
+                if (!(it == 0 && i == 0)) { mbar_wait_cluster(ed0 + 8u * slot, (ed_par >> slot) & 1u); ed_par ^= 1u << slot; }
+              }
+              if (cur.z & OP_X) {
+                if (cur.z & OP_SX) { mbar_wait_cluster(xr, xr_par); xr_par ^= 1u; }
+                else { mbar_wait_cluster(en0 + 8u * slot, (en_par >> slot) & 1u); en_par ^= 1u << slot; }
+              }
+              const uint32_t idesc = (cur.z & OP_N16) ? idesc16 : (cur.z & OP_N128) ? idesc128 : idesc256;
+              mbar_wait_addr(wf0 + 8u * stage, phase);        // my half of the slab ...
+              mbar_wait_cluster(wp0 + 8u * stage, phase);     // ... and the peer's
+              tc_fence_after();
+              umma2_bf16_k64(d_tmem, cur.x, ring_lo0 + stage * (P2_STAGE_BYTES >> 4), idesc, (cur.z & OP_FIRST) ? 0u : 1u);
+              umma_commit_mc2(we0 + 8u * stage);              // slab halves free in both CTAs once these MMAs have read them
+              if (++stage == P2_STAGES) { stage = 0; phase ^= 1; }
+              ++i;
+              if (cur.z & OP_LAST) {
+                umma_commit_mc2(af0 + 8u * slot);
+                if (cur.z & OP_SXDONE) umma_commit_mc2(xf);
+                if (cur.z & OP_TILE_LAST) umma_commit_mc2(a0f0 + 8u * slot);
                 break;
               }
             }
@@ -888,7 +1393,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
     uint32_t a0_par = 0, xf_par = 0, it = 0;
     bool first_shared = true;
     const int n_uses = sm.n_uses;
-    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x, ++it) {
+    for (int64_t quad = cl0; quad < n_quads; quad += n_cl, ++it) {
+      const int64_t pair = 2 * quad + rank;
       float pos[2][3], dir[2][3];
       const float* emb[2] = {nullptr, nullptr};
 #pragma unroll
@@ -946,7 +1452,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
           store_pk64(base, row, pk);
           fence_proxy_async();
           __syncwarp();
-          if (lane == 0) mbar_arrive(us == 0 ? &sm.enc_ready[slot] : &sm.x_ready);
+          if (lane == 0) mbar_arrive_leader(smem_u32(us == 0 ? &sm.enc_ready[slot] : &sm.x_ready), rank);
         }
       }
     }
@@ -959,7 +1465,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
     const int row = q * 32 + lane;
     const uint32_t row_off = (uint32_t)row * 128u, row_x = (uint32_t)row & 7u;
     uint32_t acc_par = 0;
-    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+    for (int64_t quad = cl0; quad < n_quads; quad += n_cl) {
+      const int64_t pair = 2 * quad + rank;
       for (int s = 0; s < pg.n_steps; ++s) {
         const uint32_t sw = lds32(smem_u32(sm.step_word) + 4u * (uint32_t)s);
         const uint32_t sb = lds32(smem_u32(sm.step_bias) + 4u * (uint32_t)s);
@@ -1050,7 +1557,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&sm.epi_done[slot]);    // accumulator drained, activation blocks published: the slot's next step may be issued
+          if (lane == 0) mbar_arrive_leader(smem_u32(&sm.epi_done[slot]), rank);    // accumulator drained, activation blocks published: the slot's next step may be issued
           if (st_head == 1) {       // combine the four blocks' partial dot products
             sm.part[g][0][row] = head_acc[0];
             named_bar_sync(1, EPI_THREADS);
@@ -1084,9 +1591,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
 
   // ---- teardown ------------------------------------------------------------------------------------------
   tc_fence_before();
-  __syncthreads();
-  if (warp == WARP_MMA) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+  cluster_sync_all();                     // no CTA leaves while its partner may still arrive on its barriers or read its shared memory
+  if (warp == WARP_MMA) { tc_fence_after(); tmem_dealloc2(tmem, 512); }
 }
+
 
 // ---- weight packing: fp32 nn.Linear weights -> bf16 slabs in the swizzled shared-memory image, schedule order ----
 struct PackSlab { int64_t w_off; int ld; int col0; int ncols; int N; int64_t dst_off; int hilo; int aux; int film; };   // aux: read the merged class-head matrix, not params   // W[n*ld + col0 + kk], kk < ncols
@@ -1303,11 +1811,16 @@ static TcPlan tc_plan(const nerfb_mlp_desc& d, int64_t P, bool sigma_only, bool 
 }
 
 #ifndef NERFB_FWD_PAIR_DEFAULT
-#define NERFB_FWD_PAIR_DEFAULT 0
+#define NERFB_FWD_PAIR_DEFAULT 1
 #endif
-static bool fwd_pair_enabled() {          // NERFB_FWD_PAIR=0/1 overrides the build default (read per call: tests flip it)
+// NERFB_FWD_PAIR (read per call): 0 = single-tile kernels everywhere; 1 (default) = tile-pair kernel for inference (measured on
+// the B200: 0.71 -> 0.62-0.66 ms at 4096 x 128, NeRF 800x800 render 4.18 -> 4.51 M rays/s); 2 = inference on a CTA pair
+// (cta_group::2; correct, but the per-layer cross-SM hand-offs make it slower: 0.70-0.75 ms); 3 = tile pair for the training
+// forward as well (correct -- the whole GPU suite passes with it -- but 1.07 ms against 1.01 ms: that kernel is bound by
+// the 2.8 GB of activation stores, not by the epilogue / MMA serialisation the pair schedule removes).
+static int fwd_pair_mode() {
   const char* e = getenv("NERFB_FWD_PAIR");
-  return e && *e ? atoi(e) != 0 : NERFB_FWD_PAIR_DEFAULT != 0;
+  return e && *e ? atoi(e) : NERFB_FWD_PAIR_DEFAULT;
 }
 static long long* g_trace = nullptr;
 extern "C" void nerfb_debug_trace(long long* device_buf) { g_trace = device_buf; }   // diagnostics only (40 x 16 slots)
@@ -1336,7 +1849,10 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   if (siren && !film) return NERFB_E_BADARG;
   if (in_mode == NERFB_IN_GRID && (save || siren || d.in_xyz > 0)) return NERFB_E_UNSUPPORTED;
   const int64_t P = (in_mode == NERFB_IN_RAYS) ? n_rows * n_samples : n_rows;
-  const bool pair = !save && fwd_pair_enabled();        // inference: two tiles in flight per SM (mlp_tc_fwd_pair_kernel)
+  int pair_mode = fwd_pair_mode();                      // two tiles in flight per SM (mlp_tc_fwd_pair_kernel / _pair2_kernel)
+  if (save) pair_mode = pair_mode == 3 ? 1 : 0;         // training forward: single-tile kernel unless asked for
+  else if (pair_mode == 3) pair_mode = 1;
+  const bool pair = pair_mode != 0;
   const TcPlan pl = tc_plan(d, P, sigma_only != 0, save != 0, pair);
   if (ws_bytes < pl.total) return NERFB_E_WORKSPACE;
   if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return NERFB_E_BADARG;
@@ -1367,9 +1883,14 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
   NERFB_CUDA(cudaGetDevice(&dev));
   static bool attr_set[64] = {};          // cudaFuncSetAttribute is per device
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<true, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<true, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair_kernel<false, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair2_kernel<false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_pair2_kernel<true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<true, false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1378,12 +1899,23 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     NERFB_CUDA(cudaFuncSetAttribute((mlp_tc_fwd_kernel<false, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
+  if (pair_mode == 2 && pl.prog.n_cls == 0 && a.n_tiles >= 4) {
+    const int64_t n_quads = (a.n_tiles + 3) >> 2;
+    const int n_cl = (int)(n_quads < NERFB_SM_COUNT / 2 ? n_quads : NERFB_SM_COUNT / 2);
+    if (siren) NERFB_LAUNCH((mlp_tc_fwd_pair2_kernel<true>), 2 * n_cl, NUM_THREADS, smem_p, stream, a);
+    else NERFB_LAUNCH((mlp_tc_fwd_pair2_kernel<false>), 2 * n_cl, NUM_THREADS, smem_p, stream, a);
+    return NERFB_OK;
+  }
   if (pair) {
     const int64_t n_pairs = (a.n_tiles + 1) >> 1;
     const int pgrid = (int)(n_pairs < NERFB_SM_COUNT ? n_pairs : NERFB_SM_COUNT);
-    if (siren) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<true, false>), pgrid, NUM_THREADS, smem_p, stream, a);
-    else if (pl.prog.n_cls > 0) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, true>), pgrid, NUM_THREADS, smem_p, stream, a);
-    else NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, false>), pgrid, NUM_THREADS, smem_p, stream, a);
+    const bool svp = a.save != nullptr;
+    if (siren && svp) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<true, false, true>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else if (siren) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<true, false, false>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else if (pl.prog.n_cls > 0 && svp) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, true, true>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else if (pl.prog.n_cls > 0) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, true, false>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else if (svp) NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, false, true>), pgrid, NUM_THREADS, smem_p, stream, a);
+    else NERFB_LAUNCH((mlp_tc_fwd_pair_kernel<false, false, false>), pgrid, NUM_THREADS, smem_p, stream, a);
     return NERFB_OK;
   }
   const int grid = (int)(a.n_tiles < NERFB_SM_COUNT ? a.n_tiles : NERFB_SM_COUNT);

@@ -12,11 +12,12 @@ from nerf_siren_b200 import _field, _lib, ops, synth  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+modes = [int(v) for v in (sys.argv[3] if len(sys.argv) > 3 else "1,2").split(",")]
 dev = torch.device("cuda:0")
 
 
 def run(kind, S, sigma_only, pair, n_rays):
-    os.environ["NERFB_FWD_PAIR"] = "1" if pair else "0"
+    os.environ["NERFB_FWD_PAIR"] = str(int(pair))
     torch.manual_seed(0)
     m = {"nerf": nb.NeRF, "siren": nb.SirenField, "cls": lambda: nb.NeRF_3D(CLS=6)}[kind]().to(dev)
     siren = kind == "siren"
@@ -43,11 +44,12 @@ def run(kind, S, sigma_only, pair, n_rays):
 for kind, S, so, nr in (("nerf", 128, False, n), ("nerf", 64, False, n), ("nerf", 64, True, n), ("nerf", 128, False, 1037), ("nerf", 64, False, 5),
                         ("siren", 128, False, n), ("siren", 64, True, n), ("cls", 128, False, n)):
     try:
-        a, ta = run(kind, S, so, False, nr)
-        b, tb = run(kind, S, so, True, nr)
-        d = (a - b).abs()
-        print(json.dumps({"kind": kind, "rays": nr, "S": S, "sigma_only": so, "single_ms": round(ta, 4), "pair_ms": round(tb, 4),
-                          "speedup": round(ta / tb, 3), "max_abs_diff": float(d.max()), "mean_abs_diff": float(d.mean()),
-                          "out_absmax": float(a.abs().max()), "finite": bool(torch.isfinite(b).all())}), flush=True)
+        a, ta = run(kind, S, so, 0, nr)
+        for mode in modes:
+            b, tb = run(kind, S, so, mode, nr)
+            d = (a - b).abs()
+            print(json.dumps({"kind": kind, "rays": nr, "S": S, "sigma_only": so, "mode": mode, "single_ms": round(ta, 4), "pair_ms": round(tb, 4),
+                              "speedup": round(ta / tb, 3), "max_abs_diff": float(d.max()), "mean_abs_diff": float(d.mean()),
+                              "out_absmax": float(a.abs().max()), "finite": bool(torch.isfinite(b).all())}), flush=True)
     except Exception as e:  # noqa: BLE001
         print(json.dumps({"kind": kind, "S": S, "sigma_only": so, "error": str(e)[:300]}), flush=True)

@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256, 1) k(const uint8_t* blob, int blob_bytes,
   if (csz > 1) cg::this_cluster().sync(); else __syncthreads();
   const int n_slabs = blob_bytes / slab;
   const long long t0 = clock64();
-  if (n_prod > 1 && warp >= 2 && warp < 2 + n_prod && lane == 0) {     // several producer warps: warp 2 + p issues slabs g = p (mod n_prod)
+  if (n_prod > 1 && n_prod < 100 && warp >= 2 && warp < 2 + n_prod && lane == 0) {     // several producer warps: warp 2 + p issues slabs g = p (mod n_prod)
     const int p0 = warp - 2;
     long long g = 0;
     for (int p = 0; p < passes; ++p)
@@ -55,6 +55,20 @@ __global__ void __launch_bounds__(256, 1) k(const uint8_t* blob, int blob_bytes,
         mbar_wait(&empty[st], ph ^ 1);
         mbar_expect_tx(&full[st], slab);
         bulk_g2s(ring + (size_t)st * slab, blob + (size_t)s * slab, slab, &full[st]);
+      }
+  } else if (n_prod >= 100 && warp == 0) {      // one slab = several smaller bulk copies on the same barrier: one lane sequentially (1xx) or one lane each (2xx)
+    const bool par = n_prod >= 200;
+    const int ns = par ? n_prod - 200 : n_prod - 100;
+    const uint32_t piece = slab / ns;
+    int st = 0; uint32_t ph = 0;
+    for (int p = 0; p < passes; ++p)
+      for (int s = 0; s < n_slabs; ++s) {
+        if (lane == 0) { mbar_wait(&empty[st], ph ^ 1); mbar_expect_tx(&full[st], slab); }
+        __syncwarp();
+        if (par) { if (lane < ns) bulk_g2s(ring + (size_t)st * slab + lane * piece, blob + (size_t)s * slab + lane * piece, piece, &full[st]); }
+        else if (lane == 0) for (int k = 0; k < ns; ++k) bulk_g2s(ring + (size_t)st * slab + k * piece, blob + (size_t)s * slab + k * piece, piece, &full[st]);
+        __syncwarp();
+        if (++st == stages) { st = 0; ph ^= 1; }
       }
   } else if (n_prod <= 1 && warp == 0 && lane == 0) {            // producer
     int st = 0; uint32_t ph = 0;

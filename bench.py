@@ -70,6 +70,10 @@ def cpu_model():
 # ------------------------------------------------------------------------------------------------------
 # clocks sampler (nvidia-smi during the timed region)
 # ------------------------------------------------------------------------------------------------------
+# the inference forward is the tile-pair kernel unless NERFB_FWD_PAIR=0 (csrc/mlp_tc.cu: fwd_pair_mode)
+INFER_KERNEL = {"0": "mlp_tc_fwd_kernel", "2": "mlp_tc_fwd_pair2_kernel (cta_group::2)"}.get(os.environ.get("NERFB_FWD_PAIR", "1"),
+                                                                                            "mlp_tc_fwd_pair_kernel")
+
 class Clocks:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -479,7 +483,7 @@ class TrainWorkload:
             ws = ops.mlp_workspace(desc, prec, n * Sf, False, False, dev)
             ms = time_kernel(lambda: ops.mlp_fwd(desc, prec, _lib.IN_RAYS, flat, None, rays, zf, n, Sf, False, False, ws), 10)
             fl = n * Sf * 2 * macs
-            out.append({"kernel": "mlp_tc_fwd_kernel" if prec == _lib.PREC_BF16 else "sgemm_strided_kernel (fp32 fwd chain)",
+            out.append({"kernel": INFER_KERNEL if prec == _lib.PREC_BF16 else "sgemm_strided_kernel (fp32 fwd chain)",
                         "bound": "tensor", "achieved": fl / ms / 1e9, "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "ms": ms,
                         "flops": fl})
             tprec = _lib.PREC_BF16 if ops.mlp_supported(desc, _lib.PREC_BF16, True) else _lib.PREC_FP32
@@ -570,7 +574,7 @@ class RenderWorkload:
             ws = ops.mlp_workspace(desc, prec, n * Sf, False, False, dev)
             ms = time_kernel(lambda: ops.mlp_fwd(desc, prec, _lib.IN_RAYS, flat, film, rays, zf, n, Sf, False, False, ws), 10)
             fl = n * Sf * 2 * self.mf
-            out.append({"kernel": ("mlp_tc_fwd_kernel<SIREN>" if self.siren else "mlp_tc_fwd_kernel") if prec == _lib.PREC_BF16
+            out.append({"kernel": (INFER_KERNEL + "<SIREN>" if self.siren else INFER_KERNEL) if prec == _lib.PREC_BF16
                         else "sgemm_strided_kernel (fp32 fwd chain)", "bound": "tensor", "achieved": fl / ms / 1e9,
                         "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "ms": ms, "flops": fl, "rows": n * Sf})
             w = torch.rand(n, self.S, device=dev)

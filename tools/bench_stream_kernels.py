@@ -57,6 +57,7 @@ cases = [
     ("composite_fwd_kernel (128 samples)", lambda: ops.composite_fwd(rawf, zf, rays, noisef, 1.0, True), n * Sf * 28 + n * 32),
     ("composite_bwd_kernel (128 samples)", lambda: ops.composite_bwd(rawf, zf, rays, noisef, 1.0, True, d_rgb=d_rgb), n * Sf * 40 + n * 24),
     ("resample_kernel", lambda: ops.resample(z, w, Si, False, u), n * (8 * S + 4 * Si + 4 * Sf)),
+    ("resample_kernel (det: render path)", lambda: ops.resample(z, w, Si, True, None), n * (8 * S + 4 * Sf)),
     ("generate_rays_kernel", lambda: ops.generate_rays(torch.eye(3, 4), 800, 800, 1111.1), 640000 * 32),
 ]
 for name, fn, by in cases:

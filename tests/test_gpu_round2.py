@@ -432,3 +432,68 @@ def test_render_fused_entry_equals_separate_kernels(S, Si, test_time, noise_std,
         out = n_mod.render_rays([mc, mf], [n_mod.Embedding(3, 10), n_mod.Embedding(3, 4)], rays, S, False, 0, 0, Si, 32768, True,
                                 test_time=test_time)
     assert "opacity_coarse" in out and (("rgb_fine" in out) == (Si > 0))
+
+
+# ------------------------------------------------------------------------------------------------------
+# (viii) the forward kernel variants (NERFB_FWD_PAIR = 0 single tile | 1 tile pair | 2 CTA pair | 3 tile pair incl. training)
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["nerf", "siren", "cls"])
+def test_forward_kernel_variants_agree(kind, monkeypatch):
+    """Same weights, same 1000 + 37 rays x 128 samples through every forward kernel of the tcgen05 arm.  The variants run the
+    same MMAs on the same operands; they differ in the K-block order of the skip layer and in how the head dot products
+    associate, so outputs agree to fp32 summation noise amplified through the bf16 re-rounding of activations: measured
+    8e-5 max-abs / 5e-8 mean-abs (NeRF), 1.2e-7 (SIREN); bounds 5e-4 / 1e-6.  Training: the record written by the
+    tile-pair forward (mode 3: activations, encodings, gate bit-masks) must drive the SAME backward kernels to the same
+    parameter gradients as the single-tile forward's record -- up to the ReLU gates that flip where the two forwards'
+    pre-activations (8e-5 apart) straddle zero, the effect test_bf16_gradients_smooth_field_against_fp32_reference
+    quantifies: measured relative L2 1.4e-2 at layer 1 (deepest in the chain), bound 3e-2 per tensor; a wrong mask
+    layout or a missing block would show as O(1)."""
+    n_mod = nb()
+    n_mod.set_precision("bf16")
+    from nerf_siren_b200 import _field, _lib, ops, synth
+    torch.manual_seed(0)
+    m = {"nerf": n_mod.NeRF, "siren": n_mod.SirenField, "cls": lambda: n_mod.NeRF_3D(CLS=6)}[kind]().to(DEV)
+    siren = kind == "siren"
+    desc = m._desc(False, 0, 0, True) if siren else m._desc(False, 10, 4, True)
+    film = m._film() if siren else None
+    n, S = 1037, 128
+    rays = synth.blender_rays(n, seed=1).to(DEV)
+    if siren:
+        rays[:, :6] *= 0.05
+    z = torch.sort(torch.rand(n, S, device=DEV, generator=torch.Generator(device=DEV).manual_seed(3)) * 4 + 2, -1)[0].contiguous()
+    flat = _field.flat_params(m).detach()
+
+    def run(mode, save):
+        monkeypatch.setenv("NERFB_FWD_PAIR", str(mode))
+        with torch.no_grad():
+            ws = ops.mlp_workspace(desc, _lib.PREC_BF16, n * S, False, save, DEV)
+            out = ops.mlp_fwd(desc, _lib.PREC_BF16, _lib.IN_RAYS, flat, film, rays, z, n, S, False, save, ws)
+            grad = None
+            if save:
+                d_raw = torch.randn(out.shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(5)) * 1e-3
+                grad, _ = ops.mlp_bwd(desc, _lib.PREC_BF16, _lib.IN_RAYS, flat, film, rays, z, n, S, out, d_raw, ws)
+            torch.cuda.synchronize()
+        return out.clone(), None if grad is None else grad.clone()
+
+    base, _ = run(0, False)
+    assert torch.isfinite(base).all()
+    for mode in (1, 2):
+        out, _ = run(mode, False)
+        d = (out - base).abs()
+        assert d.max().item() <= 5e-4 and d.mean().item() <= 1e-6, (mode, d.max().item(), d.mean().item())
+    if not n_mod.ops.mlp_supported(desc, _lib.PREC_BF16, True):
+        return
+    out0, g0 = run(0, True)
+    out3, g3 = run(3, True)
+    d = (out3 - out0).abs()
+    assert d.max().item() <= 5e-4 and d.mean().item() <= 1e-6, (d.max().item(), d.mean().item())
+    off = 0
+    assert g0.numel() == sum(p.numel() for p in m.parameters())
+    for k, p in m.named_parameters():
+        a, b = g0[off:off + p.numel()].double(), g3[off:off + p.numel()].double()
+        off += p.numel()
+        if float(a.norm()) == 0.0:               # tensors the backward does not produce (FiLM vectors)
+            assert float(b.norm()) == 0.0, k
+            continue
+        rel = ((a - b).norm() / a.norm()).item()
+        assert rel <= 3e-2, (k, rel)

@@ -73,6 +73,12 @@ def cpu_model():
 # the inference forward is the tile-pair kernel unless NERFB_FWD_PAIR=0 (csrc/mlp_tc.cu: fwd_pair_mode)
 INFER_KERNEL = {"0": "mlp_tc_fwd_kernel", "2": "mlp_tc_fwd_pair2_kernel (cta_group::2)"}.get(os.environ.get("NERFB_FWD_PAIR", "1"),
                                                                                             "mlp_tc_fwd_pair_kernel")
+# the backward of the plain NeRF is the fused launch unless NERFB_BWD_FUSED=0 (csrc/mlp_tc_bwd.cu: fused_plan); NeRF_3D / SIREN
+# keep dgrad -> wgrad unless NERFB_BWD_FUSED=1
+def bwd_kernel_name(cls):
+    mode = os.environ.get("NERFB_BWD_FUSED", "2")
+    fused = mode == "1" or (mode == "2" and not cls)
+    return "mlp_tc_bwd_fused_kernel (dgrad chain + wgrad CTAs, one launch)" if fused else "mlp_tc_bwd (dgrad chain + wgrad)"
 
 class Clocks:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -496,7 +502,7 @@ class TrainWorkload:
             d_raw = torch.randn_like(rawf) * 1e-3
             ms = time_kernel(lambda: ops.mlp_bwd(desc, tprec, _lib.IN_RAYS, flat, None, rays, zf, n, Sf, rawf, d_raw, ws), 5, 2)
             fl = n * Sf * ((FLOP_CLS_TRAIN_PER_SAMPLE if self.cls else FLOP_TRAIN_PER_SAMPLE) - 2 * macs)
-            out.append({"kernel": "mlp_tc_bwd (dgrad chain + wgrad)" if tprec == _lib.PREC_BF16 else
+            out.append({"kernel": bwd_kernel_name(self.cls) if tprec == _lib.PREC_BF16 else
                         "sgemm_strided_kernel (fp32 bwd chain)", "bound": "tensor", "achieved": fl / ms / 1e9,
                         "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "ms": ms, "flops": fl})
         return [finish_roofline(r, peaks) for r in out]

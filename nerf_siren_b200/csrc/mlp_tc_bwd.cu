@@ -15,6 +15,12 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 
+// -DNERFB_TRACE_BUILD compiles the clock64 timeline probes of the fused backward in (tools/trace_fused.py); the product build has none
+#ifdef NERFB_TRACE_BUILD
+#define NERFB_TRACE(...) __VA_ARGS__
+#else
+#define NERFB_TRACE(...)
+#endif
 using namespace tc;
 
 TcFwdLayout tc_fwd_layout(const nerfb_mlp_desc& d, int64_t P);     // mlp_tc.cu
@@ -84,6 +90,7 @@ struct DgradArgs {
   const float* out; const float* d_out;
   const uint8_t* fwd_rec; uint8_t* bwd_rec;
   int64_t P; int64_t n_tiles;
+  long long* trace_chain;          // diagnostics (NERFB_TRACE_BUILD): store-lane timeline of chain CTA 0
 };
 
 // Fused backward (mlp_tc_bwd_fused_kernel): the dgrad chain CTAs hand every dZ packet (one step's 2 / 4 blocks) to the
@@ -95,7 +102,9 @@ constexpr int F_FLAG_STRIDE = 32;          // uint32 words between per-CTA count
 constexpr int F_MAX_Q = 32;
 struct FusedCtl {
   int Nc;                          // chain CTAs = blocks [0, Nc); wgrad CTAs = blocks [Nc, Nc + n_units * G)
-  int G;                           // wgrad CTAs per unit: CTA j of a unit owns tiles t = j (mod G)
+  int G;                           // nominal wgrad CTAs per unit (NERFB_FUSED_G); the budget n_units * G is split by measured cost:
+  int unit_G[16];                  // wgrad CTAs of unit u: CTA j of the unit owns tiles t = j (mod unit_G[u])
+  int unit_w0[16];                 // first wgrad CTA (relative to Nc) of unit u
   int q;                           // packet ring slots per chain CTA
   int PK;                          // packets per tile: prologue + n_steps
   int m_head;                      // items that read the head block
@@ -119,6 +128,7 @@ struct __align__(1024) SmemD {
   uint64_t g_free[4];                    // the store lane has read block j out to HBM
   uint64_t acc_full[2];
   uint32_t tmem_base;
+  uint32_t slot_ok;                 // fused launch: ring packets whose slot the scout lane has seen free
 };
 
 }  // namespace
@@ -186,6 +196,7 @@ __device__ __forceinline__ void dgrad_role(const DgradArgs& args, const FusedCtl
     for (int i = 0; i < N_STAGES; ++i) { mbar_init(&sm.w_full[i], 1); mbar_init(&sm.w_empty[i], 1); }
     for (int i = 0; i < 4; ++i) { mbar_init(&sm.a_ready[i], D_EPI_WARPS); mbar_init(&sm.g_free[i], 1); }
     mbar_init(&sm.acc_full[0], 1); mbar_init(&sm.acc_full[1], 1);
+    sm.slot_ok = 0u;
     fence_barrier_init();
   }
   if (warp == D_WARP_MMA) tmem_alloc(&sm.tmem_base, 512);
@@ -208,6 +219,21 @@ __device__ __forceinline__ void dgrad_role(const DgradArgs& args, const FusedCtl
             if (++stage == N_STAGES) { stage = 0; phase ^= 1; }
           }
       }
+    } else if (lane == 1 && FUSED) {       // ===== slot scout (fused): polls the consumers' counters AHEAD of the store lane =====
+      // the L2 round trip + acquire of "slot n % q has been read out" costs the store lane ~1400 clk per packet on its critical
+      // path (tools/trace_fused.py); here it overlaps the block stores and the store lane only polls shared memory
+      uint32_t expect[F_MAX_Q];
+      for (int i = 0; i < F_MAX_Q; ++i) expect[i] = 0;
+      const uint32_t* const cons = fc.consumed + (size_t)cta * fc.q;
+      const uint32_t ok = smem_u32(&sm.slot_ok);
+      uint32_t slot = 0;
+      for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta)
+        for (int s = -1; s < pg.n_steps; ++s) {
+          gflag_wait_ge(cons + slot, expect[slot]);
+          expect[slot] += (uint32_t)fc.pk_need[s + 1];
+          cnt_publish(ok);
+          if (++slot == (uint32_t)fc.q) slot = 0;
+        }
     }
   } else if (warp == D_WARP_MMA) {
     if (lane == 0) {                       // ===== MMA issuer =====
@@ -269,10 +295,10 @@ __device__ __forceinline__ void dgrad_role(const DgradArgs& args, const FusedCtl
       // a packet is PUBLISHED (produced[cta] = n + 1, release) once its stores have completed, which is checked lazily --
       // F_LAG bulk groups later -- so the lane never sits on the ~1 us store latency.  q >= 3 keeps the wait chain
       // well-founded: the packet whose slot is awaited was published at least one packet ago.
-      constexpr uint32_t F_LAG = 3;
+      constexpr uint32_t F_LAG = 7;            // 3 -> 7: with 3 the lane waited ~2300 clk per packet for the store issued 3 blocks earlier
       uint32_t a_par = 0, pend = 0;
       uint32_t n = 0, grp = 0, pub = 0;          // packets fully issued, bulk groups committed, packets published
-      uint32_t last_grp[4] = {0, 0, 0, 0};       // index of the last bulk group of packet (n & 3)
+      uint32_t last_grp[8] = {0, 0, 0, 0, 0, 0, 0, 0};       // index of the last bulk group of packet (n & 7)
       uint32_t expect[F_MAX_Q];
       for (int i = 0; i < F_MAX_Q; ++i) expect[i] = 0;
       uint32_t* const prod = fc.produced + (size_t)cta * F_FLAG_STRIDE;
@@ -282,22 +308,33 @@ __device__ __forceinline__ void dgrad_role(const DgradArgs& args, const FusedCtl
       for (int64_t tile = cta; tile < args.n_tiles; tile += n_cta) {
         for (int s = -1; s < pg.n_steps; ++s) {
           const int nb = s < 0 ? pg.n_pro : 4;
-          gflag_wait_ge(cons + slot, expect[slot]);
-          expect[slot] += (uint32_t)fc.pk_need[s + 1];
+          NERFB_TRACE(long long* trc = args.trace_chain; const bool tr = trc && cta == 0 && n < 150; long long tpub = 0, twa = 0; if (tr) trc[n * 8 + 0] = clock64();)
+          if ((int32_t)(cnt_load(smem_u32(&sm.slot_ok)) - (n + 1)) < 0) {
+            // About to block on a ring slot.  The lagged publication below would leave the packets already stored UNPUBLISHED
+            // for the whole stall, and the wgrad CTA waiting for one of them is the very one whose progress frees slots
+            // elsewhere: flush and publish first.
+            if (pub < n) { bulk_wait_all0(); fence_proxy_async_all(); pub = n; st_release_gpu(prod, pub); }
+            cnt_wait(smem_u32(&sm.slot_ok), n + 1);
+          }
+          NERFB_TRACE(if (tr) trc[n * 8 + 1] = clock64(); const uint32_t n_here = n;)
           uint8_t* dst = ring + (size_t)slot * F_PKT_BYTES;
           for (int j = 0; j < nb; ++j) {
+            NERFB_TRACE(const long long ta0 = clock64();)
             mbar_wait_relaxed(&sm.a_ready[j], (a_par >> j) & 1u); a_par ^= 1u << j;
+            NERFB_TRACE(twa += clock64() - ta0;)
             bulk_s2g(dst + j * BLK_BYTES, sm.g[j], BLK_BYTES);
             bulk_commit(); ++grp; bulk_wait_read1();
             if (pend) mbar_arrive_addr(pend);
             pend = smem_u32(&sm.g_free[j]);
-            if (j == nb - 1) { last_grp[n & 3u] = grp - 1; ++n; }
-            if (pub < n && grp - 1 - last_grp[pub & 3u] >= F_LAG) {      // the oldest unpublished packet's stores are >= F_LAG groups back
-              bulk_wait_all3();
-              fence_proxy_async_all();
-              ++pub; st_release_gpu(prod, pub);
+            if (j == nb - 1) { last_grp[n & 7u] = grp - 1; ++n; }
+            if (pub < n && grp - 1 - last_grp[pub & 7u] >= F_LAG) {      // the oldest unpublished packet's stores are >= F_LAG groups back
+              NERFB_TRACE(const long long tp0 = clock64();)
+              bulk_wait_all7();
+              ++pub; st_release_gpu(prod, pub);        // the stores are complete (wait_group): the flag's release orders them; no proxy fence on this path
+              NERFB_TRACE(tpub += clock64() - tp0;)
             }
           }
+          NERFB_TRACE(if (tr) { trc[n_here * 8 + 2] = twa; trc[n_here * 8 + 3] = tpub; trc[n_here * 8 + 4] = clock64(); })
           if (++slot == (uint32_t)fc.q) slot = 0;
         }
       }
@@ -507,6 +544,7 @@ struct __align__(1024) SmemW {
   uint64_t full[W_STAGES], empty[W_STAGES];
   uint64_t acc_done, acc_free;
   uint32_t tmem_base;
+  uint32_t scout_cnt;                // fused launch: (tile, item) pairs whose dZ packet the scout lane has seen published
 };
 
 __global__ void __launch_bounds__(W_THREADS, 1) mlp_tc_wgrad_kernel(const __grid_constant__ WgradArgs args) {
@@ -663,16 +701,21 @@ struct FusedWArgs {
   float* partial; float* grad; float* aux;
 };
 
-__device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const FusedCtl& fc, uint8_t* smem_raw) {
+__device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const FusedCtl& fc, uint8_t* smem_raw, long long* trace) {
+  (void)trace;
   SmemW& sm = *reinterpret_cast<SmemW*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int w = (int)blockIdx.x - fc.Nc, u = w / fc.G, jg = w % fc.G;
+  const int w = (int)blockIdx.x - fc.Nc;
+  int u = 0;
+  while (u + 1 < args.n_units && w >= fc.unit_w0[u + 1]) ++u;
+  const int G = fc.unit_G[u], jg = w - fc.unit_w0[u];
   const int n_it = args.unit_n[u];
-  const int my_tiles = (int)((args.n_tiles - jg + fc.G - 1) / fc.G);       // tiles jg, jg + G, ... (n_tiles >= G is guaranteed by the host)
+  const int my_tiles = (int)((args.n_tiles - jg + G - 1) / G);             // tiles jg, jg + G, ... (n_tiles >= G is guaranteed by the host)
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < W_STAGES; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 5); }
     mbar_init(&sm.acc_done, 1); mbar_init(&sm.acc_free, 4);
+    sm.scout_cnt = 0u;
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
@@ -682,12 +725,22 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
   const uint32_t tmem = sm.tmem_base;
 
   if (warp == 0) {
-    if (lane == 0) {                         // ===== producer: dZ halves from the chain CTAs' rings (L2), input halves from the forward record (HBM) =====
-      int st = 0; uint32_t ph = 0;
+    {                                        // ===== producer: dZ halves from the chain CTAs' rings (L2), input halves from the forward record (HBM) =====
+      // The per-ITEM overhead of this lane, not the MMAs, bounded the fused launch (tools/trace_fused.py: ~900 clk flag round
+      // trip + ~870 clk fence + ~2200 clk for 16 sequential copies per item; a unit of four items then needs 4 x 4600 clk
+      // per tile).  So: the chain CTA's packet counter is re-read only when the cached value does not already cover the
+      // packet (one read usually covers every item of a tile), the proxy fence follows only a fresh read, and lanes 0..7
+      // issue one 8 KB copy each (dZ blocks on lanes 0..3, input blocks on 4..7) after lane 0 has posted the byte count.
+      // ... and the flag polling has moved to a SCOUT lane (warp 6) that runs ahead through the same (tile, item) sequence and
+      // counts the packets it has seen into shared memory; this lane only waits on that counter, so the L2 round trip and
+      // the proxy fence of item i + 1 overlap the stage wait and the copies of item i.
+      int st = 0; uint32_t ph = 0, n_seen = 0;
       const uint64_t stream_once = l2_policy_evict_first();
+      NERFB_TRACE(long long acc_flag = 0, acc_empty = 0; const long long t_begin = clock64();)
       for (int ti = 0; ti < my_tiles; ++ti) {
-        const int64_t tile = jg + (int64_t)ti * fc.G;
+        const int64_t tile = jg + (int64_t)ti * G;
         const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+        NERFB_TRACE(const bool tr = trace && w == 0 && ti < 120 && lane == 0; if (tr) trace[ti * 8 + 0] = clock64();)
         for (int li = 0; li < n_it; ++li) {
           const int it = args.unit_item[u][li];
           const WItem& im = args.item[it];
@@ -695,22 +748,64 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
           const uint8_t* dzp;
           if (pk >= 0) {
             const uint32_t n = k * (uint32_t)fc.PK + (uint32_t)pk;
-            gflag_wait_ge(fc.produced + (size_t)c * F_FLAG_STRIDE, n + 1);
             dzp = fc.ring + ((size_t)c * fc.q + n % (uint32_t)fc.q) * F_PKT_BYTES;
           } else {
-            gflag_wait_ge(fc.hprod + (size_t)c * F_FLAG_STRIDE, 4u * (k + 1));
             dzp = fc.hring + ((size_t)c * F_HQ + k % F_HQ) * (2 * BLK_BYTES);
           }
-          fence_proxy_async_all();
+          ++n_seen;
+          if (lane == 0) {
+            NERFB_TRACE(const long long tf0 = clock64();)
+            cnt_wait(smem_u32(&sm.scout_cnt), n_seen);
+            NERFB_TRACE(acc_flag += clock64() - tf0;)
+          }
+          NERFB_TRACE(if (tr && li == 0) { trace[ti * 8 + 1] = clock64(); trace[ti * 8 + 2] = trace[ti * 8 + 1]; })
           const uint8_t* ap = args.fwd_rec + tile * (int64_t)args.fwd_tile_bytes + im.a_off;
+          const bool mine = lane < 4 ? lane < im.nM : (lane < 8 && lane - 4 < im.nN);
           for (int half = 0; half < 2; ++half) {
-            mbar_wait(&sm.empty[st], ph ^ 1);
-            mbar_expect_tx(&sm.full[st], (uint32_t)(im.nM + im.nN) * W_HALF);
-            for (int j = 0; j < im.nM; ++j) bulk_g2s(sm.stage[st] + j * W_HALF, dzp + j * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st]);
-            for (int j = 0; j < im.nN; ++j)
-              bulk_g2s_hint(sm.stage[st] + (4 + j) * W_HALF, ap + j * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st], stream_once);
+            if (lane == 0) {
+              NERFB_TRACE(const long long te0 = clock64();)
+              mbar_wait(&sm.empty[st], ph ^ 1);
+              NERFB_TRACE(acc_empty += clock64() - te0;)
+              mbar_expect_tx(&sm.full[st], (uint32_t)(im.nM + im.nN) * W_HALF);
+            }
+            NERFB_TRACE(if (tr && li == 0 && half == 0) trace[ti * 8 + 3] = clock64();)
+            __syncwarp();                      // packet seen + byte count posted before any lane's copy
+            if (mine) {
+              if (lane < 4) bulk_g2s(sm.stage[st] + lane * W_HALF, dzp + lane * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st]);
+              else bulk_g2s_hint(sm.stage[st] + lane * W_HALF, ap + (lane - 4) * BLK_BYTES + half * W_HALF, W_HALF, &sm.full[st], stream_once);
+            }
             if (++st == W_STAGES) { st = 0; ph ^= 1; }
           }
+          NERFB_TRACE(if (tr && li == 0) trace[ti * 8 + 4] = clock64();)
+        }
+      }
+      // per-CTA totals behind the two timelines: [total, packet waits, stage waits, unit, items, tiles]
+      NERFB_TRACE(if (trace && lane == 0) { long long* o = trace + 120 * 8 + 150 * 8 + (size_t)w * 8; o[0] = clock64() - t_begin; o[1] = acc_flag; o[2] = acc_empty; o[3] = u; o[4] = n_it; o[5] = my_tiles; })
+    }
+  } else if (warp == 6) {
+    if (lane == 0) {                         // ===== scout: polls the chain CTAs' packet counters ahead of the copy issuer =====
+      const uint32_t cnt = smem_u32(&sm.scout_cnt);
+      for (int ti = 0; ti < my_tiles; ++ti) {
+        const int64_t tile = jg + (int64_t)ti * G;
+        const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+        uint32_t seen = 0u, hseen = 0u;        // last values read of this chain CTA's packet / head counters (monotonic)
+        for (int li = 0; li < n_it; ++li) {
+          const int pk = args.item_pk[args.unit_item[u][li]];
+          bool fresh = false;
+          if (pk >= 0) {
+            const uint32_t n = k * (uint32_t)fc.PK + (uint32_t)pk;
+            if ((int32_t)(seen - (n + 1)) < 0) {
+              const uint32_t* flag = fc.produced + (size_t)c * F_FLAG_STRIDE;
+              gflag_wait_ge(flag, n + 1);
+              seen = ld_acquire_gpu(flag); fresh = true;
+            }
+          } else if ((int32_t)(hseen - 4u * (k + 1)) < 0) {
+            const uint32_t* flag = fc.hprod + (size_t)c * F_FLAG_STRIDE;
+            gflag_wait_ge(flag, 4u * (k + 1));
+            hseen = ld_acquire_gpu(flag); fresh = true;
+          }
+          if (fresh) fence_proxy_async_all();
+          cnt_publish(cnt);                    // release: the issuer's copies follow its acquire of this counter
         }
       }
     }
@@ -718,13 +813,16 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
     if (lane == 0) {                         // ===== MMA issuer =====
       int st = 0; uint32_t ph = 0;
       for (int ti = 0; ti < my_tiles; ++ti) {
+        NERFB_TRACE(const bool tr = trace && w == 0 && ti < 120;)
         for (int li = 0; li < n_it; ++li) {
           const int it = args.unit_item[u][li];
           const WItem& im = args.item[it];
           const uint32_t idesc = umma_idesc_bf16(128, im.N, 1, 1);
           const uint32_t col0 = (uint32_t)args.item_col[it][0], col1 = (uint32_t)args.item_col[it][1];
           for (int half = 0; half < 2; ++half) {
+            NERFB_TRACE(if (tr && li == 0 && half == 0) trace[ti * 8 + 5] = clock64();)
             mbar_wait(&sm.full[st], ph);
+            NERFB_TRACE(if (tr && li == 0 && half == 0) trace[ti * 8 + 6] = clock64();)
             tc_fence_after();
             const uint32_t base = smem_u32(sm.stage[st]);
 #pragma unroll
@@ -733,6 +831,7 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
                 umma_bf16(tmem + (mh ? col1 : col0), umma_desc_mn128(base + mh * 2 * W_HALF + ks * 2048, W_HALF),
                           umma_desc_mn128(base + 4 * W_HALF + ks * 2048, W_HALF), idesc, (ti > 0 || half > 0 || ks > 0) ? 1u : 0u);
             umma_commit(&sm.empty[st]);
+            NERFB_TRACE(if (tr && li == 0 && half == 1) trace[ti * 8 + 7] = clock64();)
             if (++st == W_STAGES) { st = 0; ph ^= 1; }
           }
         }
@@ -748,7 +847,7 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
 #pragma unroll
     for (int li = 0; li < F_UNIT_ITEMS; ++li) { b0[li] = 0.f; b1[li] = 0.f; }
     for (int ti = 0; ti < my_tiles; ++ti) {
-      const int64_t tile = jg + (int64_t)ti * fc.G;
+      const int64_t tile = jg + (int64_t)ti * G;
       const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
 #pragma unroll
       for (int li = 0; li < F_UNIT_ITEMS; ++li) {
@@ -822,20 +921,21 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
-struct FusedArgs { DgradArgs d; FusedCtl fc; FusedWArgs w; };
+struct FusedArgs { DgradArgs d; FusedCtl fc; FusedWArgs w; long long* trace; };
 
 template <bool SIREN>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_bwd_fused_kernel(const __grid_constant__ FusedArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   if ((int)blockIdx.x < args.fc.Nc) dgrad_role<SIREN, true>(args.d, args.fc, smem_raw, (int)blockIdx.x, args.fc.Nc);
-  else wgrad_fused_role(args.w, args.fc, smem_raw);
+  else wgrad_fused_role(args.w, args.fc, smem_raw, args.trace);
 }
 
 // grad[w_off + r * ld + col0 + n] += sum over the G partials of the item's unit
-__global__ void __launch_bounds__(256) reduce_partials_fused_kernel(const __grid_constant__ FusedWArgs ra, int G) {
+__global__ void __launch_bounds__(256) reduce_partials_fused_kernel(const __grid_constant__ FusedWArgs ra, const __grid_constant__ FusedCtl fcr) {
   const int it = blockIdx.x;
   const WItem& im = ra.item[it];
   const int u = ra.item_unit[it];
+  const int G = fcr.unit_G[u];
   const int n_it = ra.unit_n[u];
   const float* base = ra.partial + (int64_t)(ra.unit_pbase[u] + ra.item_pslot[it]) * W_SLOT;
   const int total = (im.m_hi - im.m_lo) * im.nvalid;
@@ -1085,8 +1185,12 @@ int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v && *v) ? atoi(v) : dflt;
 }
+// NERFB_BWD_FUSED: 0 = three launches (dgrad -> HBM record -> wgrad), 1 = fused launch wherever it is expressible, 2 (default) =
+// fused launch where it was measured to be at least as fast on the B200: plain NeRF (4096 x 128: 1.94 ms either way, but 5 GB less
+// HBM traffic per fine pass -> under the power cap the step sustains 4.66 ms instead of 4.81 ms); NeRF_3D (more wgrad items per tile)
+// and SIREN keep the 3-launch path (NeRF_3D measured 4.9 ms fused against 4.07 ms).
 #ifndef NERFB_BWD_FUSED_DEFAULT
-#define NERFB_BWD_FUSED_DEFAULT 0          // flipped to 1 once the fused launch is validated on the B200 (tools/check_fused_bwd.py)
+#define NERFB_BWD_FUSED_DEFAULT 2
 #endif
 struct FusedPlan {
   bool on;
@@ -1105,8 +1209,10 @@ int item_clk(const WItem& im) {
 FusedPlan fused_plan(const BwdPlan& pl) {
   FusedPlan fp{};
   fp.on = false;
-  if (env_int("NERFB_BWD_FUSED", NERFB_BWD_FUSED_DEFAULT) == 0) return fp;
+  const int mode = env_int("NERFB_BWD_FUSED", NERFB_BWD_FUSED_DEFAULT);
+  if (mode == 0) return fp;
   const BProgram& pg = pl.prog;
+  if (mode == 2 && (pg.siren || pg.n_cls > 0)) return fp;
   const WgradArgs& wg = pl.wg;
   FusedWArgs& w = fp.w;
   w.n_items = wg.n_items;
@@ -1156,8 +1262,8 @@ FusedPlan fused_plan(const BwdPlan& pl) {
     }
   }
   FusedCtl& fc = fp.fc;
-  fc.G = env_int("NERFB_FUSED_G", 6);
-  fc.q = env_int("NERFB_FUSED_Q", 8);
+  fc.G = env_int("NERFB_FUSED_G", 8);
+  fc.q = env_int("NERFB_FUSED_Q", 10);
   if (fc.G < 1 || fc.q < 3 || fc.q > F_MAX_Q) return fp;
   fc.Nc = NERFB_SM_COUNT - nu * fc.G;
   fc.PK = pg.n_steps + 1;
@@ -1167,7 +1273,34 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   for (int i = 0; i <= MAX_BSTEPS; ++i) fc.pk_need[i] = 0;
   for (int i = 0; i < w.n_items; ++i) { if (w.item_pk[i] < 0) ++fc.m_head; else ++fc.pk_need[w.item_pk[i]]; }
   int pbase = 0;
-  for (int u = 0; u < nu; ++u) { w.unit_pbase[u] = pbase; pbase += fc.G * w.unit_n[u]; }
+  // Split the n_units * G wgrad CTAs by the measured per-tile cost of a unit's producer lane (tools/trace_fused.py on the
+  // B200: ~2.8k clk for a one-item unit, ~2.1k clk per item for multi-item units -- the stage / copy-issue hand-shakes,
+  // not the MMAs, dominate), largest remainder first, at least one CTA per unit.
+  {
+    const int budget = nu * fc.G;
+    double cost[F_MAX_UNITS], tot = 0.0;
+    for (int u = 0; u < nu; ++u) { cost[u] = w.unit_n[u] == 1 ? 2800.0 : 300.0 + 2050.0 * w.unit_n[u]; tot += cost[u]; }   // measured busy clk per tile: 2.8k / 4.4k (2 items) / 8.5k (4 items)
+    int given = 0;
+    double frac[F_MAX_UNITS];
+    for (int u = 0; u < nu; ++u) {
+      const double share = budget * cost[u] / tot;
+      fc.unit_G[u] = (int)share < 1 ? 1 : (int)share;
+      frac[u] = share - (int)share; given += fc.unit_G[u];
+    }
+    while (given < budget) {
+      int best = 0;
+      for (int u = 1; u < nu; ++u) if (frac[u] > frac[best]) best = u;
+      ++fc.unit_G[best]; frac[best] = -1.0; ++given;
+    }
+    while (given > budget) {           // the >= 1 floor overshot: take from the largest
+      int best = 0;
+      for (int u = 1; u < nu; ++u) if (fc.unit_G[u] > fc.unit_G[best]) best = u;
+      --fc.unit_G[best]; --given;
+    }
+    int w0 = 0;
+    for (int u = 0; u < nu; ++u) { fc.unit_w0[u] = w0; w0 += fc.unit_G[u]; }
+  }
+  for (int u = 0; u < nu; ++u) { w.unit_pbase[u] = pbase; pbase += fc.unit_G[u] * w.unit_n[u]; }
   fp.grid = fc.Nc + nu * fc.G;
   int64_t off = 0;
   fp.off_ring = off;    off += (int64_t)fc.Nc * fc.q * F_PKT_BYTES;
@@ -1181,6 +1314,9 @@ FusedPlan fused_plan(const BwdPlan& pl) {
 }
 
 }  // namespace
+
+static long long* g_trace_bwd = nullptr;
+extern "C" void nerfb_debug_trace_bwd(long long* device_buf) { g_trace_bwd = device_buf; }   // diagnostics only (tools/trace_fused.py)
 
 // The backward workspace follows the forward's: packed W^T slabs | head vectors | then EITHER the 3-launch path's per-tile dZ
 // record + partials, OR the fused path's rings + flags + partials (decided by the same plan function in both entry points).
@@ -1244,11 +1380,13 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     fa.w.fwd_rec = fwd_rec; fa.w.fwd_tile_bytes = pl.prog.fwd_tile_bytes; fa.w.n_tiles = pl.n_tiles;
     fa.w.partial = reinterpret_cast<float*>(fb + fp.off_partial); fa.w.grad = grad;
     fa.w.aux = reinterpret_cast<float*>(fb + fp.off_aux);
+    fa.trace = g_trace_bwd;
+    fa.d.trace_chain = g_trace_bwd ? g_trace_bwd + 120 * 8 : nullptr;
     NERFB_CUDA(cudaMemsetAsync(flags, 0, (size_t)fp.flags_bytes, (cudaStream_t)stream));
     if (d.n_cls > 0) NERFB_CUDA(cudaMemsetAsync(fa.w.aux + 16 * 256, 0, 128 * 4, (cudaStream_t)stream));
     if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<true>, fp.grid, NUM_THREADS, smem_f, stream, fa);
     else NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<false>, fp.grid, NUM_THREADS, smem_f, stream, fa);
-    NERFB_LAUNCH(reduce_partials_fused_kernel, dim3(fa.w.n_items, 32), 256, 0, stream, fa.w, fp.fc.G);
+    NERFB_LAUNCH(reduce_partials_fused_kernel, dim3(fa.w.n_items, 32), 256, 0, stream, fa.w, fa.fc);
     if (d.n_cls > 0) {
       const NerfOffsets o = nerf_offsets(d);
       NERFB_LAUNCH(parse_chain_kernel, 512, 256, 0, stream, params, (const float*)fa.w.aux, d.n_cls, o.w_p0, o.b_p0, o.w_p1, o.b_p1, grad);

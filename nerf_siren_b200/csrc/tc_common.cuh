@@ -180,6 +180,13 @@ __device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, 
                ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
 __device__ __forceinline__ void bulk_wait_all3() { asm volatile("cp.async.bulk.wait_group 3;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all7() { asm volatile("cp.async.bulk.wait_group 7;" ::: "memory"); }
+__device__ __forceinline__ uint4 ld_relaxed_gpu_v4(const uint32_t* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 // generic <-> async proxy ordering for ALL state spaces (global data written / read by bulk copies and by ld/st)
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 

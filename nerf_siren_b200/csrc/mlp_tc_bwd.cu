@@ -1192,6 +1192,19 @@ int env_int(const char* name, int dflt) {
 #ifndef NERFB_BWD_FUSED_DEFAULT
 #define NERFB_BWD_FUSED_DEFAULT 2
 #endif
+// The fused launch spins on flags written by OTHER CTAs of the same grid: every one of its NERFB_SM_COUNT CTAs must be resident
+// at once (one per SM; the kernel's shared memory admits exactly one).  Checked per device, once: the device has that many SMs;
+// anything else (a smaller part, a MIG slice) silently keeps the 3-launch path, which has no such requirement.
+static bool fused_device_ok() {
+  static int cached[64] = {};            // 0 unknown, 1 ok, 2 not ok
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+  if (cached[dev] == 0) {
+    int sms = 0;
+    cached[dev] = (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms >= NERFB_SM_COUNT) ? 1 : 2;
+  }
+  return cached[dev] == 1;
+}
 struct FusedPlan {
   bool on;
   FusedCtl fc; FusedWArgs w;
@@ -1210,7 +1223,7 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   FusedPlan fp{};
   fp.on = false;
   const int mode = env_int("NERFB_BWD_FUSED", NERFB_BWD_FUSED_DEFAULT);
-  if (mode == 0) return fp;
+  if (mode == 0 || !fused_device_ok()) return fp;
   const BProgram& pg = pl.prog;
   if (mode == 2 && (pg.siren || pg.n_cls > 0)) return fp;
   const WgradArgs& wg = pl.wg;

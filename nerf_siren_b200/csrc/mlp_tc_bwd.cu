@@ -737,20 +737,31 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
       int st = 0; uint32_t ph = 0, n_seen = 0;
       const uint64_t stream_once = l2_policy_evict_first();
       NERFB_TRACE(long long acc_flag = 0, acc_empty = 0; const long long t_begin = clock64();)
+      int tc_c = jg % fc.Nc; uint32_t tc_k = (uint32_t)(jg / fc.Nc);
+      int it_nM[F_UNIT_ITEMS], it_nN[F_UNIT_ITEMS], it_aoff[F_UNIT_ITEMS], it_pk[F_UNIT_ITEMS];     // the unit's items, out of the parameter bank once
+#pragma unroll
+      for (int li = 0; li < F_UNIT_ITEMS; ++li) {
+        const int it = args.unit_item[u][li < n_it ? li : 0];
+        it_nM[li] = args.item[it].nM; it_nN[li] = args.item[it].nN; it_aoff[li] = args.item[it].a_off; it_pk[li] = args.item_pk[it];
+      }
+      const uint32_t qq = (uint32_t)fc.q, PKn = (uint32_t)fc.PK;
       for (int ti = 0; ti < my_tiles; ++ti) {
         const int64_t tile = jg + (int64_t)ti * G;
-        const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+        const int c = tc_c; const uint32_t k = tc_k;      // tile = c + k * Nc, tracked incrementally (no 64-bit div / mod per tile)
+        tc_c += G; while (tc_c >= fc.Nc) { tc_c -= fc.Nc; ++tc_k; }
         NERFB_TRACE(const bool tr = trace && w == 0 && ti < 120 && lane == 0; if (tr) trace[ti * 8 + 0] = clock64();)
-        for (int li = 0; li < n_it; ++li) {
-          const int it = args.unit_item[u][li];
-          const WItem& im = args.item[it];
-          const int pk = args.item_pk[it];
+        const uint8_t* const arec = args.fwd_rec + tile * (int64_t)args.fwd_tile_bytes;
+#pragma unroll
+        for (int li = 0; li < F_UNIT_ITEMS; ++li) {
+          if (li >= n_it) break;
+          struct { int nM, nN; } im = {it_nM[li], it_nN[li]};
+          const int pk = it_pk[li];
           const uint8_t* dzp;
           if (pk >= 0) {
-            const uint32_t n = k * (uint32_t)fc.PK + (uint32_t)pk;
-            dzp = fc.ring + ((size_t)c * fc.q + n % (uint32_t)fc.q) * F_PKT_BYTES;
+            const uint32_t n = k * PKn + (uint32_t)pk;
+            dzp = fc.ring + ((size_t)((uint32_t)c * qq + n % qq)) * F_PKT_BYTES;
           } else {
-            dzp = fc.hring + ((size_t)c * F_HQ + k % F_HQ) * (2 * BLK_BYTES);
+            dzp = fc.hring + ((size_t)((uint32_t)c * F_HQ + k % F_HQ)) * (2 * BLK_BYTES);
           }
           ++n_seen;
           if (lane == 0) {
@@ -759,7 +770,7 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
             NERFB_TRACE(acc_flag += clock64() - tf0;)
           }
           NERFB_TRACE(if (tr && li == 0) { trace[ti * 8 + 1] = clock64(); trace[ti * 8 + 2] = trace[ti * 8 + 1]; })
-          const uint8_t* ap = args.fwd_rec + tile * (int64_t)args.fwd_tile_bytes + im.a_off;
+          const uint8_t* ap = arec + it_aoff[li];
           const bool mine = lane < 4 ? lane < im.nM : (lane < 8 && lane - 4 < im.nN);
           for (int half = 0; half < 2; ++half) {
             if (lane == 0) {
@@ -785,9 +796,11 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
   } else if (warp == 6) {
     if (lane == 0) {                         // ===== scout: polls the chain CTAs' packet counters ahead of the copy issuer =====
       const uint32_t cnt = smem_u32(&sm.scout_cnt);
+      int tc_c = jg % fc.Nc; uint32_t tc_k = (uint32_t)(jg / fc.Nc);
       for (int ti = 0; ti < my_tiles; ++ti) {
         const int64_t tile = jg + (int64_t)ti * G;
-        const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+        const int c = tc_c; const uint32_t k = tc_k;      // tile = c + k * Nc, tracked incrementally (no 64-bit div / mod per tile)
+        tc_c += G; while (tc_c >= fc.Nc) { tc_c -= fc.Nc; ++tc_k; }
         uint32_t seen = 0u, hseen = 0u;        // last values read of this chain CTA's packet / head counters (monotonic)
         for (int li = 0; li < n_it; ++li) {
           const int pk = args.item_pk[args.unit_item[u][li]];
@@ -846,9 +859,11 @@ __device__ __forceinline__ void wgrad_fused_role(const FusedWArgs& args, const F
     float b0[F_UNIT_ITEMS], b1[F_UNIT_ITEMS];
 #pragma unroll
     for (int li = 0; li < F_UNIT_ITEMS; ++li) { b0[li] = 0.f; b1[li] = 0.f; }
-    for (int ti = 0; ti < my_tiles; ++ti) {
+    int tc_c = jg % fc.Nc; uint32_t tc_k = (uint32_t)(jg / fc.Nc);
+      for (int ti = 0; ti < my_tiles; ++ti) {
       const int64_t tile = jg + (int64_t)ti * G;
-      const int c = (int)(tile % fc.Nc); const uint32_t k = (uint32_t)(tile / fc.Nc);
+      const int c = tc_c; const uint32_t k = tc_k;
+      tc_c += G; while (tc_c >= fc.Nc) { tc_c -= fc.Nc; ++tc_k; }
 #pragma unroll
       for (int li = 0; li < F_UNIT_ITEMS; ++li) {
         if (li < n_it) {
@@ -1278,7 +1293,7 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   fc.G = env_int("NERFB_FUSED_G", 8);
   fc.q = env_int("NERFB_FUSED_Q", 10);
   if (fc.G < 1 || fc.q < 3 || fc.q > F_MAX_Q) return fp;
-  fc.Nc = NERFB_SM_COUNT - nu * fc.G;
+  fc.Nc = NERFB_SM_COUNT - env_int("NERFB_FUSED_BUDGET", nu * fc.G);
   fc.PK = pg.n_steps + 1;
   // the fused grid needs every wgrad CTA to own tiles and the chain CTAs several rounds each; small problems keep the 3-launch path
   if (fc.Nc < 16 || pl.n_tiles < 4 * (int64_t)NERFB_SM_COUNT) return fp;
@@ -1290,9 +1305,10 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   // B200: ~2.8k clk for a one-item unit, ~2.1k clk per item for multi-item units -- the stage / copy-issue hand-shakes,
   // not the MMAs, dominate), largest remainder first, at least one CTA per unit.
   {
-    const int budget = nu * fc.G;
+    const int budget = env_int("NERFB_FUSED_BUDGET", nu * fc.G);
     double cost[F_MAX_UNITS], tot = 0.0;
-    for (int u = 0; u < nu; ++u) { cost[u] = w.unit_n[u] == 1 ? 2800.0 : 300.0 + 2050.0 * w.unit_n[u]; tot += cost[u]; }   // measured busy clk per tile: 2.8k / 4.4k (2 items) / 8.5k (4 items)
+    const double c1 = env_int("NERFB_FUSED_C1", 2800), c0 = env_int("NERFB_FUSED_C0", 300), cn = env_int("NERFB_FUSED_CN", 2050);   // tuning knobs
+    for (int u = 0; u < nu; ++u) { cost[u] = w.unit_n[u] == 1 ? c1 : c0 + cn * w.unit_n[u]; tot += cost[u]; }   // measured busy clk per tile: 2.8k / 4.4k (2 items) / 8.5k (4 items)
     int given = 0;
     double frac[F_MAX_UNITS];
     for (int u = 0; u < nu; ++u) {
@@ -1314,7 +1330,7 @@ FusedPlan fused_plan(const BwdPlan& pl) {
     for (int u = 0; u < nu; ++u) { fc.unit_w0[u] = w0; w0 += fc.unit_G[u]; }
   }
   for (int u = 0; u < nu; ++u) { w.unit_pbase[u] = pbase; pbase += fc.unit_G[u] * w.unit_n[u]; }
-  fp.grid = fc.Nc + nu * fc.G;
+  fp.grid = NERFB_SM_COUNT;
   int64_t off = 0;
   fp.off_ring = off;    off += (int64_t)fc.Nc * fc.q * F_PKT_BYTES;
   fp.off_hring = off;   off += (int64_t)fc.Nc * F_HQ * 2 * BLK_BYTES;

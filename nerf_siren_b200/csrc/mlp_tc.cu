@@ -1035,7 +1035,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mlp_tc_fwd_pair_kernel(const _
           NERFB_TRACE(if (tr) args.trace[tev * 16 + 9] = clock64();)
           float head_acc[3] = {0.f, 0.f, 0.f};
           // training: the store lane has read out everything this slot's blocks held before (X copy + s earlier events of this tile)
+          NERFB_TRACE(const long long tc0 = clock64();)
           if (SAVE && saving && g < st_out) cnt_wait(smem_u32(&sm.st_cnt[slot]), it * (uint32_t)(pg.n_steps + 1) + 1u + (uint32_t)s);
+          NERFB_TRACE(if (tr) args.trace[tev * 16 + 11] = clock64() - tc0;)
           const uint32_t t_addr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)slot * 256u + 64u * (uint32_t)g;
           if (g < nb) {
             const float4* bias4 = reinterpret_cast<const float4*>(args.bias + sb) + 16 * g;      // L1-resident table, warp-uniform address

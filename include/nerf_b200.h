@@ -241,6 +241,19 @@ int64_t nerfb_pack_vol_workspace_bytes(int64_t n_voxels);
 int nerfb_pack_vol(const float* rgbsigma, int64_t n_voxels, float neg_step, uint32_t* pairs, int64_t capacity,
                    int64_t* n_valid, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- nerfb_pack_vol for callers that cannot allocate ------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * nerfb_pack_vol, but the per-chunk counts / offsets live in a file-scope `static __device__` array of the library
+ * (192 KiB, held by every GPU that loads the library until exit) instead of a caller-provided workspace; the entry
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library call).  Limit: n_voxels <=
+ * nerfb_pack_vol_static_max_voxels() = 2^24 (a 256^3 grid); larger inputs return NERFB_E_WORKSPACE with a message on
+ * stderr -- use nerfb_pack_vol then.  All calls on a device share the array (it keeps the last call's contents; nothing
+ * in it has to be cleared between calls): calls that OVERLAP on the GPU (different streams without ordering) race. */
+int64_t nerfb_pack_vol_static_max_voxels(void);
+int nerfb_pack_vol_static(const float* rgbsigma, int64_t n_voxels, float neg_step, uint32_t* pairs, int64_t capacity,
+                          int64_t* n_valid, void* stream);
+
 /* ---- diagnostics: how many kernels this library has launched in this process ------------------- */
 int64_t nerfb_launch_count(void);
 

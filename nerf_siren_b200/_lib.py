@@ -71,6 +71,8 @@ SIGNATURES = {
     "nerfb_finish_image": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "nerfb_pack_vol_workspace_bytes": (_L, [_L]),
     "nerfb_pack_vol": (_I, [_P, _L, _F, _P, _L, _P, _P, _L, _P]),
+    "nerfb_pack_vol_static_max_voxels": (_L, []),
+    "nerfb_pack_vol_static": (_I, [_P, _L, _F, _P, _L, _P, _P]),
     "nerfb_adam_step": (_I, [_P, _P, _P, _P, _L, C.c_double, C.c_double, C.c_double, C.c_double, _L, _F, _P]),
 }
 

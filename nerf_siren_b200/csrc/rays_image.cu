@@ -8,6 +8,7 @@
 //   nerfb_pack_vol      -- extract_mesh.ipynb cell 7: the sparse `.vol` volume Unity renders, 8 bytes per
 //     voxel with alpha > 0, from the dense (N^3, 4) [rgb sigma] query of kernel (1).
 // All are pure streaming kernels (HBM-bound): 32 B per ray out; 12 + 4 (+12) B in, 3 + 4 B out per pixel; 16 B in per voxel.
+#include <cstdio>
 #include "common.cuh"
 
 namespace {
@@ -233,6 +234,56 @@ extern "C" int nerfb_pack_vol(const float* rgbsigma, int64_t n_voxels, float neg
   NERFB_LAUNCH(vol_count_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, cnt);
   NERFB_LAUNCH(vol_scan_kernel, 1, 1024, 0, stream, cnt, n_chunks, off, n_valid);
   if (capacity > 0) NERFB_LAUNCH(vol_write_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, off, capacity, reinterpret_cast<uint2*>(pairs));
+  return NERFB_OK;
+}
+
+// ---- nerfb_pack_vol without a caller-provided workspace (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) ----
+// The per-chunk counts and offsets live in a file-scope device array of fixed size: 2^24 voxels (a 256^3 grid) = 16,384 chunks
+// of 1024 voxels = 64 KiB of counts + 128 KiB of offsets = 192 KiB, held by every GPU that loads the library until exit.
+// In host code `g_vol_scratch` is only a host-side stand-in for the symbol: its DEVICE address is looked up once per device
+// (with that device current) by cudaGetSymbolAddress and that pointer is what the kernels get.  Every call on a device shares
+// the array and finds the previous call's contents in it; nothing has to start at zero (every word a kernel reads is written
+// earlier in the same call: vol_count_kernel writes all n_chunks counts, vol_scan_kernel all n_chunks offsets), but two calls
+// that overlap on the GPU (different streams, no ordering between them) race on it.
+constexpr int64_t VOL_STATIC_MAX_VOXELS = (int64_t)1 << 24;
+constexpr int64_t VOL_STATIC_MAX_CHUNKS = VOL_STATIC_MAX_VOXELS / VOL_CHUNK;
+constexpr int64_t VOL_STATIC_CNT_BYTES = (VOL_STATIC_MAX_CHUNKS * 4 + 255) & ~(int64_t)255;
+constexpr int64_t VOL_STATIC_BYTES = VOL_STATIC_CNT_BYTES + VOL_STATIC_MAX_CHUNKS * 8;
+static __device__ __align__(256) unsigned char g_vol_scratch[VOL_STATIC_BYTES];
+
+extern "C" int64_t nerfb_pack_vol_static_max_voxels(void) { return VOL_STATIC_MAX_VOXELS; }
+
+extern "C" int nerfb_pack_vol_static(const float* rgbsigma, int64_t n_voxels, float neg_step, uint32_t* pairs, int64_t capacity,
+                                     int64_t* n_valid, void* stream) {
+  NERFB_CHECK_ARG(rgbsigma && n_valid && n_voxels >= 0 && capacity >= 0 && (pairs || capacity == 0));
+  if (n_voxels > VOL_STATIC_MAX_VOXELS) {
+    fprintf(stderr, "nerf_b200: nerfb_pack_vol_static: n_voxels = %lld exceeds the built-in scratch (max %lld voxels); use nerfb_pack_vol "
+            "with a caller-provided workspace\n", (long long)n_voxels, (long long)VOL_STATIC_MAX_VOXELS);
+    return NERFB_E_WORKSPACE;
+  }
+  NERFB_CHECK_ARG((reinterpret_cast<uintptr_t>(rgbsigma) & 15) == 0 && (reinterpret_cast<uintptr_t>(pairs) & 7) == 0);
+  int dev = 0;
+  NERFB_CUDA(cudaGetDevice(&dev));
+  static unsigned char* scratch_dev[64] = {};          // device address of g_vol_scratch, per device
+  unsigned char* scratch = (dev >= 0 && dev < 64) ? scratch_dev[dev] : nullptr;
+  if (!scratch) {
+    void* ptr = nullptr;
+    NERFB_CUDA(cudaGetSymbolAddress(&ptr, g_vol_scratch));      // the current device's copy of the symbol
+    if (!ptr) return (int)cudaErrorInvalidSymbol;
+    scratch = static_cast<unsigned char*>(ptr);
+    if (dev >= 0 && dev < 64) scratch_dev[dev] = scratch;
+  }
+  // an empty volume has ZERO chunks here: the scan then writes *n_valid = 0 without reading a count nobody wrote in this call
+  // (the shared scratch still holds the previous call's counts)
+  const int64_t n_chunks = ceil_div64(n_voxels, VOL_CHUNK);
+  uint32_t* cnt = reinterpret_cast<uint32_t*>(scratch);
+  int64_t* off = reinterpret_cast<int64_t*>(scratch + VOL_STATIC_CNT_BYTES);
+  const float4* v = reinterpret_cast<const float4*>(rgbsigma);
+  const int grid = (int)(n_chunks < NERFB_SM_COUNT * 8 ? n_chunks : NERFB_SM_COUNT * 8);
+  if (n_chunks > 0) NERFB_LAUNCH(vol_count_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, cnt);
+  NERFB_LAUNCH(vol_scan_kernel, 1, 1024, 0, stream, cnt, n_chunks, off, n_valid);
+  if (capacity > 0 && n_chunks > 0) NERFB_LAUNCH(vol_write_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, off, capacity, reinterpret_cast<uint2*>(pairs));
   return NERFB_OK;
 }
 

@@ -77,7 +77,7 @@ INFER_KERNEL = {"0": "mlp_tc_fwd_kernel", "2": "mlp_tc_fwd_pair2_kernel (cta_gro
 # keep dgrad -> wgrad unless NERFB_BWD_FUSED=1
 def bwd_kernel_name(cls):
     mode = os.environ.get("NERFB_BWD_FUSED", "2")
-    fused = mode == "1" or (mode == "2" and not cls)
+    fused = mode in ("1", "2")          # "2" (default): fused for NeRF and NeRF_3D, 3 launches for SIREN (no SIREN training config here)
     return "mlp_tc_bwd_fused_kernel (dgrad chain + wgrad CTAs, one launch)" if fused else "mlp_tc_bwd (dgrad chain + wgrad)"
 
 class Clocks:

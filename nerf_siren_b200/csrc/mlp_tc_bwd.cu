@@ -1201,9 +1201,9 @@ int env_int(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 // NERFB_BWD_FUSED: 0 = three launches (dgrad -> HBM record -> wgrad), 1 = fused launch wherever it is expressible, 2 (default) =
-// fused launch where it was measured to be at least as fast on the B200: plain NeRF (4096 x 128: 1.94 ms either way, but 5 GB less
-// HBM traffic per fine pass -> under the power cap the step sustains 4.66 ms instead of 4.81 ms); NeRF_3D (more wgrad items per tile)
-// and SIREN keep the 3-launch path (NeRF_3D measured 4.9 ms fused against 4.07 ms).
+// fused launch where it was measured to be at least as fast on the B200: plain NeRF (4096 x 128: 1.88 ms against 1.93 ms, and 5.9 GB less
+// HBM traffic per fine pass -> under the power cap the step sustains 4.60 ms instead of 4.81 ms) and NeRF_3D (8192 x 128: 3.87 ms against
+// 4.02 ms once the ring holds a whole tile's 12 packets); SIREN keeps the 3-launch path.
 #ifndef NERFB_BWD_FUSED_DEFAULT
 #define NERFB_BWD_FUSED_DEFAULT 2
 #endif
@@ -1240,7 +1240,7 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   const int mode = env_int("NERFB_BWD_FUSED", NERFB_BWD_FUSED_DEFAULT);
   if (mode == 0 || !fused_device_ok()) return fp;
   const BProgram& pg = pl.prog;
-  if (mode == 2 && (pg.siren || pg.n_cls > 0)) return fp;
+  if (mode == 2 && pg.siren) return fp;      // SIREN: the sine-gate chain is the slow side (2.83 ms fused at best against 2.61 ms)
   const WgradArgs& wg = pl.wg;
   FusedWArgs& w = fp.w;
   w.n_items = wg.n_items;
@@ -1291,9 +1291,10 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   }
   FusedCtl& fc = fp.fc;
   fc.G = env_int("NERFB_FUSED_G", 8);
-  fc.q = env_int("NERFB_FUSED_Q", 10);
+  fc.q = env_int("NERFB_FUSED_Q", pg.n_steps + 2);      // ring slots = one more than the packets of a tile (prologue + n_steps): NeRF 10 packets -> 11 (10: equal, 9: 3.7 ms instead of 1.9), NeRF_3D 11 -> 12 (11: 4.63 ms, 12: 4.06 ms)
   if (fc.G < 1 || fc.q < 3 || fc.q > F_MAX_Q) return fp;
-  fc.Nc = NERFB_SM_COUNT - env_int("NERFB_FUSED_BUDGET", nu * fc.G);
+  const int budget_dflt = nu * fc.G < 84 ? nu * fc.G : 84;      // wgrad CTAs: NeRF 10 units -> 80 (74..82 equal), NeRF_3D 11 units -> 84 (88: 4.06 ms, 84: 3.87 ms, 92: 4.38 ms)
+  fc.Nc = NERFB_SM_COUNT - env_int("NERFB_FUSED_BUDGET", budget_dflt);
   fc.PK = pg.n_steps + 1;
   // the fused grid needs every wgrad CTA to own tiles and the chain CTAs several rounds each; small problems keep the 3-launch path
   if (fc.Nc < 16 || pl.n_tiles < 4 * (int64_t)NERFB_SM_COUNT) return fp;
@@ -1305,7 +1306,7 @@ FusedPlan fused_plan(const BwdPlan& pl) {
   // B200: ~2.8k clk for a one-item unit, ~2.1k clk per item for multi-item units -- the stage / copy-issue hand-shakes,
   // not the MMAs, dominate), largest remainder first, at least one CTA per unit.
   {
-    const int budget = env_int("NERFB_FUSED_BUDGET", nu * fc.G);
+    const int budget = env_int("NERFB_FUSED_BUDGET", budget_dflt);
     double cost[F_MAX_UNITS], tot = 0.0;
     const double c1 = env_int("NERFB_FUSED_C1", 2800), c0 = env_int("NERFB_FUSED_C0", 300), cn = env_int("NERFB_FUSED_CN", 2050);   // tuning knobs
     for (int u = 0; u < nu; ++u) { cost[u] = w.unit_n[u] == 1 ? c1 : c0 + cn * w.unit_n[u]; tot += cost[u]; }   // measured busy clk per tile: 2.8k / 4.4k (2 items) / 8.5k (4 items)

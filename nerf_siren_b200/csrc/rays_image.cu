@@ -226,14 +226,16 @@ extern "C" int nerfb_pack_vol(const float* rgbsigma, int64_t n_voxels, float neg
                   workspace && workspace_bytes >= nerfb_pack_vol_workspace_bytes(n_voxels));
   NERFB_CHECK_ARG((reinterpret_cast<uintptr_t>(rgbsigma) & 15) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0 &&
                   (reinterpret_cast<uintptr_t>(pairs) & 7) == 0);
-  const int64_t n_chunks = ceil_div64(n_voxels > 0 ? n_voxels : 1, VOL_CHUNK);
+  // an empty volume has ZERO chunks: the scan then writes *n_valid = 0 instead of summing a count no kernel of this call wrote
+  const int64_t n_chunks = ceil_div64(n_voxels, VOL_CHUNK);
+  const int64_t n_chunks_ws = n_chunks > 0 ? n_chunks : 1;      // the workspace layout is sized for >= 1 chunk
   uint32_t* cnt = static_cast<uint32_t*>(workspace);
-  int64_t* off = reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + ((n_chunks * 4 + 255) & ~(int64_t)255));
+  int64_t* off = reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + ((n_chunks_ws * 4 + 255) & ~(int64_t)255));
   const float4* v = reinterpret_cast<const float4*>(rgbsigma);
   const int grid = (int)(n_chunks < NERFB_SM_COUNT * 8 ? n_chunks : NERFB_SM_COUNT * 8);
-  NERFB_LAUNCH(vol_count_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, cnt);
+  if (n_chunks > 0) NERFB_LAUNCH(vol_count_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, cnt);
   NERFB_LAUNCH(vol_scan_kernel, 1, 1024, 0, stream, cnt, n_chunks, off, n_valid);
-  if (capacity > 0) NERFB_LAUNCH(vol_write_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, off, capacity, reinterpret_cast<uint2*>(pairs));
+  if (capacity > 0 && n_chunks > 0) NERFB_LAUNCH(vol_write_kernel, grid, VOL_BLOCK, 0, stream, v, n_voxels, neg_step, off, capacity, reinterpret_cast<uint2*>(pairs));
   return NERFB_OK;
 }
 

@@ -36,35 +36,49 @@ sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ p
 
 // S % 4 == 0: one thread per 4 consecutive samples -- 6 depth evaluations for 4 outputs instead of 12, one 8-byte load of
 // (near, far), 16-byte loads / stores of the random numbers and the result.  Same arithmetic, bit-identical output.
+// Two such groups per loop iteration with both groups' loads issued before any arithmetic: the kernel is a pure stream
+// (164 MB in, 164 MB out per 800 x 800 image) and one 16-byte load per thread in flight left HBM at 54 % of the copy rate.
+__device__ __forceinline__ float4 sample4(float2 nf, float4 pr4, float perturb, int use_disp, int i0, int S) {
+  float zc[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const int i = i0 - 1 + k;
+    zc[k] = (i >= 0 && i < S && (perturb > 0.f || (k >= 1 && k <= 4))) ? z_at(nf.x, nf.y, i, S, use_disp) : 0.f;
+  }
+  float o[4] = {zc[1], zc[2], zc[3], zc[4]};
+  if (perturb > 0.f) {                                                                 // rendering.py:215-222
+    const float prv[4] = {pr4.x, pr4.y, pr4.z, pr4.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = i0 + k;
+      const float z = zc[k + 1];
+      const float lower = (i > 0) ? __fmul_rn(0.5f, __fadd_rn(zc[k], z)) : z;
+      const float upper = (i < S - 1) ? __fmul_rn(0.5f, __fadd_rn(z, zc[k + 2])) : z;
+      o[k] = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), __fmul_rn(perturb, prv[k])));
+    }
+  }
+  return make_float4(o[0], o[1], o[2], o[3]);
+}
+
 __global__ void __launch_bounds__(256)
 sample_coarse_v4_kernel(const float* __restrict__ rays, const float* __restrict__ perturb_rand, float perturb,
                         int use_disp, int64_t total4, int S, float* __restrict__ z_out) {
   const int S4 = S >> 2;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total4;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = idx / S4;
-    const int i0 = (int)(idx - r * S4) * 4;
-    const float2 nf = __ldg(reinterpret_cast<const float2*>(rays + r * 8 + 6));
-    float zc[6];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const int i = i0 - 1 + k;
-      zc[k] = (i >= 0 && i < S && (perturb > 0.f || (k >= 1 && k <= 4))) ? z_at(nf.x, nf.y, i, S, use_disp) : 0.f;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total4; idx += 2 * stride) {
+    const int64_t idx1 = idx + stride;
+    const bool two = idx1 < total4;
+    const int64_t r0 = idx / S4, r1 = two ? idx1 / S4 : r0;
+    const int i00 = (int)(idx - r0 * S4) * 4, i01 = two ? (int)(idx1 - r1 * S4) * 4 : i00;
+    const float2 nf0 = __ldg(reinterpret_cast<const float2*>(rays + r0 * 8 + 6));
+    const float2 nf1 = __ldg(reinterpret_cast<const float2*>(rays + r1 * 8 + 6));
+    float4 pr0 = make_float4(0.f, 0.f, 0.f, 0.f), pr1 = pr0;
+    if (perturb > 0.f) {
+      pr0 = __ldg(reinterpret_cast<const float4*>(perturb_rand + r0 * S + i00));
+      if (two) pr1 = __ldg(reinterpret_cast<const float4*>(perturb_rand + r1 * S + i01));
     }
-    float o[4] = {zc[1], zc[2], zc[3], zc[4]};
-    if (perturb > 0.f) {                                                                 // rendering.py:215-222
-      const float4 pr4 = __ldg(reinterpret_cast<const float4*>(perturb_rand + r * S + i0));
-      const float prv[4] = {pr4.x, pr4.y, pr4.z, pr4.w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = i0 + k;
-        const float z = zc[k + 1];
-        const float lower = (i > 0) ? __fmul_rn(0.5f, __fadd_rn(zc[k], z)) : z;
-        const float upper = (i < S - 1) ? __fmul_rn(0.5f, __fadd_rn(z, zc[k + 2])) : z;
-        o[k] = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), __fmul_rn(perturb, prv[k])));
-      }
-    }
-    *reinterpret_cast<float4*>(z_out + r * S + i0) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(z_out + r0 * S + i00) = sample4(nf0, pr0, perturb, use_disp, i00, S);
+    if (two) *reinterpret_cast<float4*>(z_out + r1 * S + i01) = sample4(nf1, pr1, perturb, use_disp, i01, S);
   }
 }
 
@@ -77,7 +91,7 @@ extern "C" int nerfb_sample_coarse(const float* rays, const float* perturb_rand,
   const bool aligned16 = ((reinterpret_cast<uintptr_t>(z_out) | reinterpret_cast<uintptr_t>(perturb_rand)) & 15) == 0 &&
                          (reinterpret_cast<uintptr_t>(rays) & 7) == 0;
   if (n_samples % 4 == 0 && aligned16) {
-    const int64_t total4 = total / 4, want4 = ceil_div64(total4, 256);
+    const int64_t total4 = total / 4, want4 = ceil_div64(total4, 512);      // two groups per thread and iteration
     const int grid4 = (int)(want4 < NERFB_SM_COUNT * 16 ? want4 : NERFB_SM_COUNT * 16);
     NERFB_LAUNCH(sample_coarse_v4_kernel, grid4, 256, 0, stream, rays, perturb_rand, perturb, use_disp, total4, n_samples, z_out);
     return NERFB_OK;

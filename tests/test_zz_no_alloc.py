@@ -92,6 +92,13 @@ def test_pack_vol_static_limits_and_edges():
     assert lib.nerfb_pack_vol_static(v.data_ptr(), 1024, -0.01, 0, 0, n_valid.data_ptr(), _stream()) == 0
     torch.cuda.synchronize()
     assert int(n_valid.item()) == 0
+    # the existing entry point agrees on the empty volume (it used to sum a stale count of its workspace)
+    ws = torch.full((4096,), 0x7F, dtype=torch.uint8, device=DEV)
+    ws_ptr = (ws.data_ptr() + 255) & ~255
+    n_valid.fill_(-7)
+    assert lib.nerfb_pack_vol(v.data_ptr(), 0, -0.01, 0, 0, n_valid.data_ptr(), ws_ptr, 2048, _stream()) == 0
+    torch.cuda.synchronize()
+    assert int(n_valid.item()) == 0
     # bad arguments
     assert lib.nerfb_pack_vol_static(0, 16, -0.01, 0, 0, n_valid.data_ptr(), _stream()) == -1
     assert lib.nerfb_pack_vol_static(v.data_ptr(), 16, -0.01, 0, 4, n_valid.data_ptr(), _stream()) == -1     # capacity without pairs

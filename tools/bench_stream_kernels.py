@@ -51,6 +51,7 @@ zf = ops.resample(z, w, Si, False, u)
 rawf = torch.rand(n, Sf, 4, device=dev)
 noisef = torch.randn(n, Sf, device=dev)
 d_rgb = torch.randn(n, 3, device=dev)
+rawf_copy = torch.empty_like(rawf)
 cases = [
     ("sample_coarse_kernel", lambda: ops.sample_coarse(rays, S, False, 1.0, pr), n * (32 + 8 * S)),
     ("composite_fwd_kernel (64 samples)", lambda: ops.composite_fwd(raw, z, rays, noise, 1.0, True), n * S * 28 + n * 32),
@@ -59,6 +60,10 @@ cases = [
     ("resample_kernel", lambda: ops.resample(z, w, Si, False, u), n * (8 * S + 4 * Si + 4 * Sf)),
     ("resample_kernel (det: render path)", lambda: ops.resample(z, w, Si, True, None), n * (8 * S + 4 * Sf)),
     ("generate_rays_kernel", lambda: ops.generate_rays(torch.eye(3, 4), 800, 800, 1111.1), 640000 * 32),
+    # what the memory system gives torch's own streaming kernels at the SAME sizes (L2 flushed): the ceiling a write-only
+    # kernel like sample_coarse (164 MB out, 20 MB in) or a 2:1 read:write kernel can be held against
+    ("reference: torch fill_ (write-only, size of the z output)", lambda: z.fill_(1.0), z.numel() * 4),
+    ("reference: torch copy_ (read + write, size of raw 128 samples)", lambda: rawf_copy.copy_(rawf), 2 * rawf.numel() * 4),
 ]
 for name, fn, by in cases:
     ms = timed(fn)

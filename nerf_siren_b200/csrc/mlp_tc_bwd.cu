@@ -1208,7 +1208,8 @@ int env_int(const char* name, int dflt) {
 #define NERFB_BWD_FUSED_DEFAULT 2
 #endif
 // The fused launch spins on flags written by OTHER CTAs of the same grid: every one of its NERFB_SM_COUNT CTAs must be resident
-// at once (one per SM; the kernel's shared memory admits exactly one).  Checked per device, once: the device has that many SMs;
+// at once (one per SM; the kernel's shared memory admits exactly one): the launch is COOPERATIVE (gang-scheduled, refused rather
+// than deadlocked when it cannot fit).  Checked per device, once: the device has that many SMs and the kernel fits an SM;
 // anything else (a smaller part, a MIG slice) silently keeps the 3-launch path, which has no such requirement.
 static bool fused_device_ok() {
   static int cached[64] = {};            // 0 unknown, 1 ok, 2 not ok
@@ -1216,7 +1217,14 @@ static bool fused_device_ok() {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
   if (cached[dev] == 0) {
     int sms = 0;
-    cached[dev] = (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms >= NERFB_SM_COUNT) ? 1 : 2;
+    int per_sm = 0;
+    const size_t smem_f = (sizeof(SmemD) > sizeof(SmemW) ? sizeof(SmemD) : sizeof(SmemW)) + 1024;
+    const bool ok = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms >= NERFB_SM_COUNT &&
+                    cudaFuncSetAttribute(mlp_tc_bwd_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f) == cudaSuccess &&
+                    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mlp_tc_bwd_fused_kernel<false>, NUM_THREADS, smem_f) == cudaSuccess &&
+                    per_sm >= 1;
+    if (!ok) cudaGetLastError();
+    cached[dev] = ok ? 1 : 2;
   }
   return cached[dev] == 1;
 }
@@ -1414,8 +1422,20 @@ int tc_mlp_bwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     fa.d.trace_chain = g_trace_bwd ? g_trace_bwd + 120 * 8 : nullptr;
     NERFB_CUDA(cudaMemsetAsync(flags, 0, (size_t)fp.flags_bytes, (cudaStream_t)stream));
     if (d.n_cls > 0) NERFB_CUDA(cudaMemsetAsync(fa.w.aux + 16 * 256, 0, 128 * 4, (cudaStream_t)stream));
-    if (pl.prog.siren) NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<true>, fp.grid, NUM_THREADS, smem_f, stream, fa);
-    else NERFB_LAUNCH(mlp_tc_bwd_fused_kernel<false>, fp.grid, NUM_THREADS, smem_f, stream, fa);
+    {
+      // COOPERATIVE launch: the CTAs of this grid spin on flags written by one another, so all of them must be resident at
+      // once.  A cooperative launch is gang-scheduled (it starts only when the whole grid fits, also next to other work on
+      // the device) and is refused with an error -- instead of deadlocking until the bounded waits trap -- when it can never fit.
+      cudaLaunchConfig_t lc = {};
+      lc.gridDim = dim3((unsigned)fp.grid); lc.blockDim = dim3(NUM_THREADS); lc.dynamicSmemBytes = smem_f; lc.stream = (cudaStream_t)stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+      lc.attrs = at; lc.numAttrs = 1;
+      cudaError_t le = pl.prog.siren ? cudaLaunchKernelEx(&lc, mlp_tc_bwd_fused_kernel<true>, fa)
+                                     : cudaLaunchKernelEx(&lc, mlp_tc_bwd_fused_kernel<false>, fa);
+      g_nerfb_launches.fetch_add(1, std::memory_order_relaxed);
+      if (le != cudaSuccess) { cudaGetLastError(); return (int)le; }
+    }
     NERFB_LAUNCH(reduce_partials_fused_kernel, dim3(fa.w.n_items, 32), 256, 0, stream, fa.w, fa.fc);
     if (d.n_cls > 0) {
       const NerfOffsets o = nerf_offsets(d);

@@ -188,6 +188,22 @@ int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* dec
                           float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
                           float* opacity_final, float* depths_fine_out, void* workspace, void* stream);
 
+/* ---- (6b) EG3D training: backward of the field and of the marcher ------------------------------------------------
+ * The reference trains through F.grid_sample + OSGDecoder + MipRayMarcher2 with torch autograd (system.py:22,75,111-120 ->
+ * eg3d_training/eg3d_renderer.py:47-60 -> volumetric_rendering/renderer.py:94-142); importance depths are detached there
+ * (renderer.py:215), so a training step is field(all samples) -> sort by depth -> marcher and these two entries are its
+ * backward.  Both recompute their forward (nothing is saved) and ACCUMULATE into their outputs where noted.
+ * nerfb_triplane_field_bwd: d_rgb (P,3), d_sigma (P) -> d_planes_cl (3,H,W,32) += (fp32 atomics; zero it first),
+ *   d_decoder (2372 floats, layout of `decoder`: W1 | b1 | W2 | b2, raw parameters) +=.
+ * nerfb_mip_march_bwd: d_rgb (R,3) / d_depth (R) / d_weights (R,S-1), each may be null -> d_colors (R,S,3), d_densities
+ *   (R,S) (overwritten).  n_samples <= 512.  Depths are not differentiated. */
+int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                             const float* coords, int64_t n_points, float box_warp, const float* d_rgb,
+                             const float* d_sigma, float* d_planes_cl, float* d_decoder, void* stream);
+int nerfb_mip_march_bwd(const float* colors, const float* densities, const float* depths, int64_t n_rays,
+                        int n_samples, int white_back, const float* d_rgb, const float* d_depth,
+                        const float* d_weights, float* d_colors, float* d_densities, void* stream);
+
 /* ---- the whole inference render behind ONE call (SURVEY 8b `nerfb_render_fused_fwd`, 7 step 4) ----------------
  * Replaces models/rendering.py:193-262 for inference (eval.py:85-96 with test_time=True, system.py:207-216 under no_grad):
  * sampling (:206-222) -> coarse embedding + MLP (:129-159) -> compositing (:161-190) -> sample_pdf + sort (:241-247) ->

@@ -65,6 +65,8 @@ SIGNATURES = {
     "nerfb_triplane_relayout": (_I, [_P, _I, _I, _I, _P, _P]),
     "nerfb_triplane_field": (_I, [_P, _I, _I, _P, _F, _P, _L, _F, _P, _P, _P]),
     "nerfb_mip_march": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P]),
+    "nerfb_triplane_field_bwd": (_I, [_P, _I, _I, _P, _F, _P, _L, _F, _P, _P, _P, _P, _P]),
+    "nerfb_mip_march_bwd": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P, _P]),
     "nerfb_triplane_render": (_I, [_P, _I, _I, _P, _F, _P, _P, _L, _I, _I, C.c_double, C.c_double, _P, _P, _I, _F, _I,
                                    _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_generate_rays": (_I, [_P, _I, _I, C.c_double, _F, _F, _I, _P, _P]),

@@ -381,6 +381,225 @@ __global__ void __launch_bounds__(TP_WARPS * 32) mip_march_kernel(const float* _
   }
 }
 
+
+// =====================================================================================================================
+// Backward of the stand-alone pieces (EG3D training, system.py:22,75,111-120 of the reference back-propagates through
+// grid_sample + OSGDecoder + MipRayMarcher2).  The fused renderer above stays the no_grad render path; training composes
+//   field (fwd / bwd)  ->  sort by depth (torch)  ->  marcher (fwd / bwd)
+// on the sample depths the fused kernel chose (importance depths are detached in the reference too, renderer.py:215).
+// =====================================================================================================================
+
+constexpr int TP_DEC_PARAMS = TP_HID * TP_C + TP_HID + 4 * TP_HID + 4;      // W1 | b1 | W2 | b2
+
+// d(run_model) for explicit coordinates: given dL/drgb (P,3), dL/dsigma (P) accumulate dL/dplanes (channels-last, fp32 atomics:
+// one coalesced 128-byte red per bilinear tap) and dL/d(decoder parameters) (per-warp register accumulators, one atomic flush).
+// One warp per point, the forward is recomputed (nothing was saved).
+__global__ void __launch_bounds__(TP_WARPS * 32) triplane_field_bwd_kernel(const float* __restrict__ planes, int H, int W,
+    const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
+    const float* __restrict__ d_rgb, const float* __restrict__ d_sigma, float* __restrict__ d_planes, float* __restrict__ d_dec) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  __shared__ __align__(16) float s_scr[TP_WARPS][64];
+  __shared__ float s_part[TP_WARPS][32 * 33];
+  float* scr = s_scr[wib];
+  int2* s_tap = reinterpret_cast<int2*>(scr);
+  float* s_feat = scr + 32;
+  float* part = s_part[wib];
+  Dec dec;
+  load_decoder(dec, decp, lr_mul, lane);
+  const float* b2p = decp + TP_HID * TP_C + TP_HID + 4 * TP_HID;
+  float b2[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) b2[k] = __ldg(b2p + k) * lr_mul;
+  float gw1a[TP_C], gw1b[TP_C], gb1a = 0.f, gb1b = 0.f, gw2a[4], gw2b[4], gb2[4];
+#pragma unroll
+  for (int c = 0; c < TP_C; ++c) { gw1a[c] = 0.f; gw1b[c] = 0.f; }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { gw2a[k] = 0.f; gw2b[k] = 0.f; gb2[k] = 0.f; }
+  for (int64_t p = (int64_t)blockIdx.x * TP_WARPS + wib; p < P; p += (int64_t)gridDim.x * TP_WARPS) {
+    const float x = __fmul_rn(coord_scale, __ldg(coords + p * 3)), y = __fmul_rn(coord_scale, __ldg(coords + p * 3 + 1)),
+                z = __fmul_rn(coord_scale, __ldg(coords + p * 3 + 2));
+    // ---- forward, keeping the intermediates ----
+    int off; float wt;
+    tap_lane(H, W, x, y, z, lane, off, wt);
+    if (lane < 12) s_tap[lane] = make_int2(off, __float_as_int(wt));
+    __syncwarp();
+    int offs[12]; float wts[12];
+    float fsum = 0.f;
+#pragma unroll
+    for (int t = 0; t < 12; ++t) {
+      const int2 q = s_tap[t];
+      offs[t] = q.x; wts[t] = __int_as_float(q.y);
+    }
+#pragma unroll
+    for (int pl = 0; pl < 3; ++pl) {
+      float acc = __ldg(planes + offs[4 * pl] + lane) * wts[4 * pl];
+      acc = fmaf(__ldg(planes + offs[4 * pl + 1] + lane), wts[4 * pl + 1], acc);
+      acc = fmaf(__ldg(planes + offs[4 * pl + 2] + lane), wts[4 * pl + 2], acc);
+      acc = fmaf(__ldg(planes + offs[4 * pl + 3] + lane), wts[4 * pl + 3], acc);
+      fsum += acc;
+    }
+    const float f = fsum / 3.f;                              // sampled_features.mean(1)
+    s_feat[lane] = f;
+    __syncwarp();
+    float pa = dec.b1a, pb = dec.b1b;
+#pragma unroll
+    for (int c = 0; c < TP_C; ++c) { const float fc = s_feat[c]; pa = fmaf(dec.w1a[c], fc, pa); pb = fmaf(dec.w1b[c], fc, pb); }
+    const float ha = softplusf(pa), hb = softplusf(pb);
+    float o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = warp_sum(fmaf(dec.w2a[k], ha, dec.w2b[k] * hb)) + b2[k];
+    // ---- upstream: sigma = o[0]; rgb_k = sigmoid(o[k]) * 1.002 - 0.001 (triplane.py:165) ----
+    float go[4];
+    go[0] = __ldg(d_sigma + p);
+#pragma unroll
+    for (int k = 1; k < 4; ++k) {
+      const float s = 1.f / (1.f + __expf(-o[k]));
+      go[k] = __ldg(d_rgb + p * 3 + k - 1) * 1.002f * s * (1.f - s);
+    }
+    float dha = 0.f, dhb = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      gw2a[k] = fmaf(go[k], ha, gw2a[k]); gw2b[k] = fmaf(go[k], hb, gw2b[k]); gb2[k] += go[k];
+      dha = fmaf(dec.w2a[k], go[k], dha); dhb = fmaf(dec.w2b[k], go[k], dhb);
+    }
+    // softplus'(x) = sigmoid(x) (1 beyond the threshold of 20)
+    const float dpa = dha * (pa > 20.f ? 1.f : 1.f / (1.f + __expf(-pa)));
+    const float dpb = dhb * (pb > 20.f ? 1.f : 1.f / (1.f + __expf(-pb)));
+    gb1a += dpa; gb1b += dpb;
+#pragma unroll
+    for (int c = 0; c < TP_C; ++c) {
+      const float fc = s_feat[c];
+      gw1a[c] = fmaf(dpa, fc, gw1a[c]); gw1b[c] = fmaf(dpb, fc, gw1b[c]);
+      part[c * 33 + lane] = fmaf(dec.w1a[c], dpa, dec.w1b[c] * dpb);       // this lane's two hidden units' share of dL/dfeat[c]
+    }
+    __syncwarp();
+    float df = 0.f;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) df += part[lane * 33 + j];                  // lane = channel
+    df *= (1.f / 3.f);
+#pragma unroll
+    for (int t = 0; t < 12; ++t)
+      if (wts[t] != 0.f) atomicAdd(d_planes + offs[t] + lane, df * wts[t]);
+    __syncwarp();
+  }
+  // ---- flush the decoder gradients: effective -> raw parameters (gains of networks_stylegan2.py:109-110); warps combine in
+  // shared memory first so a block issues ONE global atomic per parameter ----
+  __shared__ float s_g[TP_DEC_PARAMS];
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
+  __syncthreads();
+  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
+#pragma unroll
+  for (int c = 0; c < TP_C; ++c) {
+    atomicAdd(s_g + lane * TP_C + c, gw1a[c] * g1);
+    atomicAdd(s_g + (lane + 32) * TP_C + c, gw1b[c] * g1);
+  }
+  float* gb1 = s_g + TP_HID * TP_C;
+  atomicAdd(gb1 + lane, gb1a * lr_mul); atomicAdd(gb1 + lane + 32, gb1b * lr_mul);
+  float* gw2 = gb1 + TP_HID;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    atomicAdd(gw2 + k * TP_HID + lane, gw2a[k] * g2);
+    atomicAdd(gw2 + k * TP_HID + lane + 32, gw2b[k] * g2);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) atomicAdd(gw2 + 4 * TP_HID + k, gb2[k] * lr_mul);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) atomicAdd(d_dec + i, s_g[i]);
+}
+
+// d(MipRayMarcher2.run_forward) (ray_marcher.py:25-57): one warp per ray, forward recomputed.  With G_i = dL/dw_i collected from
+// every path (weights, rgb = sum w c_mid [+ 1 - sum w], depth = sum w z_mid / sum w), t_i = 1 - alpha_i + 1e-10, T_i = prod_{j<i} t_j:
+//   dL/dalpha_i = G_i T_i - (sum_{k>i} G_k w_k) / t_i,   dL/ddens_mid_i = dL/dalpha_i * delta_i * exp(-dens_i delta_i) * sigmoid(pre_i),
+//   dL/dc_mid_i = w_i dL/drgb;  mid-point values split their gradient half / half onto the two samples of the interval.
+// The depth clamp to the call-global [min, max] never binds for a weighted mean of the ray's own mid-points; sum w = 0 (depth = inf ->
+// clamped constant) passes no depth gradient.  Depths are not differentiated (the reference detaches the importance samples).
+__global__ void __launch_bounds__(TP_WARPS * 32) mip_march_bwd_kernel(const float* __restrict__ colors, const float* __restrict__ dens,
+    const float* __restrict__ depths, int64_t R, int S, int white_back, const float* __restrict__ g_rgb, const float* __restrict__ g_depth,
+    const float* __restrict__ g_w, float* __restrict__ d_colors, float* __restrict__ d_dens) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* s = smem + (size_t)wib * 9 * S;
+  float *s_d = s, *s_sig = s + S, *s_r = s + 2 * S, *s_g = s + 3 * S, *s_b = s + 4 * S;
+  float *s_T = s + 5 * S, *s_G = s + 6 * S, *s_w = s + 7 * S, *s_dp = s + 8 * S;       // per interval
+  for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < R; r += (int64_t)gridDim.x * TP_WARPS) {
+    for (int i = lane; i < S; i += 32) {
+      s_d[i] = __ldg(depths + r * S + i); s_sig[i] = __ldg(dens + r * S + i);
+      s_r[i] = __ldg(colors + (r * S + i) * 3); s_g[i] = __ldg(colors + (r * S + i) * 3 + 1); s_b[i] = __ldg(colors + (r * S + i) * 3 + 2);
+    }
+    __syncwarp();
+    const float gr = g_rgb ? __ldg(g_rgb + r * 3) : 0.f, gg = g_rgb ? __ldg(g_rgb + r * 3 + 1) : 0.f, gb = g_rgb ? __ldg(g_rgb + r * 3 + 2) : 0.f;
+    const float gd = g_depth ? __ldg(g_depth + r) : 0.f;
+    // pass 1: forward; T_i, w_i per interval; sum w, sum w z_mid
+    float carry = 1.f, wsum = 0.f, wz = 0.f;
+    for (int base = 0; base < S - 1; base += 32) {
+      const int i = base + lane;
+      const bool on = i < S - 1;
+      float alpha = 0.f, zmid = 0.f;
+      if (on) {
+        const float d0 = s_d[i], d1 = s_d[i + 1];
+        zmid = 0.5f * (d0 + d1);
+        const float dm = softplusf(0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f);
+        alpha = 1.f - expf(-dm * (d1 - d0));
+      }
+      float t = on ? (1.f - alpha) + 1e-10f : 1.f;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t *= q; }
+      float excl = __shfl_up_sync(0xffffffffu, t, 1);
+      if (lane == 0) excl = 1.f;
+      const float T = carry * excl;
+      carry *= __shfl_sync(0xffffffffu, t, 31);
+      const float w = on ? alpha * T : 0.f;
+      if (on) { s_T[i] = T; s_w[i] = w; }
+      wsum += w; wz = fmaf(w, zmid, wz);
+    }
+    wsum = warp_sum(wsum); wz = warp_sum(wz);
+    const bool depth_ok = gd != 0.f && wsum > 0.f;
+    const float depth = depth_ok ? wz / wsum : 0.f;
+    __syncwarp();
+    // G_i
+    for (int i = lane; i < S - 1; i += 32) {
+      const float cr = 0.5f * (s_r[i] + s_r[i + 1]), cg = 0.5f * (s_g[i] + s_g[i + 1]), cb = 0.5f * (s_b[i] + s_b[i + 1]);
+      float G = (g_w ? __ldg(g_w + r * (S - 1) + i) : 0.f) + gr * cr + gg * cg + gb * cb;
+      if (white_back) G -= gr + gg + gb;
+      if (depth_ok) G += gd * (0.5f * (s_d[i] + s_d[i + 1]) - depth) / wsum;
+      s_G[i] = G;
+    }
+    __syncwarp();
+    // pass 2: backward over the intervals with a running suffix sum of G_k w_k
+    float suffix = 0.f;
+    for (int base = ((S - 2) / 32) * 32; base >= 0; base -= 32) {
+      const int i = base + lane;
+      const bool on = i < S - 1;
+      const float gw = on ? s_G[i] * s_w[i] : 0.f;
+      float incl = gw;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_down_sync(0xffffffffu, incl, o); if (lane + o < 32) incl += q; }
+      const float after = suffix + (incl - gw);
+      suffix += __shfl_sync(0xffffffffu, incl, 0);
+      if (on) {
+        const float d0 = s_d[i], d1 = s_d[i + 1], delta = d1 - d0;
+        const float pre = 0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f;
+        const float dm = softplusf(pre);
+        const float e = expf(-dm * delta);                   // 1 - alpha
+        const float t = e + 1e-10f;
+        const float dalpha = s_G[i] * s_T[i] - after / t;
+        const float sg = pre > 20.f ? 1.f : 1.f / (1.f + __expf(-pre));
+        s_dp[i] = dalpha * delta * e * sg;                   // dL/d(dens_mid before the softplus shift)
+      }
+    }
+    __syncwarp();
+    for (int i = lane; i < S; i += 32) {
+      const float a = i < S - 1 ? s_dp[i] : 0.f, b = i > 0 ? s_dp[i - 1] : 0.f;
+      d_dens[r * S + i] = 0.5f * (a + b);
+      const float wc = 0.5f * ((i < S - 1 ? s_w[i] : 0.f) + (i > 0 ? s_w[i - 1] : 0.f));
+      d_colors[(r * S + i) * 3 + 0] = wc * gr; d_colors[(r * S + i) * 3 + 1] = wc * gg; d_colors[(r * S + i) * 3 + 2] = wc * gb;
+    }
+    __syncwarp();
+  }
+}
+
 inline int grid_for(int64_t units) {
   const int64_t want = ceil_div64(units, TP_WARPS);
   const int64_t cap = (int64_t)NERFB_SM_COUNT * 8;           // 8 resident 256-thread CTAs per SM
@@ -456,5 +675,33 @@ extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const
   const int64_t cap = (int64_t)NERFB_SM_COUNT * 2;
   NERFB_LAUNCH(triplane_render_kernel, (int)(want < cap ? want : cap), TP_WARPS * 32, smem, stream, a);
   NERFB_LAUNCH(depth_clamp_kernel, (unsigned)ceil_div64(n_rays, 256), 256, 0, stream, depth_coarse, depth_final, n_rays, a.mm);
+  return NERFB_OK;
+}
+
+// ---- backward entries (EG3D training) ------------------------------------------------------------------------------
+extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                        const float* coords, int64_t n_points, float box_warp, const float* d_rgb,
+                                        const float* d_sigma, float* d_planes_cl, float* d_decoder, void* stream) {
+  NERFB_CHECK_ARG(planes_cl && decoder && d_planes_cl && d_decoder && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
+  if (n_points == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(coords && d_rgb && d_sigma);
+  const int64_t want = ceil_div64(n_points, TP_WARPS);
+  const int grid = (int)(want < NERFB_SM_COUNT * 2 ? want : NERFB_SM_COUNT * 2);     // one decoder-gradient flush per block
+  NERFB_LAUNCH(triplane_field_bwd_kernel, grid, TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords, n_points,
+               (float)(2.0 / (double)box_warp), d_rgb, d_sigma, d_planes_cl, d_decoder);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_mip_march_bwd(const float* colors, const float* densities, const float* depths, int64_t n_rays,
+                                   int n_samples, int white_back, const float* d_rgb, const float* d_depth,
+                                   const float* d_weights, float* d_colors, float* d_densities, void* stream) {
+  NERFB_CHECK_ARG(d_colors && d_densities && n_rays >= 0 && n_samples >= 2);
+  if (n_samples > 512) return NERFB_E_UNSUPPORTED;
+  if (n_rays == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(colors && densities && depths);
+  const size_t smem = (size_t)TP_WARPS * 9 * n_samples * sizeof(float);
+  if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(mip_march_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NERFB_LAUNCH(mip_march_bwd_kernel, grid_for(n_rays), TP_WARPS * 32, smem, stream, colors, densities, depths, n_rays, n_samples,
+               white_back, d_rgb, d_depth, d_weights, d_colors, d_densities);
   return NERFB_OK;
 }

@@ -5,9 +5,12 @@
     eg3d_training/triplane.py:144-167   OSGDecoder        (over networks_stylegan2.py:95-122 FullyConnectedLayer)
 
 Same class / function names, argument meaning, state-dict keys (``net.0.weight`` ...) and output tuple as the
-reference; all arithmetic runs in the hand-written kernels of csrc/triplane.cu (kernel 6).  Inference only (the
-reference's EG3DSystem renders through this path under ``torch.no_grad`` in eval_eg3d.py:63-75); there is no CPU
-fallback and no torch-op fallback.
+reference; all arithmetic runs in the hand-written kernels of csrc/triplane.cu (kernel 6).  Under ``torch.no_grad`` (the
+reference's eval_eg3d.py:63-75) a render is ONE fused launch per batch element.  With grad enabled and planes / decoder
+parameters that require grad (the reference's training step, system.py:111-120) the same calls run a differentiable
+schedule: field kernel and marcher kernel forward, ``nerfb_triplane_field_bwd`` and ``nerfb_mip_march_bwd`` backward
+(torch autograd only chains them and does the sort / gather of renderer.py:160-170).  There is no CPU fallback and no
+torch-op fallback for the field or the marcher.
 """
 from __future__ import annotations
 
@@ -61,9 +64,14 @@ class OSGDecoder(nn.Module):
             nn.Softplus(),
             FullyConnectedLayer(self.hidden_dim, 1 + options.get("decoder_output_dim", 3), lr_multiplier=self.lr_mul))
 
-    def flat(self) -> torch.Tensor:
-        return torch.cat([self.net[0].weight.reshape(-1), self.net[0].bias, self.net[2].weight.reshape(-1),
-                          self.net[2].bias]).detach().float().contiguous()
+    def flat(self, detach: bool = True) -> torch.Tensor:
+        """The 2372 raw parameters in the kernels' order.  ``detach=False`` keeps the autograd edge to the four tensors, so a
+        gradient w.r.t. the flat vector is split back onto ``net.{0,2}.{weight,bias}`` by torch."""
+        f = torch.cat([self.net[0].weight.reshape(-1), self.net[0].bias, self.net[2].weight.reshape(-1), self.net[2].bias])
+        return (f.detach() if detach else f).float().contiguous()
+
+    def wants_grad(self) -> bool:
+        return any(p.requires_grad for p in self.parameters())
 
     def forward(self, sampled_features, ray_directions=None):
         raise NotImplementedError(
@@ -94,13 +102,58 @@ class _Planes:
         return self.cl
 
 
-def _refuse_grad(planes, decoder, what):
-    """Kernel (6) is the render path (the reference renders through it under no_grad, eval_eg3d.py:63-75); there is no
-    backward kernel, so a call that autograd would expect to differentiate must fail loudly instead of training nothing."""
-    if torch.is_grad_enabled() and (planes.requires_grad or any(p.requires_grad for p in decoder.parameters())):
-        raise RuntimeError(f"{what}: the EG3D tri-plane path of nerf_siren_b200 is forward-only (no backward kernel for the "
-                           "plane gather / decoder / marcher); call it under torch.no_grad(). EG3D training "
-                           "(system.py:111-120 of the reference) is not provided.")
+def _training(planes, decoder) -> bool:
+    """True when autograd expects this call to be differentiated (grad mode on and a plane / decoder leaf requires grad)."""
+    return torch.is_grad_enabled() and (planes.requires_grad or decoder.wants_grad())
+
+
+class _FieldFn(torch.autograd.Function):
+    """run_model of one batch element (renderer.py:144-151, triplane.py:155-167) with its hand-written backward:
+    forward nerfb_triplane_field, backward nerfb_triplane_field_bwd (recomputes the gather and the hidden layer per point,
+    scatters into channels-last plane gradients).  ``planes`` is the reference layout (3, 32, H, W); coordinates get no
+    gradient (the reference detaches the importance depths, renderer.py:214, and the coarse depths are constants)."""
+
+    @staticmethod
+    def forward(ctx, planes, dec_flat, lr_mul, coords, box_warp):
+        cl = ops.triplane_relayout(planes)
+        rgb, sigma = ops.triplane_field(cl, dec_flat, lr_mul, coords, box_warp)
+        ctx.save_for_backward(cl, dec_flat, coords)
+        ctx.lr_mul, ctx.box_warp = lr_mul, box_warp
+        return rgb, sigma
+
+    @staticmethod
+    def backward(ctx, d_rgb, d_sigma):
+        cl, dec_flat, coords = ctx.saved_tensors
+        d_rgb = torch.zeros(coords.shape[0], 3, device=coords.device) if d_rgb is None else d_rgb.float().contiguous()
+        d_sigma = torch.zeros(coords.shape[0], device=coords.device) if d_sigma is None else d_sigma.float().contiguous()
+        d_cl, d_dec = ops.triplane_field_bwd(cl, dec_flat, ctx.lr_mul, coords, ctx.box_warp, d_rgb, d_sigma)
+        return d_cl.permute(0, 3, 1, 2), d_dec, None, None, None
+
+
+class _MarchFn(torch.autograd.Function):
+    """MipRayMarcher2 (ray_marcher.py:25-57) on (rays, S) rows: forward nerfb_mip_march, backward nerfb_mip_march_bwd.
+    Depths get no gradient (see _FieldFn)."""
+
+    @staticmethod
+    def forward(ctx, colors, densities, depths, white_back):
+        rgb, depth, w = ops.mip_march(colors, densities, depths, white_back)
+        ctx.save_for_backward(colors, densities, depths)
+        ctx.white_back = white_back
+        return rgb, depth, w
+
+    @staticmethod
+    def backward(ctx, d_rgb, d_depth, d_w):
+        colors, densities, depths = ctx.saved_tensors
+        c = lambda t: None if t is None else t.float().contiguous()
+        d_c, d_s = ops.mip_march_bwd(colors, densities, depths, ctx.white_back, c(d_rgb), c(d_depth), c(d_w))
+        return d_c, d_s, None, None
+
+
+def _march(colors, densities, depths, white_back):
+    colors, densities, depths = colors.float().contiguous(), densities.float().contiguous(), depths.float().contiguous()
+    if torch.is_grad_enabled() and (colors.requires_grad or densities.requires_grad):
+        return _MarchFn.apply(colors, densities, depths, bool(white_back))
+    return ops.mip_march(colors, densities, depths, bool(white_back))
 
 
 class MipRayMarcher2(nn.Module):
@@ -113,8 +166,8 @@ class MipRayMarcher2(nn.Module):
         if rendering_options["clamp_mode"] != "softplus":
             assert False, "MipRayMarcher only supports `clamp_mode`=`softplus`!"
         B, R, S, _ = depths.shape
-        rgb, depth, w = ops.mip_march(colors.reshape(B * R, S, 3), densities.reshape(B * R, S), depths.reshape(B * R, S),
-                                      bool(rendering_options.get("white_back", False)))
+        rgb, depth, w = _march(colors.reshape(B * R, S, 3), densities.reshape(B * R, S), depths.reshape(B * R, S),
+                               bool(rendering_options.get("white_back", False)))
         return rgb.view(B, R, 3), depth.view(B, R, 1), w.view(B, R, S - 1, 1)
 
     def forward(self, colors, densities, depths, rendering_options):
@@ -153,7 +206,6 @@ class ImportanceRenderer(nn.Module):
 
     def forward(self, planes, decoder, ray_origins, ray_directions, rendering_options, rand_coarse=None, u=None):
         opts = rendering_options
-        _refuse_grad(planes, decoder, "ImportanceRenderer.forward")
         if opts.get("clamp_mode", "softplus") != "softplus":
             assert False, "MipRayMarcher only supports `clamp_mode`=`softplus`!"
         if opts.get("density_noise", 0) > 0:
@@ -175,8 +227,18 @@ class ImportanceRenderer(nn.Module):
         elif isinstance(rs, torch.Tensor):
             start_arr, end_arr, rs, re = rs, re, 0.0, 0.0
         outs = [[] for _ in range(6)]
+        train = _training(planes, decoder)
         for b in range(B):                          # planes differ per batch element; rays of one element form one launch
             self.seed += 1
+            if train:
+                res = self._forward_train(planes[b], decoder, ray_origins[b].contiguous(), ray_directions[b].contiguous(), opts,
+                                          float(rs), float(re), None if start_arr is None else start_arr[b].reshape(-1).contiguous(),
+                                          None if end_arr is None else end_arr[b].reshape(-1).contiguous(),
+                                          None if rand_coarse is None else rand_coarse[b].reshape(R, -1),
+                                          None if u is None else u.reshape(B, R, -1)[b])
+                for k in range(6):
+                    outs[k].append(res[k])
+                continue
             res = ops.triplane_render(
                 self._cache.get(planes, b) if B == 1 else ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
                 ray_origins[b].contiguous(), ray_directions[b].contiguous(), opts["depth_resolution"], n_imp, float(rs), float(re),
@@ -190,13 +252,53 @@ class ImportanceRenderer(nn.Module):
         rgb_c, depth_c, op_c, rgb_f, depth_f, op_f = [torch.stack(o, 0) for o in outs]
         return rgb_c, depth_c.unsqueeze(-1), op_c.unsqueeze(-1), rgb_f, depth_f.unsqueeze(-1), op_f.unsqueeze(-1)
 
+    def _forward_train(self, planes_b, decoder, o, d, opts, rs, re, start_arr, end_arr, rand_coarse, u):
+        """renderer.py:94-142 for one batch element with an autograd graph.  (1) The fused render kernel runs once WITHOUT
+        grad on explicit random numbers and hands back the importance depths (they are detached in the reference too,
+        renderer.py:214); (2) the coarse depths are the same stratified samples restated with torch ops (renderer.py:172-195,
+        constants for autograd); (3) ONE differentiable field launch decodes all R x (S + Si) points; (4) coarse marcher on
+        the first S samples, sort + gather (renderer.py:160-170), final marcher."""
+        R = o.shape[0]
+        S, Si = int(opts["depth_resolution"]), int(opts["depth_resolution_importance"])
+        wb, disp = bool(opts.get("white_back", False)), bool(opts.get("disparity_space_sampling", False))
+        g = torch.Generator(device=o.device).manual_seed(self.seed)
+        rand_coarse = (torch.rand(R, S, device=o.device, generator=g) if rand_coarse is None else rand_coarse.float()).contiguous()
+        u = (torch.rand(R, Si, device=o.device, generator=g) if u is None else u.float()).contiguous()
+        dec_ng = decoder.flat()
+        with torch.no_grad():
+            cl = ops.triplane_relayout(planes_b.detach())
+            fine = ops.triplane_render(cl, dec_ng, decoder.lr_mul, o, d, S, Si, rs, re, start_arr, end_arr, disp,
+                                       float(opts["box_warp"]), wb, rand_coarse, u, self.seed, return_depths_fine=True)[6]
+            if disp:
+                t = torch.linspace(0, 1, S, device=o.device).expand(R, S) + rand_coarse * (1 / (S - 1))
+                coarse = 1. / (1. / rs * (1. - t) + 1. / re * t)
+            elif start_arr is not None:
+                steps = torch.arange(S, dtype=torch.float32, device=o.device) / (S - 1)
+                span = (end_arr - start_arr).unsqueeze(1)
+                coarse = start_arr.unsqueeze(1) + steps * span + rand_coarse * (span / (S - 1))
+            else:
+                coarse = torch.linspace(rs, re, S, device=o.device).expand(R, S) + rand_coarse * ((re - rs) / (S - 1))
+            depths = torch.cat([coarse, fine], 1)                                            # (R, S + Si)
+            coords = (o.unsqueeze(1) + depths.unsqueeze(-1) * d.unsqueeze(1)).reshape(-1, 3).contiguous()
+        rgb, sigma = _FieldFn.apply(planes_b, decoder.flat(detach=False), decoder.lr_mul, coords, float(opts["box_warp"]))
+        rgb, sigma = rgb.view(R, S + Si, 3), sigma.view(R, S + Si)
+        rgb_c, depth_c, w_c = _march(rgb[:, :S], sigma[:, :S], coarse, wb)
+        all_d, idx = torch.sort(depths, dim=1)
+        rgb_f, depth_f, w_f = _march(torch.gather(rgb, 1, idx.unsqueeze(-1).expand(-1, -1, 3)), torch.gather(sigma, 1, idx), all_d, wb)
+        return rgb_c, depth_c, w_c.sum(1), rgb_f, depth_f, w_f.sum(1)
+
     def run_model(self, planes, decoder, sample_coordinates, sample_directions, options):
         """renderer.py:144-151 -> {'rgb': (N, M, 3), 'sigma': (N, M, 1)}."""
         if options.get("density_noise", 0) > 0:
             raise NotImplementedError("density_noise > 0 is not on the render path")
-        _refuse_grad(planes, decoder, "ImportanceRenderer.run_model")
         N, M, _ = sample_coordinates.shape
         rgbs, sigmas = [], []
+        if _training(planes, decoder):
+            for b in range(N):
+                rgb, sigma = _FieldFn.apply(planes[b], decoder.flat(detach=False), decoder.lr_mul,
+                                            sample_coordinates[b].detach().float().contiguous(), float(options["box_warp"]))
+                rgbs.append(rgb); sigmas.append(sigma)
+            return {"rgb": torch.stack(rgbs, 0), "sigma": torch.stack(sigmas, 0).unsqueeze(-1)}
         for b in range(N):
             rgb, sigma = ops.triplane_field(ops.triplane_relayout(planes[b]), decoder.flat(), decoder.lr_mul,
                                             sample_coordinates[b].contiguous(), float(options["box_warp"]))
@@ -214,8 +316,8 @@ DEFAULT_RENDERING_KWARGS = {
 
 class LearnedPlanes(nn.Module):
     """Stand-in for the plane source: a (1, 96, H, W) feature image held as a parameter (so it moves with ``.to()`` and
-    lands in checkpoints).  It is NOT trainable through this package: kernel (6) has no backward, and the renderer refuses
-    grad-enabled calls.  The reference produces the planes
+    lands in checkpoints).  It trains through the renderer's differentiable schedule (plane gradients come from
+    nerfb_triplane_field_bwd).  The reference produces the planes
     with a StyleGAN2 backbone (``TriPlaneGenerator.backbone.synthesis``, eg3d_training/triplane.py:61), which is outside the
     render_rays path (out of scope); any module / callable returning (B, 96, H, W) can take its place."""
 

@@ -304,6 +304,34 @@ def mip_march(colors, densities, depths, white_back=False):
     return rgb, depth, weights
 
 
+def triplane_field_bwd(planes_cl, decoder_flat, lr_mul, coords, box_warp, d_rgb, d_sigma):
+    """Backward of triplane_field: returns (d_planes_cl (3,H,W,32), d_decoder_flat (2372,))."""
+    h, w = _check_planes_cl(planes_cl)
+    p = coords.shape[0]
+    d_planes = torch.zeros_like(planes_cl)
+    d_dec = torch.zeros_like(decoder_flat)
+    if p == 0:
+        return d_planes, d_dec
+    check(lib.nerfb_triplane_field_bwd(_req(planes_cl, "planes_cl"), h, w, _req(decoder_flat, "decoder"), float(lr_mul),
+                                       _req(coords, "coords"), p, float(box_warp), _req(d_rgb, "d_rgb"), _req(d_sigma, "d_sigma"),
+                                       d_planes.data_ptr(), d_dec.data_ptr(), _stream()), "nerfb_triplane_field_bwd")
+    return d_planes, d_dec
+
+
+def mip_march_bwd(colors, densities, depths, white_back, d_rgb=None, d_depth=None, d_weights=None):
+    """Backward of mip_march: returns (d_colors (R,S,3), d_densities (R,S))."""
+    r, s = depths.shape
+    d_colors = torch.zeros(r, s, 3, device=depths.device, dtype=torch.float32)
+    d_dens = torch.zeros(r, s, device=depths.device, dtype=torch.float32)
+    if r == 0:
+        return d_colors, d_dens
+    check(lib.nerfb_mip_march_bwd(_req(colors, "colors"), _req(densities, "densities"), _req(depths, "depths"), r, s,
+                                  int(bool(white_back)), _req(d_rgb, "d_rgb", allow_none=True), _req(d_depth, "d_depth", allow_none=True),
+                                  _req(d_weights, "d_weights", allow_none=True), d_colors.data_ptr(), d_dens.data_ptr(), _stream()),
+          "nerfb_mip_march_bwd")
+    return d_colors, d_dens
+
+
 def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, n_importance, ray_start, ray_end,
                     ray_start_arr=None, ray_end_arr=None, disparity=False, box_warp=1.0, white_back=False,
                     rand_coarse=None, u=None, seed=0, return_depths_fine=False):
@@ -413,7 +441,7 @@ def _on_tensor_device(fn):
 
 
 for _name in ("sample_coarse", "embed", "composite_fwd", "composite_bwd", "searchsorted", "sample_pdf", "resample",
-              "adam_step", "mlp_fwd", "mlp_bwd", "render_fused", "triplane_relayout", "triplane_field", "mip_march", "triplane_render",
+              "adam_step", "mlp_fwd", "mlp_bwd", "render_fused", "triplane_relayout", "triplane_field", "triplane_field_bwd", "mip_march", "mip_march_bwd", "triplane_render",
               "finish_image", "sigma_grid", "pack_vol"):
     globals()[_name] = _on_tensor_device(globals()[_name])
 del _name

@@ -193,16 +193,20 @@ def test_fresh_plane_tensors_are_never_served_from_the_cache():
         assert not torch.equal(a, b)
 
 
-def test_grad_enabled_calls_are_refused():
-    """Kernel (6) has no backward: a grad-enabled call on trainable planes / decoder raises instead of silently training
-    nothing."""
+def test_untrainable_calls_take_the_fused_path():
+    """Nothing requires grad -> the single fused launch (bit-identical with the no_grad call), grad mode or not.  The
+    differentiable schedule is covered by tests/test_gpu_eg3d_train.py."""
     g = gold("g10_eg3d_small")
     planes, dec, ro, rd, opts = setup(g)
     m = nb().eg3d
     decoder = m.OSGDecoder(32, {"decoder_lr_mul": 1, "decoder_output_dim": 3}).to(DEV)
-    with pytest.raises(RuntimeError, match="forward-only"):
-        m.ImportanceRenderer()(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts)
     for p in decoder.parameters():
         p.requires_grad_(False)
-    out = m.ImportanceRenderer()(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts)      # nothing trainable: allowed
-    assert torch.isfinite(out[3]).all()
+    kw = dict(rand_coarse=g["rand_coarse"].to(DEV), u=g["u"].to(DEV))
+    ren = m.ImportanceRenderer()
+    out = ren(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts, **kw)
+    with torch.no_grad():
+        out2 = ren(planes.to(DEV), decoder, ro.to(DEV), rd.to(DEV), opts, **kw)
+    assert all(torch.equal(a, b) for a, b in zip(out, out2)) and not out[3].requires_grad
+
+

@@ -1,0 +1,195 @@
+"""GPU parity tests for the EG3D training backward (SURVEY rows a11-a13 widened to the reference's training step,
+system.py:111-120): nerfb_triplane_field_bwd and nerfb_mip_march_bwd through the C ABI and through the host mirror's
+autograd functions, against torch autograd over the CPU oracle (oracle/eg3d_oracle.py, fp32; it is pinned to the
+reference by the g10_eg3d_* fixtures).  Tolerances (fp32 on both sides; the kernels accumulate plane gradients with
+atomics and the decoder gradients in another order): relative L2 1e-4 for the unit tests, 2e-3 end to end (the fused
+render's importance depths can land on the other side of a neighbouring sample for a handful of rays; the reference
+detaches them, so the gradient is piecewise smooth in them)."""
+import pytest
+import torch
+
+from oracle import eg3d_oracle as E
+from tests._util import gold
+from tests.test_eg3d_oracle_golden import setup
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+DEC_KEYS = ["net.0.weight", "net.0.bias", "net.2.weight", "net.2.bias"]
+
+
+def nb():
+    import nerf_siren_b200
+    return nerf_siren_b200
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+
+
+def flat(dec):
+    return torch.cat([dec[k].reshape(-1) for k in DEC_KEYS])
+
+
+def leaf_dec(seed, lr_mul=1.0):
+    dec = E.decoder_init(seed=seed)
+    if lr_mul != 1.0:                              # FullyConnectedLayer stores weight / lr_multiplier
+        dec = {k: (v / lr_mul if k.endswith("weight") else v) for k, v in dec.items()}
+    return {k: v.clone().requires_grad_(True) for k, v in dec.items()}
+
+
+@pytest.mark.parametrize("res,n,lr_mul,box", [(16, 700, 1.0, 1.0), (64, 5000, 0.5, 2.0), (33, 257, 2.0, 1.0)])
+def test_field_backward_matches_autograd(res, n, lr_mul, box):
+    """d(planes), d(decoder) of run_model for random cotangents; a third of the points lie outside the box (zero padding:
+    no plane gradient from the taps that fall off the edge) and the plane is not square-friendly in the third case."""
+    planes = (E.planes_init(seed=res, res=res)[0] * 0.7).requires_grad_(True)              # (3, 32, res, res)
+    dec = leaf_dec(res + 1, lr_mul)
+    g = torch.Generator().manual_seed(res + 2)
+    coords = (torch.rand(n, 3, generator=g) - 0.5) * box * 1.5
+    d_rgb, d_sigma = torch.randn(n, 3, generator=g), torch.randn(n, generator=g)
+    rgb, sigma = E.run_model(planes[None], dec, coords[None], box, lr_mul)
+    (rgb[0] * d_rgb).sum().add((sigma[0, :, 0] * d_sigma).sum()).backward()
+    ops = nb().ops
+    cl = ops.triplane_relayout(planes.detach().to(DEV))
+    d_cl, d_dec = ops.triplane_field_bwd(cl, flat(dec).detach().to(DEV), lr_mul, coords.to(DEV), box, d_rgb.to(DEV), d_sigma.to(DEV))
+    assert rel(d_cl.permute(0, 3, 1, 2).cpu(), planes.grad) < 1e-4
+    assert rel(d_dec.cpu(), torch.cat([dec[k].grad.reshape(-1) for k in DEC_KEYS])) < 1e-4
+    # determinism of the decoder part is not promised (atomics), but a second call must agree to rounding
+    d_cl2, d_dec2 = ops.triplane_field_bwd(cl, flat(dec).detach().to(DEV), lr_mul, coords.to(DEV), box, d_rgb.to(DEV), d_sigma.to(DEV))
+    assert rel(d_cl2, d_cl) < 1e-5 and rel(d_dec2, d_dec) < 1e-5
+
+
+def test_field_backward_edges():
+    ops = nb().ops
+    cl = torch.randn(3, 8, 8, 32, device=DEV)
+    dec = torch.randn(2372, device=DEV) * 0.1
+    d_cl, d_dec = ops.triplane_field_bwd(cl, dec, 1.0, torch.zeros(0, 3, device=DEV), 1.0, torch.zeros(0, 3, device=DEV), torch.zeros(0, device=DEV))
+    assert d_cl.shape == cl.shape and not d_cl.any() and not d_dec.any()
+    # all points outside the box: the decoder still sees its biases (gradients on net.0.bias / net.2.*), planes get none
+    co = torch.full((64, 3), 7.0, device=DEV)
+    d_cl, d_dec = ops.triplane_field_bwd(cl, dec, 1.0, co, 1.0, torch.ones(64, 3, device=DEV), torch.ones(64, device=DEV))
+    assert not d_cl.any() and not d_dec[:2048].any() and d_dec[2048:].abs().sum() > 0
+    # NaN coordinate: taps nothing, contributes like an outside point, poisons nothing
+    co[0, 0] = float("nan")
+    d_cl, d_dec = ops.triplane_field_bwd(cl, dec, 1.0, co, 1.0, torch.ones(64, 3, device=DEV), torch.ones(64, device=DEV))
+    assert torch.isfinite(d_cl).all() and torch.isfinite(d_dec).all()
+    with pytest.raises(RuntimeError):
+        ops.triplane_field_bwd(cl.cpu(), dec, 1.0, co, 1.0, torch.ones(64, 3, device=DEV), torch.ones(64, device=DEV))
+
+
+@pytest.mark.parametrize("R,S,white", [(37, 24, False), (200, 96, True), (5, 2, False), (64, 129, True)])
+def test_marcher_backward_matches_autograd(R, S, white):
+    """All three cotangents (rgb, depth, weights) at once; S = 2 is the single-interval edge, S = 129 crosses the 32-lane
+    chunks of the scan; densities span dead (-20) to saturated (+30) intervals."""
+    g = torch.Generator().manual_seed(R * 1000 + S)
+    colors = torch.rand(1, R, S, 3, generator=g).requires_grad_(True)
+    dens = (torch.randn(1, R, S, 1, generator=g) * 6 + 1).requires_grad_(True)
+    depths = (2.0 + torch.rand(1, R, S, 1, generator=g).cumsum(2) * (1.0 / S))
+    d_rgb, d_depth, d_w = torch.randn(R, 3, generator=g), torch.randn(R, generator=g), torch.randn(R, S - 1, generator=g)
+    rgb, depth, w = E.mip_ray_march(colors, dens, depths, white)
+    ((rgb[0] * d_rgb).sum() + (depth[0, :, 0] * d_depth).sum() + (w[0, :, :, 0] * d_w).sum()).backward()
+    ops = nb().ops
+    args = (colors.detach()[0].to(DEV).contiguous(), dens.detach()[0, :, :, 0].to(DEV).contiguous(), depths[0, :, :, 0].to(DEV).contiguous())
+    d_c, d_s = ops.mip_march_bwd(*args, white, d_rgb.to(DEV), d_depth.to(DEV), d_w.to(DEV))
+    assert rel(d_c.cpu(), colors.grad[0]) < 1e-4
+    assert rel(d_s.cpu(), dens.grad[0, :, :, 0]) < 1e-4
+    # each cotangent alone (the other pointers null)
+    for k, kw in enumerate([dict(d_rgb=d_rgb.to(DEV)), dict(d_depth=d_depth.to(DEV)), dict(d_weights=d_w.to(DEV))]):
+        colors.grad = dens.grad = None
+        rgb, depth, w = E.mip_ray_march(colors, dens, depths, white)
+        [(rgb[0] * d_rgb).sum(), (depth[0, :, 0] * d_depth).sum(), (w[0, :, :, 0] * d_w).sum()][k].backward()
+        d_c, d_s = ops.mip_march_bwd(*args, white, **kw)
+        assert rel(d_s.cpu(), dens.grad[0, :, :, 0]) < 1e-4, k
+        if colors.grad is not None and colors.grad.abs().sum() > 0:
+            assert rel(d_c.cpu(), colors.grad[0]) < 1e-4, k
+        else:
+            assert not d_c.any()
+
+
+def test_marcher_backward_empty_ray_has_zero_depth_gradient():
+    """A ray whose weights sum to 0 gets depth = nan -> inf -> clamp (ray_marcher.py:45-47): no gradient through it."""
+    ops = nb().ops
+    colors = torch.rand(3, 8, 3, device=DEV)
+    dens = torch.full((3, 8), -1e4, device=DEV)
+    depths = torch.linspace(1, 2, 8, device=DEV).expand(3, 8).contiguous()
+    d_c, d_s = ops.mip_march_bwd(colors, dens, depths, False, None, torch.ones(3, device=DEV), None)
+    assert torch.isfinite(d_s).all() and not d_s.any() and not d_c.any()
+
+
+@pytest.mark.parametrize("name", ["small", "white", "disp"])
+def test_training_step_gradients_match_oracle_autograd(name):
+    """The host mirror's differentiable schedule end to end (ImportanceRenderer.forward with trainable planes and decoder,
+    the reference's loss: MSE of coarse + fine colours, system.py:111-120 / losses.py) against autograd over the oracle on
+    the fixtures' inputs and random numbers."""
+    gd = gold("g10_eg3d_" + name)
+    planes, dec0, ro, rd, opts = setup(gd)
+    target = torch.rand(ro.shape[1], 3, generator=torch.Generator().manual_seed(3))
+    # oracle
+    p_ref = planes.clone().requires_grad_(True)
+    dec = {k: v.clone().requires_grad_(True) for k, v in dec0.items()}
+    out = E.importance_render(p_ref, dec, ro, rd, opts, gd["rand_coarse"], gd["u"])
+    loss_ref = ((out[0][0] - target) ** 2).mean() + ((out[3][0] - target) ** 2).mean() + 0.1 * out[5].mean() + 0.05 * out[4].mean()
+    loss_ref.backward()
+    # this package
+    m = nb().eg3d
+    decoder = m.OSGDecoder(32, {"decoder_lr_mul": 1, "decoder_output_dim": 3})
+    decoder.load_state_dict(dec0)
+    decoder = decoder.to(DEV)
+    p = torch.nn.Parameter(planes.clone().to(DEV))
+    got = m.ImportanceRenderer()(p, decoder, ro.to(DEV), rd.to(DEV), opts, rand_coarse=gd["rand_coarse"].to(DEV), u=gd["u"].to(DEV))
+    for a, b in zip(got, out):
+        torch.testing.assert_close(a.detach().cpu(), b.detach(), rtol=0, atol=1e-3)
+    t = target.to(DEV)
+    loss = ((got[0][0] - t) ** 2).mean() + ((got[3][0] - t) ** 2).mean() + 0.1 * got[5].mean() + 0.05 * got[4].mean()
+    assert abs(float(loss.detach()) - float(loss_ref.detach())) < 1e-4
+    loss.backward()
+    assert rel(p.grad.cpu(), p_ref.grad) < 2e-3
+    sd = dict(decoder.named_parameters())
+    for k in DEC_KEYS:
+        assert rel(sd[k].grad.cpu(), dec[k].grad) < 2e-3, k
+
+
+def test_training_reduces_the_loss_and_eval_path_sees_the_update():
+    """Ten Adam steps on planes + decoder through EG3D_Renderer.render (the object NeRFSystem_eg3d trains,
+    eg3d_renderer.py:6-67): the loss drops, and the fused no_grad render reflects the updated planes (cache keyed on
+    _version)."""
+    m = nb().eg3d
+    torch.manual_seed(0)
+    kw = dict(m.DEFAULT_RENDERING_KWARGS, depth_resolution=24, depth_resolution_importance=24, ray_start=2.2, ray_end=3.3, box_warp=1.0)
+    ren = m.EG3D_Renderer(m.LearnedPlanes(resolution=64), kw).to(DEV)
+    ro, rd = E.camera_rays(512, seed=1)
+    ro, rd = ro[0].to(DEV), rd[0].to(DEV)
+    target = torch.rand(512, 3, device=DEV) * 0.5 + 0.25
+    opt = torch.optim.Adam(ren.parameters(), lr=2e-2)
+    losses = []
+    with torch.no_grad():
+        before = ren.render(-1, ro, rd)["rgb_fine"].clone()
+    for _ in range(10):
+        opt.zero_grad()
+        out = ren.render(-1, ro, rd)
+        loss = ((out["rgb_coarse"] - target) ** 2).mean() + ((out["rgb_fine"] - target) ** 2).mean()
+        loss.backward()
+        opt.step()
+        losses.append(float(loss.detach()))
+    assert losses[-1] < 0.7 * losses[0], losses
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in ren.parameters())
+    with torch.no_grad():
+        after = ren.render(-1, ro, rd)["rgb_fine"]
+    assert float(((after - target) ** 2).mean()) < float(((before - target) ** 2).mean())
+
+
+def test_run_model_is_differentiable_through_the_mirror():
+    """renderer.run_model (what extract_color_mesh_eg3d.py samples, and what a density regulariser would differentiate)."""
+    m = nb().eg3d
+    planes = E.planes_init(seed=9, res=32)
+    dec0 = E.decoder_init(seed=10)
+    coords = (torch.rand(1, 300, 3, generator=torch.Generator().manual_seed(11)) - 0.5)
+    p_ref = planes.clone().requires_grad_(True)
+    rgb, sigma = E.run_model(p_ref, dec0, coords, 1.0)
+    (rgb.sum() + (sigma ** 2).sum()).backward()
+    decoder = m.OSGDecoder(32, {"decoder_lr_mul": 1, "decoder_output_dim": 3})
+    decoder.load_state_dict(dec0)
+    decoder = decoder.to(DEV)
+    p = torch.nn.Parameter(planes.clone().to(DEV))
+    out = m.ImportanceRenderer().run_model(p, decoder, coords.to(DEV), None, {"box_warp": 1.0})
+    (out["rgb"].sum() + (out["sigma"] ** 2).sum()).backward()
+    assert rel(p.grad.cpu(), p_ref.grad) < 1e-4

@@ -391,107 +391,155 @@ __global__ void __launch_bounds__(TP_WARPS * 32) mip_march_kernel(const float* _
 
 constexpr int TP_DEC_PARAMS = TP_HID * TP_C + TP_HID + 4 * TP_HID + 4;      // W1 | b1 | W2 | b2
 
-// d(run_model) for explicit coordinates: given dL/drgb (P,3), dL/dsigma (P) accumulate dL/dplanes (channels-last, fp32 atomics:
-// one coalesced 128-byte red per bilinear tap) and dL/d(decoder parameters) (per-warp register accumulators, one atomic flush).
-// One warp per point, the forward is recomputed (nothing was saved).
-__global__ void __launch_bounds__(TP_WARPS * 32) triplane_field_bwd_kernel(const float* __restrict__ planes, int H, int W,
+// d(run_model) for explicit coordinates: given dL/drgb (P,3), dL/dsigma (P) accumulate dL/dplanes (channels-last, fp32
+// reductions: each bilinear tap is one 128-byte row, issued as 8 lanes x red.v4.f32, four taps per warp instruction) and
+// dL/d(decoder parameters).  One warp per point, the forward is recomputed (nothing was saved).
+// Register plan (<= 128, two 8-warp blocks per SM): the 64 x 32 first-layer matrix lives in shared memory TWICE -- [c][j] for
+// the forward (lane = hidden units j, j + 32 reads its row conflict-free) and [j][c] for dL/dfeat (lane = channel c) -- and the
+// only large register array is the W1 gradient, kept transposed: lane c accumulates gw1[j] += dpre[j] * feat_c, so the same
+// broadcast of dpre[0..63] (16 LDS.128) feeds both dL/dfeat and the W1 gradient and no cross-lane transposition is needed.
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_field_bwd_kernel(const float* __restrict__ planes, int H, int W,
     const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
     const float* __restrict__ d_rgb, const float* __restrict__ d_sigma, float* __restrict__ d_planes, float* __restrict__ d_dec) {
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  __shared__ __align__(16) float s_scr[TP_WARPS][64];
-  __shared__ float s_part[TP_WARPS][32 * 33];
+  __shared__ __align__(16) float2 s_w1[TP_C * 32];           // [c][lane] = (W1[lane][c], W1[lane + 32][c]), times the layer gain
+  __shared__ __align__(16) float2 s_w1t[(TP_HID / 2) * TP_C];  // [j / 2][c] = (W1[j][c], W1[j + 1][c]), j even
+  __shared__ __align__(16) float s_scr[TP_WARPS][64];        // taps (12 x int2) | features (32)
+  __shared__ __align__(16) float s_dpre[TP_WARPS][TP_HID];
+  __shared__ float s_g[TP_DEC_PARAMS];
+  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
+  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) {
+    const float w = __fmul_rn(__ldg(decp + i), g1);           // i = j * 32 + c
+    const int j = i >> 5, c = i & (TP_C - 1);
+    reinterpret_cast<float*>(s_w1t)[((j >> 1) * TP_C + c) * 2 + (j & 1)] = w;
+    reinterpret_cast<float*>(s_w1)[(c * 32 + (j & 31)) * 2 + (j >> 5)] = w;
+  }
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
   float* scr = s_scr[wib];
   int2* s_tap = reinterpret_cast<int2*>(scr);
   float* s_feat = scr + 32;
-  float* part = s_part[wib];
-  Dec dec;
-  load_decoder(dec, decp, lr_mul, lane);
-  const float* b2p = decp + TP_HID * TP_C + TP_HID + 4 * TP_HID;
-  float b2[4];
+  float* s_dp = s_dpre[wib];
+  const float* b1p = decp + TP_HID * TP_C;
+  const float* w2p = b1p + TP_HID;
+  const float b1a = __ldg(b1p + lane) * lr_mul, b1b = __ldg(b1p + lane + 32) * lr_mul;
+  float w2a[4], w2b[4], b2[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) b2[k] = __ldg(b2p + k) * lr_mul;
-  float gw1a[TP_C], gw1b[TP_C], gb1a = 0.f, gb1b = 0.f, gw2a[4], gw2b[4], gb2[4];
+  for (int k = 0; k < 4; ++k) {
+    w2a[k] = __fmul_rn(__ldg(w2p + k * TP_HID + lane), g2);
+    w2b[k] = __fmul_rn(__ldg(w2p + k * TP_HID + lane + 32), g2);
+    b2[k] = __ldg(w2p + 4 * TP_HID + k) * lr_mul;
+  }
+  float2 gw1[TP_HID / 2];                                     // lane = channel c: dL/dW1_eff[j][c], j = 2 i, 2 i + 1
 #pragma unroll
-  for (int c = 0; c < TP_C; ++c) { gw1a[c] = 0.f; gw1b[c] = 0.f; }
+  for (int j = 0; j < TP_HID / 2; ++j) gw1[j] = make_float2(0.f, 0.f);
+  float gb1a = 0.f, gb1b = 0.f, gw2a[4], gw2b[4], gb2[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) { gw2a[k] = 0.f; gw2b[k] = 0.f; gb2[k] = 0.f; }
-  for (int64_t p = (int64_t)blockIdx.x * TP_WARPS + wib; p < P; p += (int64_t)gridDim.x * TP_WARPS) {
-    const float x = __fmul_rn(coord_scale, __ldg(coords + p * 3)), y = __fmul_rn(coord_scale, __ldg(coords + p * 3 + 1)),
-                z = __fmul_rn(coord_scale, __ldg(coords + p * 3 + 2));
+  __syncthreads();
+  const int grp = lane >> 3, sub4 = (lane & 7) * 4;
+  // the per-point scalars (coordinates, cotangents) of the NEXT point are loaded one iteration ahead
+  const int64_t stride = (int64_t)gridDim.x * TP_WARPS;
+  int64_t p = (int64_t)blockIdx.x * TP_WARPS + wib;
+  float nx = 0.f, ny = 0.f, nz = 0.f, ng0 = 0.f, ng1 = 0.f, ng2 = 0.f, ng3 = 0.f;
+  if (p < P) {
+    nx = __ldg(coords + p * 3); ny = __ldg(coords + p * 3 + 1); nz = __ldg(coords + p * 3 + 2);
+    ng0 = __ldg(d_sigma + p); ng1 = __ldg(d_rgb + p * 3); ng2 = __ldg(d_rgb + p * 3 + 1); ng3 = __ldg(d_rgb + p * 3 + 2);
+  }
+  for (; p < P; p += stride) {
+    const float x = __fmul_rn(coord_scale, nx), y = __fmul_rn(coord_scale, ny), z = __fmul_rn(coord_scale, nz);
+    const float gsig = ng0, gr0 = ng1, gr1 = ng2, gr2 = ng3;
     // ---- forward, keeping the intermediates ----
     int off; float wt;
     tap_lane(H, W, x, y, z, lane, off, wt);
     if (lane < 12) s_tap[lane] = make_int2(off, __float_as_int(wt));
     __syncwarp();
-    int offs[12]; float wts[12];
+    {
+      const int64_t pn = p + stride;
+      if (pn < P) {
+        nx = __ldg(coords + pn * 3); ny = __ldg(coords + pn * 3 + 1); nz = __ldg(coords + pn * 3 + 2);
+        ng0 = __ldg(d_sigma + pn); ng1 = __ldg(d_rgb + pn * 3); ng2 = __ldg(d_rgb + pn * 3 + 1); ng3 = __ldg(d_rgb + pn * 3 + 2);
+      }
+    }
     float fsum = 0.f;
 #pragma unroll
-    for (int t = 0; t < 12; ++t) {
-      const int2 q = s_tap[t];
-      offs[t] = q.x; wts[t] = __int_as_float(q.y);
-    }
-#pragma unroll
     for (int pl = 0; pl < 3; ++pl) {
-      float acc = __ldg(planes + offs[4 * pl] + lane) * wts[4 * pl];
-      acc = fmaf(__ldg(planes + offs[4 * pl + 1] + lane), wts[4 * pl + 1], acc);
-      acc = fmaf(__ldg(planes + offs[4 * pl + 2] + lane), wts[4 * pl + 2], acc);
-      acc = fmaf(__ldg(planes + offs[4 * pl + 3] + lane), wts[4 * pl + 3], acc);
+      const int4 q0 = *reinterpret_cast<const int4*>(s_tap + 4 * pl), q1 = *reinterpret_cast<const int4*>(s_tap + 4 * pl + 2);
+      float acc = __ldg(planes + q0.x + lane) * __int_as_float(q0.y);
+      acc = fmaf(__ldg(planes + q0.z + lane), __int_as_float(q0.w), acc);
+      acc = fmaf(__ldg(planes + q1.x + lane), __int_as_float(q1.y), acc);
+      acc = fmaf(__ldg(planes + q1.z + lane), __int_as_float(q1.w), acc);
       fsum += acc;
     }
     const float f = fsum / 3.f;                              // sampled_features.mean(1)
     s_feat[lane] = f;
     __syncwarp();
-    float pa = dec.b1a, pb = dec.b1b;
+    float2 pab0 = make_float2(b1a, b1b), pab1 = make_float2(0.f, 0.f);      // two-wide FMAs (FFMA2): both hidden units at once
 #pragma unroll
-    for (int c = 0; c < TP_C; ++c) { const float fc = s_feat[c]; pa = fmaf(dec.w1a[c], fc, pa); pb = fmaf(dec.w1b[c], fc, pb); }
+    for (int c4 = 0; c4 < TP_C; c4 += 4) {
+      const float4 fc = *reinterpret_cast<const float4*>(s_feat + c4);
+      pab0 = __ffma2_rn(s_w1[(c4 + 0) * 32 + lane], make_float2(fc.x, fc.x), pab0);
+      pab1 = __ffma2_rn(s_w1[(c4 + 1) * 32 + lane], make_float2(fc.y, fc.y), pab1);
+      pab0 = __ffma2_rn(s_w1[(c4 + 2) * 32 + lane], make_float2(fc.z, fc.z), pab0);
+      pab1 = __ffma2_rn(s_w1[(c4 + 3) * 32 + lane], make_float2(fc.w, fc.w), pab1);
+    }
+    const float pa = pab0.x + pab1.x, pb = pab0.y + pab1.y;
     const float ha = softplusf(pa), hb = softplusf(pb);
     float o[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) o[k] = warp_sum(fmaf(dec.w2a[k], ha, dec.w2b[k] * hb)) + b2[k];
+    for (int k = 0; k < 4; ++k) o[k] = warp_sum(fmaf(w2a[k], ha, w2b[k] * hb)) + b2[k];
     // ---- upstream: sigma = o[0]; rgb_k = sigmoid(o[k]) * 1.002 - 0.001 (triplane.py:165) ----
     float go[4];
-    go[0] = __ldg(d_sigma + p);
+    go[0] = gsig;
+    const float gr[3] = {gr0, gr1, gr2};
 #pragma unroll
     for (int k = 1; k < 4; ++k) {
       const float s = 1.f / (1.f + __expf(-o[k]));
-      go[k] = __ldg(d_rgb + p * 3 + k - 1) * 1.002f * s * (1.f - s);
+      go[k] = gr[k - 1] * 1.002f * s * (1.f - s);
     }
     float dha = 0.f, dhb = 0.f;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       gw2a[k] = fmaf(go[k], ha, gw2a[k]); gw2b[k] = fmaf(go[k], hb, gw2b[k]); gb2[k] += go[k];
-      dha = fmaf(dec.w2a[k], go[k], dha); dhb = fmaf(dec.w2b[k], go[k], dhb);
+      dha = fmaf(w2a[k], go[k], dha); dhb = fmaf(w2b[k], go[k], dhb);
     }
     // softplus'(x) = sigmoid(x) (1 beyond the threshold of 20)
     const float dpa = dha * (pa > 20.f ? 1.f : 1.f / (1.f + __expf(-pa)));
     const float dpb = dhb * (pb > 20.f ? 1.f : 1.f / (1.f + __expf(-pb)));
     gb1a += dpa; gb1b += dpb;
-#pragma unroll
-    for (int c = 0; c < TP_C; ++c) {
-      const float fc = s_feat[c];
-      gw1a[c] = fmaf(dpa, fc, gw1a[c]); gw1b[c] = fmaf(dpb, fc, gw1b[c]);
-      part[c * 33 + lane] = fmaf(dec.w1a[c], dpa, dec.w1b[c] * dpb);       // this lane's two hidden units' share of dL/dfeat[c]
-    }
+    s_dp[lane] = dpa; s_dp[lane + 32] = dpb;
     __syncwarp();
-    float df = 0.f;
-#pragma unroll 8
-    for (int j = 0; j < 32; ++j) df += part[lane * 33 + j];                  // lane = channel
-    df *= (1.f / 3.f);
+    // ---- lane = channel: dL/dfeat_c = sum_j W1[j][c] dpre_j, and the W1 gradient of this channel's column ----
+    float2 dfa = make_float2(0.f, 0.f), dfb = make_float2(0.f, 0.f);
+    const float2 ff = make_float2(f, f);
 #pragma unroll
-    for (int t = 0; t < 12; ++t)
-      if (wts[t] != 0.f) atomicAdd(d_planes + offs[t] + lane, df * wts[t]);
+    for (int j4 = 0; j4 < TP_HID; j4 += 4) {
+      const float4 dq = *reinterpret_cast<const float4*>(s_dp + j4);
+      const float2 d01 = make_float2(dq.x, dq.y), d23 = make_float2(dq.z, dq.w);
+      dfa = __ffma2_rn(s_w1t[(j4 >> 1) * TP_C + lane], d01, dfa);       gw1[j4 >> 1] = __ffma2_rn(d01, ff, gw1[j4 >> 1]);
+      dfb = __ffma2_rn(s_w1t[((j4 >> 1) + 1) * TP_C + lane], d23, dfb); gw1[(j4 >> 1) + 1] = __ffma2_rn(d23, ff, gw1[(j4 >> 1) + 1]);
+    }
+    const float df = ((dfa.x + dfa.y) + (dfb.x + dfb.y)) * (1.f / 3.f);
+    // 8 lanes x 4 channels cover one tap's 128-byte row; the 4 lane groups take the 4 corners of a plane
+    const float v0 = __shfl_sync(0xffffffffu, df, sub4), v1 = __shfl_sync(0xffffffffu, df, sub4 + 1),
+                v2 = __shfl_sync(0xffffffffu, df, sub4 + 2), v3 = __shfl_sync(0xffffffffu, df, sub4 + 3);
+#pragma unroll
+    for (int pl = 0; pl < 3; ++pl) {
+      const int2 q = s_tap[4 * pl + grp];
+      const float w = __int_as_float(q.y);
+      if (w != 0.f) red_add_v4(d_planes + q.x + sub4, v0 * w, v1 * w, v2 * w, v3 * w);
+    }
     __syncwarp();
   }
   // ---- flush the decoder gradients: effective -> raw parameters (gains of networks_stylegan2.py:109-110); warps combine in
   // shared memory first so a block issues ONE global atomic per parameter ----
-  __shared__ float s_g[TP_DEC_PARAMS];
-  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
-  __syncthreads();
-  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
 #pragma unroll
-  for (int c = 0; c < TP_C; ++c) {
-    atomicAdd(s_g + lane * TP_C + c, gw1a[c] * g1);
-    atomicAdd(s_g + (lane + 32) * TP_C + c, gw1b[c] * g1);
+  for (int j = 0; j < TP_HID / 2; ++j) {
+    atomicAdd(s_g + (2 * j) * TP_C + lane, gw1[j].x * g1);
+    atomicAdd(s_g + (2 * j + 1) * TP_C + lane, gw1[j].y * g1);
   }
   float* gb1 = s_g + TP_HID * TP_C;
   atomicAdd(gb1 + lane, gb1a * lr_mul); atomicAdd(gb1 + lane + 32, gb1b * lr_mul);

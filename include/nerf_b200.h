@@ -196,13 +196,25 @@ int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* dec
  * nerfb_triplane_field_bwd: d_rgb (P,3), d_sigma (P) -> d_planes_cl (3,H,W,32) += (fp32 atomics; zero it first),
  *   d_decoder (2372 floats, layout of `decoder`: W1 | b1 | W2 | b2, raw parameters) +=.
  * nerfb_mip_march_bwd: d_rgb (R,3) / d_depth (R) / d_weights (R,S-1), each may be null -> d_colors (R,S,3), d_densities
- *   (R,S) (overwritten).  n_samples <= 512.  Depths are not differentiated. */
+ *   (R,S) (overwritten).  n_samples <= 512.  Depths are not differentiated.
+ * nerfb_triplane_render_train: nerfb_triplane_render (same arguments, same six outputs, same single launch) that also
+ *   writes samples_out (R, 5, S + Si) = depth | sigma | r | g | b of every sample, the S stratified samples first, then the
+ *   Si importance samples, unsorted -- all a training step has to keep between its forward and its backward (coarse
+ *   marcher backward on [0, S), sort by depth + final marcher backward on all, nerfb_triplane_field_bwd on the points
+ *   rays_o + depth * rays_d). */
 int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
                              const float* coords, int64_t n_points, float box_warp, const float* d_rgb,
                              const float* d_sigma, float* d_planes_cl, float* d_decoder, void* stream);
 int nerfb_mip_march_bwd(const float* colors, const float* densities, const float* depths, int64_t n_rays,
                         int n_samples, int white_back, const float* d_rgb, const float* d_depth,
                         const float* d_weights, float* d_colors, float* d_densities, void* stream);
+int nerfb_triplane_render_train(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                                const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                                const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                                float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                                float* opacity_final, float* samples_out, void* workspace, void* stream);
 
 /* ---- the whole inference render behind ONE call (SURVEY 8b `nerfb_render_fused_fwd`, 7 step 4) ----------------
  * Replaces models/rendering.py:193-262 for inference (eval.py:85-96 with test_time=True, system.py:207-216 under no_grad):

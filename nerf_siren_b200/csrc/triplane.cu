@@ -242,6 +242,7 @@ struct RenderArgs {
   const float* rand_coarse; const float* u; uint64_t seed;
   float *rgb_c, *depth_c, *opac_c, *rgb_f, *depth_f, *opac_f;
   float* depths_fine_out;        // optional (R, Si): the importance samples, for stage parity tests
+  float* samples_out;            // optional (R, 5, S + Si): depth | sigma | r | g | b of every sample, coarse then importance, unsorted
   uint32_t* mm;
 };
 
@@ -324,6 +325,10 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
       }
       __syncwarp();
     }
+    if (a.samples_out) {                                     // what the training backward needs (nothing else is saved)
+      float* so = a.samples_out + r * 5 * St;
+      for (int i = lane; i < 5 * St; i += 32) so[i] = A[i];
+    }
     // ---- unify_samples (renderer.py:160-170): rank-by-counting sort of the depths, payload moved along ----
     for (int k = lane; k < St; k += 32) {
       const float xk = A[k];
@@ -394,23 +399,27 @@ constexpr int TP_DEC_PARAMS = TP_HID * TP_C + TP_HID + 4 * TP_HID + 4;      // W
 // d(run_model) for explicit coordinates: given dL/drgb (P,3), dL/dsigma (P) accumulate dL/dplanes (channels-last, fp32
 // reductions: each bilinear tap is one 128-byte row, issued as 8 lanes x red.v4.f32, four taps per warp instruction) and
 // dL/d(decoder parameters).  One warp per point, the forward is recomputed (nothing was saved).
-// Register plan (<= 128, two 8-warp blocks per SM): the 64 x 32 first-layer matrix lives in shared memory TWICE -- [c][j] for
-// the forward (lane = hidden units j, j + 32 reads its row conflict-free) and [j][c] for dL/dfeat (lane = channel c) -- and the
-// only large register array is the W1 gradient, kept transposed: lane c accumulates gw1[j] += dpre[j] * feat_c, so the same
-// broadcast of dpre[0..63] (16 LDS.128) feeds both dL/dfeat and the W1 gradient and no cross-lane transposition is needed.
+// Register plan: the kernel is latency-bound, so registers buy warps.  The 64 x 32 first-layer matrix lives in shared memory
+// TWICE -- [c][j] for the forward (lane = hidden units j, j + 32) and [j][c] for dL/dfeat (lane = channel c).  Its gradient
+// dW1 = sum_p dpre_p (x) feat_p is NOT accumulated per warp (64 registers per lane): every warp parks dpre (64) and feat (32)
+// of TPB_NB points in a block tile, and after a block barrier each of the 256 threads adds the tile's 8 * TPB_NB outer
+// products into the EIGHT entries of dW1 it owns (row j = tid / 4, columns 8 (tid % 4) ..+7).
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-__global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_field_bwd_kernel(const float* __restrict__ planes, int H, int W,
+constexpr int TPB_NB = 4;                        // points per warp between two block barriers
+constexpr int TPB_TILE = TP_WARPS * TPB_NB;      // points per tile
+
+__global__ void __launch_bounds__(TP_WARPS * 32, 3) triplane_field_bwd_kernel(const float* __restrict__ planes, int H, int W,
     const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
     const float* __restrict__ d_rgb, const float* __restrict__ d_sigma, float* __restrict__ d_planes, float* __restrict__ d_dec) {
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   __shared__ __align__(16) float2 s_w1[TP_C * 32];           // [c][lane] = (W1[lane][c], W1[lane + 32][c]), times the layer gain
   __shared__ __align__(16) float2 s_w1t[(TP_HID / 2) * TP_C];  // [j / 2][c] = (W1[j][c], W1[j + 1][c]), j even
-  __shared__ __align__(16) float s_scr[TP_WARPS][64];        // taps (12 x int2) | features (32)
-  __shared__ __align__(16) float s_dpre[TP_WARPS][TP_HID];
-  __shared__ float s_g[TP_DEC_PARAMS];
+  __shared__ __align__(16) float s_scr[TP_WARPS][48];        // taps of two points (2 x 12 x int2)
+  __shared__ __align__(16) float s_tile[TPB_TILE * (TP_HID + TP_C)];      // per point: dpre (64) | feat (32); reused as the flush buffer
+  static_assert(TPB_NB % 2 == 0 && TPB_TILE * (TP_HID + TP_C) >= TP_DEC_PARAMS, "flush buffer aliases the tile");
   const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
   for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) {
     const float w = __fmul_rn(__ldg(decp + i), g1);           // i = j * 32 + c
@@ -418,11 +427,7 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_field_bwd_kernel(co
     reinterpret_cast<float*>(s_w1t)[((j >> 1) * TP_C + c) * 2 + (j & 1)] = w;
     reinterpret_cast<float*>(s_w1)[(c * 32 + (j & 31)) * 2 + (j >> 5)] = w;
   }
-  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
-  float* scr = s_scr[wib];
-  int2* s_tap = reinterpret_cast<int2*>(scr);
-  float* s_feat = scr + 32;
-  float* s_dp = s_dpre[wib];
+  int2* s_tap = reinterpret_cast<int2*>(s_scr[wib]);
   const float* b1p = decp + TP_HID * TP_C;
   const float* w2p = b1p + TP_HID;
   const float b1a = __ldg(b1p + lane) * lr_mul, b1b = __ldg(b1p + lane + 32) * lr_mul;
@@ -433,113 +438,156 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_field_bwd_kernel(co
     w2b[k] = __fmul_rn(__ldg(w2p + k * TP_HID + lane + 32), g2);
     b2[k] = __ldg(w2p + 4 * TP_HID + k) * lr_mul;
   }
-  float2 gw1[TP_HID / 2];                                     // lane = channel c: dL/dW1_eff[j][c], j = 2 i, 2 i + 1
+  float2 gw1[4];                                              // dL/dW1_eff[own_j][own_c + 0..7]
 #pragma unroll
-  for (int j = 0; j < TP_HID / 2; ++j) gw1[j] = make_float2(0.f, 0.f);
+  for (int i = 0; i < 4; ++i) gw1[i] = make_float2(0.f, 0.f);
+  const int own_j = threadIdx.x >> 2, own_c = (threadIdx.x & 3) * 8;
   float gb1a = 0.f, gb1b = 0.f, gw2a[4], gw2b[4], gb2[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) { gw2a[k] = 0.f; gw2b[k] = 0.f; gb2[k] = 0.f; }
   __syncthreads();
   const int grp = lane >> 3, sub4 = (lane & 7) * 4;
-  // the per-point scalars (coordinates, cotangents) of the NEXT point are loaded one iteration ahead
-  const int64_t stride = (int64_t)gridDim.x * TP_WARPS;
-  int64_t p = (int64_t)blockIdx.x * TP_WARPS + wib;
-  float nx = 0.f, ny = 0.f, nz = 0.f, ng0 = 0.f, ng1 = 0.f, ng2 = 0.f, ng3 = 0.f;
-  if (p < P) {
-    nx = __ldg(coords + p * 3); ny = __ldg(coords + p * 3 + 1); nz = __ldg(coords + p * 3 + 2);
-    ng0 = __ldg(d_sigma + p); ng1 = __ldg(d_rgb + p * 3); ng2 = __ldg(d_rgb + p * 3 + 1); ng3 = __ldg(d_rgb + p * 3 + 2);
-  }
-  for (; p < P; p += stride) {
-    const float x = __fmul_rn(coord_scale, nx), y = __fmul_rn(coord_scale, ny), z = __fmul_rn(coord_scale, nz);
-    const float gsig = ng0, gr0 = ng1, gr1 = ng2, gr2 = ng3;
-    // ---- forward, keeping the intermediates ----
-    int off; float wt;
-    tap_lane(H, W, x, y, z, lane, off, wt);
-    if (lane < 12) s_tap[lane] = make_int2(off, __float_as_int(wt));
-    __syncwarp();
-    {
-      const int64_t pn = p + stride;
-      if (pn < P) {
-        nx = __ldg(coords + pn * 3); ny = __ldg(coords + pn * 3 + 1); nz = __ldg(coords + pn * 3 + 2);
-        ng0 = __ldg(d_sigma + pn); ng1 = __ldg(d_rgb + pn * 3); ng2 = __ldg(d_rgb + pn * 3 + 1); ng3 = __ldg(d_rgb + pn * 3 + 2);
+  // tiles of TPB_TILE consecutive points; warp w takes points w * TPB_NB .. + TPB_NB - 1 of the tile
+  const int64_t n_tiles = (P + TPB_TILE - 1) / TPB_TILE;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t p0 = tile * TPB_TILE + wib * TPB_NB;
+    // two points per pass: every first-layer weight fetched from shared memory serves both, and the two dependency chains
+    // (gather -> hidden layer -> warp sums -> dL/dfeat) overlap
+#pragma unroll 1
+    for (int ip = 0; ip < TPB_NB; ip += 2) {
+      float* t_dp0 = s_tile + (wib * TPB_NB + ip) * (TP_HID + TP_C);
+      float* t_dp1 = t_dp0 + (TP_HID + TP_C);
+      float* t_f0 = t_dp0 + TP_HID;
+      float* t_f1 = t_dp1 + TP_HID;
+      if (p0 + ip >= P) {                                     // tail: the tile pass must see zeros
+        t_dp0[lane] = 0.f; t_dp0[lane + 32] = 0.f; t_f0[lane] = 0.f;
+        t_dp1[lane] = 0.f; t_dp1[lane + 32] = 0.f; t_f1[lane] = 0.f;
+        continue;
       }
-    }
-    float fsum = 0.f;
+      const bool two = p0 + ip + 1 < P;                       // an odd tail re-reads the last point with zero cotangents
+      const int64_t pp[2] = {p0 + ip, two ? p0 + ip + 1 : p0 + ip};
+      float go[2][4];
 #pragma unroll
-    for (int pl = 0; pl < 3; ++pl) {
-      const int4 q0 = *reinterpret_cast<const int4*>(s_tap + 4 * pl), q1 = *reinterpret_cast<const int4*>(s_tap + 4 * pl + 2);
-      float acc = __ldg(planes + q0.x + lane) * __int_as_float(q0.y);
-      acc = fmaf(__ldg(planes + q0.z + lane), __int_as_float(q0.w), acc);
-      acc = fmaf(__ldg(planes + q1.x + lane), __int_as_float(q1.y), acc);
-      acc = fmaf(__ldg(planes + q1.z + lane), __int_as_float(q1.w), acc);
-      fsum += acc;
-    }
-    const float f = fsum / 3.f;                              // sampled_features.mean(1)
-    s_feat[lane] = f;
-    __syncwarp();
-    float2 pab0 = make_float2(b1a, b1b), pab1 = make_float2(0.f, 0.f);      // two-wide FMAs (FFMA2): both hidden units at once
+      for (int u = 0; u < 2; ++u) {
+        const float x = __fmul_rn(coord_scale, __ldg(coords + pp[u] * 3)), y = __fmul_rn(coord_scale, __ldg(coords + pp[u] * 3 + 1)),
+                    z = __fmul_rn(coord_scale, __ldg(coords + pp[u] * 3 + 2));
+        const bool on = u == 0 || two;
+        go[u][0] = on ? __ldg(d_sigma + pp[u]) : 0.f;
 #pragma unroll
-    for (int c4 = 0; c4 < TP_C; c4 += 4) {
-      const float4 fc = *reinterpret_cast<const float4*>(s_feat + c4);
-      pab0 = __ffma2_rn(s_w1[(c4 + 0) * 32 + lane], make_float2(fc.x, fc.x), pab0);
-      pab1 = __ffma2_rn(s_w1[(c4 + 1) * 32 + lane], make_float2(fc.y, fc.y), pab1);
-      pab0 = __ffma2_rn(s_w1[(c4 + 2) * 32 + lane], make_float2(fc.z, fc.z), pab0);
-      pab1 = __ffma2_rn(s_w1[(c4 + 3) * 32 + lane], make_float2(fc.w, fc.w), pab1);
-    }
-    const float pa = pab0.x + pab1.x, pb = pab0.y + pab1.y;
-    const float ha = softplusf(pa), hb = softplusf(pb);
-    float o[4];
+        for (int k = 0; k < 3; ++k) go[u][k + 1] = on ? __ldg(d_rgb + pp[u] * 3 + k) : 0.f;
+        int off; float wt;
+        tap_lane(H, W, x, y, z, lane, off, wt);
+        if (lane < 12) s_tap[12 * u + lane] = make_int2(off, __float_as_int(wt));
+      }
+      __syncwarp();
+      // ---- forward, keeping the intermediates ----
+      float f[2];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) o[k] = warp_sum(fmaf(w2a[k], ha, w2b[k] * hb)) + b2[k];
-    // ---- upstream: sigma = o[0]; rgb_k = sigmoid(o[k]) * 1.002 - 0.001 (triplane.py:165) ----
-    float go[4];
-    go[0] = gsig;
-    const float gr[3] = {gr0, gr1, gr2};
+      for (int u = 0; u < 2; ++u) {
+        float fsum = 0.f;
 #pragma unroll
-    for (int k = 1; k < 4; ++k) {
-      const float s = 1.f / (1.f + __expf(-o[k]));
-      go[k] = gr[k - 1] * 1.002f * s * (1.f - s);
-    }
-    float dha = 0.f, dhb = 0.f;
+        for (int pl = 0; pl < 3; ++pl) {
+          const int4 q0 = *reinterpret_cast<const int4*>(s_tap + 12 * u + 4 * pl), q1 = *reinterpret_cast<const int4*>(s_tap + 12 * u + 4 * pl + 2);
+          float acc = __ldg(planes + q0.x + lane) * __int_as_float(q0.y);
+          acc = fmaf(__ldg(planes + q0.z + lane), __int_as_float(q0.w), acc);
+          acc = fmaf(__ldg(planes + q1.x + lane), __int_as_float(q1.y), acc);
+          acc = fmaf(__ldg(planes + q1.z + lane), __int_as_float(q1.w), acc);
+          fsum += acc;
+        }
+        f[u] = fsum / 3.f;                                    // sampled_features.mean(1)
+      }
+      t_f0[lane] = f[0]; t_f1[lane] = f[1];
+      __syncwarp();
+      float2 pre[2] = {make_float2(b1a, b1b), make_float2(b1a, b1b)};       // two-wide FMAs (FFMA2): both hidden units at once
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      gw2a[k] = fmaf(go[k], ha, gw2a[k]); gw2b[k] = fmaf(go[k], hb, gw2b[k]); gb2[k] += go[k];
-      dha = fmaf(w2a[k], go[k], dha); dhb = fmaf(w2b[k], go[k], dhb);
-    }
-    // softplus'(x) = sigmoid(x) (1 beyond the threshold of 20)
-    const float dpa = dha * (pa > 20.f ? 1.f : 1.f / (1.f + __expf(-pa)));
-    const float dpb = dhb * (pb > 20.f ? 1.f : 1.f / (1.f + __expf(-pb)));
-    gb1a += dpa; gb1b += dpb;
-    s_dp[lane] = dpa; s_dp[lane + 32] = dpb;
-    __syncwarp();
-    // ---- lane = channel: dL/dfeat_c = sum_j W1[j][c] dpre_j, and the W1 gradient of this channel's column ----
-    float2 dfa = make_float2(0.f, 0.f), dfb = make_float2(0.f, 0.f);
-    const float2 ff = make_float2(f, f);
+      for (int c4 = 0; c4 < TP_C; c4 += 4) {
+        const float4 fa = *reinterpret_cast<const float4*>(t_f0 + c4), fb = *reinterpret_cast<const float4*>(t_f1 + c4);
+        const float2 wa = s_w1[(c4 + 0) * 32 + lane], wb = s_w1[(c4 + 1) * 32 + lane], wc = s_w1[(c4 + 2) * 32 + lane], wd = s_w1[(c4 + 3) * 32 + lane];
+        pre[0] = __ffma2_rn(wa, make_float2(fa.x, fa.x), pre[0]); pre[1] = __ffma2_rn(wa, make_float2(fb.x, fb.x), pre[1]);
+        pre[0] = __ffma2_rn(wb, make_float2(fa.y, fa.y), pre[0]); pre[1] = __ffma2_rn(wb, make_float2(fb.y, fb.y), pre[1]);
+        pre[0] = __ffma2_rn(wc, make_float2(fa.z, fa.z), pre[0]); pre[1] = __ffma2_rn(wc, make_float2(fb.z, fb.z), pre[1]);
+        pre[0] = __ffma2_rn(wd, make_float2(fa.w, fa.w), pre[0]); pre[1] = __ffma2_rn(wd, make_float2(fb.w, fb.w), pre[1]);
+      }
+      float ha[2], hb[2], o[2][4];
 #pragma unroll
-    for (int j4 = 0; j4 < TP_HID; j4 += 4) {
-      const float4 dq = *reinterpret_cast<const float4*>(s_dp + j4);
-      const float2 d01 = make_float2(dq.x, dq.y), d23 = make_float2(dq.z, dq.w);
-      dfa = __ffma2_rn(s_w1t[(j4 >> 1) * TP_C + lane], d01, dfa);       gw1[j4 >> 1] = __ffma2_rn(d01, ff, gw1[j4 >> 1]);
-      dfb = __ffma2_rn(s_w1t[((j4 >> 1) + 1) * TP_C + lane], d23, dfb); gw1[(j4 >> 1) + 1] = __ffma2_rn(d23, ff, gw1[(j4 >> 1) + 1]);
-    }
-    const float df = ((dfa.x + dfa.y) + (dfb.x + dfb.y)) * (1.f / 3.f);
-    // 8 lanes x 4 channels cover one tap's 128-byte row; the 4 lane groups take the 4 corners of a plane
-    const float v0 = __shfl_sync(0xffffffffu, df, sub4), v1 = __shfl_sync(0xffffffffu, df, sub4 + 1),
-                v2 = __shfl_sync(0xffffffffu, df, sub4 + 2), v3 = __shfl_sync(0xffffffffu, df, sub4 + 3);
+      for (int u = 0; u < 2; ++u) { ha[u] = softplusf(pre[u].x); hb[u] = softplusf(pre[u].y); }
 #pragma unroll
-    for (int pl = 0; pl < 3; ++pl) {
-      const int2 q = s_tap[4 * pl + grp];
-      const float w = __int_as_float(q.y);
-      if (w != 0.f) red_add_v4(d_planes + q.x + sub4, v0 * w, v1 * w, v2 * w, v3 * w);
+      for (int k = 0; k < 4; ++k) {
+        float s0 = fmaf(w2a[k], ha[0], w2b[k] * hb[0]), s1 = fmaf(w2a[k], ha[1], w2b[k] * hb[1]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, d); s1 += __shfl_xor_sync(0xffffffffu, s1, d); }
+        o[0][k] = s0 + b2[k]; o[1][k] = s1 + b2[k];
+      }
+      // ---- upstream: sigma = o[0]; rgb_k = sigmoid(o[k]) * 1.002 - 0.001 (triplane.py:165) ----
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+#pragma unroll
+        for (int k = 1; k < 4; ++k) {
+          const float sg = 1.f / (1.f + __expf(-o[u][k]));
+          go[u][k] *= 1.002f * sg * (1.f - sg);
+        }
+        float dha = 0.f, dhb = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          gw2a[k] = fmaf(go[u][k], ha[u], gw2a[k]); gw2b[k] = fmaf(go[u][k], hb[u], gw2b[k]); gb2[k] += go[u][k];
+          dha = fmaf(w2a[k], go[u][k], dha); dhb = fmaf(w2b[k], go[u][k], dhb);
+        }
+        // softplus'(x) = sigmoid(x) (1 beyond the threshold of 20)
+        const float dpa = dha * (pre[u].x > 20.f ? 1.f : 1.f / (1.f + __expf(-pre[u].x)));
+        const float dpb = dhb * (pre[u].y > 20.f ? 1.f : 1.f / (1.f + __expf(-pre[u].y)));
+        gb1a += dpa; gb1b += dpb;
+        float* t_dp = u ? t_dp1 : t_dp0;
+        t_dp[lane] = dpa; t_dp[lane + 32] = dpb;
+      }
+      __syncwarp();
+      // ---- lane = channel: dL/dfeat_c = sum_j W1[j][c] dpre_j ----
+      float2 dfa[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)}, dfb[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+      for (int j4 = 0; j4 < TP_HID; j4 += 4) {
+        const float4 da = *reinterpret_cast<const float4*>(t_dp0 + j4), db = *reinterpret_cast<const float4*>(t_dp1 + j4);
+        const float2 w01 = s_w1t[(j4 >> 1) * TP_C + lane], w23 = s_w1t[((j4 >> 1) + 1) * TP_C + lane];
+        dfa[0] = __ffma2_rn(w01, make_float2(da.x, da.y), dfa[0]); dfb[0] = __ffma2_rn(w23, make_float2(da.z, da.w), dfb[0]);
+        dfa[1] = __ffma2_rn(w01, make_float2(db.x, db.y), dfa[1]); dfb[1] = __ffma2_rn(w23, make_float2(db.z, db.w), dfb[1]);
+      }
+      // 8 lanes x 4 channels cover one tap's 128-byte row; the 4 lane groups take the 4 corners of a plane
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const float df = ((dfa[u].x + dfa[u].y) + (dfb[u].x + dfb[u].y)) * (1.f / 3.f);
+        const float v0 = __shfl_sync(0xffffffffu, df, sub4), v1 = __shfl_sync(0xffffffffu, df, sub4 + 1),
+                    v2 = __shfl_sync(0xffffffffu, df, sub4 + 2), v3 = __shfl_sync(0xffffffffu, df, sub4 + 3);
+        if (u == 0 || two) {
+#pragma unroll
+          for (int pl = 0; pl < 3; ++pl) {
+            const int2 q = s_tap[12 * u + 4 * pl + grp];
+            const float w = __int_as_float(q.y);
+            if (w != 0.f) red_add_v4(d_planes + q.x + sub4, v0 * w, v1 * w, v2 * w, v3 * w);
+          }
+        }
+      }
+      __syncwarp();
     }
-    __syncwarp();
+    __syncthreads();
+    // ---- the tile's outer products into this thread's 8 entries of dW1 ----
+#pragma unroll 8
+    for (int t = 0; t < TPB_TILE; ++t) {
+      const float* tp = s_tile + t * (TP_HID + TP_C);
+      const float d = tp[own_j];
+      const float4 f0 = *reinterpret_cast<const float4*>(tp + TP_HID + own_c), f1 = *reinterpret_cast<const float4*>(tp + TP_HID + own_c + 4);
+      const float2 dd = make_float2(d, d);
+      gw1[0] = __ffma2_rn(dd, make_float2(f0.x, f0.y), gw1[0]); gw1[1] = __ffma2_rn(dd, make_float2(f0.z, f0.w), gw1[1]);
+      gw1[2] = __ffma2_rn(dd, make_float2(f1.x, f1.y), gw1[2]); gw1[3] = __ffma2_rn(dd, make_float2(f1.z, f1.w), gw1[3]);
+    }
+    __syncthreads();
   }
   // ---- flush the decoder gradients: effective -> raw parameters (gains of networks_stylegan2.py:109-110); warps combine in
   // shared memory first so a block issues ONE global atomic per parameter ----
-#pragma unroll
-  for (int j = 0; j < TP_HID / 2; ++j) {
-    atomicAdd(s_g + (2 * j) * TP_C + lane, gw1[j].x * g1);
-    atomicAdd(s_g + (2 * j + 1) * TP_C + lane, gw1[j].y * g1);
+  float* s_g = s_tile;
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
+  __syncthreads();
+  {
+    float* o = s_g + own_j * TP_C + own_c;                    // sole owner of these 8
+    o[0] = gw1[0].x * g1; o[1] = gw1[0].y * g1; o[2] = gw1[1].x * g1; o[3] = gw1[1].y * g1;
+    o[4] = gw1[2].x * g1; o[5] = gw1[2].y * g1; o[6] = gw1[3].x * g1; o[7] = gw1[3].y * g1;
   }
   float* gb1 = s_g + TP_HID * TP_C;
   atomicAdd(gb1 + lane, gb1a * lr_mul); atomicAdd(gb1 + lane + 32, gb1b * lr_mul);
@@ -692,13 +740,13 @@ extern "C" int nerfb_mip_march(const float* colors, const float* densities, cons
   return NERFB_OK;
 }
 
-extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
-                                     const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
-                                     int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
-                                     const float* ray_end_arr, int disparity, float box_warp, int white_back,
-                                     const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
-                                     float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
-                                     float* opacity_final, float* depths_fine_out, void* workspace, void* stream) {
+static int triplane_render_impl(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                                const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                                const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                                float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                                float* opacity_final, float* depths_fine_out, float* samples_out, void* workspace, void* stream) {
   NERFB_CHECK_ARG(planes_cl && decoder && rgb_coarse && depth_coarse && opacity_coarse && rgb_final && depth_final &&
                   opacity_final && workspace);
   NERFB_CHECK_ARG(n_rays >= 0 && n_samples >= 4 && n_importance >= 1 && H >= 1 && W >= 1 && box_warp != 0.f);
@@ -713,7 +761,7 @@ extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const
   a.end_arr = ray_end_arr; a.disparity = disparity; a.coord_scale = (float)(2.0 / (double)box_warp); a.white_back = white_back;
   a.rand_coarse = rand_coarse; a.u = u; a.seed = seed;
   a.rgb_c = rgb_coarse; a.depth_c = depth_coarse; a.opac_c = opacity_coarse; a.rgb_f = rgb_final; a.depth_f = depth_final;
-  a.opac_f = opacity_final; a.depths_fine_out = depths_fine_out; a.mm = static_cast<uint32_t*>(workspace);
+  a.opac_f = opacity_final; a.depths_fine_out = depths_fine_out; a.samples_out = samples_out; a.mm = static_cast<uint32_t*>(workspace);
   const size_t smem = (size_t)TP_WARPS * (((11 * (n_samples + n_importance) + 2 * n_samples + 3) & ~3) + 128) * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
   if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(triplane_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -726,6 +774,32 @@ extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const
   return NERFB_OK;
 }
 
+extern "C" int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                     const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                     int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                                     const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                                     const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                                     float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                                     float* opacity_final, float* depths_fine_out, void* workspace, void* stream) {
+  return triplane_render_impl(planes_cl, H, W, decoder, lr_mul, rays_o, rays_d, n_rays, n_samples, n_importance, ray_start, ray_end,
+                              ray_start_arr, ray_end_arr, disparity, box_warp, white_back, rand_coarse, u, seed, rgb_coarse, depth_coarse,
+                              opacity_coarse, rgb_final, depth_final, opacity_final, depths_fine_out, nullptr, workspace, stream);
+}
+
+// The same launch, additionally writing every sample's (depth, sigma, r, g, b): the forward of a training step.
+extern "C" int nerfb_triplane_render_train(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
+                                           const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                           int n_importance, double ray_start, double ray_end, const float* ray_start_arr,
+                                           const float* ray_end_arr, int disparity, float box_warp, int white_back,
+                                           const float* rand_coarse, const float* u, uint64_t seed, float* rgb_coarse,
+                                           float* depth_coarse, float* opacity_coarse, float* rgb_final, float* depth_final,
+                                           float* opacity_final, float* samples_out, void* workspace, void* stream) {
+  NERFB_CHECK_ARG(samples_out != nullptr);
+  return triplane_render_impl(planes_cl, H, W, decoder, lr_mul, rays_o, rays_d, n_rays, n_samples, n_importance, ray_start, ray_end,
+                              ray_start_arr, ray_end_arr, disparity, box_warp, white_back, rand_coarse, u, seed, rgb_coarse, depth_coarse,
+                              opacity_coarse, rgb_final, depth_final, opacity_final, nullptr, samples_out, workspace, stream);
+}
+
 // ---- backward entries (EG3D training) ------------------------------------------------------------------------------
 extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
                                         const float* coords, int64_t n_points, float box_warp, const float* d_rgb,
@@ -733,8 +807,8 @@ extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, co
   NERFB_CHECK_ARG(planes_cl && decoder && d_planes_cl && d_decoder && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
   if (n_points == 0) return NERFB_OK;
   NERFB_CHECK_ARG(coords && d_rgb && d_sigma);
-  const int64_t want = ceil_div64(n_points, TP_WARPS);
-  const int grid = (int)(want < NERFB_SM_COUNT * 2 ? want : NERFB_SM_COUNT * 2);     // one decoder-gradient flush per block
+  const int64_t want = ceil_div64(n_points, TPB_TILE);
+  const int grid = (int)(want < NERFB_SM_COUNT * 3 ? want : NERFB_SM_COUNT * 3);     // one decoder-gradient flush per block
   NERFB_LAUNCH(triplane_field_bwd_kernel, grid, TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords, n_points,
                (float)(2.0 / (double)box_warp), d_rgb, d_sigma, d_planes_cl, d_decoder);
   return NERFB_OK;

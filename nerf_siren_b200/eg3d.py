@@ -7,10 +7,11 @@
 Same class / function names, argument meaning, state-dict keys (``net.0.weight`` ...) and output tuple as the
 reference; all arithmetic runs in the hand-written kernels of csrc/triplane.cu (kernel 6).  Under ``torch.no_grad`` (the
 reference's eval_eg3d.py:63-75) a render is ONE fused launch per batch element.  With grad enabled and planes / decoder
-parameters that require grad (the reference's training step, system.py:111-120) the same calls run a differentiable
-schedule: field kernel and marcher kernel forward, ``nerfb_triplane_field_bwd`` and ``nerfb_mip_march_bwd`` backward
-(torch autograd only chains them and does the sort / gather of renderer.py:160-170).  There is no CPU fallback and no
-torch-op fallback for the field or the marcher.
+parameters that require grad (the reference's training step, system.py:111-120) the render is the same fused launch
+that additionally keeps the samples (``nerfb_triplane_render_train``), and its backward is ``nerfb_mip_march_bwd`` (coarse
+samples, then the depth-sorted union) followed by ``nerfb_triplane_field_bwd``; torch only does the sort / gather /
+scatter of renderer.py:160-170.  ``run_model`` and ``MipRayMarcher2`` are differentiable on their own through the same
+two backward kernels.  There is no CPU fallback and no torch-op fallback for the field or the marcher.
 """
 from __future__ import annotations
 
@@ -149,6 +150,49 @@ class _MarchFn(torch.autograd.Function):
         return d_c, d_s, None, None
 
 
+class _RenderFn(torch.autograd.Function):
+    """ImportanceRenderer.forward of one batch element (renderer.py:94-142) as ONE autograd node: the forward is the fused
+    render launch (nerfb_triplane_render_train: the six outputs plus every sample's depth / sigma / colour, 20 bytes per
+    sample, the only thing kept for the backward); the backward runs the marcher backward on the coarse samples and on the
+    depth-sorted union (renderer.py:160-170; the sort / gather / scatter are torch ops), adds the two per-sample
+    cotangents and hands them to the field backward.  Ray origins / directions / depths get no gradient (importance depths
+    are detached in the reference, renderer.py:214)."""
+
+    @staticmethod
+    def forward(ctx, planes, dec_flat, lr_mul, o, d, S, Si, rs, re, start_arr, end_arr, disp, box_warp, wb, rand_coarse, u, seed):
+        cl = ops.triplane_relayout(planes)
+        *outs, samples = ops.triplane_render(cl, dec_flat, lr_mul, o, d, S, Si, rs, re, start_arr, end_arr, disp, box_warp, wb,
+                                             rand_coarse, u, seed, return_samples=True)
+        ctx.save_for_backward(cl, dec_flat, o, d, samples)
+        ctx.cfg = (lr_mul, S, Si, box_warp, wb)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, g_rgb_c, g_depth_c, g_op_c, g_rgb_f, g_depth_f, g_op_f):
+        cl, dec_flat, o, d, samples = ctx.saved_tensors
+        lr_mul, S, Si, box_warp, wb = ctx.cfg
+        R, St = o.shape[0], S + Si
+        c = lambda t: None if t is None else t.float().contiguous()
+        per_w = lambda g, n: None if g is None else g.float().reshape(R, 1).expand(R, n).contiguous()   # opacity = weights.sum()
+        depth, sigma, rgb = samples[:, 0], samples[:, 1], samples[:, 2:5].transpose(1, 2)                # (R,St) (R,St) (R,St,3)
+        d_rgb = torch.zeros(R, St, 3, device=o.device)
+        d_sig = torch.zeros(R, St, device=o.device)
+        if g_rgb_c is not None or g_depth_c is not None or g_op_c is not None:
+            dc, ds = ops.mip_march_bwd(rgb[:, :S].contiguous(), sigma[:, :S].contiguous(), depth[:, :S].contiguous(), wb,
+                                       c(g_rgb_c), c(g_depth_c), per_w(g_op_c, S - 1))
+            d_rgb[:, :S], d_sig[:, :S] = dc, ds
+        if g_rgb_f is not None or g_depth_f is not None or g_op_f is not None:
+            all_d, idx = torch.sort(depth, dim=1, stable=True)
+            idx3 = idx.unsqueeze(-1).expand(-1, -1, 3)
+            dc, ds = ops.mip_march_bwd(torch.gather(rgb, 1, idx3).contiguous(), torch.gather(sigma, 1, idx), all_d, wb,
+                                       c(g_rgb_f), c(g_depth_f), per_w(g_op_f, St - 1))
+            d_rgb.scatter_add_(1, idx3, dc)
+            d_sig.scatter_add_(1, idx, ds)
+        coords = torch.addcmul(o.unsqueeze(1), depth.unsqueeze(-1), d.unsqueeze(1)).reshape(-1, 3)
+        d_cl, d_dec = ops.triplane_field_bwd(cl, dec_flat, lr_mul, coords, box_warp, d_rgb.view(-1, 3), d_sig.view(-1))
+        return (d_cl.permute(0, 3, 1, 2), d_dec) + (None,) * 15
+
+
 def _march(colors, densities, depths, white_back):
     colors, densities, depths = colors.float().contiguous(), densities.float().contiguous(), depths.float().contiguous()
     if torch.is_grad_enabled() and (colors.requires_grad or densities.requires_grad):
@@ -253,39 +297,14 @@ class ImportanceRenderer(nn.Module):
         return rgb_c, depth_c.unsqueeze(-1), op_c.unsqueeze(-1), rgb_f, depth_f.unsqueeze(-1), op_f.unsqueeze(-1)
 
     def _forward_train(self, planes_b, decoder, o, d, opts, rs, re, start_arr, end_arr, rand_coarse, u):
-        """renderer.py:94-142 for one batch element with an autograd graph.  (1) The fused render kernel runs once WITHOUT
-        grad on explicit random numbers and hands back the importance depths (they are detached in the reference too,
-        renderer.py:214); (2) the coarse depths are the same stratified samples restated with torch ops (renderer.py:172-195,
-        constants for autograd); (3) ONE differentiable field launch decodes all R x (S + Si) points; (4) coarse marcher on
-        the first S samples, sort + gather (renderer.py:160-170), final marcher."""
-        R = o.shape[0]
-        S, Si = int(opts["depth_resolution"]), int(opts["depth_resolution_importance"])
-        wb, disp = bool(opts.get("white_back", False)), bool(opts.get("disparity_space_sampling", False))
-        g = torch.Generator(device=o.device).manual_seed(self.seed)
-        rand_coarse = (torch.rand(R, S, device=o.device, generator=g) if rand_coarse is None else rand_coarse.float()).contiguous()
-        u = (torch.rand(R, Si, device=o.device, generator=g) if u is None else u.float()).contiguous()
-        dec_ng = decoder.flat()
-        with torch.no_grad():
-            cl = ops.triplane_relayout(planes_b.detach())
-            fine = ops.triplane_render(cl, dec_ng, decoder.lr_mul, o, d, S, Si, rs, re, start_arr, end_arr, disp,
-                                       float(opts["box_warp"]), wb, rand_coarse, u, self.seed, return_depths_fine=True)[6]
-            if disp:
-                t = torch.linspace(0, 1, S, device=o.device).expand(R, S) + rand_coarse * (1 / (S - 1))
-                coarse = 1. / (1. / rs * (1. - t) + 1. / re * t)
-            elif start_arr is not None:
-                steps = torch.arange(S, dtype=torch.float32, device=o.device) / (S - 1)
-                span = (end_arr - start_arr).unsqueeze(1)
-                coarse = start_arr.unsqueeze(1) + steps * span + rand_coarse * (span / (S - 1))
-            else:
-                coarse = torch.linspace(rs, re, S, device=o.device).expand(R, S) + rand_coarse * ((re - rs) / (S - 1))
-            depths = torch.cat([coarse, fine], 1)                                            # (R, S + Si)
-            coords = (o.unsqueeze(1) + depths.unsqueeze(-1) * d.unsqueeze(1)).reshape(-1, 3).contiguous()
-        rgb, sigma = _FieldFn.apply(planes_b, decoder.flat(detach=False), decoder.lr_mul, coords, float(opts["box_warp"]))
-        rgb, sigma = rgb.view(R, S + Si, 3), sigma.view(R, S + Si)
-        rgb_c, depth_c, w_c = _march(rgb[:, :S], sigma[:, :S], coarse, wb)
-        all_d, idx = torch.sort(depths, dim=1)
-        rgb_f, depth_f, w_f = _march(torch.gather(rgb, 1, idx.unsqueeze(-1).expand(-1, -1, 3)), torch.gather(sigma, 1, idx), all_d, wb)
-        return rgb_c, depth_c, w_c.sum(1), rgb_f, depth_f, w_f.sum(1)
+        """renderer.py:94-142 for one batch element as one autograd node (_RenderFn): the same fused launch as under
+        no_grad -- identical outputs -- which also keeps every sample for the backward."""
+        return _RenderFn.apply(planes_b, decoder.flat(detach=False), decoder.lr_mul, o, d, int(opts["depth_resolution"]),
+                               int(opts["depth_resolution_importance"]), rs, re, start_arr, end_arr,
+                               bool(opts.get("disparity_space_sampling", False)), float(opts["box_warp"]),
+                               bool(opts.get("white_back", False)),
+                               None if rand_coarse is None else rand_coarse.float().contiguous(),
+                               None if u is None else u.float().contiguous(), self.seed)
 
     def run_model(self, planes, decoder, sample_coordinates, sample_directions, options):
         """renderer.py:144-151 -> {'rgb': (N, M, 3), 'sigma': (N, M, 1)}."""

@@ -334,7 +334,11 @@ def mip_march_bwd(colors, densities, depths, white_back, d_rgb=None, d_depth=Non
 
 def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, n_importance, ray_start, ray_end,
                     ray_start_arr=None, ray_end_arr=None, disparity=False, box_warp=1.0, white_back=False,
-                    rand_coarse=None, u=None, seed=0, return_depths_fine=False):
+                    rand_coarse=None, u=None, seed=0, return_depths_fine=False, return_samples=False):
+    """-> (rgb_c, depth_c, opacity_c, rgb_f, depth_f, opacity_f[, depths_fine (R, Si)] [, samples (R, 5, S + Si)]).
+    ``return_samples`` selects nerfb_triplane_render_train (the forward of a training step)."""
+    if return_depths_fine and return_samples:
+        raise ValueError("samples already hold the importance depths: samples[:, 0, n_samples:]")
     h, w = _check_planes_cl(planes_cl)
     if rays_o.dim() != 2 or rays_o.shape[1] != 3 or rays_d.shape != rays_o.shape:
         raise ValueError("rays_o / rays_d must be (R, 3)")
@@ -348,6 +352,17 @@ def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, 
            torch.empty(r, 3, device=dev), torch.empty(r, device=dev), torch.empty(r, device=dev)]
     fine = torch.empty(r, n_importance, device=dev) if return_depths_fine else None
     ws = torch.empty(4, device=dev, dtype=torch.int32)
+    if return_samples:
+        samples = torch.empty(r, 5, n_samples + n_importance, device=dev)
+        if r:
+            check(lib.nerfb_triplane_render_train(
+                _req(planes_cl, "planes_cl"), h, w, _req(decoder_flat, "decoder"), float(lr_mul), _req(rays_o, "rays_o"),
+                _req(rays_d, "rays_d"), r, int(n_samples), int(n_importance), float(ray_start), float(ray_end),
+                _req(ray_start_arr, "ray_start_arr", allow_none=True), _req(ray_end_arr, "ray_end_arr", allow_none=True),
+                int(bool(disparity)), float(box_warp), int(bool(white_back)), _req(rand_coarse, "rand_coarse", allow_none=True),
+                _req(u, "u", allow_none=True), int(seed) & 0xFFFFFFFFFFFFFFFF, *[o.data_ptr() for o in out],
+                samples.data_ptr(), ws.data_ptr(), _stream()), "nerfb_triplane_render_train")
+        return (*out, samples)
     if r == 0:
         return (*out, fine) if return_depths_fine else tuple(out)
     check(lib.nerfb_triplane_render(

@@ -3,8 +3,8 @@ system.py:111-120): nerfb_triplane_field_bwd and nerfb_mip_march_bwd through the
 autograd functions, against torch autograd over the CPU oracle (oracle/eg3d_oracle.py, fp32; it is pinned to the
 reference by the g10_eg3d_* fixtures).  Tolerances (fp32 on both sides; the kernels accumulate plane gradients with
 atomics and the decoder gradients in another order): relative L2 1e-4 for the unit tests, 2e-3 end to end (the fused
-render's importance depths can land on the other side of a neighbouring sample for a handful of rays; the reference
-detaches them, so the gradient is piecewise smooth in them)."""
+render's importance depths differ from the oracle's in the last bits and can land on the other side of a neighbouring
+sample for a handful of rays; the reference detaches them, so the gradient is only piecewise smooth in them)."""
 import pytest
 import torch
 
@@ -138,6 +138,9 @@ def test_training_step_gradients_match_oracle_autograd(name):
     got = m.ImportanceRenderer()(p, decoder, ro.to(DEV), rd.to(DEV), opts, rand_coarse=gd["rand_coarse"].to(DEV), u=gd["u"].to(DEV))
     for a, b in zip(got, out):
         torch.testing.assert_close(a.detach().cpu(), b.detach(), rtol=0, atol=1e-3)
+    with torch.no_grad():                                   # the training forward IS the fused render launch: identical outputs
+        same = m.ImportanceRenderer()(p, decoder, ro.to(DEV), rd.to(DEV), opts, rand_coarse=gd["rand_coarse"].to(DEV), u=gd["u"].to(DEV))
+    assert all(torch.equal(a.detach(), b) for a, b in zip(got, same)) and got[3].requires_grad
     t = target.to(DEV)
     loss = ((got[0][0] - t) ** 2).mean() + ((got[3][0] - t) ** 2).mean() + 0.1 * got[5].mean() + 0.05 * got[4].mean()
     assert abs(float(loss.detach()) - float(loss_ref.detach())) < 1e-4
@@ -175,6 +178,36 @@ def test_training_reduces_the_loss_and_eval_path_sees_the_update():
     with torch.no_grad():
         after = ren.render(-1, ro, rd)["rgb_fine"]
     assert float(((after - target) ** 2).mean()) < float(((before - target) ** 2).mean())
+
+
+def test_render_train_entry_writes_the_samples_of_the_render():
+    """nerfb_triplane_render_train = nerfb_triplane_render + samples (R, 5, S + Si): same six outputs bit for bit; the sample
+    depths are the stratified then the importance depths; sigma / colour equal the stand-alone field at those points; and
+    ray_start / ray_end arrays plus the in-kernel generator are accepted."""
+    gd = gold("g10_eg3d_small")
+    planes, dec0, ro, rd, opts = setup(gd)
+    ops = nb().ops
+    R, S, Si = int(gd["R"]), int(gd["S"]), int(gd["Si"])
+    cl = ops.triplane_relayout(planes[0].to(DEV))
+    dec = flat(dec0).to(DEV)
+    args = (cl, dec, 1.0, ro[0].to(DEV), rd[0].to(DEV), S, Si, opts["ray_start"], opts["ray_end"], None, None, False, opts["box_warp"], False,
+            gd["rand_coarse"].reshape(R, S).to(DEV), gd["u"].reshape(R, Si).to(DEV), 0)
+    plain = ops.triplane_render(*args, return_depths_fine=True)
+    train = ops.triplane_render(*args, return_samples=True)
+    assert all(torch.equal(a, b) for a, b in zip(plain[:6], train[:6]))
+    smp = train[6]
+    assert smp.shape == (R, 5, S + Si) and torch.equal(smp[:, 0, S:], plain[6])
+    torch.testing.assert_close(smp[:, 0, :S].cpu(), gd["depths_coarse"].reshape(R, S), rtol=0, atol=1e-6)
+    coords = (ro[0].to(DEV).unsqueeze(1) + smp[:, 0].unsqueeze(-1) * rd[0].to(DEV).unsqueeze(1)).reshape(-1, 3).contiguous()
+    rgb, sigma = ops.triplane_field(cl, dec, 1.0, coords, opts["box_warp"])
+    torch.testing.assert_close(smp[:, 1].reshape(-1), sigma, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(smp[:, 2:5].transpose(1, 2).reshape(-1, 3), rgb, rtol=0, atol=2e-5)
+    lo, hi = torch.full((R,), 2.3, device=DEV), torch.full((R,), 3.2, device=DEV)
+    auto = ops.triplane_render(cl, dec, 1.0, ro[0].to(DEV), rd[0].to(DEV), S, Si, 0.0, 0.0, lo, hi, False, opts["box_warp"], True, None, None, 7,
+                               return_samples=True)
+    assert torch.isfinite(auto[6]).all() and float(auto[6][:, 0].min()) >= 2.3
+    with pytest.raises(ValueError):
+        ops.triplane_render(*args, return_depths_fine=True, return_samples=True)
 
 
 def test_run_model_is_differentiable_through_the_mirror():

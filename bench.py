@@ -12,6 +12,7 @@
     cls_train     configs[3]: NeRF_3D (CLS=6) semantic-head training (render_rays_3d + MSECELoss), LLFF-shaped rays,
                   8192 rays / GPU                                                                            (weak)
     eg3d          configs[4]: EG3D tri-plane renderer, 3x32x256^2 planes, 128x128 rays, 48+48 samples, one replica / GPU
+    eg3d_train    configs[4] shape, training step (system.py:111-120): planes + OSGDecoder trained on 16,384 rays / step
 
 One "step" = one pass of the hot path over one batch.  `value`: inputs resident in HBM; `e2e`: the same step through the
 public API with HOST (pinned) inputs copied in and the result read back every step.  Every line carries `roofline` (dominant
@@ -243,6 +244,24 @@ def cpu_step_factory(config: str, n_rays: int):
             with torch.no_grad():
                 E.importance_render(planes, dec, ro, rd, opts, rc, u)
         return step, n_rays, f"{n_rays} rays x (48 + 48) samples, tri-plane renderer forward, per step"
+    if config == "eg3d_train":
+        from oracle import eg3d_oracle as E
+        planes = E.planes_init(seed=5, res=256).requires_grad_(True)
+        dec = {k: v.requires_grad_(True) for k, v in E.decoder_init(seed=6).items()}
+        ro, rd = E.camera_rays(n_rays, seed=7)
+        opts = {"depth_resolution": EG3D_S, "depth_resolution_importance": EG3D_S, "ray_start": 2.2, "ray_end": 3.3,
+                "box_warp": 1.0, "white_back": False, "disparity_space_sampling": False, "clamp_mode": "softplus"}
+        g = torch.Generator().manual_seed(1)
+        rc, u = torch.rand(1, n_rays, EG3D_S, 1, generator=g), torch.rand(n_rays, EG3D_S, generator=g)
+        target = torch.rand(n_rays, 3, generator=g)
+        opt = torch.optim.Adam([planes, *dec.values()], lr=1e-3)
+
+        def step():
+            opt.zero_grad()
+            out = E.importance_render(planes, dec, ro, rd, opts, rc, u)
+            (((out[0][0] - target) ** 2).mean() + ((out[3][0] - target) ** 2).mean()).backward()
+            opt.step()
+        return step, n_rays, f"{n_rays} rays x (48 + 48) samples, tri-plane renderer forward + autograd backward + Adam, per step"
     raise ValueError(config)
 
 
@@ -298,6 +317,7 @@ METRICS = {
     "cls_train": "rays/s, NeRF_3D (CLS=6) semantic-head coarse+fine training step (64+64 samples)",
     "eg3d": "rays/s, EG3D tri-plane renderer (3x32x256^2 planes, 48+48 samples)",
     "cls_train_strong": "rays/s, NeRF_3D (CLS=6) semantic-head training step, 8192 rays GLOBAL batch (64+64 samples)",
+    "eg3d_train": "rays/s, EG3D tri-plane renderer training step (3x32x256^2 planes + OSGDecoder, 48+48 samples)",
 }
 WORKLOADS = {
     "train": "configs[1]: NeRF coarse+fine training step, 4096 rays/GPU, 64+64 samples, bf16",
@@ -306,10 +326,12 @@ WORKLOADS = {
     "cls_train": "configs[3]: nerf_cls semantic-head training, LLFF-shaped 504x378 rays, batch 8192 per GPU",
     "eg3d": "configs[4]: EG3D triplane renderer (volumetric_rendering ray_marcher), 3x32x256^2 planes, 96 samples/ray, 128x128 rays",
     "cls_train_strong": "configs[3], strong scaling: nerf_cls semantic-head training, LLFF-shaped rays, 8192 rays global batch split over the GPUs",
+    "eg3d_train": "configs[4] shape, training: planes 3x32x256^2 + OSGDecoder optimised on 128x128 rays, 96 samples/ray, MSE on coarse + fine colours, Adam",
 }
-CPU_SAMPLE_RAYS = {"train": 256, "cls_train": 256, "cls_train_strong": 256, "render": 1024, "siren_render": 1024, "eg3d": 1024}
+CPU_SAMPLE_RAYS = {"train": 256, "cls_train": 256, "cls_train_strong": 256, "render": 1024, "siren_render": 1024, "eg3d": 1024,
+                   "eg3d_train": 512}
 SCALING = {"train": "weak", "cls_train": "weak", "cls_train_strong": "strong", "render": "strong", "siren_render": "strong",
-           "eg3d": "weak"}
+           "eg3d": "weak", "eg3d_train": "weak"}
 
 
 def run_reference(args):
@@ -660,6 +682,94 @@ class Eg3dWorkload:
         return [finish_roofline(r, peaks)]
 
 
+class Eg3dTrainWorkload:
+    """EG3D training step at the configs[4] shape (the reference's EG3DSystem.training_step, system.py:111-120): 16,384 rays
+    of one view against target colours -> EG3D_Renderer.render with grad (one fused launch keeping its samples) -> MSE on
+    coarse + fine colours -> backward (marcher backward x 2, field backward) -> Adam (kernel 5) on planes and decoder.  One
+    independent replica per GPU (the reference trains EG3D on one GPU; nothing to exchange here)."""
+
+    def __init__(self, cx: Ctx):
+        torch, nb = cx.torch, cx.nb
+        from nerf_siren_b200 import synth
+        self.cx = cx
+        kw = dict(nb.eg3d.DEFAULT_RENDERING_KWARGS, depth_resolution=EG3D_S, depth_resolution_importance=EG3D_S, ray_start=2.2,
+                  ray_end=3.3, box_warp=1.0)
+        self.ren = nb.eg3d.EG3D_Renderer(nb.eg3d.LearnedPlanes(resolution=256), kw).to(cx.dev)
+        with torch.no_grad():
+            self.ren.plane_source.planes.copy_(synth.eg3d_planes(256, 32, seed=5).reshape(1, 96, 256, 256))
+        self.params = [p for p in self.ren.parameters()]
+        self.m = [torch.zeros_like(p) for p in self.params]
+        self.v = [torch.zeros_like(p) for p in self.params]
+        o, d = synth.eg3d_camera_rays(EG3D_RAYS, seed=7 + cx.rank)
+        g = torch.Generator().manual_seed(11)
+        tgt = torch.rand(EG3D_RAYS, 3, generator=g)
+        self.h_o, self.h_d, self.h_t = o.pin_memory(), d.pin_memory(), tgt.pin_memory()
+        self.d_o, self.d_d, self.d_t = o.to(cx.dev), d.to(cx.dev), tgt.to(cx.dev)
+        self.n = EG3D_RAYS
+        self.units_per_step = self.n * cx.world
+        self.h2d, self.d2h = self.n * 36, 4
+        self.t = 0
+        self.losses = []
+        self.loss_host = torch.empty(1).pin_memory()
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=cx.dev)
+
+    def _step(self, o, d, tgt):
+        nb = self.cx.nb
+        for p in self.params:
+            p.grad = None
+        out = self.ren.render(-1, o, d)
+        loss = ((out["rgb_coarse"] - tgt) ** 2).mean() + ((out["rgb_fine"] - tgt) ** 2).mean()     # losses.py:8-21 shape
+        loss.backward()
+        self.t += 1
+        for p, m, v in zip(self.params, self.m, self.v):
+            nb.ops.adam_step(p.data.view(-1), p.grad.contiguous().view(-1), m.view(-1), v.view(-1), self.t, lr=1e-3)
+        return loss.detach()
+
+    def step_resident(self, i):
+        self.flush.zero_()
+        self._step(self.d_o, self.d_d, self.d_t)
+
+    def step_e2e(self, i):
+        dev = self.cx.dev
+        self.flush.zero_()
+        loss = self._step(self.h_o.to(dev, non_blocking=True), self.h_d.to(dev, non_blocking=True), self.h_t.to(dev, non_blocking=True))
+        self.loss_host.copy_(loss.reshape(1), non_blocking=True)
+        self.cx.torch.cuda.current_stream().synchronize()
+        self.losses.append(float(self.loss_host[0]))
+
+    def launches(self):
+        return self.cx.nb.ops.launch_count()
+
+    def config(self):
+        return {"rays_per_gpu": self.n, "samples": "48 coarse + 48 importance", "planes": "3 x 32 x 256 x 256 fp32 (trained) + OSGDecoder 2,372 parameters",
+                "loss": "MSE(rgb_coarse) + MSE(rgb_fine)", "optimizer": "Adam lr 1e-3 (nerfb_adam_step)",
+                "parallelism": f"{self.cx.world} independent replica(s) (replicas only: nothing to exchange)",
+                "l2": "256 MB written before every step (planes start cold in L2)"}
+
+    def rooflines(self):
+        peaks, nb, torch = self.cx.peaks, self.cx.nb, self.cx.torch
+        P = self.n * 2 * EG3D_S
+        planes = self.ren.plane_source.planes.detach().view(3, 32, 256, 256)
+        cl, dec = nb.ops.triplane_relayout(planes), self.ren.decoder.flat()
+        g = torch.Generator(device=self.cx.dev).manual_seed(3)
+        with torch.no_grad():
+            smp = nb.ops.triplane_render(cl, dec, 1.0, self.d_o, self.d_d, EG3D_S, EG3D_S, 2.2, 3.3, None, None, False, 1.0, False,
+                                         None, None, 1, return_samples=True)[6]
+        coords = torch.addcmul(self.d_o.unsqueeze(1), smp[:, 0].unsqueeze(-1), self.d_d.unsqueeze(1)).reshape(-1, 3).contiguous()
+        d_rgb, d_sig = torch.randn(P, 3, device=self.cx.dev, generator=g), torch.randn(P, device=self.cx.dev, generator=g)
+        ms_b = time_kernel(lambda: nb.ops.triplane_field_bwd(cl, dec, 1.0, coords, 1.0, d_rgb, d_sig), 20)
+        ms_f = time_kernel(lambda: nb.ops.triplane_render(cl, dec, 1.0, self.d_o, self.d_d, EG3D_S, EG3D_S, 2.2, 3.3, None, None, False,
+                                                          1.0, False, None, None, 1, return_samples=True), 20)
+        out = []
+        for name, ms, by, note in (
+                ("triplane_field_bwd_kernel", ms_b, P * 3072, "algorithmic bytes = 1,536 B of bilinear taps gathered + 1,536 B of plane-gradient "
+                 "rows reduced per sample (both served by L2; includes the zero-fill of the 25 MB gradient image)"),
+                ("triplane_render_kernel", ms_f, P * 1536 + P * 20, "training forward: 1,536 B of taps per sample + 20 B per sample kept for the backward")):
+            out.append(finish_roofline({"kernel": name, "bound": "hbm", "achieved": by / ms / 1e6, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                        "ms": ms, "bytes": by, "note": note}, peaks))
+        return out
+
+
 def make_workload(cx: Ctx, config: str, args):
     if config == "train":
         return TrainWorkload(cx, False, args.no_graph)
@@ -673,6 +783,8 @@ def make_workload(cx: Ctx, config: str, args):
         return RenderWorkload(cx, True)
     if config == "eg3d":
         return Eg3dWorkload(cx)
+    if config == "eg3d_train":
+        return Eg3dTrainWorkload(cx)
     raise ValueError(config)
 
 
@@ -734,7 +846,7 @@ def run_ours(args):
     line = {
         "metric": METRICS[cfg], "value": m["value"], "unit": "rays/s", "n_gpus": cx.world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": m["ms"], "higher_is_better": True, "scaling": SCALING[cfg], "vs_baseline": None,
-        "dtype": ("f32" if cfg == "eg3d" else ("bf16" if bf16 else "bf16 fwd / f32 bwd")), "data": "synthetic",
+        "dtype": ("f32" if cfg in ("eg3d", "eg3d_train") else ("bf16" if bf16 else "bf16 fwd / f32 bwd")), "data": "synthetic",
         "config": dict({"workload": WORKLOADS[cfg]}, **wl.config()),
         "clocks": m["clocks"],
         "e2e": {"value": m["e2e_value"], "unit": "rays/s", "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,

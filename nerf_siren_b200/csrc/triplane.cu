@@ -605,6 +605,307 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 3) triplane_field_bwd_kernel(co
   for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) atomicAdd(d_dec + i, s_g[i]);
 }
 
+// ---- the same backward with the decoder's four small GEMMs on the tensor cores -------------------------------------------
+// The CUDA-core kernel above is bound by the shared-memory data pipe: a mat-vec on CUDA cores needs every feature / every
+// dpre on every lane, and a warp-uniform shared load delivers ONE useful word per wavefront (232 wavefronts per point
+// measured, ~70 % of the pipe).  mma.sync fragments are distributed over the lanes, so nothing is broadcast.  A warp takes
+// 16 points at a time (M = 16):
+//   GEMM1  pre^T [16 x 64]  = F^T [16 x 32] . W1^T            A from shared (features), B from shared (W1), C in registers
+//   GEMM2  dF^T  [16 x 32]  = dpre^T [16 x 64] . W1            A = GEMM1's C registers (k slots permuted), B from shared
+//   GEMM3  dW1^T [32 x 64] += F [32 x 16 pts] . dpre [16 x 64] accumulators in registers for the whole kernel
+//   GEMM4  dW2^T [64 x  4] += h^T [64 x 16 pts] . go [16 x 4]  (N padded to 8)
+// all as m16n8k8 TF32 with the 3-term split (a_lo b_hi + a_hi b_lo + a_hi b_hi, fp32 accumulate): fp32-grade accuracy.
+// Gather / scatter: a lane is (point slot = lane / 8, channel quad = lane % 8): 8 lanes x 16 B cover a tap's 128-byte row, a
+// warp instruction serves four points, every lane computes its own point's 12 taps (no tap broadcast either).
+constexpr int TM_PTS = 16;
+constexpr int TM_WARPS = 12;     // warps per block (one block per SM): the kernel is latency-bound, registers cap the count
+constexpr int TM_FS = 36;      // features [pt][ch]: stride = 4 (mod 32): (pt over lane / 4, ch over lane % 4) is conflict-free
+constexpr int TM_FT = 20;      // features [ch][pt]: stride = 4 (mod 16)
+constexpr int TM_DP = 72;      // dpre / h [pt][hid]: stride = 8 (mod 32): (pt over lane % 4, hid over lane / 4) is conflict-free
+constexpr int TM_W1 = 36;      // W1 [hid][ch]
+constexpr int TM_WARP_FLOATS = TM_PTS * TM_FS + TP_C * TM_FT + 2 * TM_PTS * TM_DP + TM_PTS * 4;
+constexpr int TM_BLOCK_FLOATS = TP_HID * TM_W1 + 4 * TP_HID + TP_HID;
+constexpr size_t TM_SMEM = (size_t)(TM_BLOCK_FLOATS + TM_WARPS * TM_WARP_FLOATS) * sizeof(float);
+static_assert(TM_WARPS * TM_WARP_FLOATS >= TP_DEC_PARAMS, "flush buffer aliases the warp areas");
+
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(x - __uint_as_float(hi)));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// c += a . b with both operands split in two TF32 terms
+__device__ __forceinline__ void mma_3x(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], float b0, float b1) {
+  uint32_t b0h, b0l, b1h, b1l;
+  tf32_split(b0, b0h, b0l); tf32_split(b1, b1h, b1l);
+  mma_tf32(c, al, b0h, b1h); mma_tf32(c, ah, b0l, b1l); mma_tf32(c, ah, b0h, b1h);
+}
+
+__global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kernel(const float* __restrict__ planes, int H, int W,
+    const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
+    const float* __restrict__ d_rgb, const float* __restrict__ d_sigma, float* __restrict__ d_planes, float* __restrict__ d_dec) {
+  extern __shared__ __align__(16) float tm_smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;                     // mma fragment coordinates
+  const int ps = lane >> 3, sub4 = (lane & 7) * 4;            // gather / scatter coordinates
+  float* W1s = tm_smem;                                       // [hid][TM_W1], times the layer gain
+  float* W2s = W1s + TP_HID * TM_W1;                          // [k][hid], times the layer gain
+  float* B1s = W2s + 4 * TP_HID;
+  float* wbase = B1s + TP_HID + wib * TM_WARP_FLOATS;
+  float* Fs = wbase;                                          // [pt][TM_FS]   features, later dL/dfeat
+  float* Ft = Fs + TM_PTS * TM_FS;                            // [ch][TM_FT]   features, transposed
+  float* DPs = Ft + TP_C * TM_FT;                             // [pt][TM_DP]   dpre
+  float* Hs = DPs + TM_PTS * TM_DP;                           // [pt][TM_DP]   hidden activations
+  float* GOs = Hs + TM_PTS * TM_DP;                           // [pt][4]       dL/d(output pre-activations)
+  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
+  const float* b1p = decp + TP_HID * TP_C;
+  const float* w2p = b1p + TP_HID;
+  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) W1s[(i >> 5) * TM_W1 + (i & 31)] = __fmul_rn(__ldg(decp + i), g1);
+  for (int i = threadIdx.x; i < 4 * TP_HID; i += blockDim.x) W2s[i] = __fmul_rn(__ldg(w2p + i), g2);
+  for (int i = threadIdx.x; i < TP_HID; i += blockDim.x) B1s[i] = __ldg(b1p + i) * lr_mul;
+  float b2[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) b2[k] = __ldg(w2p + 4 * TP_HID + k) * lr_mul;
+  float gw1[2][8][4];                                         // dW1^T: [m tile: ch 16 mt + g (+8)][n tile: hid 8 nt + 2 t (+1)]
+  float gw2[4][4];                                            // dW2^T: [m tile: hid 16 mt + g (+8)][k = 2 t (+1), t < 2 of a padded 8]
+  float gb1[8][2], gb2[4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { gw1[0][nt][i] = 0.f; gw1[1][nt][i] = 0.f; gw2[nt >> 1][i] = 0.f; }
+    gb1[nt][0] = 0.f; gb1[nt][1] = 0.f;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) gb2[k] = 0.f;
+  __syncthreads();
+  const int64_t n_batches = (P + TM_PTS - 1) / TM_PTS;
+  for (int64_t batch = (int64_t)blockIdx.x * TM_WARPS + wib; batch < n_batches; batch += (int64_t)gridDim.x * TM_WARPS) {
+    // The 16 points of a batch are n_batches apart, NOT consecutive: callers pass ray-major samples, and neighbours along a ray
+    // fall into the same texels -- four of them in one red instruction serialise on the same L2 address (measured: 1.64 ms
+    // on a render's samples against 1.34 ms on random points).  Consecutive batches (the block's other warps) still take
+    // neighbouring points, so the gathers keep their L1 / L2 locality.
+    auto point = [&](int i) { return (int64_t)i * n_batches + batch; };
+    // ---- gather: four points per round, 8 lanes x float4 per tap row ----
+#pragma unroll 1
+    for (int r = 0; r < TM_PTS / 4; ++r) {
+      const int pt = 4 * r + ps;
+      const int64_t q = point(pt) < P ? point(pt) : P - 1;    // tail points re-read the last point; their cotangents are 0
+      const float x = __fmul_rn(coord_scale, __ldg(coords + q * 3)), y = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 1)),
+                  z = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 2));
+      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int pl = 0; pl < 3; ++pl) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          int off; float wt;
+          tap_lane(H, W, x, y, z, 4 * pl + c, off, wt);
+          const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off + sub4));
+          acc.x = fmaf(v.x, wt, acc.x); acc.y = fmaf(v.y, wt, acc.y); acc.z = fmaf(v.z, wt, acc.z); acc.w = fmaf(v.w, wt, acc.w);
+        }
+        f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
+      }
+      f.x /= 3.f; f.y /= 3.f; f.z /= 3.f; f.w /= 3.f;         // sampled_features.mean(1)
+      *reinterpret_cast<float4*>(Fs + pt * TM_FS + sub4) = f;
+      Ft[(sub4 + 0) * TM_FT + pt] = f.x; Ft[(sub4 + 1) * TM_FT + pt] = f.y; Ft[(sub4 + 2) * TM_FT + pt] = f.z; Ft[(sub4 + 3) * TM_FT + pt] = f.w;
+    }
+    __syncwarp();
+    // ---- GEMM1: pre^T[pt][hid]; C fragment: rows pt = g, g + 8; columns hid = 8 nt + 2 t, + 1 ----
+    float pre[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const float2 b = *reinterpret_cast<const float2*>(B1s + 8 * nt + 2 * t);
+      pre[nt][0] = b.x; pre[nt][1] = b.y; pre[nt][2] = b.x; pre[nt][3] = b.y;
+    }
+#pragma unroll
+    for (int kt = 0; kt < 4; ++kt) {
+      uint32_t ah[4], al[4];
+      tf32_split(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
+      tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
+      tf32_split(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
+      tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)                          // B[k = ch][n = hid] = W1[hid][ch]
+        mma_3x(pre[nt], ah, al, W1s[(8 * nt + g) * TM_W1 + 8 * kt + t], W1s[(8 * nt + g) * TM_W1 + 8 * kt + t + 4]);
+    }
+    // ---- hidden activations, second layer, upstream cotangents ----
+    float o[2][4];                                            // [pt g, g + 8][k]
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { o[0][k] = 0.f; o[1][k] = 0.f; }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      float h[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) h[i] = softplusf(pre[nt][i]);
+      *reinterpret_cast<float2*>(Hs + g * TM_DP + 8 * nt + 2 * t) = make_float2(h[0], h[1]);
+      *reinterpret_cast<float2*>(Hs + (g + 8) * TM_DP + 8 * nt + 2 * t) = make_float2(h[2], h[3]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
+        o[0][k] = fmaf(w.x, h[0], fmaf(w.y, h[1], o[0][k]));
+        o[1][k] = fmaf(w.x, h[2], fmaf(w.y, h[3], o[1][k]));
+      }
+      // softplus'(x) = sigmoid(x) = 1 - exp(-softplus(x)) (1 beyond the threshold of 20); kept in place of pre
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pre[nt][i] = pre[nt][i] > 20.f ? 1.f : 1.f - __expf(-h[i]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        o[u][k] += __shfl_xor_sync(0xffffffffu, o[u][k], 1);
+        o[u][k] += __shfl_xor_sync(0xffffffffu, o[u][k], 2);
+        o[u][k] += b2[k];
+      }
+    }
+    float go[2][4];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int64_t q = point(g + 8 * u);
+      const bool on = q < P;
+      go[u][0] = on ? __ldg(d_sigma + q) : 0.f;
+#pragma unroll
+      for (int k = 1; k < 4; ++k) {
+        const float sg = 1.f / (1.f + __expf(-o[u][k]));      // rgb_k = sigmoid(o_k) * 1.002 - 0.001 (triplane.py:165)
+        go[u][k] = on ? __ldg(d_rgb + q * 3 + k - 1) * 1.002f * sg * (1.f - sg) : 0.f;
+      }
+      if (t == 0) *reinterpret_cast<float4*>(GOs + (g + 8 * u) * 4) = make_float4(go[u][0], go[u][1], go[u][2], go[u][3]);
+      if (t == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) gb2[k] += go[u][k];
+      }
+    }
+    // dpre[pt][hid] = sigmoid(pre) * sum_k W2[k][hid] go[pt][k], in the C-fragment layout of GEMM1 (in place of pre)
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      float dh[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
+        dh[0] = fmaf(w.x, go[0][k], dh[0]); dh[1] = fmaf(w.y, go[0][k], dh[1]);
+        dh[2] = fmaf(w.x, go[1][k], dh[2]); dh[3] = fmaf(w.y, go[1][k], dh[3]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pre[nt][i] *= dh[i];
+      gb1[nt][0] += pre[nt][0] + pre[nt][2]; gb1[nt][1] += pre[nt][1] + pre[nt][3];
+      *reinterpret_cast<float2*>(DPs + g * TM_DP + 8 * nt + 2 * t) = make_float2(pre[nt][0], pre[nt][1]);
+      *reinterpret_cast<float2*>(DPs + (g + 8) * TM_DP + 8 * nt + 2 * t) = make_float2(pre[nt][2], pre[nt][3]);
+    }
+    // ---- GEMM2: dF^T[pt][ch] = dpre^T . W1; A = the C fragments above with k slot t <-> hid 2 t, slot t + 4 <-> hid 2 t + 1 ----
+    float df[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) { df[nt][0] = 0.f; df[nt][1] = 0.f; df[nt][2] = 0.f; df[nt][3] = 0.f; }
+#pragma unroll
+    for (int kt = 0; kt < 8; ++kt) {
+      uint32_t ah[4], al[4];
+      tf32_split(pre[kt][0], ah[0], al[0]); tf32_split(pre[kt][2], ah[1], al[1]);
+      tf32_split(pre[kt][1], ah[2], al[2]); tf32_split(pre[kt][3], ah[3], al[3]);
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)                          // B[k = hid][n = ch] = W1[hid][ch]
+        mma_3x(df[nt], ah, al, W1s[(8 * kt + 2 * t) * TM_W1 + 8 * nt + g], W1s[(8 * kt + 2 * t + 1) * TM_W1 + 8 * nt + g]);
+    }
+    __syncwarp();                                             // GEMM1's reads of Fs are done: Fs now carries dL/dfeat / 3
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      *reinterpret_cast<float2*>(Fs + g * TM_FS + 8 * nt + 2 * t) = make_float2(df[nt][0] * (1.f / 3.f), df[nt][1] * (1.f / 3.f));
+      *reinterpret_cast<float2*>(Fs + (g + 8) * TM_FS + 8 * nt + 2 * t) = make_float2(df[nt][2] * (1.f / 3.f), df[nt][3] * (1.f / 3.f));
+    }
+    __syncwarp();
+    // ---- scatter: plane gradients as red.v4 rows, four points per round (taps recomputed: no registers held across the GEMMs) ----
+#pragma unroll 1
+    for (int r = 0; r < TM_PTS / 4; ++r) {
+      const int pt = 4 * r + ps;
+      if (point(pt) < P) {
+        const int64_t q = point(pt);
+        const float x = __fmul_rn(coord_scale, __ldg(coords + q * 3)), y = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 1)),
+                    z = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 2));
+        const float4 v = *reinterpret_cast<const float4*>(Fs + pt * TM_FS + sub4);
+#pragma unroll
+        for (int c = 0; c < 12; ++c) {
+          int off; float wt;
+          tap_lane(H, W, x, y, z, c, off, wt);
+#ifdef TPB_NO_RED
+          if (wt == 123.456f) red_add_v4(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt);
+#else
+          if (wt != 0.f) red_add_v4(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt);
+#endif
+        }
+      }
+    }
+    // ---- GEMM3: dW1^T[ch][hid] += F[ch][pt] . dpre[pt][hid] ----
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) {
+      uint32_t ah[2][4], al[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        tf32_split(Ft[(16 * mt + g) * TM_FT + 8 * kt + t], ah[mt][0], al[mt][0]);
+        tf32_split(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t], ah[mt][1], al[mt][1]);
+        tf32_split(Ft[(16 * mt + g) * TM_FT + 8 * kt + t + 4], ah[mt][2], al[mt][2]);
+        tf32_split(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t + 4], ah[mt][3], al[mt][3]);
+      }
+      // GEMM4: dW2^T[hid][k] += h^T[hid][pt] . go[pt][k]; B = go, columns k >= 4 of the padded tile are zero
+      {
+        const float q0 = g < 4 ? GOs[(8 * kt + t) * 4 + (g & 3)] : 0.f, q1 = g < 4 ? GOs[(8 * kt + t + 4) * 4 + (g & 3)] : 0.f;
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+          uint32_t hh[4], hl[4];
+          tf32_split(Hs[(8 * kt + t) * TM_DP + 16 * mt + g], hh[0], hl[0]);
+          tf32_split(Hs[(8 * kt + t) * TM_DP + 16 * mt + g + 8], hh[1], hl[1]);
+          tf32_split(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g], hh[2], hl[2]);
+          tf32_split(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g + 8], hh[3], hl[3]);
+          mma_3x(gw2[mt], hh, hl, q0, q1);
+        }
+      }
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {                        // B[k = pt][n = hid]
+        const float d0 = DPs[(8 * kt + t) * TM_DP + 8 * nt + g], d1 = DPs[(8 * kt + t + 4) * TM_DP + 8 * nt + g];
+        uint32_t b0h, b0l, b1h, b1l;
+        tf32_split(d0, b0h, b0l); tf32_split(d1, b1h, b1l);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          mma_tf32(gw1[mt][nt], al[mt], b0h, b1h); mma_tf32(gw1[mt][nt], ah[mt], b0l, b1l); mma_tf32(gw1[mt][nt], ah[mt], b0h, b1h);
+        }
+      }
+    }
+    __syncwarp();                                             // the next batch overwrites the warp's buffers
+  }
+  // ---- flush: effective -> raw parameters (gains of networks_stylegan2.py:109-110), one global atomic per parameter per block ----
+  __syncthreads();
+  float* s_g = B1s + TP_HID;                                  // the warp areas
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) s_g[i] = 0.f;
+  __syncthreads();
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {                          // dW1[hid][ch] = dW1^T[ch][hid]
+      const int ch = 16 * mt + g, hid = 8 * nt + 2 * t;
+      atomicAdd(s_g + hid * TP_C + ch, gw1[mt][nt][0] * g1); atomicAdd(s_g + (hid + 1) * TP_C + ch, gw1[mt][nt][1] * g1);
+      atomicAdd(s_g + hid * TP_C + ch + 8, gw1[mt][nt][2] * g1); atomicAdd(s_g + (hid + 1) * TP_C + ch + 8, gw1[mt][nt][3] * g1);
+    }
+  }
+  float* gb1s = s_g + TP_HID * TP_C;
+  float* gw2s = gb1s + TP_HID;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    atomicAdd(gb1s + 8 * nt + 2 * t, gb1[nt][0] * lr_mul); atomicAdd(gb1s + 8 * nt + 2 * t + 1, gb1[nt][1] * lr_mul);
+  }
+  if (t < 2) {
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+      atomicAdd(gw2s + (2 * t) * TP_HID + 16 * mt + g, gw2[mt][0] * g2); atomicAdd(gw2s + (2 * t + 1) * TP_HID + 16 * mt + g, gw2[mt][1] * g2);
+      atomicAdd(gw2s + (2 * t) * TP_HID + 16 * mt + g + 8, gw2[mt][2] * g2); atomicAdd(gw2s + (2 * t + 1) * TP_HID + 16 * mt + g + 8, gw2[mt][3] * g2);
+    }
+  }
+  if (t == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) atomicAdd(gw2s + 4 * TP_HID + k, gb2[k] * lr_mul);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < TP_DEC_PARAMS; i += blockDim.x) atomicAdd(d_dec + i, s_g[i]);
+}
+
 // d(MipRayMarcher2.run_forward) (ray_marcher.py:25-57): one warp per ray, forward recomputed.  With G_i = dL/dw_i collected from
 // every path (weights, rgb = sum w c_mid [+ 1 - sum w], depth = sum w z_mid / sum w), t_i = 1 - alpha_i + 1e-10, T_i = prod_{j<i} t_j:
 //   dL/dalpha_i = G_i T_i - (sum_{k>i} G_k w_k) / t_i,   dL/ddens_mid_i = dL/dalpha_i * delta_i * exp(-dens_i delta_i) * sigmoid(pre_i),
@@ -807,6 +1108,21 @@ extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, co
   NERFB_CHECK_ARG(planes_cl && decoder && d_planes_cl && d_decoder && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
   if (n_points == 0) return NERFB_OK;
   NERFB_CHECK_ARG(coords && d_rgb && d_sigma);
+  static const int use_mma = [] { const char* e = getenv("NERFB_TP_BWD_MMA"); return e ? atoi(e) : 1; }();
+  if (use_mma) {                                              // tensor-core decoder (default); 0 selects the CUDA-core kernel
+    static bool attr_set[64] = {};
+    int dev = 0;
+    NERFB_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      NERFB_CUDA(cudaFuncSetAttribute(triplane_field_bwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM));
+      attr_set[dev] = true;
+    }
+    const int64_t want_m = ceil_div64(ceil_div64(n_points, TM_PTS), TM_WARPS);
+    const int grid_m = (int)(want_m < NERFB_SM_COUNT ? want_m : NERFB_SM_COUNT);
+    NERFB_LAUNCH(triplane_field_bwd_mma_kernel, grid_m, TM_WARPS * 32, TM_SMEM, stream, planes_cl, H, W, decoder, lr_mul, coords,
+                 n_points, (float)(2.0 / (double)box_warp), d_rgb, d_sigma, d_planes_cl, d_decoder);
+    return NERFB_OK;
+  }
   const int64_t want = ceil_div64(n_points, TPB_TILE);
   const int grid = (int)(want < NERFB_SM_COUNT * 3 ? want : NERFB_SM_COUNT * 3);     // one decoder-gradient flush per block
   NERFB_LAUNCH(triplane_field_bwd_kernel, grid, TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords, n_points,

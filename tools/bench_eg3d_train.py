@@ -60,16 +60,21 @@ colors, dens = torch.rand(R, 96, 3, device=DEV, generator=g), torch.randn(R, 96,
 depths = torch.sort(torch.rand(R, 96, device=DEV, generator=g) + 2.2, dim=1)[0].contiguous()
 g_rgb = torch.randn(R, 3, device=DEV, generator=g)
 
+with torch.no_grad():
+    smp = ops.triplane_render(cl, dec, 1.0, o, d, 48, 48, 2.2, 3.3, None, None, False, 1.0, False, None, None, 1, return_samples=True)[6]
+ray_coords = torch.addcmul(o.unsqueeze(1), smp[:, 0].unsqueeze(-1), d.unsqueeze(1)).reshape(-1, 3).contiguous()
 t_inf = timed(render_nograd)
 t_fwd = timed(lambda: fwd())
 t_step = timed(step)
 t_field = timed(lambda: ops.triplane_field(cl, dec, 1.0, coords, 1.0))
 t_fbwd = timed(lambda: ops.triplane_field_bwd(cl, dec, 1.0, coords, 1.0, d_rgb, d_sigma))
+t_fbwd_ray = timed(lambda: ops.triplane_field_bwd(cl, dec, 1.0, ray_coords, 1.0, d_rgb, d_sigma))
 t_mbwd = timed(lambda: ops.mip_march_bwd(colors, dens, depths, False, g_rgb, None, None))
 print(f"rays {R} planes {RES}^2 samples 48+48 ({P} points)")
 print(f"  fused no_grad render            {t_inf:8.3f} ms  ({R / t_inf / 1e3:.2f} M rays/s)")
 print(f"  differentiable forward          {t_fwd:8.3f} ms")
 print(f"  forward + backward              {t_step:8.3f} ms  ({R / t_step / 1e3:.2f} M rays/s)")
 print(f"  nerfb_triplane_field  ({P} pts) {t_field:8.3f} ms")
-print(f"  nerfb_triplane_field_bwd        {t_fbwd:8.3f} ms  ({P * 12 * 128 / t_fbwd / 1e6:.1f} GB/s of 128 B plane-gradient reductions)")
+print(f"  nerfb_triplane_field_bwd        {t_fbwd:8.3f} ms  on uniformly random points ({P * 12 * 128 / t_fbwd / 1e6:.1f} GB/s of 128 B plane-gradient reductions)")
+print(f"  nerfb_triplane_field_bwd        {t_fbwd_ray:8.3f} ms  on the render's own sample points (ray-coherent, unsorted: S coarse then Si importance)")
 print(f"  nerfb_mip_march_bwd ({R} x 96)  {t_mbwd:8.3f} ms")

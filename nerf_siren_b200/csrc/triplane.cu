@@ -97,6 +97,114 @@ __device__ __forceinline__ void tap_lane(int H, int W, float x, float y, float z
   off = ((p * H + yi) * W + xi) * TP_C;
 }
 
+// ---- the decoder on the tensor cores (mma.sync m16n8k8 TF32, 3-term split: fp32-grade accuracy) -----------------------
+// A mat-vec on CUDA cores needs every feature on every lane, and a warp-uniform shared load (or a shuffle) delivers ONE useful
+// word per wavefront of the shared-memory data pipe; mma fragments are distributed over the lanes, nothing is broadcast.
+// A warp evaluates 16 points at a time: pre^T [16 x 64] = F^T [16 x 32] . W1^T, A from the per-warp feature tile, B from the
+// block's copy of W1, C in registers (rows pt = lane / 4, + 8; columns hid = 8 nt + 2 (lane % 4), + 1).
+constexpr int TM_PTS = 16;
+constexpr int TM_FS = 36;      // features [pt][ch]: stride = 4 (mod 32): (pt over lane / 4, ch over lane % 4) is conflict-free
+constexpr int TM_W1 = 36;      // W1 [hid][ch]
+constexpr int TM_DEC_FLOATS = TP_HID * TM_W1 + 4 * TP_HID + TP_HID;       // W1s | W2s [k][hid] | B1s
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(x - __uint_as_float(hi)));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// c += a . b with both operands split in two TF32 terms
+__device__ __forceinline__ void mma_3x(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], float b0, float b1) {
+  uint32_t b0h, b0l, b1h, b1l;
+  tf32_split(b0, b0h, b0l); tf32_split(b1, b1h, b1l);
+  mma_tf32(c, al, b0h, b1h); mma_tf32(c, ah, b0l, b1l); mma_tf32(c, ah, b0h, b1h);
+}
+
+
+// block-wide: the decoder's effective weights (gains of networks_stylegan2.py:109-110) into shared memory
+__device__ __forceinline__ void load_decoder_mma(float* W1s, const float* __restrict__ decp, float lr_mul) {
+  float* W2s = W1s + TP_HID * TM_W1;
+  float* B1s = W2s + 4 * TP_HID;
+  const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
+  const float* b1p = decp + TP_HID * TP_C;
+  const float* w2p = b1p + TP_HID;
+  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) W1s[(i >> 5) * TM_W1 + (i & 31)] = __fmul_rn(__ldg(decp + i), g1);
+  for (int i = threadIdx.x; i < 4 * TP_HID; i += blockDim.x) W2s[i] = __fmul_rn(__ldg(w2p + i), g2);
+  for (int i = threadIdx.x; i < TP_HID; i += blockDim.x) B1s[i] = __ldg(b1p + i) * lr_mul;
+}
+
+// gather of ONE point by 8 lanes (sub4 = 4 (lane % 8): four channels each): all 12 taps computed by the lane itself, rows read
+// as float4; same tap order and rounding as field_eval.  Returns sampled_features.mean(1) for the lane's four channels.
+__device__ __forceinline__ float4 gather_quad(const float* __restrict__ planes, int H, int W, float x, float y, float z, int sub4) {
+  float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int pl = 0; pl < 3; ++pl) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      int off; float wt;
+      tap_lane(H, W, x, y, z, 4 * pl + c, off, wt);
+      const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off + sub4));
+      acc.x = fmaf(v.x, wt, acc.x); acc.y = fmaf(v.y, wt, acc.y); acc.z = fmaf(v.z, wt, acc.z); acc.w = fmaf(v.w, wt, acc.w);
+    }
+    f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
+  }
+  f.x /= 3.f; f.y /= 3.f; f.z /= 3.f; f.w /= 3.f;
+  return f;
+}
+
+// run_model for the 16 points whose features sit in Fs[pt][TM_FS] (written by gather_quad, __syncwarp'ed by the caller).
+// out[u][0] = sigma, out[u][1..3] = rgb of point (lane / 4) + 8 u, identical on the four lanes of a group.
+__device__ __forceinline__ void decode16(const float* Fs, const float* W1s, const float (&b2)[4], int lane, float (&out)[2][4]) {
+  const float* W2s = W1s + TP_HID * TM_W1;
+  const float* B1s = W2s + 4 * TP_HID;
+  const int g = lane >> 2, t = lane & 3;
+  float pre[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    const float2 b = *reinterpret_cast<const float2*>(B1s + 8 * nt + 2 * t);
+    pre[nt][0] = b.x; pre[nt][1] = b.y; pre[nt][2] = b.x; pre[nt][3] = b.y;
+  }
+#pragma unroll
+  for (int kt = 0; kt < 4; ++kt) {
+    uint32_t ah[4], al[4];
+    tf32_split(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
+    tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
+    tf32_split(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
+    tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+      mma_3x(pre[nt], ah, al, W1s[(8 * nt + g) * TM_W1 + 8 * kt + t], W1s[(8 * nt + g) * TM_W1 + 8 * kt + t + 4]);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { out[0][k] = 0.f; out[1][k] = 0.f; }
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    float h[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = softplusf(pre[nt][i]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
+      out[0][k] = fmaf(w.x, h[0], fmaf(w.y, h[1], out[0][k]));
+      out[1][k] = fmaf(w.x, h[2], fmaf(w.y, h[3], out[1][k]));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float v = out[u][k];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      v += b2[k];
+      if (k > 0) v = __fsub_rn(__fmul_rn(__fdividef(1.f, 1.f + __expf(-v)), 1.002f), 0.001f);     // triplane.py:165
+      out[u][k] = v;
+    }
+  }
+}
+
 // run_model for one point (renderer.py:144-151 + triplane.py:155-167).  Returns on lane 0: sigma, lane 8 / 16 / 24: r, g, b.
 // s_tap: 12 x (offset, weight) as int2, s_feat: 32 floats; the caller alternates two such buffers between consecutive samples.
 __device__ __forceinline__ float field_eval(const float* __restrict__ planes, int H, int W, float x, float y, float z,
@@ -252,21 +360,34 @@ __device__ __forceinline__ float linspace_ab(float a, float b, int i, int n) {
   return (i < n / 2) ? __fmaf_rn((float)i, step, a) : __fmaf_rn(-(float)(n - 1 - i), step, b);
 }
 
-__global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const RenderArgs a) {
-  extern __shared__ float smem[];
+// MMA: the decoder of 16 samples at a time on the tensor cores (decode16) instead of one sample at a time on CUDA cores with the
+// first-layer weights in 64 registers per lane (field_eval); the NERFB_TP_MMA=0 build keeps the latter.
+template <bool MMA>
+__global__ void __launch_bounds__(TP_WARPS * 32, MMA ? 3 : 2) triplane_render_kernel(const RenderArgs a) {
+  extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int S = a.S, Si = a.Si, St = S + Si;
   // per warp: two sample sets of 5 arrays (depth, sigma, r, g, b) x St, weights St, bins / cdf 2 x S
   const int scr_off = (11 * St + 2 * S + 3) & ~3;            // 16-byte aligned scratch behind the per-ray arrays
-  float* base = smem + (size_t)wib * (scr_off + 128);
+  constexpr int SCR = MMA ? TM_PTS * TM_FS : 128;             // MMA: the feature tile of 16 samples
+  float* const W1s = smem;                                    // MMA: the block's decoder weights in front of the warp areas
+  float* base = smem + (MMA ? TM_DEC_FLOATS : 0) + (size_t)wib * (scr_off + SCR);
   float* const A = base;               // sample set A: [depth | sigma | r | g | b] x St, coarse [0,S) then fine [S,St)
   float* const B = base + 5 * St;      // sample set B: the merged, sorted samples
   float* s_w = base + 10 * St;
   float* s_bins = s_w + St;
   float* s_cdf = s_bins + S;
-  float* s_scr = base + scr_off;               // 2 x [12 x (offset, weight) | 32 features]
+  float* s_scr = base + scr_off;               // 2 x [12 x (offset, weight) | 32 features], or the MMA feature tile
   Dec dec;
-  load_decoder(dec, a.dec, a.lr_mul, lane);
+  float b2[4] = {0.f, 0.f, 0.f, 0.f};
+  if (MMA) {
+    load_decoder_mma(W1s, a.dec, a.lr_mul);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) b2[k] = __ldg(a.dec + TP_HID * TP_C + TP_HID + 4 * TP_HID + k) * a.lr_mul;
+    __syncthreads();
+  } else {
+    load_decoder(dec, a.dec, a.lr_mul, lane);
+  }
   for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < a.R; r += (int64_t)gridDim.x * TP_WARPS) {
     const float ox = __ldg(a.o + r * 3), oy = __ldg(a.o + r * 3 + 1), oz = __ldg(a.o + r * 3 + 2);
     const float dx = __ldg(a.d + r * 3), dy = __ldg(a.d + r * 3 + 1), dz = __ldg(a.d + r * 3 + 2);
@@ -292,6 +413,31 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 2) triplane_render_kernel(const
     for (int pass = 0; pass < 2; ++pass) {
       // ---- field pass over the coarse (pass 0) / importance (pass 1) samples: ONE copy of the decoder code ----
       const int s0 = pass ? S : 0, s1 = pass ? St : S;
+      if (MMA) {
+#pragma unroll 1
+        for (int sb = s0; sb < s1; sb += TM_PTS) {
+#pragma unroll 1
+          for (int rr = 0; rr < TM_PTS / 4; ++rr) {           // four samples per round, 8 lanes x float4 per tap row
+            const int pt = 4 * rr + (lane >> 3);
+            const float t = A[min(sb + pt, s1 - 1)];          // a ragged last batch re-reads the last sample
+            const float4 f = gather_quad(a.planes, a.H, a.W, __fmul_rn(a.coord_scale, __fadd_rn(ox, __fmul_rn(t, dx))),
+                                         __fmul_rn(a.coord_scale, __fadd_rn(oy, __fmul_rn(t, dy))),
+                                         __fmul_rn(a.coord_scale, __fadd_rn(oz, __fmul_rn(t, dz))), (lane & 7) * 4);
+            *reinterpret_cast<float4*>(s_scr + pt * TM_FS + (lane & 7) * 4) = f;
+          }
+          __syncwarp();
+          float out[2][4];
+          decode16(s_scr, W1s, b2, lane, out);
+          if ((lane & 3) == 0) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int s = sb + (lane >> 2) + 8 * u;
+              if (s < s1) { A[St + s] = out[u][0]; A[2 * St + s] = out[u][1]; A[3 * St + s] = out[u][2]; A[4 * St + s] = out[u][3]; }
+            }
+          }
+          __syncwarp();
+        }
+      } else
 #pragma unroll 2
       for (int s = s0; s < s1; ++s) {
         const float t = A[s];
@@ -361,6 +507,44 @@ __global__ void __launch_bounds__(TP_WARPS * 32) triplane_field_kernel(const flo
     __syncwarp();
     if (lane == 0) sigma[p] = v;
     else if ((lane & 7) == 0) rgb[p * 3 + (lane >> 3) - 1] = v;
+  }
+}
+
+// the same, 16 points per warp pass with the decoder on the tensor cores
+__global__ void __launch_bounds__(TP_WARPS * 32, 3) triplane_field_mma_kernel(const float* __restrict__ planes, int H, int W,
+    const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
+    float* __restrict__ rgb, float* __restrict__ sigma) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  __shared__ __align__(16) float s_dec[TM_DEC_FLOATS];
+  __shared__ __align__(16) float s_f[TP_WARPS][TM_PTS * TM_FS];
+  float* Fs = s_f[wib];
+  load_decoder_mma(s_dec, decp, lr_mul);
+  float b2[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) b2[k] = __ldg(decp + TP_HID * TP_C + TP_HID + 4 * TP_HID + k) * lr_mul;
+  __syncthreads();
+  const int64_t n_batches = (P + TM_PTS - 1) / TM_PTS;
+  for (int64_t batch = (int64_t)blockIdx.x * TP_WARPS + wib; batch < n_batches; batch += (int64_t)gridDim.x * TP_WARPS) {
+    const int64_t p0 = batch * TM_PTS;
+#pragma unroll 1
+    for (int rr = 0; rr < TM_PTS / 4; ++rr) {
+      const int pt = 4 * rr + (lane >> 3);
+      const int64_t q = p0 + pt < P ? p0 + pt : P - 1;
+      const float4 f = gather_quad(planes, H, W, __fmul_rn(coord_scale, __ldg(coords + q * 3)), __fmul_rn(coord_scale, __ldg(coords + q * 3 + 1)),
+                                   __fmul_rn(coord_scale, __ldg(coords + q * 3 + 2)), (lane & 7) * 4);
+      *reinterpret_cast<float4*>(Fs + pt * TM_FS + (lane & 7) * 4) = f;
+    }
+    __syncwarp();
+    float out[2][4];
+    decode16(Fs, s_dec, b2, lane, out);
+    if ((lane & 3) == 0) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int64_t q = p0 + (lane >> 2) + 8 * u;
+        if (q < P) { sigma[q] = out[u][0]; rgb[q * 3] = out[u][1]; rgb[q * 3 + 1] = out[u][2]; rgb[q * 3 + 2] = out[u][3]; }
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -617,31 +801,13 @@ __global__ void __launch_bounds__(TP_WARPS * 32, 3) triplane_field_bwd_kernel(co
 // all as m16n8k8 TF32 with the 3-term split (a_lo b_hi + a_hi b_lo + a_hi b_hi, fp32 accumulate): fp32-grade accuracy.
 // Gather / scatter: a lane is (point slot = lane / 8, channel quad = lane % 8): 8 lanes x 16 B cover a tap's 128-byte row, a
 // warp instruction serves four points, every lane computes its own point's 12 taps (no tap broadcast either).
-constexpr int TM_PTS = 16;
 constexpr int TM_WARPS = 12;     // warps per block (one block per SM): the kernel is latency-bound, registers cap the count
-constexpr int TM_FS = 36;      // features [pt][ch]: stride = 4 (mod 32): (pt over lane / 4, ch over lane % 4) is conflict-free
 constexpr int TM_FT = 20;      // features [ch][pt]: stride = 4 (mod 16)
 constexpr int TM_DP = 72;      // dpre / h [pt][hid]: stride = 8 (mod 32): (pt over lane % 4, hid over lane / 4) is conflict-free
-constexpr int TM_W1 = 36;      // W1 [hid][ch]
 constexpr int TM_WARP_FLOATS = TM_PTS * TM_FS + TP_C * TM_FT + 2 * TM_PTS * TM_DP + TM_PTS * 4;
 constexpr int TM_BLOCK_FLOATS = TP_HID * TM_W1 + 4 * TP_HID + TP_HID;
 constexpr size_t TM_SMEM = (size_t)(TM_BLOCK_FLOATS + TM_WARPS * TM_WARP_FLOATS) * sizeof(float);
 static_assert(TM_WARPS * TM_WARP_FLOATS >= TP_DEC_PARAMS, "flush buffer aliases the warp areas");
-
-__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(x - __uint_as_float(hi)));
-}
-__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-// c += a . b with both operands split in two TF32 terms
-__device__ __forceinline__ void mma_3x(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], float b0, float b1) {
-  uint32_t b0h, b0l, b1h, b1l;
-  tf32_split(b0, b0h, b0l); tf32_split(b1, b1h, b1l);
-  mma_tf32(c, al, b0h, b1h); mma_tf32(c, ah, b0l, b1l); mma_tf32(c, ah, b0h, b1h);
-}
 
 __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kernel(const float* __restrict__ planes, int H, int W,
     const float* __restrict__ decp, float lr_mul, const float* __restrict__ coords, int64_t P, float coord_scale,
@@ -997,6 +1163,9 @@ __global__ void __launch_bounds__(TP_WARPS * 32) mip_march_bwd_kernel(const floa
   }
 }
 
+// NERFB_TP_MMA=0 selects the CUDA-core decoder in all tri-plane kernels (read per call: tests flip it)
+inline bool tp_use_mma() { const char* e = getenv("NERFB_TP_MMA"); return e ? atoi(e) != 0 : true; }
+
 inline int grid_for(int64_t units) {
   const int64_t want = ceil_div64(units, TP_WARPS);
   const int64_t cap = (int64_t)NERFB_SM_COUNT * 8;           // 8 resident 256-thread CTAs per SM
@@ -1019,6 +1188,13 @@ extern "C" int nerfb_triplane_field(const float* planes_cl, int H, int W, const 
   NERFB_CHECK_ARG(planes_cl && decoder && rgb && sigma && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
   if (n_points == 0) return NERFB_OK;
   NERFB_CHECK_ARG(coords);
+  if (tp_use_mma()) {
+    const int64_t want = ceil_div64(ceil_div64(n_points, TM_PTS), TP_WARPS);
+    const int64_t cap = (int64_t)NERFB_SM_COUNT * 3;
+    NERFB_LAUNCH(triplane_field_mma_kernel, (int)(want < cap ? want : cap), TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul,
+                 coords, n_points, (float)(2.0 / (double)box_warp), rgb, sigma);
+    return NERFB_OK;
+  }
   NERFB_LAUNCH(triplane_field_kernel, grid_for(n_points), TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords,
                n_points, (float)(2.0 / (double)box_warp), rgb, sigma);
   return NERFB_OK;
@@ -1063,14 +1239,19 @@ static int triplane_render_impl(const float* planes_cl, int H, int W, const floa
   a.rand_coarse = rand_coarse; a.u = u; a.seed = seed;
   a.rgb_c = rgb_coarse; a.depth_c = depth_coarse; a.opac_c = opacity_coarse; a.rgb_f = rgb_final; a.depth_f = depth_final;
   a.opac_f = opacity_final; a.depths_fine_out = depths_fine_out; a.samples_out = samples_out; a.mm = static_cast<uint32_t*>(workspace);
-  const size_t smem = (size_t)TP_WARPS * (((11 * (n_samples + n_importance) + 2 * n_samples + 3) & ~3) + 128) * sizeof(float);
+  const bool mma = tp_use_mma();
+  const size_t per_warp = ((11 * (n_samples + n_importance) + 2 * n_samples + 3) & ~3) + (mma ? TM_PTS * TM_FS : 128);
+  const size_t smem = ((size_t)TP_WARPS * per_warp + (mma ? TM_DEC_FLOATS : 0)) * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
-  if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(triplane_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem > 48 * 1024)
+    NERFB_CUDA(mma ? cudaFuncSetAttribute(triplane_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                   : cudaFuncSetAttribute(triplane_render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   NERFB_LAUNCH(minmax_init_kernel, 1, 32, 0, stream, a.mm);
-  // register-heavy kernel (64 decoder weights per lane): grid = resident CTAs only, rays strided
+  // grid = resident CTAs only, rays strided (the CUDA-core variant is register-heavy: 64 decoder weights per lane)
   const int64_t want = ceil_div64(n_rays, TP_WARPS);
-  const int64_t cap = (int64_t)NERFB_SM_COUNT * 2;
-  NERFB_LAUNCH(triplane_render_kernel, (int)(want < cap ? want : cap), TP_WARPS * 32, smem, stream, a);
+  const int64_t cap = (int64_t)NERFB_SM_COUNT * (mma ? 3 : 2);
+  if (mma) NERFB_LAUNCH(triplane_render_kernel<true>, (int)(want < cap ? want : cap), TP_WARPS * 32, smem, stream, a);
+  else NERFB_LAUNCH(triplane_render_kernel<false>, (int)(want < cap ? want : cap), TP_WARPS * 32, smem, stream, a);
   NERFB_LAUNCH(depth_clamp_kernel, (unsigned)ceil_div64(n_rays, 256), 256, 0, stream, depth_coarse, depth_final, n_rays, a.mm);
   return NERFB_OK;
 }
@@ -1108,8 +1289,7 @@ extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, co
   NERFB_CHECK_ARG(planes_cl && decoder && d_planes_cl && d_decoder && n_points >= 0 && H >= 1 && W >= 1 && box_warp != 0.f);
   if (n_points == 0) return NERFB_OK;
   NERFB_CHECK_ARG(coords && d_rgb && d_sigma);
-  static const int use_mma = [] { const char* e = getenv("NERFB_TP_BWD_MMA"); return e ? atoi(e) : 1; }();
-  if (use_mma) {                                              // tensor-core decoder (default); 0 selects the CUDA-core kernel
+  if (tp_use_mma()) {                                              // tensor-core decoder (default); 0 selects the CUDA-core kernel
     static bool attr_set[64] = {};
     int dev = 0;
     NERFB_CUDA(cudaGetDevice(&dev));

@@ -28,8 +28,16 @@ def test_relayout_is_a_pure_permutation():
     assert torch.equal(nb().ops.triplane_relayout(planes), planes.permute(0, 2, 3, 1).contiguous())
 
 
+@pytest.fixture(params=["1", "0"], ids=["tensor-core-decoder", "cuda-core-decoder"])
+def decoder_arm(request, monkeypatch):
+    """NERFB_TP_MMA: 1 (default) = the decoder's first layer as mma.sync TF32 x3 on 16 samples at a time, 0 = one sample at a
+    time on CUDA cores.  Read per call by the library; both arms carry the same tolerances."""
+    monkeypatch.setenv("NERFB_TP_MMA", request.param)
+    return request.param
+
+
 @pytest.mark.parametrize("name", CASES)
-def test_field_matches_reference(name):
+def test_field_matches_reference(name, decoder_arm):
     g = gold("g10_eg3d_" + name)
     planes, dec, ro, rd, opts = setup(g)
     R, S = int(g["R"]), int(g["S"])
@@ -40,7 +48,7 @@ def test_field_matches_reference(name):
     torch.testing.assert_close(sigma.cpu(), g["field_sigma"][0, :, 0], rtol=1e-5, atol=1e-4)
 
 
-def test_field_outside_box_and_nonfinite_coordinates():
+def test_field_outside_box_and_nonfinite_coordinates(decoder_arm):
     """zeros padding: outside the planes the features are 0 and the decoder sees only its biases; NaN coordinates tap nothing."""
     g = gold("g10_eg3d_small")
     planes, dec, _, _, opts = setup(g)
@@ -80,7 +88,7 @@ def test_marcher_zero_weight_rays_clamp_to_global_max_depth():
 
 
 @pytest.mark.parametrize("name", CASES)
-def test_fused_render_matches_reference(name):
+def test_fused_render_matches_reference(name, decoder_arm):
     g = gold("g10_eg3d_" + name)
     planes, dec, ro, rd, opts = setup(g)
     R, S, Si = int(g["R"]), int(g["S"]), int(g["Si"])
@@ -126,7 +134,7 @@ def test_renderer_module_is_a_drop_in():
     assert all(torch.equal(x, y) for x, y in zip(a, b)) and all(torch.isfinite(x).all() for x in a)
 
 
-def test_full_size_properties_config5():
+def test_full_size_properties_config5(decoder_arm):
     """BASELINE config 5 shape: 3 x 32 x 256^2 planes, 128^2 = 16,384 rays, 48 + 48 samples.  Size-independent
     properties: opacity in [0, 1], colours inside the sigmoid clamp range, depths inside [ray_start, ray_end + delta],
     white_back identity rgb_wb = rgb + 1 - opacity, and per-ray independence (a sub-batch renders identically)."""

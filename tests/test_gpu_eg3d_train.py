@@ -37,8 +37,15 @@ def leaf_dec(seed, lr_mul=1.0):
     return {k: v.clone().requires_grad_(True) for k, v in dec.items()}
 
 
+@pytest.fixture(params=["1", "0"], ids=["tensor-core-decoder", "cuda-core-decoder"])
+def decoder_arm(request, monkeypatch):
+    """NERFB_TP_MMA: 1 (default) = decoder GEMMs as mma.sync TF32 x3, 0 = the CUDA-core kernels.  Read per call by the library."""
+    monkeypatch.setenv("NERFB_TP_MMA", request.param)
+    return request.param
+
+
 @pytest.mark.parametrize("res,n,lr_mul,box", [(16, 700, 1.0, 1.0), (64, 5000, 0.5, 2.0), (33, 257, 2.0, 1.0)])
-def test_field_backward_matches_autograd(res, n, lr_mul, box):
+def test_field_backward_matches_autograd(res, n, lr_mul, box, decoder_arm):
     """d(planes), d(decoder) of run_model for random cotangents; a third of the points lie outside the box (zero padding:
     no plane gradient from the taps that fall off the edge) and the plane is not square-friendly in the third case."""
     planes = (E.planes_init(seed=res, res=res)[0] * 0.7).requires_grad_(True)              # (3, 32, res, res)
@@ -58,7 +65,7 @@ def test_field_backward_matches_autograd(res, n, lr_mul, box):
     assert rel(d_cl2, d_cl) < 1e-5 and rel(d_dec2, d_dec) < 1e-5
 
 
-def test_field_backward_edges():
+def test_field_backward_edges(decoder_arm):
     ops = nb().ops
     cl = torch.randn(3, 8, 8, 32, device=DEV)
     dec = torch.randn(2372, device=DEV) * 0.1
@@ -116,7 +123,7 @@ def test_marcher_backward_empty_ray_has_zero_depth_gradient():
 
 
 @pytest.mark.parametrize("name", ["small", "white", "disp"])
-def test_training_step_gradients_match_oracle_autograd(name):
+def test_training_step_gradients_match_oracle_autograd(name, decoder_arm):
     """The host mirror's differentiable schedule end to end (ImportanceRenderer.forward with trainable planes and decoder,
     the reference's loss: MSE of coarse + fine colours, system.py:111-120 / losses.py) against autograd over the oracle on
     the fixtures' inputs and random numbers."""

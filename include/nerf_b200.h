@@ -201,13 +201,21 @@ int nerfb_triplane_render(const float* planes_cl, int H, int W, const float* dec
  *   writes samples_out (R, 5, S + Si) = depth | sigma | r | g | b of every sample, the S stratified samples first, then the
  *   Si importance samples, unsorted -- all a training step has to keep between its forward and its backward (coarse
  *   marcher backward on [0, S), sort by depth + final marcher backward on all, nerfb_triplane_field_bwd on the points
- *   rays_o + depth * rays_d). */
+ *   rays_o + depth * rays_d).
+ * nerfb_triplane_samples_bwd: exactly that middle part in one launch, one warp per ray: from samples (R, 5, S + Si) and the
+ *   cotangents of the six outputs (rgb (R,3), depth (R), opacity (R), coarse and final; each may be null) -> per sample in
+ *   the kept order: coords (R*(S+Si), 3) = rays_o + depth * rays_d (the forward's rounding), d_rgb (R*(S+Si), 3), d_sigma
+ *   (R*(S+Si)): the inputs of nerfb_triplane_field_bwd.  The union is sorted by (depth, index) as the forward does. */
 int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
                              const float* coords, int64_t n_points, float box_warp, const float* d_rgb,
                              const float* d_sigma, float* d_planes_cl, float* d_decoder, void* stream);
 int nerfb_mip_march_bwd(const float* colors, const float* densities, const float* depths, int64_t n_rays,
                         int n_samples, int white_back, const float* d_rgb, const float* d_depth,
                         const float* d_weights, float* d_colors, float* d_densities, void* stream);
+int nerfb_triplane_samples_bwd(const float* samples, const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                               int n_importance, int white_back, const float* d_rgb_coarse, const float* d_depth_coarse,
+                               const float* d_opacity_coarse, const float* d_rgb_final, const float* d_depth_final,
+                               const float* d_opacity_final, float* coords, float* d_rgb, float* d_sigma, void* stream);
 int nerfb_triplane_render_train(const float* planes_cl, int H, int W, const float* decoder, float lr_mul,
                                 const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
                                 int n_importance, double ray_start, double ray_end, const float* ray_start_arr,

@@ -69,6 +69,7 @@ SIGNATURES = {
     "nerfb_mip_march_bwd": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P, _P]),
     "nerfb_triplane_render": (_I, [_P, _I, _I, _P, _F, _P, _P, _L, _I, _I, C.c_double, C.c_double, _P, _P, _I, _F, _I,
                                    _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "nerfb_triplane_samples_bwd": (_I, [_P, _P, _P, _L, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_triplane_render_train": (_I, [_P, _I, _I, _P, _F, _P, _P, _L, _I, _I, C.c_double, C.c_double, _P, _P, _I, _F, _I,
                                          _P, _P, C.c_uint64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "nerfb_generate_rays": (_I, [_P, _I, _I, C.c_double, _F, _F, _I, _P, _P]),

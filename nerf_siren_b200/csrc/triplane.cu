@@ -1078,6 +1078,72 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
 //   dL/dc_mid_i = w_i dL/drgb;  mid-point values split their gradient half / half onto the two samples of the interval.
 // The depth clamp to the call-global [min, max] never binds for a weighted mean of the ray's own mid-points; sum w = 0 (depth = inf ->
 // clamped constant) passes no depth gradient.  Depths are not differentiated (the reference detaches the importance samples).
+// the per-ray core: S sorted samples in shared memory -> per INTERVAL s_w[i] (weights) and s_dp[i] (dL/d density mid-point, before
+// the shift of the softplus); s_T / s_G are scratch.  g_w: per-interval cotangents of this ray (global, may be null) plus the
+// scalar g_w_all added to every interval (the cotangent of opacity = sum of the weights).
+__device__ __forceinline__ void march_bwd_ray(const float* s_d, const float* s_sig, const float* s_r, const float* s_g, const float* s_b,
+                                              int S, int white_back, float gr, float gg, float gb, float gd, const float* __restrict__ g_w,
+                                              float g_w_all, float* s_T, float* s_G, float* s_w, float* s_dp, int lane) {
+  // pass 1: forward; T_i, w_i per interval; sum w, sum w z_mid
+  float carry = 1.f, wsum = 0.f, wz = 0.f;
+  for (int base = 0; base < S - 1; base += 32) {
+    const int i = base + lane;
+    const bool on = i < S - 1;
+    float alpha = 0.f, zmid = 0.f;
+    if (on) {
+      const float d0 = s_d[i], d1 = s_d[i + 1];
+      zmid = 0.5f * (d0 + d1);
+      const float dm = softplusf(0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f);
+      alpha = 1.f - expf(-dm * (d1 - d0));
+    }
+    float t = on ? (1.f - alpha) + 1e-10f : 1.f;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t *= q; }
+    float excl = __shfl_up_sync(0xffffffffu, t, 1);
+    if (lane == 0) excl = 1.f;
+    const float T = carry * excl;
+    carry *= __shfl_sync(0xffffffffu, t, 31);
+    const float w = on ? alpha * T : 0.f;
+    if (on) { s_T[i] = T; s_w[i] = w; }
+    wsum += w; wz = fmaf(w, zmid, wz);
+  }
+  wsum = warp_sum(wsum); wz = warp_sum(wz);
+  const bool depth_ok = gd != 0.f && wsum > 0.f;
+  const float depth = depth_ok ? wz / wsum : 0.f;
+  __syncwarp();
+  for (int i = lane; i < S - 1; i += 32) {
+    const float cr = 0.5f * (s_r[i] + s_r[i + 1]), cg = 0.5f * (s_g[i] + s_g[i + 1]), cb = 0.5f * (s_b[i] + s_b[i + 1]);
+    float G = (g_w ? __ldg(g_w + i) : 0.f) + g_w_all + gr * cr + gg * cg + gb * cb;
+    if (white_back) G -= gr + gg + gb;
+    if (depth_ok) G += gd * (0.5f * (s_d[i] + s_d[i + 1]) - depth) / wsum;
+    s_G[i] = G;
+  }
+  __syncwarp();
+  // pass 2: backward over the intervals with a running suffix sum of G_k w_k
+  float suffix = 0.f;
+  for (int base = ((S - 2) / 32) * 32; base >= 0; base -= 32) {
+    const int i = base + lane;
+    const bool on = i < S - 1;
+    const float gw = on ? s_G[i] * s_w[i] : 0.f;
+    float incl = gw;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_down_sync(0xffffffffu, incl, o); if (lane + o < 32) incl += q; }
+    const float after = suffix + (incl - gw);
+    suffix += __shfl_sync(0xffffffffu, incl, 0);
+    if (on) {
+      const float d0 = s_d[i], d1 = s_d[i + 1], delta = d1 - d0;
+      const float pre = 0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f;
+      const float dm = softplusf(pre);
+      const float e = expf(-dm * delta);                   // 1 - alpha
+      const float t = e + 1e-10f;
+      const float dalpha = s_G[i] * s_T[i] - after / t;
+      const float sg = pre > 20.f ? 1.f : 1.f / (1.f + __expf(-pre));
+      s_dp[i] = dalpha * delta * e * sg;
+    }
+  }
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(TP_WARPS * 32) mip_march_bwd_kernel(const float* __restrict__ colors, const float* __restrict__ dens,
     const float* __restrict__ depths, int64_t R, int S, int white_back, const float* __restrict__ g_rgb, const float* __restrict__ g_depth,
     const float* __restrict__ g_w, float* __restrict__ d_colors, float* __restrict__ d_dens) {
@@ -1094,70 +1160,83 @@ __global__ void __launch_bounds__(TP_WARPS * 32) mip_march_bwd_kernel(const floa
     __syncwarp();
     const float gr = g_rgb ? __ldg(g_rgb + r * 3) : 0.f, gg = g_rgb ? __ldg(g_rgb + r * 3 + 1) : 0.f, gb = g_rgb ? __ldg(g_rgb + r * 3 + 2) : 0.f;
     const float gd = g_depth ? __ldg(g_depth + r) : 0.f;
-    // pass 1: forward; T_i, w_i per interval; sum w, sum w z_mid
-    float carry = 1.f, wsum = 0.f, wz = 0.f;
-    for (int base = 0; base < S - 1; base += 32) {
-      const int i = base + lane;
-      const bool on = i < S - 1;
-      float alpha = 0.f, zmid = 0.f;
-      if (on) {
-        const float d0 = s_d[i], d1 = s_d[i + 1];
-        zmid = 0.5f * (d0 + d1);
-        const float dm = softplusf(0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f);
-        alpha = 1.f - expf(-dm * (d1 - d0));
-      }
-      float t = on ? (1.f - alpha) + 1e-10f : 1.f;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t *= q; }
-      float excl = __shfl_up_sync(0xffffffffu, t, 1);
-      if (lane == 0) excl = 1.f;
-      const float T = carry * excl;
-      carry *= __shfl_sync(0xffffffffu, t, 31);
-      const float w = on ? alpha * T : 0.f;
-      if (on) { s_T[i] = T; s_w[i] = w; }
-      wsum += w; wz = fmaf(w, zmid, wz);
-    }
-    wsum = warp_sum(wsum); wz = warp_sum(wz);
-    const bool depth_ok = gd != 0.f && wsum > 0.f;
-    const float depth = depth_ok ? wz / wsum : 0.f;
-    __syncwarp();
-    // G_i
-    for (int i = lane; i < S - 1; i += 32) {
-      const float cr = 0.5f * (s_r[i] + s_r[i + 1]), cg = 0.5f * (s_g[i] + s_g[i + 1]), cb = 0.5f * (s_b[i] + s_b[i + 1]);
-      float G = (g_w ? __ldg(g_w + r * (S - 1) + i) : 0.f) + gr * cr + gg * cg + gb * cb;
-      if (white_back) G -= gr + gg + gb;
-      if (depth_ok) G += gd * (0.5f * (s_d[i] + s_d[i + 1]) - depth) / wsum;
-      s_G[i] = G;
-    }
-    __syncwarp();
-    // pass 2: backward over the intervals with a running suffix sum of G_k w_k
-    float suffix = 0.f;
-    for (int base = ((S - 2) / 32) * 32; base >= 0; base -= 32) {
-      const int i = base + lane;
-      const bool on = i < S - 1;
-      const float gw = on ? s_G[i] * s_w[i] : 0.f;
-      float incl = gw;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const float q = __shfl_down_sync(0xffffffffu, incl, o); if (lane + o < 32) incl += q; }
-      const float after = suffix + (incl - gw);
-      suffix += __shfl_sync(0xffffffffu, incl, 0);
-      if (on) {
-        const float d0 = s_d[i], d1 = s_d[i + 1], delta = d1 - d0;
-        const float pre = 0.5f * (s_sig[i] + s_sig[i + 1]) - 1.f;
-        const float dm = softplusf(pre);
-        const float e = expf(-dm * delta);                   // 1 - alpha
-        const float t = e + 1e-10f;
-        const float dalpha = s_G[i] * s_T[i] - after / t;
-        const float sg = pre > 20.f ? 1.f : 1.f / (1.f + __expf(-pre));
-        s_dp[i] = dalpha * delta * e * sg;                   // dL/d(dens_mid before the softplus shift)
-      }
-    }
-    __syncwarp();
+    march_bwd_ray(s_d, s_sig, s_r, s_g, s_b, S, white_back, gr, gg, gb, gd, g_w ? g_w + r * (S - 1) : nullptr, 0.f, s_T, s_G, s_w, s_dp, lane);
     for (int i = lane; i < S; i += 32) {
       const float a = i < S - 1 ? s_dp[i] : 0.f, b = i > 0 ? s_dp[i - 1] : 0.f;
       d_dens[r * S + i] = 0.5f * (a + b);
       const float wc = 0.5f * ((i < S - 1 ? s_w[i] : 0.f) + (i > 0 ? s_w[i - 1] : 0.f));
       d_colors[(r * S + i) * 3 + 0] = wc * gr; d_colors[(r * S + i) * 3 + 1] = wc * gg; d_colors[(r * S + i) * 3 + 2] = wc * gb;
+    }
+    __syncwarp();
+  }
+}
+
+// The renderer's backward up to the field (renderer.py:94-142 differentiated by hand): from the samples nerfb_triplane_render_train
+// kept (depth | sigma | r | g | b, S stratified then Si importance, unsorted) and the cotangents of the six outputs, one warp per
+// ray runs the marcher backward on the S coarse samples, rank-sorts all S + Si by depth exactly as the forward's unify_samples
+// (value, then index), runs the marcher backward on the union, carries the result back through the ranks and writes, per sample in
+// the ORIGINAL order: the point (rays_o + depth * rays_d, same rounding as the forward), dL/drgb and dL/dsigma -- the inputs of
+// nerfb_triplane_field_bwd.  Depths carry no gradient (importance depths are detached, renderer.py:214).
+__global__ void __launch_bounds__(TP_WARPS * 32) triplane_samples_bwd_kernel(const float* __restrict__ samples, const float* __restrict__ ro,
+    const float* __restrict__ rd, int64_t R, int S, int Si, int white_back, const float* __restrict__ g_rgb_c, const float* __restrict__ g_depth_c,
+    const float* __restrict__ g_op_c, const float* __restrict__ g_rgb_f, const float* __restrict__ g_depth_f, const float* __restrict__ g_op_f,
+    float* __restrict__ coords, float* __restrict__ d_rgb, float* __restrict__ d_sigma) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int St = S + Si;
+  float* A = smem + (size_t)wib * 19 * St;                   // samples as kept: [depth | sigma | r | g | b] x St
+  float* B = A + 5 * St;                                      // the same, sorted by depth
+  float *s_T = B + 5 * St, *s_G = s_T + St, *s_w = s_G + St, *s_dp = s_w + St;
+  float* o_sig = s_dp + St;                                   // accumulated per ORIGINAL sample: dL/dsigma, dL/drgb
+  float *o_r = o_sig + St, *o_g = o_r + St, *o_b = o_g + St;
+  int* s_rank = reinterpret_cast<int*>(o_b + St);
+  for (int64_t r = (int64_t)blockIdx.x * TP_WARPS + wib; r < R; r += (int64_t)gridDim.x * TP_WARPS) {
+    for (int i = lane; i < 5 * St; i += 32) A[i] = __ldg(samples + r * 5 * St + i);
+    const float ox = __ldg(ro + r * 3), oy = __ldg(ro + r * 3 + 1), oz = __ldg(ro + r * 3 + 2);
+    const float dx = __ldg(rd + r * 3), dy = __ldg(rd + r * 3 + 1), dz = __ldg(rd + r * 3 + 2);
+    __syncwarp();
+    for (int i = lane; i < St; i += 32) {
+      const float t = A[i];
+      float* c = coords + (r * St + i) * 3;
+      c[0] = __fadd_rn(ox, __fmul_rn(t, dx)); c[1] = __fadd_rn(oy, __fmul_rn(t, dy)); c[2] = __fadd_rn(oz, __fmul_rn(t, dz));
+    }
+    // ---- coarse marcher: samples [0, S) are ascending as drawn ----
+    {
+      const float gr = g_rgb_c ? __ldg(g_rgb_c + r * 3) : 0.f, gg = g_rgb_c ? __ldg(g_rgb_c + r * 3 + 1) : 0.f, gb = g_rgb_c ? __ldg(g_rgb_c + r * 3 + 2) : 0.f;
+      march_bwd_ray(A, A + St, A + 2 * St, A + 3 * St, A + 4 * St, S, white_back, gr, gg, gb, g_depth_c ? __ldg(g_depth_c + r) : 0.f, nullptr,
+                    g_op_c ? __ldg(g_op_c + r) : 0.f, s_T, s_G, s_w, s_dp, lane);
+      for (int i = lane; i < St; i += 32) {
+        float ds = 0.f, wc = 0.f;
+        if (i < S) {
+          ds = 0.5f * ((i < S - 1 ? s_dp[i] : 0.f) + (i > 0 ? s_dp[i - 1] : 0.f));
+          wc = 0.5f * ((i < S - 1 ? s_w[i] : 0.f) + (i > 0 ? s_w[i - 1] : 0.f));
+        }
+        o_sig[i] = ds; o_r[i] = wc * gr; o_g[i] = wc * gg; o_b[i] = wc * gb;
+      }
+      __syncwarp();
+    }
+    // ---- unify_samples (renderer.py:160-170): the forward's rank-by-counting sort ----
+    for (int k = lane; k < St; k += 32) {
+      const float xk = A[k];
+      int rank = 0;
+      for (int m = 0; m < St; ++m) { const float xm = A[m]; rank += (xm < xk) || (xm == xk && m < k); }
+      s_rank[k] = rank;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) B[q * St + rank] = A[q * St + k];
+    }
+    __syncwarp();
+    {
+      const float gr = g_rgb_f ? __ldg(g_rgb_f + r * 3) : 0.f, gg = g_rgb_f ? __ldg(g_rgb_f + r * 3 + 1) : 0.f, gb = g_rgb_f ? __ldg(g_rgb_f + r * 3 + 2) : 0.f;
+      march_bwd_ray(B, B + St, B + 2 * St, B + 3 * St, B + 4 * St, St, white_back, gr, gg, gb, g_depth_f ? __ldg(g_depth_f + r) : 0.f, nullptr,
+                    g_op_f ? __ldg(g_op_f + r) : 0.f, s_T, s_G, s_w, s_dp, lane);
+      for (int k = lane; k < St; k += 32) {
+        const int j = s_rank[k];
+        const float ds = 0.5f * ((j < St - 1 ? s_dp[j] : 0.f) + (j > 0 ? s_dp[j - 1] : 0.f));
+        const float wc = 0.5f * ((j < St - 1 ? s_w[j] : 0.f) + (j > 0 ? s_w[j - 1] : 0.f));
+        d_sigma[r * St + k] = o_sig[k] + ds;
+        float* c = d_rgb + (r * St + k) * 3;
+        c[0] = o_r[k] + wc * gr; c[1] = o_g[k] + wc * gg; c[2] = o_b[k] + wc * gb;
+      }
     }
     __syncwarp();
   }
@@ -1307,6 +1386,23 @@ extern "C" int nerfb_triplane_field_bwd(const float* planes_cl, int H, int W, co
   const int grid = (int)(want < NERFB_SM_COUNT * 3 ? want : NERFB_SM_COUNT * 3);     // one decoder-gradient flush per block
   NERFB_LAUNCH(triplane_field_bwd_kernel, grid, TP_WARPS * 32, 0, stream, planes_cl, H, W, decoder, lr_mul, coords, n_points,
                (float)(2.0 / (double)box_warp), d_rgb, d_sigma, d_planes_cl, d_decoder);
+  return NERFB_OK;
+}
+
+extern "C" int nerfb_triplane_samples_bwd(const float* samples, const float* rays_o, const float* rays_d, int64_t n_rays, int n_samples,
+                                          int n_importance, int white_back, const float* d_rgb_coarse, const float* d_depth_coarse,
+                                          const float* d_opacity_coarse, const float* d_rgb_final, const float* d_depth_final,
+                                          const float* d_opacity_final, float* coords, float* d_rgb, float* d_sigma, void* stream) {
+  NERFB_CHECK_ARG(coords && d_rgb && d_sigma && n_rays >= 0 && n_samples >= 4 && n_importance >= 1);
+  if (n_samples + n_importance > TP_MAX_S) return NERFB_E_UNSUPPORTED;
+  if (n_rays == 0) return NERFB_OK;
+  NERFB_CHECK_ARG(samples && rays_o && rays_d);
+  const size_t smem = (size_t)TP_WARPS * 19 * (n_samples + n_importance) * sizeof(float);
+  if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
+  if (smem > 48 * 1024) NERFB_CUDA(cudaFuncSetAttribute(triplane_samples_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NERFB_LAUNCH(triplane_samples_bwd_kernel, grid_for(n_rays), TP_WARPS * 32, smem, stream, samples, rays_o, rays_d, n_rays, n_samples,
+               n_importance, white_back, d_rgb_coarse, d_depth_coarse, d_opacity_coarse, d_rgb_final, d_depth_final, d_opacity_final,
+               coords, d_rgb, d_sigma);
   return NERFB_OK;
 }
 

@@ -153,9 +153,9 @@ class _MarchFn(torch.autograd.Function):
 class _RenderFn(torch.autograd.Function):
     """ImportanceRenderer.forward of one batch element (renderer.py:94-142) as ONE autograd node: the forward is the fused
     render launch (nerfb_triplane_render_train: the six outputs plus every sample's depth / sigma / colour, 20 bytes per
-    sample, the only thing kept for the backward); the backward runs the marcher backward on the coarse samples and on the
-    depth-sorted union (renderer.py:160-170; the sort / gather / scatter are torch ops), adds the two per-sample
-    cotangents and hands them to the field backward.  Ray origins / directions / depths get no gradient (importance depths
+    sample, the only thing kept for the backward); the backward is two launches: nerfb_triplane_samples_bwd (marcher backward
+    on the coarse samples and on the depth-sorted union, renderer.py:160-170, per-sample cotangents and points) and
+    nerfb_triplane_field_bwd.  Ray origins / directions / depths get no gradient (importance depths
     are detached in the reference, renderer.py:214)."""
 
     @staticmethod
@@ -171,25 +171,10 @@ class _RenderFn(torch.autograd.Function):
     def backward(ctx, g_rgb_c, g_depth_c, g_op_c, g_rgb_f, g_depth_f, g_op_f):
         cl, dec_flat, o, d, samples = ctx.saved_tensors
         lr_mul, S, Si, box_warp, wb = ctx.cfg
-        R, St = o.shape[0], S + Si
-        c = lambda t: None if t is None else t.float().contiguous()
-        per_w = lambda g, n: None if g is None else g.float().reshape(R, 1).expand(R, n).contiguous()   # opacity = weights.sum()
-        depth, sigma, rgb = samples[:, 0], samples[:, 1], samples[:, 2:5].transpose(1, 2)                # (R,St) (R,St) (R,St,3)
-        d_rgb = torch.zeros(R, St, 3, device=o.device)
-        d_sig = torch.zeros(R, St, device=o.device)
-        if g_rgb_c is not None or g_depth_c is not None or g_op_c is not None:
-            dc, ds = ops.mip_march_bwd(rgb[:, :S].contiguous(), sigma[:, :S].contiguous(), depth[:, :S].contiguous(), wb,
-                                       c(g_rgb_c), c(g_depth_c), per_w(g_op_c, S - 1))
-            d_rgb[:, :S], d_sig[:, :S] = dc, ds
-        if g_rgb_f is not None or g_depth_f is not None or g_op_f is not None:
-            all_d, idx = torch.sort(depth, dim=1, stable=True)
-            idx3 = idx.unsqueeze(-1).expand(-1, -1, 3)
-            dc, ds = ops.mip_march_bwd(torch.gather(rgb, 1, idx3).contiguous(), torch.gather(sigma, 1, idx), all_d, wb,
-                                       c(g_rgb_f), c(g_depth_f), per_w(g_op_f, St - 1))
-            d_rgb.scatter_add_(1, idx3, dc)
-            d_sig.scatter_add_(1, idx, ds)
-        coords = torch.addcmul(o.unsqueeze(1), depth.unsqueeze(-1), d.unsqueeze(1)).reshape(-1, 3)
-        d_cl, d_dec = ops.triplane_field_bwd(cl, dec_flat, lr_mul, coords, box_warp, d_rgb.view(-1, 3), d_sig.view(-1))
+        c = lambda t: None if t is None else t.float().reshape(o.shape[0], -1).contiguous()
+        coords, d_rgb, d_sig = ops.triplane_samples_bwd(samples, o, d, S, Si, wb, c(g_rgb_c), c(g_depth_c), c(g_op_c), c(g_rgb_f),
+                                                        c(g_depth_f), c(g_op_f))
+        d_cl, d_dec = ops.triplane_field_bwd(cl, dec_flat, lr_mul, coords, box_warp, d_rgb, d_sig)
         return (d_cl.permute(0, 3, 1, 2), d_dec) + (None,) * 15
 
 

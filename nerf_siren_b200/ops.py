@@ -332,6 +332,25 @@ def mip_march_bwd(colors, densities, depths, white_back, d_rgb=None, d_depth=Non
     return d_colors, d_dens
 
 
+def triplane_samples_bwd(samples, rays_o, rays_d, n_samples, n_importance, white_back, d_rgb_c=None, d_depth_c=None, d_opacity_c=None,
+                         d_rgb_f=None, d_depth_f=None, d_opacity_f=None):
+    """Backward of the renderer down to its samples: -> (coords (R*St, 3), d_rgb (R*St, 3), d_sigma (R*St,)), the inputs of
+    triplane_field_bwd.  ``samples`` (R, 5, St) as returned by triplane_render(..., return_samples=True)."""
+    r, st = samples.shape[0], n_samples + n_importance
+    if tuple(samples.shape) != (r, 5, st):
+        raise ValueError(f"samples must be (R, 5, {st})")
+    dev = samples.device
+    coords, d_rgb, d_sigma = torch.empty(r * st, 3, device=dev), torch.empty(r * st, 3, device=dev), torch.empty(r * st, device=dev)
+    if r == 0:
+        return coords, d_rgb, d_sigma
+    check(lib.nerfb_triplane_samples_bwd(
+        _req(samples, "samples"), _req(rays_o, "rays_o"), _req(rays_d, "rays_d"), r, int(n_samples), int(n_importance), int(bool(white_back)),
+        _req(d_rgb_c, "d_rgb_c", allow_none=True), _req(d_depth_c, "d_depth_c", allow_none=True), _req(d_opacity_c, "d_opacity_c", allow_none=True),
+        _req(d_rgb_f, "d_rgb_f", allow_none=True), _req(d_depth_f, "d_depth_f", allow_none=True), _req(d_opacity_f, "d_opacity_f", allow_none=True),
+        coords.data_ptr(), d_rgb.data_ptr(), d_sigma.data_ptr(), _stream()), "nerfb_triplane_samples_bwd")
+    return coords, d_rgb, d_sigma
+
+
 def triplane_render(planes_cl, decoder_flat, lr_mul, rays_o, rays_d, n_samples, n_importance, ray_start, ray_end,
                     ray_start_arr=None, ray_end_arr=None, disparity=False, box_warp=1.0, white_back=False,
                     rand_coarse=None, u=None, seed=0, return_depths_fine=False, return_samples=False):
@@ -456,7 +475,7 @@ def _on_tensor_device(fn):
 
 
 for _name in ("sample_coarse", "embed", "composite_fwd", "composite_bwd", "searchsorted", "sample_pdf", "resample",
-              "adam_step", "mlp_fwd", "mlp_bwd", "render_fused", "triplane_relayout", "triplane_field", "triplane_field_bwd", "mip_march", "mip_march_bwd", "triplane_render",
+              "adam_step", "mlp_fwd", "mlp_bwd", "render_fused", "triplane_relayout", "triplane_field", "triplane_field_bwd", "mip_march", "mip_march_bwd", "triplane_samples_bwd", "triplane_render",
               "finish_image", "sigma_grid", "pack_vol"):
     globals()[_name] = _on_tensor_device(globals()[_name])
 del _name

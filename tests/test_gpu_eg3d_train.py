@@ -134,7 +134,8 @@ def test_training_step_gradients_match_oracle_autograd(name, decoder_arm):
     p_ref = planes.clone().requires_grad_(True)
     dec = {k: v.clone().requires_grad_(True) for k, v in dec0.items()}
     out = E.importance_render(p_ref, dec, ro, rd, opts, gd["rand_coarse"], gd["u"])
-    loss_ref = ((out[0][0] - target) ** 2).mean() + ((out[3][0] - target) ** 2).mean() + 0.1 * out[5].mean() + 0.05 * out[4].mean()
+    loss_ref = (((out[0][0] - target) ** 2).mean() + ((out[3][0] - target) ** 2).mean() + 0.1 * out[5].mean() + 0.05 * out[4].mean()
+                + 0.07 * out[2].mean() + 0.03 * out[1].mean())
     loss_ref.backward()
     # this package
     m = nb().eg3d
@@ -149,7 +150,8 @@ def test_training_step_gradients_match_oracle_autograd(name, decoder_arm):
         same = m.ImportanceRenderer()(p, decoder, ro.to(DEV), rd.to(DEV), opts, rand_coarse=gd["rand_coarse"].to(DEV), u=gd["u"].to(DEV))
     assert all(torch.equal(a.detach(), b) for a, b in zip(got, same)) and got[3].requires_grad
     t = target.to(DEV)
-    loss = ((got[0][0] - t) ** 2).mean() + ((got[3][0] - t) ** 2).mean() + 0.1 * got[5].mean() + 0.05 * got[4].mean()
+    loss = (((got[0][0] - t) ** 2).mean() + ((got[3][0] - t) ** 2).mean() + 0.1 * got[5].mean() + 0.05 * got[4].mean()
+            + 0.07 * got[2].mean() + 0.03 * got[1].mean())
     assert abs(float(loss.detach()) - float(loss_ref.detach())) < 1e-4
     loss.backward()
     assert rel(p.grad.cpu(), p_ref.grad) < 2e-3
@@ -215,6 +217,47 @@ def test_render_train_entry_writes_the_samples_of_the_render():
     assert torch.isfinite(auto[6]).all() and float(auto[6][:, 0].min()) >= 2.3
     with pytest.raises(ValueError):
         ops.triplane_render(*args, return_depths_fine=True, return_samples=True)
+
+
+@pytest.mark.parametrize("R,S,Si,white", [(300, 24, 24, False), (64, 48, 48, True), (33, 12, 40, False)])
+def test_samples_backward_equals_the_marcher_backward_composition(R, S, Si, white):
+    """nerfb_triplane_samples_bwd against the same thing composed from nerfb_mip_march_bwd and torch's stable sort / gather /
+    scatter (renderer.py:160-170), all six cotangents at once and the importance depths interleaved with (and in 12 + 40
+    outnumbering) the coarse ones; duplicates among the depths exercise the (value, index) tie rule."""
+    ops = nb().ops
+    g = torch.Generator(device=DEV).manual_seed(R + S)
+    St = S + Si
+    coarse = 2.0 + torch.rand(R, S, device=DEV, generator=g).cumsum(1) / S
+    fine = 2.0 + torch.rand(R, Si, device=DEV, generator=g) * 1.1
+    fine[:, 0] = coarse[:, S // 2]                       # a tie between a coarse and an importance depth
+    fine[:, 1] = fine[:, 2]                              # and between two importance depths
+    samples = torch.empty(R, 5, St, device=DEV)
+    samples[:, 0] = torch.cat([coarse, fine], 1)
+    samples[:, 1] = torch.randn(R, St, device=DEV, generator=g) * 5 + 1
+    samples[:, 2:5] = torch.rand(R, 3, St, device=DEV, generator=g)
+    o, d = torch.randn(R, 3, device=DEV, generator=g), torch.randn(R, 3, device=DEV, generator=g)
+    cot = [torch.randn(R, 3, device=DEV, generator=g), torch.randn(R, device=DEV, generator=g), torch.randn(R, device=DEV, generator=g),
+           torch.randn(R, 3, device=DEV, generator=g), torch.randn(R, device=DEV, generator=g), torch.randn(R, device=DEV, generator=g)]
+    coords, d_rgb, d_sig = ops.triplane_samples_bwd(samples, o, d, S, Si, white, *cot)
+    depth, sigma, rgb = samples[:, 0], samples[:, 1], samples[:, 2:5].transpose(1, 2)
+    want_rgb, want_sig = torch.zeros(R, St, 3, device=DEV), torch.zeros(R, St, device=DEV)
+    dc, ds = ops.mip_march_bwd(rgb[:, :S].contiguous(), sigma[:, :S].contiguous(), depth[:, :S].contiguous(), white, cot[0], cot[1],
+                               cot[2].reshape(R, 1).expand(R, S - 1).contiguous())
+    want_rgb[:, :S], want_sig[:, :S] = dc, ds
+    all_d, idx = torch.sort(depth, dim=1, stable=True)
+    idx3 = idx.unsqueeze(-1).expand(-1, -1, 3)
+    dc, ds = ops.mip_march_bwd(torch.gather(rgb, 1, idx3).contiguous(), torch.gather(sigma, 1, idx), all_d, white, cot[3], cot[4],
+                               cot[5].reshape(R, 1).expand(R, St - 1).contiguous())
+    want_rgb.scatter_add_(1, idx3, dc)
+    want_sig.scatter_add_(1, idx, ds)
+    assert rel(d_rgb.view(R, St, 3), want_rgb) < 1e-6 and rel(d_sig.view(R, St), want_sig) < 1e-6
+    torch.testing.assert_close(coords.view(R, St, 3), o.unsqueeze(1) + depth.unsqueeze(-1) * d.unsqueeze(1), rtol=0, atol=1e-6)
+    # null cotangents = zero cotangents
+    only_f = ops.triplane_samples_bwd(samples, o, d, S, Si, white, None, None, None, cot[3], None, None)
+    zeros = [torch.zeros_like(c) for c in cot]
+    zeros[3] = cot[3]
+    ref_f = ops.triplane_samples_bwd(samples, o, d, S, Si, white, *zeros)
+    assert torch.equal(only_f[1], ref_f[1]) and torch.equal(only_f[2], ref_f[2])
 
 
 def test_run_model_is_differentiable_through_the_mirror():

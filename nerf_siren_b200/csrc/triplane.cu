@@ -105,7 +105,8 @@ __device__ __forceinline__ void tap_lane(int H, int W, float x, float y, float z
 constexpr int TM_PTS = 16;
 constexpr int TM_FS = 36;      // features [pt][ch]: stride = 4 (mod 32): (pt over lane / 4, ch over lane % 4) is conflict-free
 constexpr int TM_W1 = 36;      // W1 [hid][ch]
-constexpr int TM_DEC_FLOATS = TP_HID * TM_W1 + 4 * TP_HID + TP_HID;       // W1s | W2s [k][hid] | B1s
+constexpr int TM_W1_FLOATS = 2 * TP_HID * TM_W1;                          // W1 split in its two TF32 terms: hi [hid][TM_W1] | lo
+constexpr int TM_DEC_FLOATS = TM_W1_FLOATS + 4 * TP_HID + TP_HID;         // W1s (hi | lo) | W2s [k][hid] | B1s
 __device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(x - __uint_as_float(hi)));
@@ -122,14 +123,26 @@ __device__ __forceinline__ void mma_3x(float (&c)[4], const uint32_t (&ah)[4], c
 }
 
 
+// the same with B = two entries of the pre-split W1 copy in shared memory (p and p + second; lo term TP_HID * TM_W1 further)
+__device__ __forceinline__ void mma_3x_w1(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], const float* p, int second) {
+  const uint32_t b0h = __float_as_uint(p[0]), b1h = __float_as_uint(p[second]);
+  const uint32_t b0l = __float_as_uint(p[TP_HID * TM_W1]), b1l = __float_as_uint(p[TP_HID * TM_W1 + second]);
+  mma_tf32(c, al, b0h, b1h); mma_tf32(c, ah, b0l, b1l); mma_tf32(c, ah, b0h, b1h);
+}
+
 // block-wide: the decoder's effective weights (gains of networks_stylegan2.py:109-110) into shared memory
 __device__ __forceinline__ void load_decoder_mma(float* W1s, const float* __restrict__ decp, float lr_mul) {
-  float* W2s = W1s + TP_HID * TM_W1;
+  float* W2s = W1s + TM_W1_FLOATS;
   float* B1s = W2s + 4 * TP_HID;
   const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
   const float* b1p = decp + TP_HID * TP_C;
   const float* w2p = b1p + TP_HID;
-  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) W1s[(i >> 5) * TM_W1 + (i & 31)] = __fmul_rn(__ldg(decp + i), g1);
+  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) {
+    uint32_t hi, lo;
+    tf32_split(__fmul_rn(__ldg(decp + i), g1), hi, lo);
+    W1s[(i >> 5) * TM_W1 + (i & 31)] = __uint_as_float(hi);
+    W1s[TP_HID * TM_W1 + (i >> 5) * TM_W1 + (i & 31)] = __uint_as_float(lo);
+  }
   for (int i = threadIdx.x; i < 4 * TP_HID; i += blockDim.x) W2s[i] = __fmul_rn(__ldg(w2p + i), g2);
   for (int i = threadIdx.x; i < TP_HID; i += blockDim.x) B1s[i] = __ldg(b1p + i) * lr_mul;
 }
@@ -157,7 +170,7 @@ __device__ __forceinline__ float4 gather_quad(const float* __restrict__ planes, 
 // run_model for the 16 points whose features sit in Fs[pt][TM_FS] (written by gather_quad, __syncwarp'ed by the caller).
 // out[u][0] = sigma, out[u][1..3] = rgb of point (lane / 4) + 8 u, identical on the four lanes of a group.
 __device__ __forceinline__ void decode16(const float* Fs, const float* W1s, const float (&b2)[4], int lane, float (&out)[2][4]) {
-  const float* W2s = W1s + TP_HID * TM_W1;
+  const float* W2s = W1s + TM_W1_FLOATS;
   const float* B1s = W2s + 4 * TP_HID;
   const int g = lane >> 2, t = lane & 3;
   float pre[8][4];
@@ -175,7 +188,7 @@ __device__ __forceinline__ void decode16(const float* Fs, const float* W1s, cons
     tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt)
-      mma_3x(pre[nt], ah, al, W1s[(8 * nt + g) * TM_W1 + 8 * kt + t], W1s[(8 * nt + g) * TM_W1 + 8 * kt + t + 4]);
+      mma_3x_w1(pre[nt], ah, al, W1s + (8 * nt + g) * TM_W1 + 8 * kt + t, 4);
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) { out[0][k] = 0.f; out[1][k] = 0.f; }
@@ -805,7 +818,7 @@ constexpr int TM_WARPS = 12;     // warps per block (one block per SM): the kern
 constexpr int TM_FT = 20;      // features [ch][pt]: stride = 4 (mod 16)
 constexpr int TM_DP = 72;      // dpre / h [pt][hid]: stride = 8 (mod 32): (pt over lane % 4, hid over lane / 4) is conflict-free
 constexpr int TM_WARP_FLOATS = TM_PTS * TM_FS + TP_C * TM_FT + 2 * TM_PTS * TM_DP + TM_PTS * 4;
-constexpr int TM_BLOCK_FLOATS = TP_HID * TM_W1 + 4 * TP_HID + TP_HID;
+constexpr int TM_BLOCK_FLOATS = TM_DEC_FLOATS;
 constexpr size_t TM_SMEM = (size_t)(TM_BLOCK_FLOATS + TM_WARPS * TM_WARP_FLOATS) * sizeof(float);
 static_assert(TM_WARPS * TM_WARP_FLOATS >= TP_DEC_PARAMS, "flush buffer aliases the warp areas");
 
@@ -816,8 +829,8 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;                     // mma fragment coordinates
   const int ps = lane >> 3, sub4 = (lane & 7) * 4;            // gather / scatter coordinates
-  float* W1s = tm_smem;                                       // [hid][TM_W1], times the layer gain
-  float* W2s = W1s + TP_HID * TM_W1;                          // [k][hid], times the layer gain
+  float* W1s = tm_smem;                                       // [hid][TM_W1] hi | lo, times the layer gain
+  float* W2s = W1s + TM_W1_FLOATS;                            // [k][hid], times the layer gain
   float* B1s = W2s + 4 * TP_HID;
   float* wbase = B1s + TP_HID + wib * TM_WARP_FLOATS;
   float* Fs = wbase;                                          // [pt][TM_FS]   features, later dL/dfeat
@@ -826,11 +839,8 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
   float* Hs = DPs + TM_PTS * TM_DP;                           // [pt][TM_DP]   hidden activations
   float* GOs = Hs + TM_PTS * TM_DP;                           // [pt][4]       dL/d(output pre-activations)
   const float g1 = lr_mul / sqrtf((float)TP_C), g2 = lr_mul / sqrtf((float)TP_HID);
-  const float* b1p = decp + TP_HID * TP_C;
-  const float* w2p = b1p + TP_HID;
-  for (int i = threadIdx.x; i < TP_HID * TP_C; i += blockDim.x) W1s[(i >> 5) * TM_W1 + (i & 31)] = __fmul_rn(__ldg(decp + i), g1);
-  for (int i = threadIdx.x; i < 4 * TP_HID; i += blockDim.x) W2s[i] = __fmul_rn(__ldg(w2p + i), g2);
-  for (int i = threadIdx.x; i < TP_HID; i += blockDim.x) B1s[i] = __ldg(b1p + i) * lr_mul;
+  const float* w2p = decp + TP_HID * TP_C + TP_HID;
+  load_decoder_mma(W1s, decp, lr_mul);
   float b2[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) b2[k] = __ldg(w2p + 4 * TP_HID + k) * lr_mul;
@@ -894,7 +904,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt)                          // B[k = ch][n = hid] = W1[hid][ch]
-        mma_3x(pre[nt], ah, al, W1s[(8 * nt + g) * TM_W1 + 8 * kt + t], W1s[(8 * nt + g) * TM_W1 + 8 * kt + t + 4]);
+        mma_3x_w1(pre[nt], ah, al, W1s + (8 * nt + g) * TM_W1 + 8 * kt + t, 4);
     }
     // ---- hidden activations, second layer, upstream cotangents ----
     float o[2][4];                                            // [pt g, g + 8][k]
@@ -970,7 +980,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       tf32_split(pre[kt][1], ah[2], al[2]); tf32_split(pre[kt][3], ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt)                          // B[k = hid][n = ch] = W1[hid][ch]
-        mma_3x(df[nt], ah, al, W1s[(8 * kt + 2 * t) * TM_W1 + 8 * nt + g], W1s[(8 * kt + 2 * t + 1) * TM_W1 + 8 * nt + g]);
+        mma_3x_w1(df[nt], ah, al, W1s + (8 * kt + 2 * t) * TM_W1 + 8 * nt + g, TM_W1);
     }
     __syncwarp();                                             // GEMM1's reads of Fs are done: Fs now carries dL/dfeat / 3
 #pragma unroll

@@ -107,9 +107,15 @@ constexpr int TM_FS = 36;      // features [pt][ch]: stride = 4 (mod 32): (pt ov
 constexpr int TM_W1 = 36;      // W1 [hid][ch]
 constexpr int TM_W1_FLOATS = 2 * TP_HID * TM_W1;                          // W1 split in its two TF32 terms: hi [hid][TM_W1] | lo
 constexpr int TM_DEC_FLOATS = TM_W1_FLOATS + 4 * TP_HID + TP_HID;         // W1s (hi | lo) | W2s [k][hid] | B1s
-__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {      // round-to-nearest terms (weights, once per block)
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(x - __uint_as_float(hi)));
+}
+// per-sample operands: hi = x with the 13 low mantissa bits cleared, lo = x - hi (exact; the tensor core ignores ITS low bits):
+// two instructions instead of the five of the rounding split (cvt.rna.tf32 is emulated with integer ops), error <= 2^-20 |x|
+__device__ __forceinline__ void tf32_split_fast(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xFFFFE000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -118,7 +124,7 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], 
 // c += a . b with both operands split in two TF32 terms
 __device__ __forceinline__ void mma_3x(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], float b0, float b1) {
   uint32_t b0h, b0l, b1h, b1l;
-  tf32_split(b0, b0h, b0l); tf32_split(b1, b1h, b1l);
+  tf32_split_fast(b0, b0h, b0l); tf32_split_fast(b1, b1h, b1l);
   mma_tf32(c, al, b0h, b1h); mma_tf32(c, ah, b0l, b1l); mma_tf32(c, ah, b0h, b1h);
 }
 
@@ -182,10 +188,10 @@ __device__ __forceinline__ void decode16(const float* Fs, const float* W1s, cons
 #pragma unroll
   for (int kt = 0; kt < 4; ++kt) {
     uint32_t ah[4], al[4];
-    tf32_split(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
-    tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
-    tf32_split(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
-    tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
+    tf32_split_fast(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
+    tf32_split_fast(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
+    tf32_split_fast(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
+    tf32_split_fast(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt)
       mma_3x_w1(pre[nt], ah, al, W1s + (8 * nt + g) * TM_W1 + 8 * kt + t, 4);
@@ -604,6 +610,11 @@ constexpr int TP_DEC_PARAMS = TP_HID * TP_C + TP_HID + 4 * TP_HID + 4;      // W
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
+// predicated on wt != 0 without a branch (twelve of these per point)
+__device__ __forceinline__ void red_add_v4_if(float* p, float a, float b, float c, float d, float wt) {
+  asm volatile("{ .reg .pred q; setp.neu.f32 q, %5, 0f00000000; @q red.global.add.v4.f32 [%0], {%1, %2, %3, %4}; }"
+               :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "f"(wt) : "memory");
+}
 
 constexpr int TPB_NB = 4;                        // points per warp between two block barriers
 constexpr int TPB_TILE = TP_WARPS * TPB_NB;      // points per tile
@@ -898,10 +909,10 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
 #pragma unroll
     for (int kt = 0; kt < 4; ++kt) {
       uint32_t ah[4], al[4];
-      tf32_split(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
-      tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
-      tf32_split(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
-      tf32_split(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
+      tf32_split_fast(Fs[g * TM_FS + 8 * kt + t], ah[0], al[0]);
+      tf32_split_fast(Fs[(g + 8) * TM_FS + 8 * kt + t], ah[1], al[1]);
+      tf32_split_fast(Fs[g * TM_FS + 8 * kt + t + 4], ah[2], al[2]);
+      tf32_split_fast(Fs[(g + 8) * TM_FS + 8 * kt + t + 4], ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt)                          // B[k = ch][n = hid] = W1[hid][ch]
         mma_3x_w1(pre[nt], ah, al, W1s + (8 * nt + g) * TM_W1 + 8 * kt + t, 4);
@@ -925,7 +936,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       }
       // softplus'(x) = sigmoid(x) = 1 - exp(-softplus(x)) (1 beyond the threshold of 20); kept in place of pre
 #pragma unroll
-      for (int i = 0; i < 4; ++i) pre[nt][i] = pre[nt][i] > 20.f ? 1.f : 1.f - __expf(-h[i]);
+      for (int i = 0; i < 4; ++i) pre[nt][i] = 1.f - __expf(-h[i]);     // (beyond the softplus threshold of 20 this is 1 to fp32)
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -976,8 +987,8 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
 #pragma unroll
     for (int kt = 0; kt < 8; ++kt) {
       uint32_t ah[4], al[4];
-      tf32_split(pre[kt][0], ah[0], al[0]); tf32_split(pre[kt][2], ah[1], al[1]);
-      tf32_split(pre[kt][1], ah[2], al[2]); tf32_split(pre[kt][3], ah[3], al[3]);
+      tf32_split_fast(pre[kt][0], ah[0], al[0]); tf32_split_fast(pre[kt][2], ah[1], al[1]);
+      tf32_split_fast(pre[kt][1], ah[2], al[2]); tf32_split_fast(pre[kt][3], ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt)                          // B[k = hid][n = ch] = W1[hid][ch]
         mma_3x_w1(df[nt], ah, al, W1s + (8 * kt + 2 * t) * TM_W1 + 8 * nt + g, TM_W1);
@@ -1002,11 +1013,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
         for (int c = 0; c < 12; ++c) {
           int off; float wt;
           tap_lane(H, W, x, y, z, c, off, wt);
-#ifdef TPB_NO_RED
-          if (wt == 123.456f) red_add_v4(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt);
-#else
-          if (wt != 0.f) red_add_v4(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt);
-#endif
+          red_add_v4_if(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt, wt);
         }
       }
     }
@@ -1016,10 +1023,10 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       uint32_t ah[2][4], al[2][4];
 #pragma unroll
       for (int mt = 0; mt < 2; ++mt) {
-        tf32_split(Ft[(16 * mt + g) * TM_FT + 8 * kt + t], ah[mt][0], al[mt][0]);
-        tf32_split(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t], ah[mt][1], al[mt][1]);
-        tf32_split(Ft[(16 * mt + g) * TM_FT + 8 * kt + t + 4], ah[mt][2], al[mt][2]);
-        tf32_split(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t + 4], ah[mt][3], al[mt][3]);
+        tf32_split_fast(Ft[(16 * mt + g) * TM_FT + 8 * kt + t], ah[mt][0], al[mt][0]);
+        tf32_split_fast(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t], ah[mt][1], al[mt][1]);
+        tf32_split_fast(Ft[(16 * mt + g) * TM_FT + 8 * kt + t + 4], ah[mt][2], al[mt][2]);
+        tf32_split_fast(Ft[(16 * mt + g + 8) * TM_FT + 8 * kt + t + 4], ah[mt][3], al[mt][3]);
       }
       // GEMM4: dW2^T[hid][k] += h^T[hid][pt] . go[pt][k]; B = go, columns k >= 4 of the padded tile are zero
       {
@@ -1027,10 +1034,10 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
 #pragma unroll
         for (int mt = 0; mt < 4; ++mt) {
           uint32_t hh[4], hl[4];
-          tf32_split(Hs[(8 * kt + t) * TM_DP + 16 * mt + g], hh[0], hl[0]);
-          tf32_split(Hs[(8 * kt + t) * TM_DP + 16 * mt + g + 8], hh[1], hl[1]);
-          tf32_split(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g], hh[2], hl[2]);
-          tf32_split(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g + 8], hh[3], hl[3]);
+          tf32_split_fast(Hs[(8 * kt + t) * TM_DP + 16 * mt + g], hh[0], hl[0]);
+          tf32_split_fast(Hs[(8 * kt + t) * TM_DP + 16 * mt + g + 8], hh[1], hl[1]);
+          tf32_split_fast(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g], hh[2], hl[2]);
+          tf32_split_fast(Hs[(8 * kt + t + 4) * TM_DP + 16 * mt + g + 8], hh[3], hl[3]);
           mma_3x(gw2[mt], hh, hl, q0, q1);
         }
       }
@@ -1038,7 +1045,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       for (int nt = 0; nt < 8; ++nt) {                        // B[k = pt][n = hid]
         const float d0 = DPs[(8 * kt + t) * TM_DP + 8 * nt + g], d1 = DPs[(8 * kt + t + 4) * TM_DP + 8 * nt + g];
         uint32_t b0h, b0l, b1h, b1l;
-        tf32_split(d0, b0h, b0l); tf32_split(d1, b1h, b1l);
+        tf32_split_fast(d0, b0h, b0l); tf32_split_fast(d1, b1h, b1l);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
           mma_tf32(gw1[mt][nt], al[mt], b0h, b1h); mma_tf32(gw1[mt][nt], ah[mt], b0l, b1l); mma_tf32(gw1[mt][nt], ah[mt], b0h, b1h);

@@ -762,7 +762,7 @@ class Eg3dTrainWorkload:
                                                           1.0, False, None, None, 1, return_samples=True), 20)
         out = []
         for name, ms, by, note in (
-                ("triplane_field_bwd_kernel", ms_b, P * 3072, "algorithmic bytes = 1,536 B of bilinear taps gathered + 1,536 B of plane-gradient "
+                ("triplane_field_bwd_mma_kernel", ms_b, P * 3072, "algorithmic bytes = 1,536 B of bilinear taps gathered + 1,536 B of plane-gradient "
                  "rows reduced per sample (both served by L2; includes the zero-fill of the 25 MB gradient image)"),
                 ("triplane_render_kernel", ms_f, P * 1536 + P * 20, "training forward: 1,536 B of taps per sample + 20 B per sample kept for the backward")):
             out.append(finish_roofline({"kernel": name, "bound": "hbm", "achieved": by / ms / 1e6, "peak": peaks["hbm_gbs"], "unit": "GB/s",

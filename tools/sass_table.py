@@ -1,6 +1,6 @@
 """profiles/sass_tcgen05.txt: per-kernel counts of the Blackwell-only SASS mnemonics in the shipped libnerf_b200.so
 (UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTCBAR = tcgen05.commit, UBLKCP = cp.async.bulk, UTCATOMSWS = TMEM alloc,
-SYNCS = mbarrier ops).  Usage: python tools/sass_table.py > profiles/sass_tcgen05.txt"""
+SYNCS = mbarrier ops; HMMA = mma.sync, here HMMA.1688.F32.TF32 of the EG3D decoder).  Usage: python tools/sass_table.py > profiles/sass_tcgen05.txt"""
 import os
 import re
 import subprocess
@@ -8,7 +8,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "nerf_siren_b200", "libnerf_b200.so")
-MN = ["UTCHMMA", "LDTM", "UTCBAR", "UBLKCP", "UTCATOMSWS", "SYNCS", "MEMBAR", "REDG", "LDG", "STG"]
+MN = ["UTCHMMA", "HMMA", "LDTM", "UTCBAR", "UBLKCP", "UTCATOMSWS", "SYNCS", "MEMBAR", "REDG", "LDG", "STG"]
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
 demangle = lambda n: subprocess.run(["cu++filt", n], capture_output=True, text=True).stdout.strip() or n
 rows, cur, counts = [], None, None

@@ -19,6 +19,7 @@ import torch
 from torch import nn
 
 from . import dp
+from .losses import loss_dict
 from .models.nerf import Embedding, NeRF
 from .models.rendering import render_rays
 
@@ -194,3 +195,67 @@ class NeRFSystem(nn.Module):
                 self.save_checkpoint(os.path.join(ckpt_dir, f"epoch={epoch}.ckpt"))
             history.append(log)
         return history
+
+
+class EG3DSystem(nn.Module):
+    """system.py:17-170 without Lightning: the caller of the EG3D path on the training side (``train.py`` builds it for the
+    tri-plane runs).  ``forward`` renders a batch of (B, 8) rays through ``EG3D_Renderer.render`` with ``conditioning_params =
+    -1`` (system.py:72-75); ``training_step`` applies ``loss_dict[hparams.loss_type]`` to the six-key result and back-propagates
+    through the hand-written kernels (fused render keeping its samples -> samples backward -> field backward);
+    ``validation_step`` renders in chunks of 4096 rays (system.py:139-146).  ``plane_source`` / ``rendering_kwargs`` are passed
+    on to ``EG3D_Renderer`` (the reference's StyleGAN2 backbone is outside this path; default: directly optimised planes)."""
+
+    def __init__(self, hparams, plane_source=None, rendering_kwargs=None):
+        super().__init__()
+        from .eg3d import EG3D_Renderer
+        self.hparams = hparams
+        self.loss = loss_dict[getattr(hparams, "loss_type", "mse")]()
+        self.eg3d_renderer = EG3D_Renderer(plane_source, rendering_kwargs)
+        self.models = [self.eg3d_renderer]
+        if getattr(hparams, "pretrained", None):
+            load_ckpt(self.eg3d_renderer, hparams.pretrained, model_name="eg3d_renderer")
+        self.global_step, self.current_epoch = 0, 0
+        self.optimizer = self.scheduler = None
+
+    def decode_batch(self, batch):
+        return batch["rays"], batch["rgbs"]
+
+    def forward(self, rays) -> Dict[str, torch.Tensor]:
+        rays = rays.reshape(-1, 8)
+        return self.eg3d_renderer.render(-1, rays[:, :3].contiguous(), rays[:, 3:6].contiguous())
+
+    def configure_optimizers(self):
+        self.optimizer = get_optimizer(self.hparams, self.models)
+        self.scheduler = get_scheduler(self.hparams, self.optimizer)
+        return [self.optimizer], [self.scheduler]
+
+    def training_step(self, batch, batch_nb=0):
+        log = {"lr": get_learning_rate(self.optimizer)}
+        rays, rgbs = self.decode_batch(batch)
+        results = self(rays)
+        log["train/loss"] = loss = self.loss(results, rgbs)
+        typ = "fine" if "rgb_fine" in results else "coarse"
+        with torch.no_grad():
+            log["train/psnr"] = psnr_ = psnr(results[f"rgb_{typ}"], rgbs)
+        return {"loss": loss, "progress_bar": {"train_psnr": psnr_}, "log": log}
+
+    @torch.no_grad()
+    def validation_step(self, batch, batch_nb=0):
+        rays, rgbs = self.decode_batch(batch)
+        rays, rgbs = rays.squeeze(), rgbs.squeeze()
+        chunk = 1024 * 4
+        results = defaultdict(list)
+        for i in range(0, rays.shape[0], chunk):
+            for k, v in self(rays[i:i + chunk]).items():
+                results[k] += [v]
+        results = {k: torch.cat(v, 0) for k, v in results.items()}
+        typ = "fine" if "rgb_fine" in results else "coarse"
+        return {"val_loss": self.loss(results, rgbs), "val_psnr": psnr(results[f"rgb_{typ}"], rgbs)}
+
+    validation_epoch_end = NeRFSystem.validation_epoch_end
+
+    def state_dict_lightning(self):
+        return {f"eg3d_renderer.{k}": v.detach().cpu() for k, v in self.eg3d_renderer.state_dict().items()}
+
+    save_checkpoint = NeRFSystem.save_checkpoint
+    fit = NeRFSystem.fit

@@ -196,3 +196,29 @@ def test_system_fit_trains_and_checkpoints(tmp_path):
         assert torch.equal(a, b)
     out = sys_(rays)                                     # system.py:199-223 result keys
     assert set(out) == {"rgb_coarse", "depth_coarse", "opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine"}
+
+
+@pytest.mark.gpu
+def test_eg3d_system_fit_trains_and_checkpoints(tmp_path):
+    """EG3DSystem (system.py:17-170 of the reference without Lightning): training_step through the fused render + the two
+    backward kernels, loss_dict['mse'] on the six-key result, chunked validation, Lightning-layout checkpoint that
+    ``hparams.pretrained`` reads back (system.py:24-25)."""
+    from nerf_siren_b200 import eg3d, system as S
+    from oracle import eg3d_oracle as E
+    torch.manual_seed(0)
+    kw = dict(eg3d.DEFAULT_RENDERING_KWARGS, depth_resolution=16, depth_resolution_importance=16, ray_start=2.2, ray_end=3.3, box_warp=1.0)
+    sys_ = S.EG3DSystem(hp(num_epochs=2, lr=2e-2), plane_source=eg3d.LearnedPlanes(resolution=32), rendering_kwargs=kw).to(DEV)
+    ro, rd = E.camera_rays(9000, seed=2)
+    rays = torch.cat([ro[0], rd[0], torch.zeros(9000, 2)], 1).to(DEV)
+    rgbs = (torch.rand(9000, 3, generator=torch.Generator().manual_seed(1)) * 0.4 + 0.3).to(DEV)
+    batches = [{"rays": rays[i:i + 1024], "rgbs": rgbs[i:i + 1024]} for i in range(0, 8192, 1024)]
+    hist = sys_.fit(batches, val_batches=[{"rays": rays[None], "rgbs": rgbs[None]}], ckpt_dir=str(tmp_path))   # 9000 rays: 3 chunks
+    assert len(hist) == 2 and hist[1]["val/loss"] < hist[0]["val/loss"] and hist[1]["val/psnr"] > hist[0]["val/psnr"]
+    assert hist[1]["train/loss"] < hist[0]["train/loss"]
+    out = sys_(rays[:100])
+    assert set(out) == {"rgb_coarse", "depth_coarse", "opacity_coarse", "rgb_fine", "depth_fine", "opacity_fine"}
+    assert out["rgb_fine"].shape == (100, 3) and out["rgb_fine"].requires_grad
+    again = S.EG3DSystem(hp(pretrained=os.path.join(tmp_path, "epoch=1.ckpt")), plane_source=eg3d.LearnedPlanes(resolution=32),
+                         rendering_kwargs=kw).to(DEV)
+    for (ka, a), (kb, b) in zip(again.eg3d_renderer.state_dict().items(), sys_.eg3d_renderer.state_dict().items()):
+        assert ka == kb and torch.equal(a, b), ka

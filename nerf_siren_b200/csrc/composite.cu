@@ -237,6 +237,75 @@ composite_bwd_kernel(const float* __restrict__ raw, int C, const float* __restri
   }
 }
 
+// The same for the common shape (C = 4, S = 32 * NCH, 16-byte aligned raw / d_raw): every input of the ray is read ONCE into
+// registers (raw as float4, z, noise, d_weights), pass 2 runs from registers (the generic kernel re-reads raw / z / noise and
+// parks T, g in shared memory), the gradient leaves as one float4 per sample.  Same arithmetic in the same order: bit-identical.
+template <int NCH>
+__global__ void __launch_bounds__(COMP_WARPS * 32)
+composite_bwd_reg_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays,
+                         const float* __restrict__ noise, float noise_std, int white_back, int64_t N,
+                         const float* __restrict__ d_rgb, const float* __restrict__ d_depth, const float* __restrict__ d_opacity,
+                         const float* __restrict__ d_weights, float* __restrict__ d_raw) {
+  constexpr int S = 32 * NCH;
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (int64_t)gridDim.x * COMP_WARPS;
+  for (int64_t r = (int64_t)blockIdx.x * COMP_WARPS + (threadIdx.x >> 5); r < N; r += nwarps) {
+    float4 rv[NCH];
+    float zv[NCH], nz[NCH], g[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int64_t i = r * S + 32 * c + lane;
+      rv[c] = __ldg(reinterpret_cast<const float4*>(raw) + i);
+      zv[c] = __ldg(z + i);
+      nz[c] = noise ? __ldg(noise + i) : 0.f;
+      g[c] = d_weights ? __ldg(d_weights + i) : 0.f;
+    }
+    const float dx = __ldg(rays + r * 8 + 3), dy = __ldg(rays + r * 8 + 4), dz = __ldg(rays + r * 8 + 5);
+    const float dnorm = sqrtf(dx * dx + dy * dy + dz * dz);
+    float gr = 0.f, gg = 0.f, gb = 0.f, gd = 0.f, go = 0.f;
+    if (d_rgb) { gr = __ldg(d_rgb + r * 3); gg = __ldg(d_rgb + r * 3 + 1); gb = __ldg(d_rgb + r * 3 + 2); }
+    if (d_depth) gd = __ldg(d_depth + r);
+    if (d_opacity) go = __ldg(d_opacity + r);
+    if (white_back) go -= (gr + gg + gb);
+    float T[NCH], alpha[NCH], tt[NCH], ee[NCH], dl[NCH];
+    bool on[NCH];
+    float carry = 1.0f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {                                // pass 1: forward
+      float zn = __shfl_down_sync(0xffffffffu, zv[c], 1);
+      const float z0 = __shfl_sync(0xffffffffu, zv[c + 1 < NCH ? c + 1 : c], 0);
+      if (lane == 31 && c + 1 < NCH) zn = z0;
+      const SampleTerms st = sample_terms(rv[c].w, nz[c], noise_std, zv[c], zn, c == NCH - 1 && lane == 31, dnorm);
+      const float incl = warp_incl_prod(st.t, lane);
+      float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) excl = 1.0f;
+      T[c] = carry * excl;
+      carry *= __shfl_sync(0xffffffffu, incl, 31);
+      float gi = go + g[c];
+      gi += gr * rv[c].x + gg * rv[c].y + gb * rv[c].z + gd * zv[c];
+      g[c] = gi;
+      alpha[c] = st.alpha; tt[c] = st.t; ee[c] = st.e; dl[c] = st.delta; on[c] = st.on;
+    }
+    float suffix = 0.f;
+#pragma unroll
+    for (int c = NCH - 1; c >= 0; --c) {                           // pass 2: backward
+      const float w = alpha[c] * T[c];
+      const float gw = g[c] * w;
+      float incl = gw;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float q = __shfl_down_sync(0xffffffffu, incl, o);
+        if (lane + o < 32) incl += q;
+      }
+      const float after = suffix + (incl - gw);
+      suffix += __shfl_sync(0xffffffffu, incl, 0);
+      const float dalpha = g[c] * T[c] - after / tt[c];
+      const float dsig = on[c] ? dalpha * dl[c] * ee[c] : 0.f;
+      reinterpret_cast<float4*>(d_raw)[r * S + 32 * c + lane] = make_float4(w * gr, w * gg, w * gb, dsig);
+    }
+  }
+}
+
 extern "C" int nerfb_composite_bwd(const float* raw, int channels, const float* z, const float* rays,
                                    const float* noise, float noise_std, int white_back, int64_t n_rays,
                                    int n_samples, const float* d_rgb, const float* d_depth,
@@ -245,6 +314,19 @@ extern "C" int nerfb_composite_bwd(const float* raw, int channels, const float* 
   NERFB_CHECK_ARG(raw && z && rays && d_raw && n_rays >= 0 && n_samples >= 1);
   NERFB_CHECK_ARG(channels == 1 || (channels >= 4 && channels <= 4 + COMP_MAX_EXTRA));
   if (n_rays == 0) return NERFB_OK;
+  const int64_t want_r = ceil_div64(n_rays, COMP_WARPS);
+  const int grid_r = (int)(want_r < NERFB_SM_COUNT * 16 ? want_r : NERFB_SM_COUNT * 16);
+  if (channels == 4 && !d_extra && ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(d_raw)) & 15) == 0 &&
+      (n_samples == 32 || n_samples == 64 || n_samples == 128)) {
+#define NERFB_COMP_BWD_REG(NCH)                                                                                              \
+  NERFB_LAUNCH(composite_bwd_reg_kernel<NCH>, grid_r, COMP_WARPS * 32, 0, stream, raw, z, rays, noise, noise_std, white_back, \
+               n_rays, d_rgb, d_depth, d_opacity, d_weights, d_raw)
+    if (n_samples == 32) NERFB_COMP_BWD_REG(1);
+    else if (n_samples == 64) NERFB_COMP_BWD_REG(2);
+    else NERFB_COMP_BWD_REG(4);
+#undef NERFB_COMP_BWD_REG
+    return NERFB_OK;
+  }
   const size_t smem = (size_t)COMP_WARPS * 2 * n_samples * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
   if (smem > 48 * 1024)

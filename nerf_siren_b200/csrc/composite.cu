@@ -120,6 +120,58 @@ composite_fwd_kernel(const float* __restrict__ raw, int C, const float* __restri
   }
 }
 
+// CT = 4 with S = 32 * NCH known at compile time: all of the ray's loads are issued before the first scan (the runtime-S loop
+// above serialises chunk k + 1's loads behind chunk k's shuffles).  Same arithmetic in the same order as composite_fwd_kernel<4>.
+template <int NCH>
+__global__ void __launch_bounds__(COMP_WARPS * 32)
+composite_fwd_reg_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rays,
+                         const float* __restrict__ noise, float noise_std, int white_back, int64_t N,
+                         float* __restrict__ weights, float* __restrict__ rgb, float* __restrict__ depth, float* __restrict__ opacity) {
+  constexpr int S = 32 * NCH;
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (int64_t)gridDim.x * COMP_WARPS;
+  for (int64_t r = (int64_t)blockIdx.x * COMP_WARPS + (threadIdx.x >> 5); r < N; r += nwarps) {
+    float4 rv[NCH];
+    float zv[NCH], nz[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int64_t i = r * S + 32 * c + lane;
+      rv[c] = __ldg(reinterpret_cast<const float4*>(raw) + i);
+      zv[c] = __ldg(z + i);
+      nz[c] = noise ? __ldg(noise + i) : 0.f;
+    }
+    const float dx = __ldg(rays + r * 8 + 3), dy = __ldg(rays + r * 8 + 4), dz = __ldg(rays + r * 8 + 5);
+    const float dnorm = sqrtf(dx * dx + dy * dy + dz * dz);
+    float carry = 1.0f, acc_r = 0.f, acc_g = 0.f, acc_b = 0.f, acc_d = 0.f, acc_w = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      float zn = __shfl_down_sync(0xffffffffu, zv[c], 1);
+      const float z0 = __shfl_sync(0xffffffffu, zv[c + 1 < NCH ? c + 1 : c], 0);
+      if (lane == 31 && c + 1 < NCH) zn = z0;
+      const SampleTerms st = sample_terms(rv[c].w, nz[c], noise_std, zv[c], zn, c == NCH - 1 && lane == 31, dnorm);
+      const float incl = warp_incl_prod(st.t, lane);
+      float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) excl = 1.0f;
+      const float T = carry * excl;
+      carry *= __shfl_sync(0xffffffffu, incl, 31);
+      const float w = st.alpha * T;
+      weights[r * S + 32 * c + lane] = w;
+      acc_w += w;
+      acc_r += w * rv[c].x; acc_g += w * rv[c].y; acc_b += w * rv[c].z; acc_d += w * zv[c];
+    }
+    acc_w = warp_sum(acc_w);
+    acc_r = warp_sum(acc_r); acc_g = warp_sum(acc_g); acc_b = warp_sum(acc_b); acc_d = warp_sum(acc_d);
+    if (lane == 0) {
+      if (opacity) opacity[r] = acc_w;
+      if (rgb) {
+        const float bg = white_back ? (1.0f - acc_w) : 0.f;
+        rgb[r * 3 + 0] = acc_r + bg; rgb[r * 3 + 1] = acc_g + bg; rgb[r * 3 + 2] = acc_b + bg;
+      }
+      if (depth) depth[r] = acc_d;
+    }
+  }
+}
+
 extern "C" int nerfb_composite_fwd(const float* raw, int channels, const float* z, const float* rays,
                                    const float* noise, float noise_std, int white_back, int64_t n_rays,
                                    int n_samples, float* weights, float* rgb, float* depth, float* opacity,
@@ -132,6 +184,15 @@ extern "C" int nerfb_composite_fwd(const float* raw, int channels, const float* 
   if (channels == 1)
     NERFB_LAUNCH(composite_fwd_kernel<1>, grid, COMP_WARPS * 32, 0, stream, raw, channels, z, rays, noise, noise_std,
                  white_back, n_rays, n_samples, weights, rgb, depth, opacity, extra);
+  else if (channels == 4 && (reinterpret_cast<uintptr_t>(raw) & 15) == 0 && n_samples == 64)
+    NERFB_LAUNCH(composite_fwd_reg_kernel<2>, grid, COMP_WARPS * 32, 0, stream, raw, z, rays, noise, noise_std, white_back, n_rays,
+                 weights, rgb, depth, opacity);
+  else if (channels == 4 && (reinterpret_cast<uintptr_t>(raw) & 15) == 0 && n_samples == 128)
+    NERFB_LAUNCH(composite_fwd_reg_kernel<4>, grid, COMP_WARPS * 32, 0, stream, raw, z, rays, noise, noise_std, white_back, n_rays,
+                 weights, rgb, depth, opacity);
+  else if (channels == 4 && (reinterpret_cast<uintptr_t>(raw) & 15) == 0 && n_samples == 192)
+    NERFB_LAUNCH(composite_fwd_reg_kernel<6>, grid, COMP_WARPS * 32, 0, stream, raw, z, rays, noise, noise_std, white_back, n_rays,
+                 weights, rgb, depth, opacity);
   else if (channels == 4 && (reinterpret_cast<uintptr_t>(raw) & 15) == 0)
     NERFB_LAUNCH(composite_fwd_kernel<4>, grid, COMP_WARPS * 32, 0, stream, raw, channels, z, rays, noise, noise_std,
                  white_back, n_rays, n_samples, weights, rgb, depth, opacity, extra);

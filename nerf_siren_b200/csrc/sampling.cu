@@ -62,13 +62,14 @@ __device__ __forceinline__ float4 sample4(float2 nf, float4 pr4, float perturb, 
 
 __global__ void __launch_bounds__(256)
 sample_coarse_v4_kernel(const float* __restrict__ rays, const float* __restrict__ perturb_rand, float perturb,
-                        int use_disp, int64_t total4, int S, float* __restrict__ z_out) {
+                        int use_disp, int64_t total4, int S, int sh, float* __restrict__ z_out) {
+  // sh = log2(S / 4) when S / 4 is a power of two (64-bit division is emulated: ~100 instructions per thread and iteration), else -1
   const int S4 = S >> 2;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total4; idx += 2 * stride) {
     const int64_t idx1 = idx + stride;
     const bool two = idx1 < total4;
-    const int64_t r0 = idx / S4, r1 = two ? idx1 / S4 : r0;
+    const int64_t r0 = sh >= 0 ? (idx >> sh) : idx / S4, r1 = two ? (sh >= 0 ? (idx1 >> sh) : idx1 / S4) : r0;
     const int i00 = (int)(idx - r0 * S4) * 4, i01 = two ? (int)(idx1 - r1 * S4) * 4 : i00;
     const float2 nf0 = __ldg(reinterpret_cast<const float2*>(rays + r0 * 8 + 6));
     const float2 nf1 = __ldg(reinterpret_cast<const float2*>(rays + r1 * 8 + 6));
@@ -93,7 +94,10 @@ extern "C" int nerfb_sample_coarse(const float* rays, const float* perturb_rand,
   if (n_samples % 4 == 0 && aligned16) {
     const int64_t total4 = total / 4, want4 = ceil_div64(total4, 512);      // two groups per thread and iteration
     const int grid4 = (int)(want4 < NERFB_SM_COUNT * 16 ? want4 : NERFB_SM_COUNT * 16);
-    NERFB_LAUNCH(sample_coarse_v4_kernel, grid4, 256, 0, stream, rays, perturb_rand, perturb, use_disp, total4, n_samples, z_out);
+    const int s4 = n_samples / 4;
+    int sh = -1;
+    if ((s4 & (s4 - 1)) == 0) for (sh = 0; (1 << sh) < s4; ++sh) {}
+    NERFB_LAUNCH(sample_coarse_v4_kernel, grid4, 256, 0, stream, rays, perturb_rand, perturb, use_disp, total4, n_samples, sh, z_out);
     return NERFB_OK;
   }
   const int64_t want = ceil_div64(total, 256);

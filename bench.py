@@ -352,7 +352,7 @@ def run_reference(args):
             "e2e": {"value": r["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if cfg == "train":
         line["config0"] = cpu_config0()
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -865,9 +865,29 @@ def run_ours(args):
         line["final_loss"] = wl.losses[-1]
     if extra:
         line["extra"] = extra
-    print(json.dumps(line), flush=True)
+    emit(line)
     cx.close()
     return 0
+
+
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints "NCCL version ..." at init on the GPU
+    boxes, from C): keep a private handle on the real stdout for the JSON line and point fd 1 at stderr for everything else."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+    return _JSON_OUT
+
+
+def emit(line):
+    out = claim_stdout()
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -890,6 +910,8 @@ def main():
             os.environ[k] = str(os.cpu_count() or 1)
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not (args.gpus > 1 and world == 1):
+        claim_stdout()                                  # before NCCL / CUDA initialise
     if args.gpus > 1 and world == 1:
         # convenience: re-launch under torchrun, one rank per GPU (the driver launches torchrun itself)
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",

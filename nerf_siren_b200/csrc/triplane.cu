@@ -71,7 +71,9 @@ __device__ __forceinline__ void load_decoder(Dec& d, const float* __restrict__ p
 // intrinsics keep the ABSOLUTE error below 2e-7 (1 + t is formed exactly to fp32, t in (0,1]), far inside the stated
 // parity tolerance, at a quarter of the instructions of log1pf(expf(x)).
 __device__ __forceinline__ float softplusf(float x) {
-  return x > 20.f ? x : fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(x)));
+  // beyond the threshold the second term is below half an ulp of x (log(1 + e^-20) = 2e-9 against ulp(20) = 1.9e-6): the sum
+  // already IS x in fp32, no select needed
+  return fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(x)));
 }
 
 // One bilinear tap per lane (lanes 0..11 = plane * 4 + corner) at normalised (gx -> W, gy -> H), zeros padding,
@@ -153,23 +155,45 @@ __device__ __forceinline__ void load_decoder_mma(float* W1s, const float* __rest
   for (int i = threadIdx.x; i < TP_HID; i += blockDim.x) B1s[i] = __ldg(b1p + i) * lr_mul;
 }
 
+// The four taps of plane p for a lane that needs them all (tap_lane's arithmetic, with what the corners share computed once:
+// two column / two row validity tests and clamps instead of eight).  Corner order as tap_lane: (x0,y0) (x1,y0) (x0,y1) (x1,y1).
+__device__ __forceinline__ void taps_plane(int H, int W, float x, float y, float z, int p, int (&off)[4], float (&wt)[4]) {
+  const float gx = p == 2 ? z : x;
+  const float gy = p == 0 ? y : (p == 1 ? z : x);
+  const float ix = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gx, 1.f), (float)W), 1.f), 0.5f);
+  const float iy = __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(gy, 1.f), (float)H), 1.f), 0.5f);
+  const float fx = floorf(ix), fy = floorf(iy);
+  const float w = ix - fx, e = 1.f - w, n = iy - fy, s = 1.f - n;
+  const float x1 = fx + 1.f, y1 = fy + 1.f;
+  const bool vx0 = fx >= 0.f && fx < (float)W, vx1 = x1 >= 0.f && x1 < (float)W;      // NaN fails every test: no tap
+  const bool vy0 = fy >= 0.f && fy < (float)H, vy1 = y1 >= 0.f && y1 < (float)H;
+  const int xi0 = min(max((int)fmaxf(fminf(fx, (float)W), -2.f), 0), W - 1), xi1 = min(max((int)fmaxf(fminf(x1, (float)W), -2.f), 0), W - 1);
+  const int yi0 = min(max((int)fmaxf(fminf(fy, (float)H), -2.f), 0), H - 1), yi1 = min(max((int)fmaxf(fminf(y1, (float)H), -2.f), 0), H - 1);
+  const int r0 = (p * H + yi0) * W, r1 = (p * H + yi1) * W;
+  off[0] = (r0 + xi0) * TP_C; off[1] = (r0 + xi1) * TP_C; off[2] = (r1 + xi0) * TP_C; off[3] = (r1 + xi1) * TP_C;
+  wt[0] = (vx0 && vy0) ? s * e : 0.f; wt[1] = (vx1 && vy0) ? s * w : 0.f;
+  wt[2] = (vx0 && vy1) ? n * e : 0.f; wt[3] = (vx1 && vy1) ? n * w : 0.f;
+}
+
 // gather of ONE point by 8 lanes (sub4 = 4 (lane % 8): four channels each): all 12 taps computed by the lane itself, rows read
-// as float4; same tap order and rounding as field_eval.  Returns sampled_features.mean(1) for the lane's four channels.
+// as float4; same tap order and rounding as field_eval except the final mean (times 1/3 instead of the IEEE division by 3: the
+// tensor-core decoder is not bit-identical to the CUDA-core one anyway).  Returns sampled_features.mean(1) for the lane's four channels.
 __device__ __forceinline__ float4 gather_quad(const float* __restrict__ planes, int H, int W, float x, float y, float z, int sub4) {
   float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int pl = 0; pl < 3; ++pl) {
+    int off[4]; float wt[4];
+    taps_plane(H, W, x, y, z, pl, off, wt);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      int off; float wt;
-      tap_lane(H, W, x, y, z, 4 * pl + c, off, wt);
-      const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off + sub4));
-      acc.x = fmaf(v.x, wt, acc.x); acc.y = fmaf(v.y, wt, acc.y); acc.z = fmaf(v.z, wt, acc.z); acc.w = fmaf(v.w, wt, acc.w);
+      const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off[c] + sub4));
+      acc.x = fmaf(v.x, wt[c], acc.x); acc.y = fmaf(v.y, wt[c], acc.y); acc.z = fmaf(v.z, wt[c], acc.z); acc.w = fmaf(v.w, wt[c], acc.w);
     }
     f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
   }
-  f.x /= 3.f; f.y /= 3.f; f.z /= 3.f; f.w /= 3.f;
+  const float third = 1.f / 3.f;
+  f.x *= third; f.y *= third; f.z *= third; f.w *= third;
   return f;
 }
 
@@ -881,20 +905,7 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
       const int64_t q = point(pt) < P ? point(pt) : P - 1;    // tail points re-read the last point; their cotangents are 0
       const float x = __fmul_rn(coord_scale, __ldg(coords + q * 3)), y = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 1)),
                   z = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 2));
-      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int pl = 0; pl < 3; ++pl) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          int off; float wt;
-          tap_lane(H, W, x, y, z, 4 * pl + c, off, wt);
-          const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off + sub4));
-          acc.x = fmaf(v.x, wt, acc.x); acc.y = fmaf(v.y, wt, acc.y); acc.z = fmaf(v.z, wt, acc.z); acc.w = fmaf(v.w, wt, acc.w);
-        }
-        f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
-      }
-      f.x /= 3.f; f.y /= 3.f; f.z /= 3.f; f.w /= 3.f;         // sampled_features.mean(1)
+      const float4 f = gather_quad(planes, H, W, x, y, z, sub4);
       *reinterpret_cast<float4*>(Fs + pt * TM_FS + sub4) = f;
       Ft[(sub4 + 0) * TM_FT + pt] = f.x; Ft[(sub4 + 1) * TM_FT + pt] = f.y; Ft[(sub4 + 2) * TM_FT + pt] = f.z; Ft[(sub4 + 3) * TM_FT + pt] = f.w;
     }
@@ -1010,10 +1021,11 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
                     z = __fmul_rn(coord_scale, __ldg(coords + q * 3 + 2));
         const float4 v = *reinterpret_cast<const float4*>(Fs + pt * TM_FS + sub4);
 #pragma unroll
-        for (int c = 0; c < 12; ++c) {
-          int off; float wt;
-          tap_lane(H, W, x, y, z, c, off, wt);
-          red_add_v4_if(d_planes + off + sub4, v.x * wt, v.y * wt, v.z * wt, v.w * wt, wt);
+        for (int pl = 0; pl < 3; ++pl) {
+          int off[4]; float wt[4];
+          taps_plane(H, W, x, y, z, pl, off, wt);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) red_add_v4_if(d_planes + off[c] + sub4, v.x * wt[c], v.y * wt[c], v.z * wt[c], v.w * wt[c], wt[c]);
         }
       }
     }

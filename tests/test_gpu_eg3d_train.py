@@ -219,8 +219,9 @@ def test_render_train_entry_writes_the_samples_of_the_render():
         ops.triplane_render(*args, return_depths_fine=True, return_samples=True)
 
 
-@pytest.mark.parametrize("R,S,Si,white", [(300, 24, 24, False), (64, 48, 48, True), (33, 12, 40, False)])
-def test_samples_backward_equals_the_marcher_backward_composition(R, S, Si, white):
+@pytest.mark.parametrize("R,S,Si,white,unsorted", [(300, 24, 24, False, False), (64, 48, 48, True, False), (33, 12, 40, False, False),
+                                                   (40, 48, 48, False, True)])
+def test_samples_backward_equals_the_marcher_backward_composition(R, S, Si, white, unsorted):
     """nerfb_triplane_samples_bwd against the same thing composed from nerfb_mip_march_bwd and torch's stable sort / gather /
     scatter (renderer.py:160-170), all six cotangents at once and the importance depths interleaved with (and in 12 + 40
     outnumbering) the coarse ones; duplicates among the depths exercise the (value, index) tie rule."""
@@ -228,6 +229,8 @@ def test_samples_backward_equals_the_marcher_backward_composition(R, S, Si, whit
     g = torch.Generator(device=DEV).manual_seed(R + S)
     St = S + Si
     coarse = 2.0 + torch.rand(R, S, device=DEV, generator=g).cumsum(1) / S
+    if unsorted:                                         # the kernels take the merge shortcut only for ascending coarse depths:
+        coarse[1::2] = coarse[1::2].flip(1)              # every other ray descending -> the full (value, index) count
     fine = 2.0 + torch.rand(R, Si, device=DEV, generator=g) * 1.1
     fine[:, 0] = coarse[:, S // 2]                       # a tie between a coarse and an importance depth
     fine[:, 1] = fine[:, 2]                              # and between two importance depths

@@ -73,7 +73,12 @@ __device__ __forceinline__ void load_decoder(Dec& d, const float* __restrict__ p
 __device__ __forceinline__ float softplusf(float x) {
   // beyond the threshold the second term is below half an ulp of x (log(1 + e^-20) = 2e-9 against ulp(20) = 1.9e-6): the sum
   // already IS x in fp32, no select needed
-  return fmaxf(x, 0.f) + __logf(1.f + __expf(-fabsf(x)));
+  // six instructions: ex2 / lg2 approximations straight (the arguments need none of __expf / __logf's range handling:
+  // -|x| log2(e) <= 0 and 1 + t in (1, 2]), the final scale folded into one FMA
+  float t, l;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(-fabsf(x) * 1.4426950408889634f));
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(1.f + t));
+  return fmaf(l, 0.6931471805599453f, fmaxf(x, 0.f));
 }
 
 // One bilinear tap per lane (lanes 0..11 = plane * 4 + corner) at normalised (gx -> W, gy -> H), zeros padding,
@@ -167,12 +172,15 @@ __device__ __forceinline__ void taps_plane(int H, int W, float x, float y, float
   const float x1 = fx + 1.f, y1 = fy + 1.f;
   const bool vx0 = fx >= 0.f && fx < (float)W, vx1 = x1 >= 0.f && x1 < (float)W;      // NaN fails every test: no tap
   const bool vy0 = fy >= 0.f && fy < (float)H, vy1 = y1 >= 0.f && y1 < (float)H;
-  const int xi0 = min(max((int)fmaxf(fminf(fx, (float)W), -2.f), 0), W - 1), xi1 = min(max((int)fmaxf(fminf(x1, (float)W), -2.f), 0), W - 1);
-  const int yi0 = min(max((int)fmaxf(fminf(fy, (float)H), -2.f), 0), H - 1), yi1 = min(max((int)fmaxf(fminf(y1, (float)H), -2.f), 0), H - 1);
+  // offsets only have to be in bounds (an invalid tap has weight 0): one sanitised float -> int per axis, the neighbour is + 1
+  const int ix0 = (int)fmaxf(fminf(fx, (float)W), -2.f), iy0 = (int)fmaxf(fminf(fy, (float)H), -2.f);
+  const int xi0 = min(max(ix0, 0), W - 1), xi1 = min(max(ix0 + 1, 0), W - 1);
+  const int yi0 = min(max(iy0, 0), H - 1), yi1 = min(max(iy0 + 1, 0), H - 1);
   const int r0 = (p * H + yi0) * W, r1 = (p * H + yi1) * W;
   off[0] = (r0 + xi0) * TP_C; off[1] = (r0 + xi1) * TP_C; off[2] = (r1 + xi0) * TP_C; off[3] = (r1 + xi1) * TP_C;
-  wt[0] = (vx0 && vy0) ? s * e : 0.f; wt[1] = (vx1 && vy0) ? s * w : 0.f;
-  wt[2] = (vx0 && vy1) ? n * e : 0.f; wt[3] = (vx1 && vy1) ? n * w : 0.f;
+  // (vx && vy) ? row * col : 0 as a product of per-axis masked factors (an invalid axis contributes an exact 0)
+  const float cx0 = vx0 ? e : 0.f, cx1 = vx1 ? w : 0.f, ry0 = vy0 ? s : 0.f, ry1 = vy1 ? n : 0.f;
+  wt[0] = ry0 * cx0; wt[1] = ry0 * cx1; wt[2] = ry1 * cx0; wt[3] = ry1 * cx1;
 }
 
 // gather of ONE point by 8 lanes (sub4 = 4 (lane % 8): four channels each): all 12 taps computed by the lane itself, rows read
@@ -184,13 +192,14 @@ __device__ __forceinline__ float4 gather_quad(const float* __restrict__ planes, 
   for (int pl = 0; pl < 3; ++pl) {
     int off[4]; float wt[4];
     taps_plane(H, W, x, y, z, pl, off, wt);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);          // two-wide FMAs: same IEEE results, half the instructions
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       const float4 v = __ldg(reinterpret_cast<const float4*>(planes + off[c] + sub4));
-      acc.x = fmaf(v.x, wt[c], acc.x); acc.y = fmaf(v.y, wt[c], acc.y); acc.z = fmaf(v.z, wt[c], acc.z); acc.w = fmaf(v.w, wt[c], acc.w);
+      const float2 ww = make_float2(wt[c], wt[c]);
+      a01 = __ffma2_rn(make_float2(v.x, v.y), ww, a01); a23 = __ffma2_rn(make_float2(v.z, v.w), ww, a23);
     }
-    f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
+    f.x += a01.x; f.y += a01.y; f.z += a23.x; f.w += a23.y;
   }
   const float third = 1.f / 3.f;
   f.x *= third; f.y *= third; f.z *= third; f.w *= third;
@@ -230,8 +239,10 @@ __device__ __forceinline__ void decode16(const float* Fs, const float* W1s, cons
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
-      out[0][k] = fmaf(w.x, h[0], fmaf(w.y, h[1], out[0][k]));
-      out[1][k] = fmaf(w.x, h[2], fmaf(w.y, h[3], out[1][k]));
+      float2 o2 = make_float2(out[0][k], out[1][k]);                         // both points of the lane in one two-wide FMA
+      o2 = __ffma2_rn(make_float2(w.y, w.y), make_float2(h[1], h[3]), o2);
+      o2 = __ffma2_rn(make_float2(w.x, w.x), make_float2(h[0], h[2]), o2);
+      out[0][k] = o2.x; out[1][k] = o2.y;
     }
   }
 #pragma unroll
@@ -969,12 +980,18 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
-        o[0][k] = fmaf(w.x, h[0], fmaf(w.y, h[1], o[0][k]));
-        o[1][k] = fmaf(w.x, h[2], fmaf(w.y, h[3], o[1][k]));
+        float2 o2 = make_float2(o[0][k], o[1][k]);
+        o2 = __ffma2_rn(make_float2(w.y, w.y), make_float2(h[1], h[3]), o2);
+        o2 = __ffma2_rn(make_float2(w.x, w.x), make_float2(h[0], h[2]), o2);
+        o[0][k] = o2.x; o[1][k] = o2.y;
       }
       // softplus'(x) = sigmoid(x) = 1 - exp(-softplus(x)) (1 beyond the threshold of 20); kept in place of pre
 #pragma unroll
-      for (int i = 0; i < 4; ++i) pre[nt][i] = 1.f - __expf(-h[i]);     // (beyond the softplus threshold of 20 this is 1 to fp32)
+      for (int i = 0; i < 4; ++i) {                                      // (beyond the softplus threshold of 20 this is 1 to fp32)
+        float en;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(en) : "f"(h[i] * -1.4426950408889634f));
+        pre[nt][i] = 1.f - en;
+      }
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -1005,13 +1022,14 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
     // dpre[pt][hid] = sigmoid(pre) * sum_k W2[k][hid] go[pt][k], in the C-fragment layout of GEMM1 (in place of pre)
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      float dh[4] = {0.f, 0.f, 0.f, 0.f};
+      float2 dh01 = make_float2(0.f, 0.f), dh23 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float2 w = *reinterpret_cast<const float2*>(W2s + k * TP_HID + 8 * nt + 2 * t);
-        dh[0] = fmaf(w.x, go[0][k], dh[0]); dh[1] = fmaf(w.y, go[0][k], dh[1]);
-        dh[2] = fmaf(w.x, go[1][k], dh[2]); dh[3] = fmaf(w.y, go[1][k], dh[3]);
+        dh01 = __ffma2_rn(w, make_float2(go[0][k], go[0][k]), dh01);
+        dh23 = __ffma2_rn(w, make_float2(go[1][k], go[1][k]), dh23);
       }
+      const float dh[4] = {dh01.x, dh01.y, dh23.x, dh23.y};
 #pragma unroll
       for (int i = 0; i < 4; ++i) pre[nt][i] *= dh[i];
       gb1[nt][0] += pre[nt][0] + pre[nt][2]; gb1[nt][1] += pre[nt][1] + pre[nt][3];
@@ -1052,7 +1070,11 @@ __global__ void __launch_bounds__(TM_WARPS * 32, 1) triplane_field_bwd_mma_kerne
           int off[4]; float wt[4];
           taps_plane(H, W, x, y, z, pl, off, wt);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) red_add_v4_if(d_planes + off[c] + sub4, v.x * wt[c], v.y * wt[c], v.z * wt[c], v.w * wt[c], wt[c]);
+          for (int c = 0; c < 4; ++c) {
+            const float2 ww = make_float2(wt[c], wt[c]);
+            const float2 p01 = __fmul2_rn(make_float2(v.x, v.y), ww), p23 = __fmul2_rn(make_float2(v.z, v.w), ww);
+            red_add_v4_if(d_planes + off[c] + sub4, p01.x, p01.y, p23.x, p23.y, wt[c]);
+          }
         }
       }
     }

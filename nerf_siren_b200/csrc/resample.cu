@@ -109,10 +109,14 @@ extern "C" int nerfb_sample_pdf(const float* bins, const float* weights, const f
 }
 
 // ---- the fused call site: z_mid -> sample_pdf(weights[1:-1]) -> cat -> sort ---------------------------
-template <int NPL>      // elements per lane of the in-register sort (n_pad / 32), 0 = shared-memory sort for other sizes
+// NPL: elements per lane of the in-register sort (n_pad / 32), 0 = shared-memory sort for other sizes.  SC / SI: the sample counts
+// when known at compile time (64 + 64 and 64 + 128, the reference's configurations), 0 = runtime: the kernel is instruction-bound
+// (~1100 warp-instructions per ray), and its many short `for (i = lane; i < Sc; i += 32)` loops unroll only with constants.
+template <int NPL, int SC, int SI>
 __global__ void __launch_bounds__(RS_WARPS * 32)
 resample_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse, const float* __restrict__ u, int det,
-                int64_t N, int Sc, int Si, int n_pad, float* __restrict__ z_fine) {
+                int64_t N, int Sc_rt, int Si_rt, int n_pad, float* __restrict__ z_fine) {
+  const int Sc = SC > 0 ? SC : Sc_rt, Si = SI > 0 ? SI : Si_rt;
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int nb = Sc - 1, St = Sc + Si;
@@ -229,17 +233,17 @@ extern "C" int nerfb_resample(const float* z_coarse, const float* weights_coarse
   const size_t smem = (size_t)RS_WARPS * (3 * n_coarse + n_pad) * sizeof(float);
   if (smem > 200 * 1024) return NERFB_E_UNSUPPORTED;
   if (smem > 48 * 1024)
-    NERFB_CUDA(cudaFuncSetAttribute(resample_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NERFB_CUDA(cudaFuncSetAttribute(resample_kernel<0, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t want = ceil_div64(n_rays, RS_WARPS);
   const int grid = (int)(want < NERFB_SM_COUNT * 16 ? want : NERFB_SM_COUNT * 16);
-  if (n_pad == 128 && smem <= 48 * 1024)
-    NERFB_LAUNCH(resample_kernel<4>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
-                 n_importance, n_pad, z_fine);
-  else if (n_pad == 256 && smem <= 48 * 1024)
-    NERFB_LAUNCH(resample_kernel<8>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
-                 n_importance, n_pad, z_fine);
-  else
-    NERFB_LAUNCH(resample_kernel<0>, grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays, n_coarse,
-                 n_importance, n_pad, z_fine);
+#define NERFB_RESAMPLE(NPL, SC, SI)                                                                                          \
+  NERFB_LAUNCH((resample_kernel<NPL, SC, SI>), grid, RS_WARPS * 32, smem, stream, z_coarse, weights_coarse, u, det, n_rays,    \
+               n_coarse, n_importance, n_pad, z_fine)
+  if (n_coarse == 64 && n_importance == 64) NERFB_RESAMPLE(4, 64, 64);
+  else if (n_coarse == 64 && n_importance == 128) NERFB_RESAMPLE(8, 64, 128);
+  else if (n_pad == 128 && smem <= 48 * 1024) NERFB_RESAMPLE(4, 0, 0);
+  else if (n_pad == 256 && smem <= 48 * 1024) NERFB_RESAMPLE(8, 0, 0);
+  else NERFB_RESAMPLE(0, 0, 0);
+#undef NERFB_RESAMPLE
   return NERFB_OK;
 }

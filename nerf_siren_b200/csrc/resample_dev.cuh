@@ -28,10 +28,13 @@ __device__ __forceinline__ void warp_build_cdf(const float* s_w, float* s_cdf, i
 
 __device__ __forceinline__ float invert_cdf(const float* s_bins, const float* s_cdf, int nb, float u, float eps,
                                             int* ind_out) {
-  int lo = 0, hi = nb;                                   // searchsorted(cdf, u, right=True): #(cdf <= u)
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (s_cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  // searchsorted(cdf, u, right=True) = #(cdf <= u).  The cdf is non-decreasing (a cumulative sum of positive terms), so the count is
+  // the largest lo with cdf[lo - 1] <= u: built bit by bit, branch-free, ceil(log2(nb + 1)) probes for every lane (the bisection
+  // loop had data-dependent trip counts and two compares per probe).
+  int lo = 0;
+  for (int step = 1 << (31 - __clz(nb)); step > 0; step >>= 1) {      // warp-uniform trip count; nb >= 1
+    const int probe = lo + step;
+    if (probe <= nb && s_cdf[probe - 1] <= u) lo = probe;
   }
   if (ind_out) *ind_out = lo;
   const int below = max(lo - 1, 0);                      // rendering.py:55-56

@@ -108,6 +108,44 @@ extern "C" int nerfb_sample_pdf(const float* bins, const float* weights, const f
   return NERFB_OK;
 }
 
+// In-register bitonic network over NPL * 32 values (element q * 32 + lane in v[q]).  SKIP_LOWER: the lower half is already
+// ascending, stages k <= half only sort the upper half.  Everything but the lane-dependent direction bits is a compile-time constant.
+template <int NPL, bool SKIP_LOWER>
+__device__ __forceinline__ void bitonic_network(float (&v)[NPL > 0 ? NPL : 1], int lane) {
+  constexpr int HALF = NPL * 16;
+#pragma unroll
+  for (int k = 2; k <= NPL * 32; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= 32) {
+        const int dq = j >> 5;
+#pragma unroll
+        for (int q = 0; q < NPL; ++q) {
+          if ((q & dq) == 0) {
+            if (SKIP_LOWER && k <= HALF && q < NPL / 2) continue;
+            const bool up = (((q * 32) & k) == 0);
+            const float a = v[q], b = v[q | dq];
+            const bool sw = (a > b) == up;
+            v[q] = sw ? b : a; v[q | dq] = sw ? a : b;
+          }
+        }
+      } else {
+        // the lower index keeps the min in an ascending block, the max in a descending one; for k < 32 the block direction
+        // depends on the lane only, for k >= 32 on q only
+        const bool lower = (lane & j) == 0;
+        const bool lane_up = (lane & k) == 0;
+#pragma unroll
+        for (int q = 0; q < NPL; ++q) {
+          if (SKIP_LOWER && k <= HALF && q < NPL / 2) continue;
+          const float o = __shfl_xor_sync(0xffffffffu, v[q], j);
+          const bool up = k < 32 ? lane_up : (((q * 32) & k) == 0);
+          v[q] = (lower == up) ? fminf(v[q], o) : fmaxf(v[q], o);
+        }
+      }
+    }
+  }
+}
+
 // ---- the fused call site: z_mid -> sample_pdf(weights[1:-1]) -> cat -> sort ---------------------------
 // NPL: elements per lane of the in-register sort (n_pad / 32), 0 = shared-memory sort for other sizes.  SC / SI: the sample counts
 // when known at compile time (64 + 64 and 64 + 128, the reference's configurations), 0 = runtime: the kernel is instruction-bound
@@ -170,35 +208,8 @@ resample_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_
         }
         presorted = !__any_sync(0xffffffffu, bad);
       }
-#pragma unroll
-      for (int k = 2; k <= NPL * 32; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-          if (j >= 32) {
-            const int dq = j >> 5;
-#pragma unroll
-            for (int q = 0; q < NPL; ++q) {
-              if ((q & dq) == 0) {
-                if (k <= HALF && q < NPL / 2 && presorted) continue;      // lower half already ascending
-                const bool up = (((q * 32) & k) == 0);
-                const float a = v[q], b = v[q | dq];
-                const bool sw = (a > b) == up;
-                v[q] = sw ? b : a; v[q | dq] = sw ? a : b;
-              }
-            }
-          } else {
-#pragma unroll
-            for (int q = 0; q < NPL; ++q) {
-              if (k <= HALF && q < NPL / 2 && presorted) continue;
-              const int idx = q * 32 + lane;
-              const float o = __shfl_xor_sync(0xffffffffu, v[q], j);
-              const bool up = (idx & k) == 0, lower = (lane & j) == 0;
-              // the lower index keeps the min in an ascending block, the max in a descending one
-              v[q] = (lower == up) ? fminf(v[q], o) : fmaxf(v[q], o);
-            }
-          }
-        }
-      }
+      if (presorted) bitonic_network<NPL, true>(v, lane);     // warp-uniform: two fully unrolled networks, no per-exchange test
+      else bitonic_network<NPL, false>(v, lane);
 #pragma unroll
       for (int q = 0; q < NPL; ++q) { const int idx = q * 32 + lane; if (idx < St) z_fine[r * St + idx] = v[q]; }
       __syncwarp();

@@ -1607,9 +1607,10 @@ struct PackArgs { int n_slabs; PackSlab slab[48]; int sw64; };   // sw64: tile-p
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params_in, PackArgs pa, uint8_t* __restrict__ blob,
                                                            const float* __restrict__ aux, const float* __restrict__ film) {
-  const PackSlab sl = pa.slab[blockIdx.x];
+  // four blocks per slab (a model has ~36 slabs: one block each left three quarters of the SMs idle and the kernel latency-bound)
+  const PackSlab sl = pa.slab[blockIdx.x >> 2];
   const float* params = sl.aux ? aux : params_in;
-  for (int idx = threadIdx.x; idx < sl.N * 8; idx += blockDim.x) {       // one 16-byte chunk per iteration
+  for (int idx = (blockIdx.x & 3) * blockDim.x + threadIdx.x; idx < sl.N * 8; idx += 4 * blockDim.x) {   // one 16-byte chunk per iteration
     const int n = idx >> 3, ch = idx & 7;
     const float fq = (sl.film >= 0 && film) ? __ldg(film + sl.film * sl.N + n) : 1.f;
     float f[8];
@@ -1864,7 +1865,7 @@ int tc_mlp_fwd(const nerfb_mlp_desc& d, int in_mode, const float* params, const 
     const NerfOffsets o = nerf_offsets(d);
     NERFB_LAUNCH(merge_parse_kernel, 16, 256, 0, stream, params, o.w_p0, o.b_p0, o.w_p1, o.b_p1, d.n_cls, weff, weff + 16 * 256);
   }
-  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs, 256, 0, stream, params, pl.pack, base + pl.off_wblob, (const float*)weff,
+  NERFB_LAUNCH(pack_weights_kernel, pl.pack.n_slabs * 4, 256, 0, stream, params, pl.pack, base + pl.off_wblob, (const float*)weff,
                siren ? film : (const float*)nullptr);
   NERFB_LAUNCH(gather_bias_kernel, pl.bias.n_segs, 256, 0, stream, params, pl.bias,
                reinterpret_cast<float*>(base + pl.off_bias), siren ? film : (const float*)nullptr,
